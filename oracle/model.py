@@ -1,0 +1,287 @@
+"""NonhydrostaticModel, update_state!, time_step! (RK3 / AB2), pressure correction (oracle; test infrastructure only).
+
+Follows the reference's
+  src/Models/NonhydrostaticModels/nonhydrostatic_model.jl:114-257         (constructor: pHY′ iff buoyancy, halo inflation,
+                                                                            order adaptation, solver choice, update_state!)
+  src/Models/NonhydrostaticModels/NonhydrostaticModels.jl:25-62           (solver choice by regular dimensions)
+  src/Models/NonhydrostaticModels/update_nonhydrostatic_model_state.jl:20-70
+  src/Models/NonhydrostaticModels/pressure_correction.jl:8-50
+  src/Models/NonhydrostaticModels/solve_for_pressure.jl:12-38,57-82
+  src/Models/NonhydrostaticModels/set_nonhydrostatic_model.jl:33-60
+  src/TimeSteppers/runge_kutta_3.jl:48-62,77-208
+  src/TimeSteppers/quasi_adams_bashforth_2.jl:39,74-175
+  src/TimeSteppers/store_tendencies.jl:6-22
+  src/TimeSteppers/clock.jl:87-116
+"""
+from fractions import Fraction
+
+import numpy as np
+
+from .grid import Bounded, Flat, round_fraction
+from .fields import Field, fill_halo_regions
+from .advection import Centered, adapt_advection_order
+from .operators import divergence_ccc, deriv, delta, interior_region
+from .solvers import FFTBasedPoissonSolver, FourierTridiagonalPoissonSolver
+from .tendencies import (VEL_LOC, CCC, momentum_tendency, tracer_tendency, tendency_region,
+                         update_hydrostatic_pressure)
+
+
+class FPlane:
+    def __init__(self, f):
+        self.f = f
+
+
+class BuoyancyTracer:
+    kind = "tracer"
+    required_tracers = ("b",)
+
+
+class SeawaterBuoyancy:
+    """SeawaterBuoyancy with a LinearEquationOfState (defaults: g = 9.80665, α = 1.67e-4, β = 7.80e-4 —
+    src/BuoyancyFormulations/seawater_buoyancy.jl, linear_equation_of_state.jl:24-37)."""
+    kind = "seawater"
+    required_tracers = ("T", "S")
+
+    def __init__(self, gravitational_acceleration=9.80665, thermal_expansion=1.67e-4, haline_contraction=7.80e-4):
+        self.g, self.alpha, self.beta = gravitational_acceleration, thermal_expansion, haline_contraction
+
+
+class ScalarDiffusivity:
+    def __init__(self, nu=0.0, kappa=0.0):
+        self.nu, self.kappa = nu, kappa
+
+    def kappa_for(self, name):
+        return self.kappa[name] if isinstance(self.kappa, dict) else self.kappa
+
+
+class Clock:
+    def __init__(self):
+        self.time = 0.0
+        self.iteration = 0
+        self.stage = 1
+        self.last_dt = np.inf
+        self.last_stage_dt = np.inf
+
+
+class NonhydrostaticModel:
+    def __init__(self, grid, advection="default", buoyancy=None, coriolis=None, closure=None, tracers=(),
+                 timestepper="RungeKutta3", hydrostatic_pressure_anomaly="default", chi=0.1):
+        FT = grid.FT
+        if advection == "default":
+            advection = Centered(FT, 2)
+        tracers = (tracers,) if isinstance(tracers, str) else tuple(tracers)
+        if buoyancy is not None:
+            for req in buoyancy.required_tracers:
+                if req not in tracers:
+                    raise ValueError(f"buoyancy requires tracer {req}")
+        adv = adapt_advection_order(advection, grid)
+        # inflate_grid_halo_size: each non-Flat dim needs at least the scheme's buffer (and 1 for the closure)
+        need = []
+        for d in range(3):
+            if grid.topology[d] == Flat:
+                need.append(0)
+                continue
+            h = max([1] + [s.B for s in adv if s is not None])
+            need.append(max(h, grid.H[d]))
+        if tuple(need) != tuple(grid.H):
+            grid = grid.with_halo(need)
+        self.grid = grid
+        self.advection = adv
+        self.buoyancy, self.coriolis, self.closure = buoyancy, coriolis, closure
+        self.velocities = tuple(Field(grid, VEL_LOC[a], name="uvw"[a]) for a in range(3))
+        self.tracers = {n: Field(grid, CCC, name=n) for n in tracers}
+        self.pNHS = Field(grid, CCC, prognostic=False, name="pNHS")
+        if hydrostatic_pressure_anomaly == "default":
+            self.pHY = Field(grid, CCC, prognostic=False, name="pHY") if buoyancy is not None else None
+        else:
+            self.pHY = Field(grid, CCC, prognostic=False, name="pHY") if hydrostatic_pressure_anomaly else None
+        # solver choice: NonhydrostaticModels.jl:25-62
+        irregular = [d for d in range(3) if not grid.regular_dim(d)]
+        if not irregular:
+            self.pressure_solver = FFTBasedPoissonSolver(grid)
+        elif len(irregular) == 1:
+            self.pressure_solver = FourierTridiagonalPoissonSolver(grid)
+        else:
+            raise ValueError("no FFT-based pressure solver for a grid stretched in more than one direction")
+        self.timestepper = timestepper
+        names = ["u", "v", "w"] + list(tracers)
+        self.Gn = {n: f.copy() for n, f in zip(names, self.prognostic_fields())}
+        self.Gm = {n: f.copy() for n, f in zip(names, self.prognostic_fields())}
+        for G in list(self.Gn.values()) + list(self.Gm.values()):
+            G.data[...] = 0
+        # RK3 coefficients stored as FT (runge_kutta_3.jl:53-62)
+        self.rk3 = dict(g1=round_fraction(Fraction(8, 15), FT), g2=round_fraction(Fraction(5, 12), FT),
+                        g3=round_fraction(Fraction(3, 4), FT), z2=round_fraction(Fraction(-17, 60), FT),
+                        z3=round_fraction(Fraction(-5, 12), FT))
+        self.chi = FT(chi)
+        self.clock = Clock()
+        update_state(self, compute_tendencies=False)
+
+    def prognostic_fields(self):
+        return list(self.velocities) + list(self.tracers.values())
+
+    def prognostic_names(self):
+        return ["u", "v", "w"] + list(self.tracers.keys())
+
+
+# ---------------------------------------------------------------------------------------------
+
+def update_state(model, compute_tendencies=True):
+    """update_state!: halo fill (normal velocities not re-imposed) → hydrostatic pressure → tendencies."""
+    fill_halo_regions(model.prognostic_fields(), fill_boundary_normal_velocities=False)
+    update_hydrostatic_pressure(model.grid, model.pHY, model.buoyancy, model.tracers)
+    if compute_tendencies:
+        compute_tendencies_(model)
+
+
+def compute_tendencies_(model):
+    for a in range(3):
+        R, G = momentum_tendency(model, a)
+        if G is not None:
+            model.Gn["uvw"[a]].at(*R)[...] = G
+    for n in model.tracers:
+        R, G = tracer_tendency(model, n)
+        model.Gn[n].at(*R)[...] = G
+
+
+def compute_source_term(model, dt):
+    """_compute_source_term! / _fourier_tridiagonal_source_term! into the solver's complex array."""
+    grid = model.grid
+    R = interior_region(grid)
+    u, v, w = model.velocities
+    div = divergence_ccc(grid, u, v, w, R)
+    solver = model.pressure_solver
+    dt = _as_dt(grid, dt)
+    if isinstance(solver, FFTBasedPoissonSolver):
+        solver.storage[...] = div / dt
+    else:
+        td = solver.td
+        solver.source_term[...] = delta(grid, td, "c", R) * div / dt
+
+
+def _as_dt(grid, dt):
+    """Δt reaches the kernels as whatever the caller passed (Float64 literal, FT product…); keep numpy scalars,
+    promote Python floats to Float64 like a Julia Float64 literal."""
+    if isinstance(dt, (np.floating,)):
+        return dt
+    return np.float64(dt)
+
+
+def calculate_pressure_correction(model, dt):
+    fill_halo_regions(list(model.velocities))                       # with wall-normal zeroing
+    compute_source_term(model, dt)
+    model.pressure_solver.solve(model.pNHS)
+    fill_halo_regions(model.pNHS)
+
+
+def pressure_correct_velocities(model, dt):
+    grid = model.grid
+    dt = _as_dt(grid, dt)
+    R = interior_region(grid)
+    for a in range(3):
+        U = model.velocities[a]
+        g = deriv(grid, model.pNHS.at, a, VEL_LOC[a], R) * dt
+        out = (U.at(*R) - g).astype(grid.FT)
+        U.at(*R)[...] = out
+
+
+def cache_previous_tendencies(model):
+    R = interior_region(model.grid)
+    for n in model.Gn:
+        model.Gm[n].at(*R)[...] = model.Gn[n].at(*R)
+
+
+def rk3_substep(model, dt, gamma, zeta):
+    FT = model.grid.FT
+    dt = FT(dt)
+    for n, f in zip(model.prognostic_names(), model.prognostic_fields()):
+        R = tendency_region(model.grid, f.loc)
+        if any(r[1] < r[0] for r in R):
+            continue
+        if zeta is None:
+            f.at(*R)[...] += dt * gamma * model.Gn[n].at(*R)
+        else:
+            f.at(*R)[...] += dt * (gamma * model.Gn[n].at(*R) + zeta * model.Gm[n].at(*R))
+
+
+def ab2_step(model, dt, chi):
+    FT = model.grid.FT
+    dt, chi = FT(dt), FT(chi)
+    not_euler = chi != FT(-0.5)
+    for n, f in zip(model.prognostic_names(), model.prognostic_fields()):
+        R = tendency_region(model.grid, f.loc)
+        if any(r[1] < r[0] for r in R):
+            continue
+        if not_euler:
+            G = (FT(1.5) + chi) * model.Gn[n].at(*R) - (FT(0.5) + chi) * model.Gm[n].at(*R)
+        else:   # `x * false` is a strong zero in Julia: stale NaNs in G⁻ do not propagate
+            G = (FT(1.5) + chi) * model.Gn[n].at(*R) - FT(0)
+        f.at(*R)[...] += dt * G
+
+
+def time_step(model, dt, euler=False):
+    """time_step!(model, Δt)."""
+    clock = model.clock
+    if clock.iteration == 0:
+        update_state(model, compute_tendencies=True)
+    if model.timestepper == "RungeKutta3":
+        c = model.rk3
+        FT = model.grid.FT
+        dtj = _as_dt(model.grid, dt)
+        first = c["g1"] * dtj
+        second = (c["g2"] + c["z2"]) * dtj
+        third = (c["g3"] + c["z3"]) * dtj
+        t_next = clock.time + float(dt)
+        # stage 1
+        rk3_substep(model, dt, c["g1"], None)
+        clock.time += float(first); clock.stage += 1; clock.last_stage_dt = float(first)
+        calculate_pressure_correction(model, first)
+        pressure_correct_velocities(model, first)
+        cache_previous_tendencies(model)
+        update_state(model)
+        # stage 2
+        rk3_substep(model, dt, c["g2"], c["z2"])
+        clock.time += float(second); clock.stage += 1; clock.last_stage_dt = float(second)
+        calculate_pressure_correction(model, second)
+        pressure_correct_velocities(model, second)
+        cache_previous_tendencies(model)
+        update_state(model)
+        # stage 3
+        rk3_substep(model, dt, c["g3"], c["z3"])
+        corrected = t_next - clock.time
+        clock.time += float(third); clock.iteration += 1; clock.stage = 1
+        clock.last_stage_dt = corrected
+        clock.last_dt = float(dt)
+        calculate_pressure_correction(model, third)
+        pressure_correct_velocities(model, third)
+        update_state(model)
+    elif model.timestepper == "QuasiAdamsBashforth2":
+        FT = model.grid.FT
+        euler = euler or (float(dt) != clock.last_dt)
+        chi = FT(-0.5) if euler else model.chi
+        ab2_step(model, dt, chi)
+        clock.time += float(dt); clock.iteration += 1; clock.stage = 1
+        clock.last_dt = float(dt); clock.last_stage_dt = float(dt)
+        calculate_pressure_correction(model, dt)
+        pressure_correct_velocities(model, dt)
+        cache_previous_tendencies(model)
+        update_state(model)
+    else:
+        raise ValueError(f"unknown timestepper {model.timestepper}")
+
+
+def set_model(model, enforce_incompressibility=True, **kwargs):
+    """set!(model; u=…, v=…, …): arrays of the field's interior size (Nx,Ny,Nz)[+1 on Bounded faces]."""
+    names = model.prognostic_names()
+    for name, value in kwargs.items():
+        if name not in names:
+            raise ValueError(f"name {name} not found in model.velocities or model.tracers.")
+        f = model.prognostic_fields()[names.index(name)]
+        f.set(value)
+        fill_halo_regions(f)
+    update_state(model, compute_tendencies=False)
+    if enforce_incompressibility:
+        one = model.grid.FT(1)
+        calculate_pressure_correction(model, one)
+        pressure_correct_velocities(model, one)
+        update_state(model, compute_tendencies=False)
