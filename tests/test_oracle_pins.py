@@ -1,0 +1,254 @@
+"""Pins the oracle against the reference's own property / analytic / known-answer tests.
+
+Each test restates one reference test and runs it on ``oracle/``:
+  test/test_poisson_solvers.jl:58-106 + test/dependencies_for_poisson_solvers.jl:13-141
+  test/test_poisson_solvers_stretched_grids.jl:12-50
+  test/test_batched_tridiagonal_solver.jl:7-42
+  test/test_time_stepping.jl:89-115,125-158,166-200,433-461
+  test/test_dynamics.jl:215-260
+"""
+import itertools
+
+import numpy as np
+import pytest
+
+import oracle as o
+from oracle.operators import divergence_ccc, laplacian_ccc, interior_region
+from oracle.fields import Field, fill_halo_regions
+
+P, B, F = o.Periodic, o.Bounded, o.Flat
+
+
+def isapprox(a, b, rtol=None):
+    """Julia's isapprox for arrays: norm(a-b) <= rtol*max(norm(a), norm(b)), rtol = sqrt(eps)."""
+    a, b = np.asarray(a), np.asarray(b)
+    if rtol is None:
+        rtol = np.sqrt(np.finfo(a.dtype).eps)
+    return np.linalg.norm((a - b).ravel()) <= rtol * max(np.linalg.norm(a.ravel()), np.linalg.norm(b.ravel()))
+
+
+def random_velocities(grid, rng):
+    U = [Field(grid, loc, name=n) for n, loc in zip("uvw", (("f", "c", "c"), ("c", "f", "c"), ("c", "c", "f")))]
+    for f in U:
+        f.set(rng.random(f.size))
+        fill_halo_regions(f)
+    return U
+
+
+def poisson_residual_ok(grid, rng):
+    """divergence_free_poisson_solution (dependencies_for_poisson_solvers.jl:79-97)."""
+    U = random_velocities(grid, rng)
+    R = interior_region(grid)
+    rhs = np.array(divergence_ccc(grid, *U, R))
+    solver = o.FFTBasedPoissonSolver(grid)
+    phi = Field(grid, ("c", "c", "c"), prognostic=False)
+    solver.storage[...] = rhs / 1            # solve_for_pressure!(ϕ, solver, Δt=1, U)
+    solver.solve(phi)
+    fill_halo_regions(phi)
+    lap = np.array(laplacian_ccc(grid, phi, R))
+    return isapprox(lap, rhs.astype(grid.FT))
+
+
+def make_grid(FT, topo, size3):
+    size = tuple(n for n, t in zip(size3, topo) if t != F)
+    kw = {}
+    for name, t in zip("xyz", topo):
+        if t != F:
+            kw[name] = (0, 1)
+    return o.RectilinearGrid(FT, size=size, topology=topo, **kw)
+
+
+TOPOS3 = list(itertools.product((P, B), repeat=3))
+TOPOS2 = [(F, P, P), (F, P, B), (F, B, B), (P, F, P), (P, F, B), (B, F, B), (P, P, F), (P, B, F), (B, B, F)]
+
+
+@pytest.mark.parametrize("topo", TOPOS3)
+@pytest.mark.parametrize("N", [7, 16])
+def test_poisson_divergence_free_3d(topo, N):
+    rng = np.random.default_rng(N)
+    assert poisson_residual_ok(make_grid(np.float64, topo, (N, N, N)), rng)
+    for size in [(1, N, N), (N, 1, N), (N, N, 1)]:
+        assert poisson_residual_ok(make_grid(np.float64, topo, size), rng)
+
+
+@pytest.mark.parametrize("topo", TOPOS2)
+def test_poisson_divergence_free_2d_flat(topo):
+    rng = np.random.default_rng(3)
+    for N in (7, 16):
+        assert poisson_residual_ok(make_grid(np.float64, topo, (N, N, N)), rng)
+
+
+@pytest.mark.parametrize("topo", TOPOS3)
+def test_poisson_rectangular_sizes(topo):
+    rng = np.random.default_rng(5)
+    for size in itertools.product((11, 16), repeat=3):
+        assert poisson_residual_ok(make_grid(np.float64, topo, size), rng)
+
+
+def test_poisson_float32():
+    rng = np.random.default_rng(7)
+    assert poisson_residual_ok(make_grid(np.float32, (P, B, B), (16, 16, 16)), rng)
+    assert poisson_residual_ok(make_grid(np.float32, (B, P, P), (7, 11, 16)), rng)
+
+
+def _analytic_error(N, topo, mode):
+    two_pi = 2 * np.pi
+    grid = o.RectilinearGrid(np.float64, size=(N, N, N), x=(0, two_pi), y=(0, two_pi), z=(0, two_pi), topology=topo)
+    solver = o.FFTBasedPoissonSolver(grid)
+    psi = {B: lambda x: np.cos(mode * x / 2), P: lambda x: np.cos(mode * x)}
+    k2 = {B: (mode / 2) ** 2, P: mode ** 2}
+    c = [grid.coords[d].C.r(1, N) for d in range(3)]
+    Psi = (psi[topo[0]](c[0])[:, None, None] * psi[topo[1]](c[1])[None, :, None] * psi[topo[2]](c[2])[None, None, :])
+    f = -(k2[topo[0]] + k2[topo[1]] + k2[topo[2]]) * Psi
+    phi = solver.solve(None, f)
+    return np.mean(np.abs(phi - Psi))
+
+
+@pytest.mark.parametrize("topo", TOPOS3)
+def test_poisson_convergence(topo):
+    for N1, N2 in ((2 ** 6, 2 ** 7), (67, 131)):
+        for mode in (1, 2):
+            e1, e2 = _analytic_error(N1, topo, mode), _analytic_error(N2, topo, mode)
+            rate = np.log(e1 / e2) / np.log(N2 / N1)
+            assert abs(rate - 2) <= 5e-3 * 2, (topo, N1, N2, mode, rate)
+
+
+# -- batched tridiagonal: test_batched_tridiagonal_solver.jl:7-42 -------------------------------
+@pytest.mark.parametrize("direction", [0, 1, 2])
+def test_batched_tridiagonal_vs_dense(direction):
+    rng = np.random.default_rng(11)
+    N = 8
+    size = [3, 4, 5]
+    size[direction] = N
+    grid = o.RectilinearGrid(np.float64, size=tuple(size), extent=(1, 1, 1), topology=(P, P, B))
+    a, c = rng.random(N - 1), rng.random(N - 1)
+    b = 3 + rng.random(N)                      # diagonally dominant
+    f = rng.random(size)
+    solver = o.BatchedTridiagonalSolver(grid, a, b, c, direction=direction)
+    phi = np.zeros(size)
+    solver.solve(phi, f)
+    M = np.diag(b) + np.diag(a, -1) + np.diag(c, 1)
+    expect = np.moveaxis(np.linalg.solve(M, np.moveaxis(f, direction, 0).reshape(N, -1)).reshape(
+        [N] + [s for d, s in enumerate(size) if d != direction]), 0, direction)
+    assert np.allclose(phi, expect, rtol=1e-12, atol=0)
+
+
+# -- Fourier-tridiagonal: test_poisson_solvers_stretched_grids.jl:12-50 -------------------------
+FACES = [1, 2, 4, 7, 11, 16, 22, 29, 37]
+
+
+def _w_from_continuity(grid, U):
+    """compute_w_from_continuity!: w[k+1] = w[k] - Δz·(δx(Ax u)+δy(Ay v))/Az, w[1] = 0."""
+    u, v, w = U
+    from oracle.operators import area, diff, delta
+    Nz = grid.N[2]
+    w.data[...] = 0
+    for k in range(1, Nz + (1 if grid.topology[2] == B else 0)):
+        R = [(1, grid.N[0]), (1, grid.N[1]), (k, k)]
+        flux = (diff(grid, lambda *r: area(grid, 0, ("f", "c", "c"), list(r)) * u.at(*r), 0, "c", R)
+                + diff(grid, lambda *r: area(grid, 1, ("c", "f", "c"), list(r)) * v.at(*r), 1, "c", R))
+        Rk1 = [R[0], R[1], (k + 1, k + 1)]
+        w.at(*Rk1)[...] = w.at(*R) - flux / area(grid, 2, ("c", "c", "c"), R)
+    return w
+
+
+@pytest.mark.parametrize("topo", [(P, P, B), (P, B, B), (B, P, B), (B, B, B), (F, P, B), (P, F, B), (F, B, B), (B, F, B)])
+def test_fourier_tridiagonal_stretched_z(topo):
+    rng = np.random.default_rng(13)
+    for N1, N2 in ((8, 8), (7, 11)):
+        size3 = (N1, N2, len(FACES) - 1)
+        size = tuple(n for n, t in zip(size3, topo) if t != F)
+        kw = {n: (0, 1) for n, t in zip("xy", topo[:2]) if t != F}
+        grid = o.RectilinearGrid(np.float64, size=size, topology=topo, z=np.array(FACES, float), **kw)
+        U = random_velocities(grid, rng)
+        _w_from_continuity(grid, U)
+        fill_halo_regions(U[2])
+        R = interior_region(grid)
+        rhs = np.array(divergence_ccc(grid, *U, R))
+        solver = o.FourierTridiagonalPoissonSolver(grid)
+        phi = Field(grid, ("c", "c", "c"), prognostic=False)
+        solver.solve(phi, rhs)
+        fill_halo_regions(phi)
+        lap = np.array(laplacian_ccc(grid, phi, R))
+        assert isapprox(lap, rhs), (topo, N1, N2)
+
+
+# -- time stepping ---------------------------------------------------------------------------------
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+def test_first_ab2_step_fields_stay_zero(FT):
+    """run_first_AB2_time_step_tests minus the user forcing (forcings are out of scope): all fields stay 0."""
+    grid = o.RectilinearGrid(FT, size=(13, 17, 19), extent=(1, 2, 3))
+    m = o.NonhydrostaticModel(grid, timestepper="QuasiAdamsBashforth2", buoyancy=o.SeawaterBuoyancy(), tracers=("T", "S"))
+    for G in m.Gn.values():
+        assert np.all(G.interior == 0)
+    o.time_step(m, 1, euler=True)
+    for f in m.prognostic_fields():
+        assert np.all(f.interior == 0)
+    assert m.clock.iteration == 1 and m.clock.time == 1.0
+
+
+def _tanh_faces(Nz, S=1.3):
+    k = np.arange(1, Nz + 2)
+    return np.tanh(S * (2 * (k - 1) / Nz - 1)) / np.tanh(S)
+
+
+@pytest.mark.parametrize("timestepper", ["QuasiAdamsBashforth2", "RungeKutta3"])
+@pytest.mark.parametrize("gridkind", ["regular", "tanh", "regular_vs"])
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+def test_incompressible_in_time(FT, gridkind, timestepper):
+    N = 32
+    z = {"regular": (-1, 1), "tanh": _tanh_faces(N), "regular_vs": np.linspace(0, 1, N + 1)}[gridkind]
+    grid = o.RectilinearGrid(FT, size=(N, N, N), x=(0, 1), y=(0, 1), z=z)
+    m = o.NonhydrostaticModel(grid, timestepper=timestepper, buoyancy=o.SeawaterBuoyancy(), tracers=("T", "S"))
+    m.tracers["T"].interior[7:24, 7:24, 7:24] += FT(0.01)
+    from oracle.model import update_state
+    update_state(m)
+    for n in range(10):                              # reference runs 1, 10 and 100; 1 and 10 here (100 in the slow suite)
+        o.time_step(m, 0.05)
+        if n == 0:
+            u, v, w = m.velocities
+            assert np.abs(divergence_ccc(m.grid, u, v, w, interior_region(m.grid))).max() < 5e-8
+    u, v, w = m.velocities
+    assert np.abs(w.interior).max() > 0
+    assert np.abs(divergence_ccc(m.grid, u, v, w, interior_region(m.grid))).max() < 5e-8
+
+
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+def test_tracer_conserved_in_channel(FT):
+    """tracer_conserved_in_channel with one isotropic ScalarDiffusivity (the anisotropic pair is out of scope)."""
+    Nx, Ny, Nz = 16, 32, 16
+    grid = o.RectilinearGrid(FT, size=(Nx, Ny, Nz), extent=(160e3, 320e3, 1024), topology=(P, B, B))
+    m = o.NonhydrostaticModel(grid, closure=o.ScalarDiffusivity(nu=1e-2, kappa=1e-2),
+                              buoyancy=o.SeawaterBuoyancy(), tracers=("T", "S"))
+    rng = np.random.default_rng(17)
+    y = grid.coords[1].C.r(1, Ny)[None, :, None]
+    z = grid.coords[2].C.r(1, Nz)[None, None, :]
+    o.set_model(m, T=10 + 1e-4 * y + 5e-3 * z + 1e-4 * rng.random((Nx, Ny, Nz)))
+    T0 = np.mean(m.tracers["T"].interior.astype(np.float64))
+    for _ in range(10):
+        o.time_step(m, 600)
+    T1 = np.mean(m.tracers["T"].interior.astype(np.float64))
+    assert abs(T1 - T0) <= Nx * Ny * Nz * np.finfo(FT).eps
+
+
+@pytest.mark.parametrize("timestepper", ["QuasiAdamsBashforth2", "RungeKutta3"])
+def test_taylor_green_vortex(timestepper):
+    N, Nt, nu = 64, 10, 1
+    dx = 1 / N
+    dt = (1 / (10 * np.pi)) * dx ** 2 / nu
+    grid = o.RectilinearGrid(np.float64, size=(N, N, 2), extent=(1, 1, 1))
+    m = o.NonhydrostaticModel(grid, timestepper=timestepper, closure=o.ScalarDiffusivity(nu=1))
+    ua = lambda y, t: -np.sin(2 * np.pi * y) * np.exp(-4 * np.pi ** 2 * nu * t)
+    va = lambda x, t: np.sin(2 * np.pi * x) * np.exp(-4 * np.pi ** 2 * nu * t)
+    xF, xC = grid.coords[0].F.r(1, N), grid.coords[0].C.r(1, N)
+    yF, yC = grid.coords[1].F.r(1, N), grid.coords[1].C.r(1, N)
+    u0 = np.broadcast_to(ua(yC, 0)[None, :, None], (N, N, 2))
+    v0 = np.broadcast_to(va(xC, 0)[:, None, None], (N, N, 2))
+    o.set_model(m, u=u0, v=v0)
+    for _ in range(Nt):
+        o.time_step(m, dt)
+    t = m.clock.time
+    ue = np.broadcast_to(ua(yC, t)[None, :, None], (N, N, 2))
+    ve = np.broadcast_to(va(xC, t)[:, None, None], (N, N, 2))
+    assert np.max(np.abs((m.velocities[0].interior - ue) / ue)) < 5e-6
+    assert np.max(np.abs((m.velocities[1].interior - ve) / ve)) < 5e-6
