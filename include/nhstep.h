@@ -1,0 +1,161 @@
+/* nhstep.h — C ABI of libnhstep.so: a B200 (sm_100a) implementation of the Oceananigans
+ * NonhydrostaticModel time step.  Plain C, no torch / C++ types in any signature.
+ *
+ * Every entry point names the reference interface (samlewin/Oceananigans.jl v0.96.19, paths relative
+ * to the reference root) that a Julia `ccall` shim would forward to it; see INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns int32_t: 0 = ok, non-zero = error; nh_last_error() gives the message
+ *     (thread-local).  No exception crosses the ABI.  There is no CPU fallback: if no CUDA device is
+ *     usable, the create calls fail.
+ *   - the library owns all device memory.  Host pointers are borrowed for the duration of a call.
+ *   - one nh_model = one device + one stream.  Calls on one handle are not thread-safe.  All calls are
+ *     asynchronous with respect to the host except nh_get_*, nh_synchronize and calls taking host pointers.
+ *   - arrays cross the ABI in the reference's layout: column-major, x fastest, either the field's
+ *     `interior` (Nx,Ny,Nz [+1 on a Bounded Face dim]) or its `parent` (interior + 2H per non-Flat dim),
+ *     element type = the grid's float type (src/Fields/field.jl:19-33, src/Grids/new_data.jl:15-70).
+ */
+#ifndef NHSTEP_H
+#define NHSTEP_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nh_grid    nh_grid;
+typedef struct nh_model   nh_model;
+typedef struct nh_poisson nh_poisson;
+typedef struct nh_tridiag nh_tridiag;
+
+enum { NH_F32 = 0, NH_F64 = 1 };
+enum { NH_PERIODIC = 0, NH_BOUNDED = 1, NH_FLAT = 2 };
+enum { NH_ADV_NONE = 0, NH_ADV_CENTERED = 1, NH_ADV_UPWIND = 2, NH_ADV_WENO = 3 };
+enum { NH_RK3 = 0, NH_AB2 = 1 };
+enum { NH_BUOYANCY_NONE = 0, NH_BUOYANCY_TRACER = 1, NH_BUOYANCY_SEAWATER_LINEAR = 2 };
+enum { NH_HOST = 0, NH_DEVICE = 1 };
+enum { NH_INTERIOR = 0, NH_PARENT = 1 };
+enum { NH_SOLVER_FFT = 0, NH_SOLVER_FOURIER_TRIDIAGONAL = 1 };
+
+/* field ids for nh_set_field / nh_get_field / halo masks */
+enum {
+  NH_FIELD_U = 0, NH_FIELD_V = 1, NH_FIELD_W = 2,
+  NH_FIELD_TRACER0 = 3,            /* tracer n = NH_FIELD_TRACER0 + n, n < NH_MAX_TRACERS */
+  NH_FIELD_PNHS = 16, NH_FIELD_PHY = 17,
+  NH_FIELD_GN0 = 32,               /* Gⁿ of prognostic field f = NH_FIELD_GN0 + f */
+  NH_FIELD_GM0 = 48                /* G⁻ of prognostic field f = NH_FIELD_GM0 + f */
+};
+#define NH_MAX_TRACERS 8
+
+/* RectilinearGrid(arch, FT; size, x, y, z, halo, topology) — src/Grids/rectilinear_grid.jl:248-275.
+ * x and y must be regular intervals; z is a regular interval (z_faces == NULL) or Nz+1 increasing faces.
+ * Flat dimensions: N = 1 is not required (N is the given extent), H is forced to 0, interval ignored. */
+typedef struct {
+  int32_t float_type;
+  int32_t N[3];
+  int32_t H[3];
+  int32_t topology[3];
+  double  x[2], y[2], z[2];
+  const double* z_faces;           /* NULL, or Nz+1 host doubles (converted to FT like the reference does) */
+} nh_grid_desc;
+
+/* NonhydrostaticModel(; grid, advection, buoyancy, coriolis, closure, tracers, timestepper,
+ *                       hydrostatic_pressure_anomaly) — src/Models/NonhydrostaticModels/nonhydrostatic_model.jl:114-239 */
+typedef struct {
+  int32_t advection_kind[3];       /* per direction (FluxFormAdvection); same value thrice for a plain scheme */
+  int32_t advection_order[3];      /* Centered 2|4, UpwindBiased 1|3|5, WENO 3|5 */
+  int32_t timestepper;             /* NH_RK3 | NH_AB2 */
+  double  ab2_chi;                 /* QuasiAdamsBashforth2 χ (default 0.1) */
+  int32_t n_tracers;
+  int32_t buoyancy_kind;
+  int32_t buoyancy_tracer[2];      /* tracer index of b (TRACER) or of T and S (SEAWATER_LINEAR) */
+  double  gravitational_acceleration, thermal_expansion, haline_contraction;
+  int32_t has_coriolis;            /* FPlane */
+  double  coriolis_f;
+  int32_t has_closure;             /* ScalarDiffusivity (explicit, isotropic) */
+  double  nu;
+  double  kappa[NH_MAX_TRACERS];
+  int32_t hydrostatic_pressure_anomaly;   /* -1 default (on iff buoyancy), 0 off, 1 on */
+  int32_t exact_arithmetic;        /* 1: kernels compiled without FMA contraction, reference expression order (parity
+                                      mode); 0: fused fast kernels where available */
+} nh_model_desc;
+
+typedef struct { double time; int64_t iteration; int32_t stage; double last_dt; double last_stage_dt; } nh_clock;
+
+const char* nh_last_error(void);
+int32_t nh_version(void);
+int32_t nh_device_count(int32_t* count);
+
+/* ---- grid ------------------------------------------------------------------------------------------------ */
+int32_t nh_grid_create(const nh_grid_desc* desc, int32_t device, nh_grid** out);
+int32_t nh_grid_destroy(nh_grid* grid);
+/* with_halo(new_halo, grid) — src/Grids/rectilinear_grid.jl (used by inflate_grid_halo_size, nonhydrostatic_model.jl:243-257) */
+int32_t nh_grid_info(const nh_grid* grid, nh_grid_desc* out);          /* desc with the final halo; z_faces = NULL */
+/* Δzᵃᵃᶜ[k], Δzᵃᵃᶠ[k] for k = 1-Hz … Nz+Hz as doubles (src/Grids/grid_generation.jl:34-135); spacing[0] = Δx, [1] = Δy */
+int32_t nh_grid_spacings(const nh_grid* grid, double* dxdy, double* dzc, double* dzf, int64_t nz_entries);
+
+/* ---- model ----------------------------------------------------------------------------------------------- */
+int32_t nh_model_create(nh_grid* grid, const nh_model_desc* desc, nh_model** out);
+int32_t nh_model_destroy(nh_model* model);
+int32_t nh_model_grid_info(const nh_model* model, nh_grid_desc* out);   /* halo after inflate_grid_halo_size */
+/* interior(field) / parent(field) in and out; `where` = NH_HOST or NH_DEVICE pointer; count = #elements in data */
+int32_t nh_field_size(const nh_model* model, int32_t field, int32_t region, int64_t size[3]);
+int32_t nh_set_field(nh_model* model, int32_t field, int32_t region, const void* data, int64_t count, int32_t where);
+int32_t nh_get_field(nh_model* model, int32_t field, int32_t region, void* data, int64_t count, int32_t where);
+/* set!(model; …) tail — set_nonhydrostatic_model.jl:44-58: fill halos of the set fields is done by nh_set_field(INTERIOR);
+ * this call = update_state!(compute_tendencies=false) [+ pressure solve and correction with Δt = 1 + update_state!] */
+int32_t nh_set_state_finalize(nh_model* model, int32_t enforce_incompressibility);
+
+/* fill_halo_regions!(fields…; fill_boundary_normal_velocities) — src/Fields/field_tuples.jl:56-119,
+ * src/BoundaryConditions/fill_halo_regions.jl:50-82.  field_mask bit f = field id f (ids < 32). */
+int32_t nh_fill_halo_regions(nh_model* model, uint32_t field_mask, int32_t fill_boundary_normal_velocities);
+/* update_state!(model; compute_tendencies) — update_nonhydrostatic_model_state.jl:20-57 */
+int32_t nh_update_state(nh_model* model, int32_t compute_tendencies);
+/* compute_tendencies!(model, callbacks) — compute_nonhydrostatic_tendencies.jl:17-54 */
+int32_t nh_compute_tendencies(nh_model* model);
+/* rk3_substep!(model, Δt, γ, ζ) — src/TimeSteppers/runge_kutta_3.jl:160-208 (has_zeta = 0 ⇒ first stage) */
+int32_t nh_rk3_substep(nh_model* model, double dt, double gamma, double zeta, int32_t has_zeta);
+/* ab2_step!(model, Δt, χ) — src/TimeSteppers/quasi_adams_bashforth_2.jl:128-175 */
+int32_t nh_ab2_step(nh_model* model, double dt, double chi);
+/* cache_previous_tendencies!(model) — src/TimeSteppers/store_tendencies.jl:12-22 */
+int32_t nh_cache_previous_tendencies(nh_model* model);
+/* calculate_pressure_correction!(model, Δt), pressure_correct_velocities!(model, Δt) — pressure_correction.jl:8-50 */
+int32_t nh_calculate_pressure_correction(nh_model* model, double dt);
+int32_t nh_pressure_correct_velocities(nh_model* model, double dt);
+/* time_step!(model, Δt; euler) — runge_kutta_3.jl:77-151 / quasi_adams_bashforth_2.jl:74-115; n_steps ≥ 1 repeats it */
+int32_t nh_time_step(nh_model* model, double dt, int32_t euler, int32_t n_steps);
+int32_t nh_clock_get(const nh_model* model, nh_clock* out);
+int32_t nh_clock_set(nh_model* model, const nh_clock* in);
+/* max |div U| and other diagnostics used by the reference tests (test/utils_for_runtests.jl:125-151) */
+int32_t nh_max_abs_divergence(nh_model* model, double* out);
+int32_t nh_synchronize(nh_model* model);
+/* raw device pointer + strides of a field (for zero-copy torch views and NCCL halo/transposes) */
+int32_t nh_field_device_ptr(nh_model* model, int32_t field, void** ptr, int64_t offset_of_111[1], int64_t strides[3]);
+int32_t nh_model_set_stream(nh_model* model, void* cuda_stream);
+/* number of kernels launched by this model since creation (bench.py's gpu_launches) */
+int32_t nh_launch_count(const nh_model* model, int64_t* count);
+
+/* ---- standalone solvers ---------------------------------------------------------------------------------- */
+/* FFTBasedPoissonSolver(grid) — src/Solvers/fft_based_poisson_solver.jl:52-74;
+ * FourierTridiagonalPoissonSolver(grid) — src/Solvers/fourier_tridiagonal_poisson_solver.jl:71-117 */
+int32_t nh_poisson_create(nh_grid* grid, int32_t kind, nh_poisson** out);
+int32_t nh_poisson_destroy(nh_poisson* solver);
+/* solve!(ϕ, solver, b, m) — fft_based_poisson_solver.jl:95-125 / fourier_tridiagonal_poisson_solver.jl:119-147 (+ set_source_term!).
+ * rhs and phi are real (Nx,Ny,Nz) arrays of the grid's float type; `where` as above.  m is the Helmholtz shift (FFT solver only). */
+int32_t nh_poisson_solve(nh_poisson* solver, const void* rhs, void* phi, double m, int32_t where);
+int32_t nh_poisson_synchronize(nh_poisson* solver);
+int32_t nh_poisson_launch_count(const nh_poisson* solver, int64_t* count);
+/* timing helper: n back-to-back solves on device-resident data, elapsed ms from CUDA events on the solver's stream */
+int32_t nh_poisson_time_solves(nh_poisson* solver, const void* rhs_dev, void* phi_dev, int32_t n, float* ms);
+
+/* BatchedTridiagonalSolver(grid; lower_diagonal, diagonal, upper_diagonal, tridiagonal_direction) + solve!(ϕ, solver, rhs)
+ * — src/Solvers/batched_tridiagonal_solver.jl:11-79,100-235.  a, c: n-1 host values (1-D), b: n host values (1-D) or
+ * Nx·Ny·Nz (3-D) when b_is_3d; direction 0|1|2.  rhs/phi real arrays of the grid float type (host). */
+int32_t nh_tridiag_create(nh_grid* grid, const double* a, const double* b, const double* c, int32_t b_is_3d,
+                          int32_t direction, nh_tridiag** out);
+int32_t nh_tridiag_solve(nh_tridiag* solver, const void* rhs, void* phi);
+int32_t nh_tridiag_destroy(nh_tridiag* solver);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,209 @@
+// kernels_basic.cuh — halo fills, RK3/AB2 substeps, source term, pressure correction, hydrostatic pressure,
+// layout conversion.  Complete (any topology) versions in the reference's expression order; the fused fast kernels
+// live in step_fast.cu.
+#pragma once
+#include "tendency_generic.cuh"
+
+#define NH_MAXF (3 + NH_MAXTR)
+
+// ---- halo fill ------------------------------------------------------------------------------------------------
+// src/BoundaryConditions/fill_halo_regions_periodic.jl:40-111, fill_halo_regions_flux.jl:14-33,
+// fill_halo_regions_open.jl:65-70.  One launch fills one direction of up to NH_MAXF fields (the tupled fill of
+// src/Fields/field_tuples.jl:88-101).
+template <typename FT>
+struct HaloJob {
+  GridDev<FT> g;
+  FT* p[NH_MAXF];
+  int mode[NH_MAXF];      // 0 skip, 1 periodic, 2 flux (mirror), 3 open (wall-normal velocity := 0)
+  int nf;
+  int d;                  // direction being filled
+  int lo[3], hi[3];       // transverse logical index range (inclusive); entry d unused
+};
+
+template <typename FT>
+__global__ void halo_fill_kernel(const __grid_constant__ HaloJob<FT> J) {
+  const GridDev<FT>& g = J.g;
+  const int d = J.d;
+  const int e1 = d == 0 ? 1 : 0, e2 = d == 2 ? 1 : 2;
+  int n1 = J.hi[e1] - J.lo[e1] + 1, n2 = J.hi[e2] - J.lo[e2] + 1;
+  long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= (long long)n1 * n2) return;
+  int a1 = J.lo[e1] + (int)(t % n1), a2 = J.lo[e2] + (int)(t / n1);
+  int f = blockIdx.y;
+  int mode = J.mode[f];
+  if (mode == 0) return;
+  FT* p = J.p[f];
+  const int N = g.N[d], H = g.H[d];
+  int c[3];
+  c[e1] = a1; c[e2] = a2;
+  auto at = [&](int q) -> FT& { c[d] = q; return p[g.idx(c[0], c[1], c[2])]; };
+  if (mode == 1) {
+    for (int h = 1; h <= H; ++h) {
+      at(h - H) = at(N - H + h);       // west halo  ← east end of the interior
+      at(N + h) = at(h);               // east halo  ← west end of the interior
+    }
+  } else if (mode == 2) {
+    at(0) = at(1);
+    at(N + 1) = at(N);
+  } else {
+    at(1) = FT(0);
+    at(N + 1) = FT(0);
+  }
+}
+
+// ---- time-stepper substeps ------------------------------------------------------------------------------------
+template <typename FT>
+struct StepJob {
+  GridDev<FT> g;
+  FT* U[NH_MAXF];
+  const FT* Gn[NH_MAXF];
+  FT* Gm[NH_MAXF];
+  int face_dim[NH_MAXF];   // 0,1,2 for u,v,w; -1 for tracers
+  int nf;
+  FT dt, c1, c2;           // RK3: c1 = γ, c2 = ζ; AB2: c1 = χ
+  int mode;                // 0: RK3 first stage, 1: RK3 stages 2,3, 2: AB2, 3: AB2 Euler (χ = -1/2), 4: G⁻ ← Gⁿ
+};
+
+template <typename FT>
+__global__ void __launch_bounds__(256) substep_kernel(const __grid_constant__ StepJob<FT> J) {
+  const GridDev<FT>& g = J.g;
+  int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  int k = blockIdx.z + 1;
+  if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
+  long long n = g.idx(i, j, k);
+  for (int f = 0; f < J.nf; ++f) {
+    if (J.mode == 4) { J.Gm[f][n] = J.Gn[f][n]; continue; }   // cache_previous_tendencies! over the interior
+    int fd = J.face_dim[f];
+    if (fd >= 0 && g.topo[fd] == NH_BOUNDED && g.N[fd] > 1 && (fd == 0 ? i : (fd == 1 ? j : k)) == 1) continue;
+    FT u = J.U[f][n];
+    if (J.mode == 0) {
+      u = u + J.dt * J.c1 * J.Gn[f][n];
+    } else if (J.mode == 1) {
+      u = u + J.dt * (J.c1 * J.Gn[f][n] + J.c2 * J.Gm[f][n]);
+    } else if (J.mode == 2) {
+      FT G = (FT(1.5) + J.c1) * J.Gn[f][n] - (FT(0.5) + J.c1) * J.Gm[f][n];
+      u = u + J.dt * G;
+    } else {
+      FT G = (FT(1.5) + J.c1) * J.Gn[f][n] - FT(0);
+      u = u + J.dt * G;
+    }
+    J.U[f][n] = u;
+  }
+}
+
+// ---- divergence, source term, pressure correction -------------------------------------------------------------
+// divᶜᶜᶜ — src/Operators/divergence_operators.jl:16-19
+template <typename FT>
+__device__ __forceinline__ FT div_ccc(const GridDev<FT>& g, const FT* u, const FT* v, const FT* w, int i, int j, int k) {
+  FT tx = FT(0), ty = FT(0), tz = FT(0);
+  if (g.topo[0] != NH_FLAT) { FT A = area_at(g, 0, 1, k); tx = A * u[g.idx(i + 1, j, k)] - A * u[g.idx(i, j, k)]; }
+  if (g.topo[1] != NH_FLAT) { FT A = area_at(g, 1, 1, k); ty = A * v[g.idx(i, j + 1, k)] - A * v[g.idx(i, j, k)]; }
+  if (g.topo[2] != NH_FLAT) { FT A = area_at(g, 2, 0, k); tz = A * w[g.idx(i, j, k + 1)] - A * w[g.idx(i, j, k)]; }
+  FT total = tx + ty;
+  total = total + tz;
+  return FT(1) / volume_at(g, 1, k) * total;
+}
+
+// _compute_source_term! / _fourier_tridiagonal_source_term! — solve_for_pressure.jl:12-38.  Δt is a Float64 at the
+// reference's call sites, so for Float32 grids the division is done in Float64 and rounded on store.
+template <typename FT, typename CT>
+__global__ void __launch_bounds__(256) source_term_kernel(GridDev<FT> g, const FT* u, const FT* v, const FT* w, double dt,
+                                                          int times_dz, CT* rhs) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  int k = blockIdx.z + 1;
+  if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
+  FT d = div_ccc(g, u, v, w, i, j, k);
+  if (times_dz) d = g.Dzc(k) * d;
+  FT r;
+  if (sizeof(FT) == 4) r = (FT)((double)d / dt); else r = (FT)(d / (FT)dt);
+  CT out; out.x = r; out.y = FT(0);
+  rhs[(long long)(i - 1) + (long long)g.N[0] * ((j - 1) + (long long)g.N[1] * (k - 1))] = out;
+}
+
+// _pressure_correct_velocities! — pressure_correction.jl:31-37 (∂p·Δt evaluated in Float64 for Float32 grids)
+template <typename FT>
+__global__ void __launch_bounds__(256) pressure_correct_kernel(GridDev<FT> g, FT* u, FT* v, FT* w, const FT* p, double dt) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  int k = blockIdx.z + 1;
+  if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
+  long long n = g.idx(i, j, k);
+  FT p0 = p[n];
+  FT gx = g.topo[0] == NH_FLAT ? FT(0) : (p0 - p[g.idx(i - 1, j, k)]) / g.dx;
+  FT gy = g.topo[1] == NH_FLAT ? FT(0) : (p0 - p[g.idx(i, j - 1, k)]) / g.dy;
+  FT gz = g.topo[2] == NH_FLAT ? FT(0) : (p0 - p[g.idx(i, j, k - 1)]) / g.Dzf(k);
+  if (sizeof(FT) == 4) {
+    u[n] = (FT)((double)u[n] - (double)gx * dt);
+    v[n] = (FT)((double)v[n] - (double)gy * dt);
+    w[n] = (FT)((double)w[n] - (double)gz * dt);
+  } else {
+    u[n] = u[n] - gx * (FT)dt;
+    v[n] = v[n] - gy * (FT)dt;
+    w[n] = w[n] - gz * (FT)dt;
+  }
+}
+
+// _update_hydrostatic_pressure! — update_hydrostatic_pressure.jl:12-20,41-49: one thread per column, top-down
+template <typename FT>
+__global__ void hydrostatic_pressure_kernel(const __grid_constant__ TendParams<FT> P, FT* pHY) {
+  const GridDev<FT>& g = P.g;
+  int i0 = g.topo[0] == NH_FLAT ? 1 : 0, j0 = g.topo[1] == NH_FLAT ? 1 : 0;
+  int ni = g.topo[0] == NH_FLAT ? g.N[0] : g.N[0] + 2, nj = g.topo[1] == NH_FLAT ? g.N[1] : g.N[1] + 2;
+  int ti = blockIdx.x * blockDim.x + threadIdx.x, tj = blockIdx.y * blockDim.y + threadIdx.y;
+  if (ti >= ni || tj >= nj) return;
+  int i = i0 + ti, j = j0 + tj;
+  const int Nz = g.N[2];
+  FT b_up = buoyancy_at(P, i, j, Nz + 1);
+  FT b_k = buoyancy_at(P, i, j, Nz);
+  FT ph = -(FT(0.5) * (b_k + b_up)) * g.Dzf(Nz + 1);
+  pHY[g.idx(i, j, Nz)] = ph;
+  for (int k = Nz - 1; k >= 1; --k) {
+    b_up = b_k;
+    b_k = buoyancy_at(P, i, j, k);
+    ph = ph - (FT(0.5) * (b_k + b_up)) * g.Dzf(k + 1);
+    pHY[g.idx(i, j, k)] = ph;
+  }
+}
+
+// copy_real_component! — fft_based_poisson_solver.jl:129-137 (dense complex N³ → halo'd real field)
+template <typename FT, typename CT>
+__global__ void __launch_bounds__(256) copy_real_kernel(GridDev<FT> g, const CT* phi, FT* p) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  int k = blockIdx.z + 1;
+  if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
+  p[g.idx(i, j, k)] = phi[(long long)(i - 1) + (long long)g.N[0] * ((j - 1) + (long long)g.N[1] * (k - 1))].x;
+}
+
+// dense (reference layout) ↔ internal layout; region given by logical lower corner and extents
+template <typename FT>
+__global__ void layout_copy_kernel(GridDev<FT> g, FT* field, FT* dense, int i0, int j0, int k0, int nx, int ny, int nz, int to_field) {
+  long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  long long tot = (long long)nx * ny * nz;
+  if (t >= tot) return;
+  int a = (int)(t % nx), b = (int)((t / nx) % ny), c = (int)(t / ((long long)nx * ny));
+  long long n = g.idx(i0 + a, j0 + b, k0 + c);
+  if (to_field) field[n] = dense[t]; else dense[t] = field[n];
+}
+
+// max |div U| over the interior (test/utils_for_runtests.jl:139-151): block maxima, finished on the host
+template <typename FT>
+__global__ void __launch_bounds__(256) max_div_kernel(GridDev<FT> g, const FT* u, const FT* v, const FT* w, double* out) {
+  long long tot = (long long)g.N[0] * g.N[1] * g.N[2];
+  double m = 0;
+  for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < tot; t += (long long)gridDim.x * blockDim.x) {
+    int i = (int)(t % g.N[0]) + 1, j = (int)((t / g.N[0]) % g.N[1]) + 1, k = (int)(t / ((long long)g.N[0] * g.N[1])) + 1;
+    double d = fabs((double)div_ccc(g, u, v, w, i, j, k));
+    m = d > m || d != d ? d : m;
+  }
+  __shared__ double sm[256];
+  sm[threadIdx.x] = m;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) { double o = sm[threadIdx.x + s]; if (o > sm[threadIdx.x] || o != o) sm[threadIdx.x] = o; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[blockIdx.x] = sm[0];
+}

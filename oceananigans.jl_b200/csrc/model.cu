@@ -1,0 +1,369 @@
+// model.cu — Model<FT>: allocation, field I/O, halo fills, update_state!, time steppers, pressure correction
+#include "model.cuh"
+
+#define KLAUNCH(lcp) do { (lcp).n++; } while (0)
+
+template <typename FT>
+FT* Model<FT>::alloc_field() {
+  bufs.emplace_back(new DevBuf<FT>());
+  bufs.back()->alloc((size_t)gh.volume());
+  return bufs.back()->p;
+}
+
+static void adapt_order(int& kind, int& B, int N, int topo) {
+  // adapt_advection_order.jl:18-51,104-110: lower the order when the dimension is shorter than the buffer
+  if (topo == NH_FLAT || kind == NH_ADV_NONE) return;
+  if (N >= B) return;
+  B = N;
+  if (kind == NH_ADV_WENO && B < 2) kind = NH_ADV_UPWIND;
+}
+
+template <typename FT>
+Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
+  desc = d;
+  device = grid.device;
+  float_type = grid.desc.float_type;
+  CUDA_CHECK(cudaSetDevice(device));
+  ntr = d.n_tracers;
+  NH_REQUIRE(ntr >= 0 && ntr <= NH_MAXTR, "too many tracers");
+  nf = 3 + ntr;
+  int maxB = 1;
+  for (int e = 0; e < 3; ++e) {
+    int kind = d.advection_kind[e], order = d.advection_order[e], B = 1;
+    if (kind == NH_ADV_CENTERED) { NH_REQUIRE(order == 2 || order == 4, "Centered order must be 2 or 4"); B = order / 2; }
+    else if (kind == NH_ADV_UPWIND) { NH_REQUIRE(order == 1 || order == 3 || order == 5, "UpwindBiased order must be 1, 3 or 5"); B = (order + 1) / 2; }
+    else if (kind == NH_ADV_WENO) {
+      NH_REQUIRE(order == 1 || order == 3 || order == 5, "WENO order must be 3 or 5");
+      B = (order + 1) / 2;
+      if (B == 1) kind = NH_ADV_UPWIND;
+    } else NH_REQUIRE(kind == NH_ADV_NONE, "unknown advection kind");
+    adapt_order(kind, B, grid.desc.N[e], grid.desc.topology[e]);
+    adv[e].kind = kind; adv[e].B = B;
+    if (kind != NH_ADV_NONE && B > maxB) maxB = B;
+  }
+  // inflate_grid_halo_size — nonhydrostatic_model.jl:243-257
+  int H[3];
+  for (int e = 0; e < 3; ++e) H[e] = grid.desc.topology[e] == NH_FLAT ? 0 : std::max(grid.desc.H[e], maxB);
+  gh.build(grid.desc, grid.zfaces, H);
+  gdesc = grid.desc; gdesc.z_faces = nullptr;
+  for (int e = 0; e < 3; ++e) gdesc.H[e] = gh.g.H[e];
+  for (int e = 0; e < 3; ++e)
+    if (gh.g.topo[e] == NH_PERIODIC) NH_REQUIRE(gh.g.H[e] <= gh.g.N[e], "halo must be <= size in a Periodic dimension");
+  if (d.buoyancy_kind == NH_BUOYANCY_TRACER) NH_REQUIRE(d.buoyancy_tracer[0] >= 0 && d.buoyancy_tracer[0] < ntr, "buoyancy tracer index");
+  if (d.buoyancy_kind == NH_BUOYANCY_SEAWATER_LINEAR)
+    NH_REQUIRE(d.buoyancy_tracer[0] >= 0 && d.buoyancy_tracer[0] < ntr && d.buoyancy_tracer[1] >= 0 && d.buoyancy_tracer[1] < ntr, "T/S tracer indices");
+
+  nhhost::Tables<FT> T;
+  nhhost::make_scheme_tables<FT>(T);
+  static_assert(sizeof(T) == sizeof(tab), "table layouts differ");
+  std::memcpy(&tab, &T, sizeof(tab));
+
+  for (int f = 0; f < nf; ++f) { F[f] = alloc_field(); Gn[f] = alloc_field(); Gm[f] = alloc_field(); }
+  pNHS = alloc_field();
+  bool want_phy = d.hydrostatic_pressure_anomaly < 0 ? d.buoyancy_kind != NH_BUOYANCY_NONE : d.hydrostatic_pressure_anomaly != 0;
+  if (want_phy) pHY = alloc_field();
+
+  solver.lc = &lc;
+  solver.stream = stream;
+  solver.create(gh, gh.z_stretched ? NH_SOLVER_FOURIER_TRIDIAGONAL : NH_SOLVER_FFT);
+  red.alloc(1024);
+
+  rk_g1 = (FT)8 / (FT)15; rk_g2 = (FT)5 / (FT)12; rk_g3 = (FT)3 / (FT)4;
+  rk_z2 = (FT)-17 / (FT)60; rk_z3 = (FT)-5 / (FT)12;
+  chi = (FT)d.ab2_chi;
+  clock.time = 0; clock.iteration = 0; clock.stage = 1; clock.last_dt = INFINITY; clock.last_stage_dt = INFINITY;
+  update_state(0);
+}
+
+template <typename FT>
+int Model<FT>::field_face_dim(int field) const {
+  int f = field;
+  if (field >= NH_FIELD_GM0) f = field - NH_FIELD_GM0;
+  else if (field >= NH_FIELD_GN0) f = field - NH_FIELD_GN0;
+  return (f >= 0 && f < 3) ? f : -1;
+}
+
+template <typename FT>
+FT* Model<FT>::field_ptr(int field) {
+  if (field >= 0 && field < nf) return F[field];
+  if (field == NH_FIELD_PNHS) return pNHS;
+  if (field == NH_FIELD_PHY) { NH_REQUIRE(pHY, "model has no hydrostatic pressure anomaly"); return pHY; }
+  if (field >= NH_FIELD_GN0 && field < NH_FIELD_GN0 + nf) return Gn[field - NH_FIELD_GN0];
+  if (field >= NH_FIELD_GM0 && field < NH_FIELD_GM0 + nf) return Gm[field - NH_FIELD_GM0];
+  throw NhError("unknown field id");
+}
+
+template <typename FT>
+void Model<FT>::field_extent(int field, int n[3]) const {
+  int fd = field_face_dim(field);
+  for (int e = 0; e < 3; ++e) n[e] = gh.g.N[e] + ((fd == e && gh.g.topo[e] == NH_BOUNDED) ? 1 : 0);
+}
+
+template <typename FT>
+void Model<FT>::field_size(int field, int region, int64_t size[3]) {
+  (void)field_ptr(field);
+  int n[3]; field_extent(field, n);
+  for (int e = 0; e < 3; ++e) size[e] = n[e] + (region == NH_PARENT ? 2 * gh.g.H[e] : 0);
+}
+
+template <typename FT>
+void Model<FT>::set_field(int field, int region, const void* data, int64_t count, int where) {
+  FT* p = field_ptr(field);
+  int64_t sz[3]; field_size(field, region, sz);
+  NH_REQUIRE(count == sz[0] * sz[1] * sz[2], "nh_set_field: element count does not match the field's size");
+  const FT* src = (const FT*)data;
+  if (where == NH_HOST) {
+    if (stage.n < (size_t)count) stage.alloc(count, false);
+    CUDA_CHECK(cudaMemcpyAsync(stage.p, data, count * sizeof(FT), cudaMemcpyHostToDevice, stream));
+    src = stage.p;
+  }
+  int lo[3]; for (int e = 0; e < 3; ++e) lo[e] = region == NH_PARENT ? 1 - gh.g.H[e] : 1;
+  layout_copy_kernel<FT><<<ceil_div(count, 256), 256, 0, stream>>>(gh.g, p, const_cast<FT*>(src), lo[0], lo[1], lo[2], (int)sz[0], (int)sz[1], (int)sz[2], 1);
+  KLAUNCH(lc);
+  CUDA_CHECK(cudaGetLastError());
+  if (where == NH_HOST) CUDA_CHECK(cudaStreamSynchronize(stream));
+}
+
+template <typename FT>
+void Model<FT>::get_field(int field, int region, void* data, int64_t count, int where) {
+  FT* p = field_ptr(field);
+  int64_t sz[3]; field_size(field, region, sz);
+  NH_REQUIRE(count == sz[0] * sz[1] * sz[2], "nh_get_field: element count does not match the field's size");
+  FT* dst = (FT*)data;
+  if (where == NH_HOST) { if (stage.n < (size_t)count) stage.alloc(count, false); dst = stage.p; }
+  int lo[3]; for (int e = 0; e < 3; ++e) lo[e] = region == NH_PARENT ? 1 - gh.g.H[e] : 1;
+  layout_copy_kernel<FT><<<ceil_div(count, 256), 256, 0, stream>>>(gh.g, p, dst, lo[0], lo[1], lo[2], (int)sz[0], (int)sz[1], (int)sz[2], 0);
+  KLAUNCH(lc);
+  CUDA_CHECK(cudaGetLastError());
+  if (where == NH_HOST) {
+    CUDA_CHECK(cudaMemcpyAsync(data, stage.p, count * sizeof(FT), cudaMemcpyDeviceToHost, stream));
+    CUDA_CHECK(cudaStreamSynchronize(stream));
+  }
+}
+
+template <typename FT>
+void Model<FT>::field_device_ptr(int field, void** ptr, int64_t* off, int64_t strides[3]) {
+  *ptr = field_ptr(field);
+  *off = gh.g.idx(1, 1, 1);
+  strides[0] = 1; strides[1] = gh.g.sy; strides[2] = gh.g.sz;
+}
+
+// fill_halo_regions! — open fill, then the three directions sorted so that Periodic runs after the others
+// (fill_halo_regions.jl:50-67,121-123,159-196; field_tuples.jl:56-101)
+template <typename FT>
+void Model<FT>::fill_halo_regions(uint32_t mask, int fill_normal) {
+  const GridDev<FT>& g = gh.g;
+  std::vector<int> ids;
+  for (int f = 0; f < 32; ++f) if (mask & (1u << f)) { (void)field_ptr(f); ids.push_back(f); }
+  if (ids.empty()) return;
+  NH_REQUIRE((int)ids.size() <= NH_MAXF, "too many fields in one halo fill");
+  auto launch = [&](HaloJob<FT>& J) {
+    const int d = J.d, e1 = d == 0 ? 1 : 0, e2 = d == 2 ? 1 : 2;
+    long long n = (long long)(J.hi[e1] - J.lo[e1] + 1) * (J.hi[e2] - J.lo[e2] + 1);
+    if (n <= 0) return;
+    dim3 grd(ceil_div(n, 128), J.nf);
+    halo_fill_kernel<FT><<<grd, 128, 0, stream>>>(J);
+    KLAUNCH(lc);
+  };
+  if (fill_normal) {
+    for (int d = 0; d < 3; ++d) {
+      if (g.topo[d] != NH_BOUNDED) continue;
+      HaloJob<FT> J; J.g = g; J.d = d; J.nf = 0;
+      for (int id : ids) if (id < 3 && id == d) { J.p[J.nf] = F[id]; J.mode[J.nf] = 3; J.nf++; }
+      if (!J.nf) continue;
+      for (int e = 0; e < 3; ++e) { J.lo[e] = 1; J.hi[e] = g.N[e]; }
+      launch(J);
+    }
+  }
+  // order: insertion sort with lt(a,b) = !(a periodic && b not periodic)
+  bool per[3]; for (int d = 0; d < 3; ++d) per[d] = g.topo[d] == NH_PERIODIC;
+  auto lt = [&](int a, int b) { return !(per[a] && !per[b]); };
+  int order[3] = {0, 1, 2};
+  for (int i = 1; i < 3; ++i) { int x = order[i], j = i; while (j > 0 && lt(x, order[j - 1])) { order[j] = order[j - 1]; --j; } order[j] = x; }
+  for (int q = 0; q < 3; ++q) {
+    int d = order[q];
+    if (g.topo[d] == NH_FLAT || g.H[d] == 0) continue;
+    HaloJob<FT> J; J.g = g; J.d = d; J.nf = 0;
+    if (per[d]) {
+      int minext[3] = {1 << 30, 1 << 30, 1 << 30};
+      for (int id : ids) { int n[3]; field_extent(id, n); for (int e = 0; e < 3; ++e) minext[e] = std::min(minext[e], n[e] + 2 * g.H[e]); }
+      for (int e = 0; e < 3; ++e) { J.lo[e] = 1 - g.H[e]; J.hi[e] = minext[e] - g.H[e]; }
+      for (int id : ids) { J.p[J.nf] = field_ptr(id); J.mode[J.nf] = 1; J.nf++; }
+    } else {
+      for (int e = 0; e < 3; ++e) { J.lo[e] = 1; J.hi[e] = g.N[e]; }
+      for (int id : ids) {
+        if (field_face_dim(id) == d) continue;        // Face field on a wall: open / no boundary condition
+        J.p[J.nf] = field_ptr(id); J.mode[J.nf] = 2; J.nf++;
+      }
+      if (!J.nf) continue;
+    }
+    launch(J);
+  }
+  CUDA_CHECK(cudaGetLastError());
+}
+
+template <typename FT>
+TendParams<FT> Model<FT>::tend_params() const {
+  TendParams<FT> P;
+  std::memset(&P, 0, sizeof(P));
+  P.g = gh.g;
+  for (int a = 0; a < 3; ++a) { P.U[a] = F[a]; P.GU[a] = Gn[a]; P.adv[a] = adv[a]; }
+  for (int t = 0; t < ntr; ++t) { P.c[t] = F[3 + t]; P.Gc[t] = Gn[3 + t]; P.kappa[t] = (FT)desc.kappa[t]; }
+  P.pHY = pHY;
+  P.ntr = ntr;
+  P.tab = tab;
+  P.buoy_kind = desc.buoyancy_kind;
+  P.iT = desc.buoyancy_tracer[0]; P.iS = desc.buoyancy_tracer[1];
+  P.grav = (FT)desc.gravitational_acceleration; P.alpha = (FT)desc.thermal_expansion; P.beta = (FT)desc.haline_contraction;
+  P.w_buoyancy = (desc.buoyancy_kind != NH_BUOYANCY_NONE && !pHY) ? 1 : 0;
+  P.has_coriolis = desc.has_coriolis; P.fcor = (FT)desc.coriolis_f;
+  P.has_closure = desc.has_closure; P.nu = (FT)desc.nu;
+  return P;
+}
+
+template <typename FT>
+void Model<FT>::update_hydrostatic_pressure() {
+  if (!pHY || desc.buoyancy_kind == NH_BUOYANCY_NONE || gh.g.topo[2] == NH_FLAT) return;
+  TendParams<FT> P = tend_params();
+  dim3 blk(32, 4), grd(ceil_div(gh.g.N[0] + 2, 32), ceil_div(gh.g.N[1] + 2, 4));
+  hydrostatic_pressure_kernel<FT><<<grd, blk, 0, stream>>>(P, pHY);
+  KLAUNCH(lc);
+}
+
+template <typename FT>
+void Model<FT>::compute_tendencies() {
+  TendParams<FT> P = tend_params();
+  dim3 blk(32, 4, 1);
+  for (int what = 0; what < nf; ++what) {
+    tendency_generic_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, what);
+    KLAUNCH(lc);
+  }
+  CUDA_CHECK(cudaGetLastError());
+}
+
+template <typename FT>
+void Model<FT>::update_state(int compute) {
+  uint32_t mask = 0; for (int f = 0; f < nf; ++f) mask |= 1u << f;
+  fill_halo_regions(mask, 0);
+  update_hydrostatic_pressure();
+  if (compute) compute_tendencies();
+}
+
+template <typename FT>
+void Model<FT>::substep_launch(int mode, FT dt, FT c1, FT c2) {
+  StepJob<FT> J;
+  J.g = gh.g; J.nf = nf; J.dt = dt; J.c1 = c1; J.c2 = c2; J.mode = mode;
+  for (int f = 0; f < nf; ++f) { J.U[f] = F[f]; J.Gn[f] = Gn[f]; J.Gm[f] = Gm[f]; J.face_dim[f] = f < 3 ? f : -1; }
+  dim3 blk(64, 4, 1);
+  substep_kernel<FT><<<grid3(blk), blk, 0, stream>>>(J);
+  KLAUNCH(lc);
+  CUDA_CHECK(cudaGetLastError());
+}
+
+template <typename FT>
+void Model<FT>::rk3_substep(double dt, double gamma, double zeta, int has_zeta) {
+  substep_launch(has_zeta ? 1 : 0, (FT)dt, (FT)gamma, (FT)zeta);
+}
+
+template <typename FT>
+void Model<FT>::ab2_step(double dt, double chi_) {
+  FT c = (FT)chi_;
+  substep_launch(c != FT(-0.5) ? 2 : 3, (FT)dt, c, FT(0));
+}
+
+template <typename FT>
+void Model<FT>::cache_previous_tendencies() { substep_launch(4, FT(0), FT(0), FT(0)); }
+
+// calculate_pressure_correction! — pressure_correction.jl:8-20
+template <typename FT>
+void Model<FT>::calculate_pressure_correction(double dt) {
+  fill_halo_regions(0x7u, 1);
+  dim3 blk(64, 4, 1);
+  CT* rhs = solver.A.p;
+  source_term_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(gh.g, F[0], F[1], F[2], dt,
+                                                            solver.kind == NH_SOLVER_FOURIER_TRIDIAGONAL ? 1 : 0, rhs);
+  KLAUNCH(lc);
+  CT* sol = solver.solve(0.0);
+  copy_real_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(gh.g, sol, pNHS);
+  KLAUNCH(lc);
+  fill_halo_regions(1u << NH_FIELD_PNHS, 1);
+  CUDA_CHECK(cudaGetLastError());
+}
+
+template <typename FT>
+void Model<FT>::pressure_correct_velocities(double dt) {
+  dim3 blk(64, 4, 1);
+  pressure_correct_kernel<FT><<<grid3(blk), blk, 0, stream>>>(gh.g, F[0], F[1], F[2], pNHS, dt);
+  KLAUNCH(lc);
+  CUDA_CHECK(cudaGetLastError());
+}
+
+// time_step! — runge_kutta_3.jl:77-151, quasi_adams_bashforth_2.jl:74-115.  The G⁻ ← Gⁿ copy of
+// store_tendencies.jl is replaced by a pointer swap (Gⁿ is fully rewritten by the next compute_tendencies!).
+template <typename FT>
+void Model<FT>::time_step(double dt, int euler) {
+  if (clock.iteration == 0) update_state(1);
+  auto swapG = [&]() { for (int f = 0; f < nf; ++f) std::swap(Gn[f], Gm[f]); };
+  if (desc.timestepper == NH_RK3) {
+    double first = (double)rk_g1 * dt;
+    double second = (double)(FT)(rk_g2 + rk_z2) * dt;
+    double third = (double)(FT)(rk_g3 + rk_z3) * dt;
+    double t_next = clock.time + dt;
+    substep_launch(0, (FT)dt, rk_g1, FT(0));
+    clock.time += first; clock.stage += 1; clock.last_stage_dt = first;
+    calculate_pressure_correction(first);
+    pressure_correct_velocities(first);
+    swapG();
+    update_state(1);
+    substep_launch(1, (FT)dt, rk_g2, rk_z2);
+    clock.time += second; clock.stage += 1; clock.last_stage_dt = second;
+    calculate_pressure_correction(second);
+    pressure_correct_velocities(second);
+    swapG();
+    update_state(1);
+    substep_launch(1, (FT)dt, rk_g3, rk_z3);
+    double corrected = t_next - clock.time;
+    clock.time += third; clock.iteration += 1; clock.stage = 1;
+    clock.last_stage_dt = corrected; clock.last_dt = dt;
+    calculate_pressure_correction(third);
+    pressure_correct_velocities(third);
+    update_state(1);
+  } else {
+    bool eul = euler || (dt != clock.last_dt);
+    FT c = eul ? FT(-0.5) : chi;
+    substep_launch(eul ? 3 : 2, (FT)dt, c, FT(0));
+    clock.time += dt; clock.iteration += 1; clock.stage = 1; clock.last_dt = dt; clock.last_stage_dt = dt;
+    calculate_pressure_correction(dt);
+    pressure_correct_velocities(dt);
+    swapG();
+    update_state(1);
+  }
+}
+
+// tail of set!(model; …) — set_nonhydrostatic_model.jl:44-58
+template <typename FT>
+void Model<FT>::set_state_finalize(int enforce) {
+  update_state(0);
+  if (enforce) {
+    calculate_pressure_correction(1.0);
+    pressure_correct_velocities(1.0);
+    update_state(0);
+  }
+}
+
+template <typename FT>
+double Model<FT>::max_abs_divergence() {
+  const int nb = 512;
+  if (red.n < (size_t)nb) red.alloc(nb);
+  max_div_kernel<FT><<<nb, 256, 0, stream>>>(gh.g, F[0], F[1], F[2], red.p);
+  KLAUNCH(lc);
+  std::vector<double> h(nb);
+  CUDA_CHECK(cudaMemcpyAsync(h.data(), red.p, nb * sizeof(double), cudaMemcpyDeviceToHost, stream));
+  CUDA_CHECK(cudaStreamSynchronize(stream));
+  double m = 0;
+  for (double v : h) if (v > m || v != v) m = v;
+  return m;
+}
+
+template struct Model<float>;
+template struct Model<double>;

@@ -1,0 +1,158 @@
+// model.cuh — host-side objects behind the opaque handles of include/nhstep.h
+#pragma once
+#include "kernels_basic.cuh"
+#include "fft_generic.cuh"
+#include "grid_host.h"
+#include <memory>
+#include <cstring>
+#include <cmath>
+
+struct nh_grid {
+  nh_grid_desc desc;
+  std::vector<double> zfaces;
+  int device;
+};
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr; size_t n = 0;
+  DevBuf() {}
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { if (p) cudaFree(p); }
+  void alloc(size_t count, bool zero = true) {
+    if (p) { cudaFree(p); p = nullptr; }
+    n = count;
+    if (count == 0) return;
+    CUDA_CHECK(cudaMalloc(&p, count * sizeof(T)));
+    if (zero) CUDA_CHECK(cudaMemset(p, 0, count * sizeof(T)));
+  }
+  void upload(const std::vector<T>& v) { alloc(v.size(), false); if (n) CUDA_CHECK(cudaMemcpy(p, v.data(), n * sizeof(T), cudaMemcpyHostToDevice)); }
+};
+
+// Host description of the grid at a given halo, with the device metric arrays.
+template <typename FT>
+struct GridHost {
+  GridDev<FT> g;
+  FT L[3];
+  bool z_stretched = false;
+  std::vector<FT> dzc_h, dzf_h;          // indexed [k + zoff]
+  DevBuf<FT> dzc_d, dzf_d;
+  void build(const nh_grid_desc& d, const std::vector<double>& zfaces, const int H[3]);
+  long long volume() const { return (long long)g.px * g.py * g.pz; }
+};
+
+struct LaunchCounter { long long n = 0; };
+
+// ---- Poisson solvers (complete path) ---------------------------------------------------------------------------
+template <typename FT>
+struct PoissonGeneric {
+  typedef typename cx_of<FT>::type CT;
+  int kind = NH_SOLVER_FFT;
+  int N[3], topo[3];
+  DevBuf<CT> A;            // FFT: storage; tridiagonal: source_term
+  DevBuf<CT> Phi;          // tridiagonal: storage (keeps its content between solves, as the reference's does)
+  DevBuf<double> lam[3];
+  DevBuf<CT> tw[3], tw4[3];
+  DevBuf<double> D;        // tridiagonal main diagonal (Float64, 3-D)
+  DevBuf<FT> tt, lower, dzc1;
+  DevBuf<double2> partial;
+  cudaStream_t stream = 0;
+  LaunchCounter* lc = nullptr;
+  LaunchCounter own_lc;
+  void create(const GridHost<FT>& gh, int kind_);
+  void transform(CT* a, int d, int mode);
+  void forward(CT* a);
+  void backward(CT* a);
+  CT* solve(double m);     // transforms whatever is in A; returns the array whose real part is the solution
+  long long count() const { return (long long)N[0] * N[1] * N[2]; }
+};
+
+// ---- model -----------------------------------------------------------------------------------------------------
+struct nh_model {
+  virtual ~nh_model() {}
+  int float_type = NH_F64;
+  int device = 0;
+  nh_model_desc desc;
+  nh_grid_desc gdesc;      // with the inflated halo
+  nh_clock clock;
+  LaunchCounter lc;
+  cudaStream_t stream = 0;
+  virtual void field_size(int field, int region, int64_t size[3]) = 0;
+  virtual void set_field(int field, int region, const void* data, int64_t count, int where) = 0;
+  virtual void get_field(int field, int region, void* data, int64_t count, int where) = 0;
+  virtual void fill_halo_regions(uint32_t mask, int fill_normal) = 0;
+  virtual void update_state(int compute_tendencies) = 0;
+  virtual void compute_tendencies() = 0;
+  virtual void rk3_substep(double dt, double gamma, double zeta, int has_zeta) = 0;
+  virtual void ab2_step(double dt, double chi) = 0;
+  virtual void cache_previous_tendencies() = 0;
+  virtual void calculate_pressure_correction(double dt) = 0;
+  virtual void pressure_correct_velocities(double dt) = 0;
+  virtual void time_step(double dt, int euler) = 0;
+  virtual void set_state_finalize(int enforce) = 0;
+  virtual double max_abs_divergence() = 0;
+  virtual void field_device_ptr(int field, void** ptr, int64_t* off, int64_t strides[3]) = 0;
+  virtual void set_stream(cudaStream_t s) { stream = s; }
+};
+
+template <typename FT>
+struct Model : nh_model {
+  typedef typename cx_of<FT>::type CT;
+  GridHost<FT> gh;
+  int ntr = 0, nf = 3;
+  std::vector<std::unique_ptr<DevBuf<FT>>> bufs;
+  FT* F[NH_MAXF];          // prognostic fields u,v,w,tracers
+  FT* Gn[NH_MAXF];
+  FT* Gm[NH_MAXF];
+  FT* pNHS = nullptr;
+  FT* pHY = nullptr;
+  SchemeDev adv[3];
+  SchemeTables<FT> tab;
+  PoissonGeneric<FT> solver;
+  DevBuf<FT> stage;        // staging for host <-> device field copies
+  DevBuf<double> red;      // reduction scratch
+  FT rk_g1, rk_g2, rk_g3, rk_z2, rk_z3, chi;
+
+  Model(const nh_grid& grid, const nh_model_desc& d);
+  FT* alloc_field();
+  FT* field_ptr(int field);
+  int field_face_dim(int field) const;         // 0,1,2 for (Gⁿ/G⁻ of) u,v,w; -1 for cell-centred fields
+  void field_extent(int field, int n[3]) const;
+  TendParams<FT> tend_params() const;
+  dim3 grid3(dim3 block) const { return dim3(ceil_div(gh.g.N[0], block.x), ceil_div(gh.g.N[1], block.y), gh.g.N[2]); }
+
+  void field_size(int field, int region, int64_t size[3]) override;
+  void set_field(int field, int region, const void* data, int64_t count, int where) override;
+  void get_field(int field, int region, void* data, int64_t count, int where) override;
+  void fill_halo_regions(uint32_t mask, int fill_normal) override;
+  void update_state(int compute_tendencies) override;
+  void compute_tendencies() override;
+  void rk3_substep(double dt, double gamma, double zeta, int has_zeta) override;
+  void ab2_step(double dt, double chi) override;
+  void cache_previous_tendencies() override;
+  void calculate_pressure_correction(double dt) override;
+  void pressure_correct_velocities(double dt) override;
+  void time_step(double dt, int euler) override;
+  void set_state_finalize(int enforce) override;
+  double max_abs_divergence() override;
+  void field_device_ptr(int field, void** ptr, int64_t* off, int64_t strides[3]) override;
+  void set_stream(cudaStream_t s) override { stream = s; solver.stream = s; }
+  void substep_launch(int mode, FT dt, FT c1, FT c2);
+  void update_hydrostatic_pressure();
+};
+
+struct nh_poisson {
+  virtual ~nh_poisson() {}
+  virtual void solve(const void* rhs, void* phi, double m, int where) = 0;
+  virtual void sync() = 0;
+  virtual long long launches() const = 0;
+  virtual float time_solves(const void* rhs, void* phi, int n) = 0;
+  int device = 0;
+};
+
+struct nh_tridiag {
+  virtual ~nh_tridiag() {}
+  virtual void solve(const void* rhs, void* phi) = 0;
+  int device = 0;
+};

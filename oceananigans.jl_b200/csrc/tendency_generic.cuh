@@ -1,0 +1,280 @@
+// tendency_generic.cuh — pointwise tendency functions for every supported configuration (any topology, stretched z,
+// Centered/UpwindBiased/WENO, FPlane, buoyancy, ScalarDiffusivity), in the reference's expression order:
+//   src/Models/NonhydrostaticModels/nonhydrostatic_tendency_kernel_functions.jl:47-78,107-138,170-200,228-259
+//   src/Advection/momentum_advection_operators.jl:46-83, tracer_advection_operators.jl:30-34
+//   src/Advection/upwind_biased_advective_fluxes.jl:23-121, centered_advective_fluxes.jl:15-33
+//   src/Coriolis/f_plane.jl:44-46, src/Operators/interpolation_operators.jl:121-131
+//   src/TurbulenceClosures/closure_kernel_operators.jl:22-48, velocity_tracer_gradients.jl:25-42
+// The fused fast kernels (tendency_fast.cu) cover the periodic WENO5 case; this file is the complete one.
+#pragma once
+#include "recon.cuh"
+
+template <typename FT>
+struct FieldGet {
+  const FT* p; const GridDev<FT>* g;
+  __device__ __forceinline__ FT operator()(int i, int j, int k) const { return p[g->idx(i, j, k)]; }
+};
+
+// Δz at a z-location (1 = centre, 0 = face)
+template <typename FT>
+__device__ __forceinline__ FT dz_at(const GridDev<FT>& g, int zc, int k) { return zc ? g.Dzc(k) : g.Dzf(k); }
+
+// A_d at a location whose z-stagger is zc: Ax = Δy·Δz, Ay = Δx·Δz, Az = Δx·Δy
+template <typename FT>
+__device__ __forceinline__ FT area_at(const GridDev<FT>& g, int d, int zc, int k) {
+  if (d == 0) return g.dy * dz_at(g, zc, k);
+  if (d == 1) return g.dx * dz_at(g, zc, k);
+  return g.dx * g.dy;
+}
+template <typename FT>
+__device__ __forceinline__ FT volume_at(const GridDev<FT>& g, int zc, int k) { return (g.dx * g.dy) * dz_at(g, zc, k); }
+
+template <typename FT>
+__device__ __forceinline__ FT delta_at(const GridDev<FT>& g, int d, int zc, int k) {
+  return d == 0 ? g.dx : (d == 1 ? g.dy : dz_at(g, zc, k));
+}
+
+// Ax_qᶠᶜᶜ-style getter: area of velocity component b at its own location times U_b
+template <typename FT, int b>
+struct AreaVelGet {
+  const FT* p; const GridDev<FT>* g;
+  __device__ __forceinline__ FT operator()(int i, int j, int k) const {
+    return area_at(*g, b, b == 2 ? 0 : 1, k) * p[g->idx(i, j, k)];
+  }
+};
+
+// advective_momentum_flux_{U_b}{u_a} at the flux location index (i,j,k)
+template <typename FT, int a, int b>
+__device__ __forceinline__ FT momentum_flux(const TendParams<FT>& P, int i, int j, int k) {
+  const GridDev<FT>& g = P.g;
+  SchemeDev s = P.adv[b];
+  if (g.topo[b] == NH_FLAT || s.kind == NH_ADV_NONE) return FT(0);
+  constexpr int sym_dim = (a == b) ? b : a;
+  constexpr int stag_c = (a == b) ? 1 : 0;
+  FieldGet<FT> ua{P.U[a], &g};
+  if (s.kind != NH_ADV_CENTERED) {
+    AreaVelGet<FT, b> Aq{P.U[b], &g};
+    FT ut = symmetric_interp<FT>(P.tab, s, g.topo[sym_dim], g.N[sym_dim], sym_dim, stag_c, i, j, k, Aq);
+    FT qR = biased_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, stag_c, ut > FT(0), i, j, k, ua);
+    return ut * qR;
+  }
+  constexpr int zc = (a != b && (a == 2 || b == 2)) ? 0 : 1;
+  FieldGet<FT> ub{P.U[b], &g};
+  FT A = area_at(g, b, zc, k);
+  return (A * symmetric_interp<FT>(P.tab, s, g.topo[sym_dim], g.N[sym_dim], sym_dim, stag_c, i, j, k, ub)) *
+         symmetric_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, stag_c, i, j, k, ua);
+}
+
+template <typename FT, int a, int b>
+__device__ __forceinline__ FT momentum_flux_diff(const TendParams<FT>& P, int i, int j, int k) {
+  if (P.g.topo[b] == NH_FLAT) return FT(0);
+  constexpr int di = b == 0, dj = b == 1, dk = b == 2;
+  if (a == b)  // target is a Face: F[i] - F[i-1]
+    return momentum_flux<FT, a, b>(P, i, j, k) - momentum_flux<FT, a, b>(P, i - di, j - dj, k - dk);
+  return momentum_flux<FT, a, b>(P, i + di, j + dj, k + dk) - momentum_flux<FT, a, b>(P, i, j, k);
+}
+
+template <typename FT, int a>
+__device__ __forceinline__ FT div_Uu(const TendParams<FT>& P, int i, int j, int k) {
+  FT total = momentum_flux_diff<FT, a, 0>(P, i, j, k) + momentum_flux_diff<FT, a, 1>(P, i, j, k);
+  total = total + momentum_flux_diff<FT, a, 2>(P, i, j, k);
+  return FT(1) / volume_at(P.g, a == 2 ? 0 : 1, k) * total;
+}
+
+template <typename FT, int b>
+__device__ __forceinline__ FT tracer_flux(const TendParams<FT>& P, const FT* c, int i, int j, int k) {
+  const GridDev<FT>& g = P.g;
+  SchemeDev s = P.adv[b];
+  if (g.topo[b] == NH_FLAT || s.kind == NH_ADV_NONE) return FT(0);
+  FT A = area_at(g, b, b == 2 ? 0 : 1, k);
+  FT ub = P.U[b][g.idx(i, j, k)];
+  FieldGet<FT> cg{c, &g};
+  if (s.kind != NH_ADV_CENTERED) {
+    FT cR = biased_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, 0, ub > FT(0), i, j, k, cg);
+    return A * ub * cR;
+  }
+  return (A * ub) * symmetric_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, 0, i, j, k, cg);
+}
+
+template <typename FT>
+__device__ __forceinline__ FT div_Uc(const TendParams<FT>& P, const FT* c, int i, int j, int k) {
+  const GridDev<FT>& g = P.g;
+  FT tx = g.topo[0] == NH_FLAT ? FT(0) : tracer_flux<FT, 0>(P, c, i + 1, j, k) - tracer_flux<FT, 0>(P, c, i, j, k);
+  FT ty = g.topo[1] == NH_FLAT ? FT(0) : tracer_flux<FT, 1>(P, c, i, j + 1, k) - tracer_flux<FT, 1>(P, c, i, j, k);
+  FT tz = g.topo[2] == NH_FLAT ? FT(0) : tracer_flux<FT, 2>(P, c, i, j, k + 1) - tracer_flux<FT, 2>(P, c, i, j, k);
+  FT total = tx + ty;
+  total = total + tz;
+  return FT(1) / volume_at(g, 1, k) * total;
+}
+
+// ---- Coriolis (FPlane): active-weighted ℑxy ------------------------------------------------------------------
+template <typename FT>
+__device__ __forceinline__ int inactive_cell(const GridDev<FT>& g, int i, int j, int k) {
+  int bad = 0;
+  if (g.topo[0] == NH_BOUNDED) bad |= (i < 1) | (i > g.N[0]);
+  if (g.topo[1] == NH_BOUNDED) bad |= (j < 1) | (j > g.N[1]);
+  if (g.topo[2] == NH_BOUNDED) bad |= (k < 1) | (k > g.N[2]);
+  return bad;
+}
+
+// not_peripheral_node at the location of velocity component q (face in dim q)
+template <typename FT, int q>
+struct ActiveGet {
+  const GridDev<FT>* g;
+  __device__ __forceinline__ FT operator()(int i, int j, int k) const {
+    int bad = inactive_cell(*g, i, j, k) | inactive_cell(*g, i - (q == 0), j - (q == 1), k - (q == 2));
+    return bad ? FT(0) : FT(1);
+  }
+};
+
+// ℑxy onto (tx_c, ty_c): ℑy(ℑx ·); each ℑ = FT(0.5)·(a + b), identity when Flat
+template <typename FT, typename G>
+__device__ __forceinline__ FT interp_x(const GridDev<FT>& g, int tc, int i, int j, int k, const G& get) {
+  if (g.topo[0] == NH_FLAT) return get(i, j, k);
+  return tc ? FT(0.5) * (get(i, j, k) + get(i + 1, j, k)) : FT(0.5) * (get(i - 1, j, k) + get(i, j, k));
+}
+template <typename FT, typename G>
+__device__ __forceinline__ FT interp_xy(const GridDev<FT>& g, int txc, int tyc, int i, int j, int k, const G& get) {
+  if (g.topo[1] == NH_FLAT) return interp_x<FT>(g, txc, i, j, k, get);
+  if (tyc) return FT(0.5) * (interp_x<FT>(g, txc, i, j, k, get) + interp_x<FT>(g, txc, i, j + 1, k, get));
+  return FT(0.5) * (interp_x<FT>(g, txc, i, j - 1, k, get) + interp_x<FT>(g, txc, i, j, k, get));
+}
+
+template <typename FT, int a>
+__device__ __forceinline__ FT f_cross_U(const TendParams<FT>& P, int i, int j, int k) {
+  if (!P.has_coriolis || a == 2) return FT(0);
+  const GridDev<FT>& g = P.g;
+  if (a == 0) {   // -f · ℑxyᶠᶜ(v) / active
+    FieldGet<FT> v{P.U[1], &g};
+    ActiveGet<FT, 1> act{&g};
+    FT active = interp_xy<FT>(g, 0, 1, i, j, k, act);
+    FT val = interp_xy<FT>(g, 0, 1, i, j, k, v);
+    FT aw = active == FT(0) ? FT(0) : val / active;
+    return (-P.fcor) * aw;
+  }
+  FieldGet<FT> u{P.U[0], &g};
+  ActiveGet<FT, 0> act{&g};
+  FT active = interp_xy<FT>(g, 1, 0, i, j, k, act);
+  FT val = interp_xy<FT>(g, 1, 0, i, j, k, u);
+  FT aw = active == FT(0) ? FT(0) : val / active;
+  return P.fcor * aw;
+}
+
+// ---- buoyancy ---------------------------------------------------------------------------------------------
+template <typename FT>
+__device__ __forceinline__ FT buoyancy_at(const TendParams<FT>& P, int i, int j, int k) {
+  long long n = P.g.idx(i, j, k);
+  if (P.buoy_kind == NH_BUOYANCY_TRACER) return P.c[P.iT][n];
+  return P.grav * (P.alpha * P.c[P.iT][n] - P.beta * P.c[P.iS][n]);
+}
+
+// ---- ScalarDiffusivity ------------------------------------------------------------------------------------
+// ∂_d q onto a Face (fc = 0: q[idx] - q[idx-1]) or a Centre (fc = 1: q[idx+1] - q[idx]), divided by Δ at the target
+template <typename FT, int d>
+__device__ __forceinline__ FT deriv(const GridDev<FT>& g, const FT* q, int target_c, int zc, int i, int j, int k) {
+  if (g.topo[d] == NH_FLAT) return FT(0);
+  constexpr int di = d == 0, dj = d == 1, dk = d == 2;
+  FT num = target_c ? q[g.idx(i + di, j + dj, k + dk)] - q[g.idx(i, j, k)]
+                    : q[g.idx(i, j, k)] - q[g.idx(i - di, j - dj, k - dk)];
+  return num / delta_at(g, d, zc, k);
+}
+
+// Σ_ab at its natural location (ccc when a == b, Face in both a and b otherwise)
+template <typename FT, int a, int b>
+__device__ __forceinline__ FT strain(const TendParams<FT>& P, int i, int j, int k) {
+  const GridDev<FT>& g = P.g;
+  if (a == b) return deriv<FT, a>(g, P.U[a], 1, 1, i, j, k);
+  constexpr int lo = a < b ? a : b, hi = a < b ? b : a;
+  constexpr int zc = (hi == 2) ? 0 : 1;     // location is a Face in z iff z is one of the two dims
+  return FT(0.5) * (deriv<FT, hi>(g, P.U[lo], 0, zc, i, j, k) + deriv<FT, lo>(g, P.U[hi], 0, zc, i, j, k));
+}
+
+template <typename FT, int a, int b>
+__device__ __forceinline__ FT viscous_Aflux(const TendParams<FT>& P, int i, int j, int k) {
+  constexpr int zc = (a != b && (a == 2 || b == 2)) ? 0 : 1;
+  return area_at(P.g, b, zc, k) * (FT(-2) * (P.nu * strain<FT, a, b>(P, i, j, k)));
+}
+
+template <typename FT, int a, int b>
+__device__ __forceinline__ FT viscous_diff(const TendParams<FT>& P, int i, int j, int k) {
+  if (P.g.topo[b] == NH_FLAT) return FT(0);
+  constexpr int di = b == 0, dj = b == 1, dk = b == 2;
+  if (a == b) return viscous_Aflux<FT, a, b>(P, i, j, k) - viscous_Aflux<FT, a, b>(P, i - di, j - dj, k - dk);
+  return viscous_Aflux<FT, a, b>(P, i + di, j + dj, k + dk) - viscous_Aflux<FT, a, b>(P, i, j, k);
+}
+
+template <typename FT, int a>
+__device__ __forceinline__ FT div_viscous_flux(const TendParams<FT>& P, int i, int j, int k) {
+  FT total = viscous_diff<FT, a, 0>(P, i, j, k) + viscous_diff<FT, a, 1>(P, i, j, k);
+  total = total + viscous_diff<FT, a, 2>(P, i, j, k);
+  return FT(1) / volume_at(P.g, a == 2 ? 0 : 1, k) * total;
+}
+
+template <typename FT, int b>
+__device__ __forceinline__ FT diffusive_Aflux(const TendParams<FT>& P, const FT* c, FT kappa, int i, int j, int k) {
+  constexpr int zc = b == 2 ? 0 : 1;
+  return area_at(P.g, b, zc, k) * (-kappa * deriv<FT, b>(P.g, c, 0, zc, i, j, k));
+}
+
+template <typename FT>
+__device__ __forceinline__ FT div_diffusive_flux(const TendParams<FT>& P, const FT* c, FT kappa, int i, int j, int k) {
+  const GridDev<FT>& g = P.g;
+  FT tx = g.topo[0] == NH_FLAT ? FT(0) : diffusive_Aflux<FT, 0>(P, c, kappa, i + 1, j, k) - diffusive_Aflux<FT, 0>(P, c, kappa, i, j, k);
+  FT ty = g.topo[1] == NH_FLAT ? FT(0) : diffusive_Aflux<FT, 1>(P, c, kappa, i, j + 1, k) - diffusive_Aflux<FT, 1>(P, c, kappa, i, j, k);
+  FT tz = g.topo[2] == NH_FLAT ? FT(0) : diffusive_Aflux<FT, 2>(P, c, kappa, i, j, k + 1) - diffusive_Aflux<FT, 2>(P, c, kappa, i, j, k);
+  FT total = tx + ty;
+  total = total + tz;
+  return FT(1) / volume_at(g, 1, k) * total;
+}
+
+// ---- the tendencies ---------------------------------------------------------------------------------------
+template <typename FT, int a>
+__device__ __forceinline__ FT velocity_tendency(const TendParams<FT>& P, int i, int j, int k) {
+  const GridDev<FT>& g = P.g;
+  FT G = -div_Uu<FT, a>(P, i, j, k);
+  if (a == 2 && P.w_buoyancy) {
+    FT bz = g.topo[2] == NH_FLAT ? buoyancy_at(P, i, j, k)
+                                 : FT(0.5) * (buoyancy_at(P, i, j, k - 1) + buoyancy_at(P, i, j, k));
+    G = G + bz;
+  } else {
+    G = G + FT(0);
+  }
+  G = G - f_cross_U<FT, a>(P, i, j, k);
+  if (a < 2) {
+    if (P.pHY) G = G - deriv<FT, a>(g, P.pHY, 0, 1, i, j, k);
+    else G = G - FT(0);
+  }
+  if (P.has_closure) G = G - div_viscous_flux<FT, a>(P, i, j, k);
+  else G = G - FT(0);
+  return G;
+}
+
+template <typename FT>
+__device__ __forceinline__ FT tracer_tendency(const TendParams<FT>& P, int n, int i, int j, int k) {
+  FT G = -div_Uc<FT>(P, P.c[n], i, j, k);
+  if (P.has_closure) G = G - div_diffusive_flux<FT>(P, P.c[n], P.kappa[n], i, j, k);
+  else G = G - FT(0);
+  return G;
+}
+
+// One thread per cell of 1:Nx × 1:Ny × 1:Nz; Face fields skip index 1 in Bounded dims (exclude_periphery,
+// src/Utils/kernel_launching.jl:90-111; compute_nonhydrostatic_tendencies.jl:104-136).
+template <typename FT>
+__global__ void __launch_bounds__(128) tendency_generic_kernel(const __grid_constant__ TendParams<FT> P, int what) {
+  const GridDev<FT>& g = P.g;
+  int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  int k = blockIdx.z + 1;
+  if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
+  long long n = g.idx(i, j, k);
+  if (what == 0) {
+    if (!(g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i == 1)) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k);
+  } else if (what == 1) {
+    if (!(g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j == 1)) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k);
+  } else if (what == 2) {
+    if (!(g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k == 1)) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k);
+  } else {
+    int t = what - 3;
+    P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k);
+  }
+}

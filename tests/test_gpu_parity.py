@@ -1,0 +1,258 @@
+"""GPU parity: the CUDA path (through the C ABI of include/nhstep.h) against the oracle on identical seeded inputs.
+
+Tolerances: Float64 rel. L2 ≤ 1e-12, Float32 ≤ 1e-5 (BASELINE.json north_star); single kernels in the parity build
+(-fmad=false, reference expression order) are held to bit-exactness where no FFT is involved.
+"""
+import itertools
+
+import numpy as np
+import pytest
+
+import oracle as o
+from oracle.model import (update_state as o_update_state, compute_tendencies_ as o_compute_tendencies,
+                          calculate_pressure_correction as o_calc_pc, pressure_correct_velocities as o_pcv,
+                          rk3_substep as o_rk3, ab2_step as o_ab2)
+from oracle.fields import fill_halo_regions as o_fill
+
+pytestmark = pytest.mark.gpu
+
+P, B, F = "Periodic", "Bounded", "Flat"
+
+
+@pytest.fixture(scope="module")
+def oc():
+    import oceananigans_jl_b200 as oc
+    assert oc.device_count() >= 1, "no CUDA device: the product has no CPU fallback"
+    return oc
+
+
+def rel_l2(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    nb = np.linalg.norm(b.ravel())
+    return np.linalg.norm((a - b).ravel()) / (nb if nb > 0 else 1.0)
+
+
+def make_pair(oc, FT, size, topo, z=None, advection=("WENO", 5), timestepper="RungeKutta3", buoyancy=None, coriolis=None,
+              closure=None, tracers=(), extent=None, x=None, y=None):
+    """The same model twice: (CUDA, oracle)."""
+    kw = {}
+    if extent is not None:
+        kw["extent"] = extent
+    else:
+        if topo[0] != F:
+            kw["x"] = x or (0, 1)
+        if topo[1] != F:
+            kw["y"] = y or (0, 1)
+        if topo[2] != F:
+            kw["z"] = z if z is not None else (0, 1)
+    g1 = oc.RectilinearGrid(FT, size=size, topology=topo, **kw)
+    g2 = o.RectilinearGrid(FT, size=size, topology=topo, **kw)
+
+    def adv(mod, FTarg):
+        if advection is None:
+            return None
+        kind, order = advection
+        return getattr(mod, kind)(FTarg, order=order) if mod is o else getattr(mod, kind)(order=order)
+    b1 = b2 = None
+    if buoyancy == "seawater":
+        b1, b2 = oc.SeawaterBuoyancy(), o.SeawaterBuoyancy()
+    elif buoyancy == "tracer":
+        b1, b2 = oc.BuoyancyTracer(), o.BuoyancyTracer()
+    c1 = oc.FPlane(coriolis) if coriolis is not None else None
+    c2 = o.FPlane(coriolis) if coriolis is not None else None
+    k1 = oc.ScalarDiffusivity(*closure) if closure else None
+    k2 = o.ScalarDiffusivity(*closure) if closure else None
+    m1 = oc.NonhydrostaticModel(g1, advection=adv(oc, None), timestepper=timestepper, buoyancy=b1, coriolis=c1, closure=k1,
+                                tracers=tracers)
+    m2 = o.NonhydrostaticModel(g2, advection=adv(o, FT), timestepper=timestepper, buoyancy=b2, coriolis=c2, closure=k2,
+                               tracers=tracers)
+    return m1, m2
+
+
+def random_ics(m2, rng, amp=1.0):
+    ics = {}
+    for n, f in zip(m2.prognostic_names(), m2.prognostic_fields()):
+        ics[n] = (amp * rng.uniform(-1, 1, f.size)).astype(m2.grid.FT)
+    return ics
+
+
+def names_fields(m1, m2):
+    for n, f2 in zip(m2.prognostic_names(), m2.prognostic_fields()):
+        f1 = m1.velocities[n] if n in "uvw" else m1.tracers[n]
+        yield n, f1, f2
+
+
+CONFIGS = [
+    # size, topo, z, advection, kwargs
+    ((12, 10, 9), (P, P, P), None, ("WENO", 5), {}),
+    ((12, 10, 9), (P, P, B), None, ("WENO", 5), dict(buoyancy="seawater", tracers=("T", "S"), coriolis=1e-2, closure=(1e-2, 2e-2))),
+    ((9, 8, 10), (B, B, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=(1e-2, 1e-2))),
+    ((9, 8, 10), (P, B, B), None, ("Centered", 4), dict(coriolis=0.5, tracers=("c",))),
+    ((9, 8, 10), (B, P, B), None, ("UpwindBiased", 5), dict(tracers=("c",))),
+    ((9, 8, 10), (P, P, B), None, ("WENO", 3), {}),
+    ((9, 8, 10), (P, P, B), None, ("UpwindBiased", 3), {}),
+    ((9, 8, 10), (P, P, B), None, ("Centered", 2), dict(closure=(1e-2, 1e-2), tracers=("c",))),
+    ((16, 16), (P, P, F), None, ("WENO", 5), {}),
+    ((16, 12), (P, F, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",))),
+    ((10, 9, 8), (P, P, B), "stretched", ("WENO", 5), dict(buoyancy="seawater", tracers=("T", "S"), closure=(1e-3, 1e-3))),
+    ((2, 9, 8), (P, P, B), None, ("WENO", 5), {}),     # order adapted in x (N < buffer)
+]
+
+
+def _z(zkind, size):
+    if zkind == "stretched":
+        Nz = size[-1]
+        k = np.arange(1, Nz + 2)
+        return np.tanh(1.3 * (2 * (k - 1) / Nz - 1)) / np.tanh(1.3)
+    return None
+
+
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+@pytest.mark.parametrize("cfg", CONFIGS, ids=[f"{c[1]}-{c[3]}-{c[2]}-{c[0]}" for c in CONFIGS])
+def test_tendencies_and_halos_bit_exact(oc, FT, cfg):
+    size, topo, zkind, adv, kw = cfg
+    m1, m2 = make_pair(oc, FT, size, topo, z=_z(zkind, size), advection=adv, **kw)
+    rng = np.random.default_rng(42)
+    ics = random_ics(m2, rng)
+    for n, f1, f2 in names_fields(m1, m2):
+        f1.set(ics[n])
+        f2.set(ics[n])
+    oc.update_state(m1, compute_tendencies=True)
+    o_update_state(m2, compute_tendencies=True)
+    for n, f1, f2 in names_fields(m1, m2):
+        np.testing.assert_array_equal(f1.parent(), f2.data, err_msg=f"parent({n}) after halo fill")
+        G1 = m1.timestepper.Gn[n].interior()
+        G2 = m2.Gn[n].interior
+        np.testing.assert_array_equal(G1, G2, err_msg=f"G{n}")
+    if m2.pHY is not None:
+        np.testing.assert_array_equal(m1.pressures.pHY.parent(), m2.pHY.data, err_msg="pHY")
+
+
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+@pytest.mark.parametrize("topo", [(P, P, P), (P, P, B), (B, B, B)])
+def test_substeps_and_normal_velocity_fill_bit_exact(oc, FT, topo):
+    m1, m2 = make_pair(oc, FT, (8, 7, 6), topo, tracers=("c",))
+    rng = np.random.default_rng(3)
+    ics = random_ics(m2, rng)
+    for n, f1, f2 in names_fields(m1, m2):
+        f1.set(ics[n]); f2.set(ics[n])
+    oc.update_state(m1); o_update_state(m2)
+    oc.rk3_substep(m1, 0.01, m2.rk3["g1"], None); o_rk3(m2, 0.01, m2.rk3["g1"], None)
+    oc.cache_previous_tendencies(m1)
+    from oracle.model import cache_previous_tendencies as o_cache
+    o_cache(m2)
+    oc.update_state(m1); o_update_state(m2)
+    oc.rk3_substep(m1, 0.01, m2.rk3["g2"], m2.rk3["z2"]); o_rk3(m2, 0.01, m2.rk3["g2"], m2.rk3["z2"])
+    oc.ab2_step(m1, 0.02, 0.1); o_ab2(m2, 0.02, 0.1)
+    oc.ab2_step(m1, 0.02, -0.5); o_ab2(m2, 0.02, -0.5)
+    oc.fill_halo_regions(list(m1.velocities.values())); o_fill(list(m2.velocities))
+    for n, f1, f2 in names_fields(m1, m2):
+        np.testing.assert_array_equal(f1.parent(), f2.data, err_msg=n)
+
+
+TOPOS3 = list(itertools.product((P, B), repeat=3))
+
+
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+@pytest.mark.parametrize("topo", TOPOS3 + [(P, P, F), (P, F, B), (F, B, B)])
+def test_pressure_correction_matches_oracle(oc, FT, tol, topo):
+    size3 = (16, 12, 10)
+    size = tuple(n for n, t in zip(size3, topo) if t != F)
+    m1, m2 = make_pair(oc, FT, size, topo)
+    rng = np.random.default_rng(5)
+    ics = random_ics(m2, rng)
+    for n, f1, f2 in names_fields(m1, m2):
+        f1.set(ics[n]); f2.set(ics[n])
+    oc.calculate_pressure_correction(m1, 0.37); o_calc_pc(m2, 0.37)
+    assert rel_l2(m1.pressures.pNHS.parent(), m2.pNHS.data) < tol * 10
+    oc.pressure_correct_velocities(m1, 0.37); o_pcv(m2, 0.37)
+    for n, f1, f2 in names_fields(m1, m2):
+        assert rel_l2(f1.interior(), f2.interior) < tol, n
+    div_tol = 1e-11 if FT == np.float64 else 5e-3
+    assert m1.max_abs_divergence() < div_tol
+
+
+def _run_steps(oc, m1, m2, ics, dt, nsteps):
+    oc.set_model(m1, **ics)
+    o.set_model(m2, **ics)
+    for _ in range(nsteps):
+        o.time_step(m2, dt)
+    oc.time_step(m1, dt, n_steps=nsteps)
+    out = {}
+    for n, f1, f2 in names_fields(m1, m2):
+        out[n] = rel_l2(f1.interior(), f2.interior)
+    out["p"] = rel_l2(m1.pressures.pNHS.interior(), m2.pNHS.interior)
+    return out
+
+
+def smooth_ics(m2, rng, amp=1.0, noise=1e-3):
+    """Σ of random-phase low-wavenumber sinusoids + small noise."""
+    g = m2.grid
+    ics = {}
+    for n, f in zip(m2.prognostic_names(), m2.prognostic_fields()):
+        shape = f.size
+        ax = [np.arange(s) / max(g.N[d], 1) for d, s in enumerate(shape)]
+        v = np.zeros(shape)
+        for _ in range(6):
+            k = rng.integers(0, 3, 3)
+            ph = rng.uniform(0, 2 * np.pi)
+            v += rng.uniform(0.2, 1) * np.cos(2 * np.pi * (k[0] * ax[0][:, None, None] + k[1] * ax[1][None, :, None]
+                                                          + k[2] * ax[2][None, None, :]) + ph)
+        v = amp * v / 3 + noise * rng.uniform(-1, 1, shape)
+        if n == "T":
+            v = 20 + 0.01 * v
+        if n == "S":
+            v = 35 + 0.01 * v
+        ics[n] = v.astype(g.FT)
+    return ics
+
+
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+def test_100_steps_triply_periodic_weno5_rk3(oc, FT, tol):
+    """BASELINE config 2 at an oracle-sized grid: u, v, w, p after 100 RK3 steps."""
+    N = 24
+    m1, m2 = make_pair(oc, FT, (N, N, N), (P, P, P), extent=(2 * np.pi,) * 3)
+    ics = smooth_ics(m2, np.random.default_rng(1234))
+    dt = 0.2 * (2 * np.pi / N) / 2.0
+    err = _run_steps(oc, m1, m2, ics, dt, 100)
+    assert all(e < tol for e in err.values()), err
+    assert m1.clock.iteration == 100 and abs(m1.clock.time - m2.clock.time) < 1e-12
+
+
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+def test_100_steps_full_physics_bounded_z(oc, FT, tol):
+    """u, v, w, T, S, p after 100 steps with SeawaterBuoyancy + FPlane + ScalarDiffusivity on (P,P,B)."""
+    m1, m2 = make_pair(oc, FT, (16, 16, 16), (P, P, B), extent=(1, 1, 1), buoyancy="seawater", tracers=("T", "S"),
+                       coriolis=1e-4, closure=(1e-3, 1e-3))
+    ics = smooth_ics(m2, np.random.default_rng(1234), amp=0.1)
+    for n in ("u", "v", "w"):
+        ics[n][...] *= 0.1
+    err = _run_steps(oc, m1, m2, ics, 2e-2, 100)
+    assert all(e < tol for e in err.values()), err
+
+
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+def test_steps_stretched_z_fourier_tridiagonal(oc, timestepper):
+    Nz = 16
+    k = np.arange(1, Nz + 2)
+    z = np.tanh(1.3 * (2 * (k - 1) / Nz - 1)) / np.tanh(1.3)
+    m1, m2 = make_pair(oc, np.float64, (16, 12, Nz), (P, P, B), z=z, timestepper=timestepper, buoyancy="seawater",
+                       tracers=("T", "S"), closure=(1e-3, 1e-3))
+    ics = smooth_ics(m2, np.random.default_rng(7), amp=0.05)
+    err = _run_steps(oc, m1, m2, ics, 1e-2, 30)
+    assert all(e < 1e-12 for e in err.values()), err
+    assert m1.max_abs_divergence() < 5e-8
+
+
+def test_thermal_bubble_regression_setup_ab2(oc):
+    """test/regression_tests/thermal_bubble_regression_test.jl:4-35 set-up (16³, AB2, FPlane, SeawaterBuoyancy,
+    ν = κ = 4e-2, Δt = 6, 10 steps) — oracle vs CUDA since the golden file is a remote DataDep."""
+    N, L = 16, 100
+    m1, m2 = make_pair(oc, np.float64, (N, N, N), (P, P, B), extent=(L, L, L), advection=("Centered", 2),
+                       timestepper="QuasiAdamsBashforth2", buoyancy="seawater", tracers=("T", "S"), coriolis=1e-4,
+                       closure=(4e-2, 4e-2))
+    T0 = np.full((N, N, N), 9.85)
+    T0[N // 4:3 * N // 4, N // 4:3 * N // 4, N // 4:3 * N // 4] += 0.01
+    ics = dict(T=T0, S=np.full((N, N, N), 35.0))
+    err = _run_steps(oc, m1, m2, ics, 6.0, 10)
+    assert all(e < 1e-12 for e in err.values()), err
