@@ -1,0 +1,268 @@
+#!/usr/bin/env python
+"""bench.py — cell-updates/s of the NonhydrostaticModel WENO5 RK3 time step (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--size 256] [--impl reference]
+
+A "step" is one time_step!(model, Δt) (3 RK3 substeps incl. 3 pressure solves) on a triply periodic Float64 grid;
+one cell-update = one grid cell advanced by one step.  Prints ONE JSON line (see the task contract): `value` is the
+device-resident throughput (CUDA events), `e2e` the same step driven through the C ABI with HOST buffers (u, v, w copied
+host→device before and u, v, w, p device→host after every step), `roofline` the dominant phase against measured HBM
+bandwidth, `cpu_baseline` the oracle (NumPy port of the reference's CPU path) on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "cell-updates/s (NonhydrostaticModel WENO step)"
+UNIT = "cell-updates/s"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def smooth_ics(N, seed):
+    """Σ of random-phase low-wavenumber sinusoids + 1e-3 noise, built per axis to stay cheap."""
+    rng = np.random.default_rng(seed)
+    x = np.arange(N) / N
+    out = {}
+    for name in "uvw":
+        v = np.zeros((N, N, N))
+        for _ in range(4):
+            k = rng.integers(0, 4, 3)
+            ph = rng.uniform(0, 2 * np.pi, 3)
+            v += (np.cos(2 * np.pi * k[0] * x + ph[0])[:, None, None] * np.cos(2 * np.pi * k[1] * x + ph[1])[None, :, None]
+                  * np.cos(2 * np.pi * k[2] * x + ph[2])[None, None, :])
+        v += 1e-3 * rng.uniform(-1, 1, (N, N, N))
+        out[name] = v
+    return out
+
+
+def cpu_oracle_rate(N, steps):
+    """The oracle (CPU restatement of the reference's CPU path) on an N³ sample of the same workload."""
+    import oracle as o
+    g = o.RectilinearGrid(np.float64, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=("Periodic",) * 3)
+    m = o.NonhydrostaticModel(g, advection=o.WENO(np.float64, 5))
+    o.set_model(m, **smooth_ics(N, 1234))
+    dt = 0.2 * (2 * np.pi / N) / 2.0
+    o.time_step(m, dt)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        o.time_step(m, dt)
+    t = time.perf_counter() - t0
+    return N ** 3 * steps / t, t / steps
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f.read().splitlines():
+            parts = [s.strip() for s in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.f.name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(np.max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return out
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    N = args.ref_size
+    rate, sps = cpu_oracle_rate(N, max(1, args.steps))
+    line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"3D triply-periodic NonhydrostaticModel {args.size}^3 Float64 WENO5 RK3 FFTBasedPoissonSolver",
+                       "sample": f"{N}^3 cells per step"},
+            "cpu_baseline": {"value": rate, "unit": UNIT, "cores": 1, "kind": "port",
+                             "sample": f"oracle (NumPy/SciPy restatement of the reference CPU path; Julia is absent), {N}^3 x {args.steps} steps"},
+            "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--size", type=int, default=256)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--ref-size", type=int, default=64)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    import oceananigans_jl_b200 as oc
+    if not torch.cuda.is_available() or oc.device_count() < 1:
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    N = args.size
+    topo = (oc.Periodic,) * 3
+    grid = oc.RectilinearGrid(np.float64, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=topo, device=local_rank)
+    model = oc.NonhydrostaticModel(grid, advection=oc.WENO(order=5), timestepper="RungeKutta3")
+    ics = smooth_ics(N, 1234 + rank)
+    oc.set_model(model, **ics)
+    dt = 0.2 * (2 * np.pi / N) / 2.0
+    cells = N ** 3
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        oc.time_step(model, dt)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    l0 = model.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        oc.time_step(model, dt)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = model.launch_count() - l0
+    clocks = sampler.stop() if sampler else None
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = cells * world * args.steps / (ms * 1e-3)
+    assert np.isfinite(model.max_abs_divergence()), "model blew up"
+
+    # ---- phases (per-kernel-group CUDA-event times; same step composed from the individual ABI calls) ----
+    FT_B = 8
+    phases = {"tendencies": 0.0, "substep": 0.0, "pressure_solve": 0.0, "pressure_correct": 0.0, "halo_fill": 0.0}
+    gam = [(8 / 15, None), (5 / 12, -17 / 60), (3 / 4, -5 / 12)]
+    nprof = max(1, min(args.steps, 3))
+
+    def timed(name, fn):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record()
+        torch.cuda.synchronize()
+        phases[name] += a.elapsed_time(b)
+    for _ in range(nprof):
+        for g_, z_ in gam:
+            sdt = (g_ + (z_ or 0.0)) * dt
+            timed("substep", lambda: oc.rk3_substep(model, dt, g_, z_))
+            timed("pressure_solve", lambda: oc.calculate_pressure_correction(model, sdt))
+            timed("pressure_correct", lambda: oc.pressure_correct_velocities(model, sdt))
+            timed("substep", lambda: oc.cache_previous_tendencies(model))
+            timed("halo_fill", lambda: oc.fill_halo_regions(model.prognostic_fields(), False))
+            timed("tendencies", lambda: oc.compute_tendencies(model))
+    for k in phases:
+        phases[k] /= nprof            # ms per step (3 substeps)
+    # algorithmic bytes per step and phase (w = 8, F = 3): tendencies+substep A = 9w + 2·12w,
+    # pressure solve B = 3·12w, pressure correction C = 3·7w
+    alg = {"tendencies": 3 * 6 * FT_B * cells, "substep": (9 + 2 * 12 - 3 * 6) * FT_B * cells,
+           "pressure_solve": 3 * 12 * FT_B * cells, "pressure_correct": 3 * 7 * FT_B * cells}
+    dom = max(alg, key=lambda k: phases[k])
+    peak, peak_kind = peaks()
+    achieved = alg[dom] / (phases[dom] * 1e-3) / 1e9
+    step_bytes = 90 * FT_B * cells
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "peak_source": peak_kind, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None,
+                "whole_step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms_per_step * 1e-3) / 1e9,
+                               "frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak},
+                "phase_ms_per_step": phases}
+
+    # ---- e2e: HOST buffers through the C ABI; H2D of u,v,w and D2H of u,v,w,p inside the timed region ----
+    host_in = {n: torch.from_numpy(np.asfortranarray(model.velocities[n].interior())).pin_memory() for n in "uvw"}
+    host_np = {n: host_in[n].numpy() for n in "uvw"}
+    e2e_steps = max(1, min(args.steps, 5))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        for n in "uvw":
+            model.velocities[n].set(host_np[n])
+        oc.fill_halo_regions(model.prognostic_fields())
+        oc.time_step(model, dt)
+        outs = [model.velocities[n].interior() for n in "uvw"] + [model.pressures.pNHS.interior()]
+        for n, a in zip("uvw", outs):
+            host_np[n][...] = a
+    barrier()
+    e2e_t = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_t], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_t = float(t.item())
+    e2e = {"value": cells * world * e2e_steps / e2e_t, "unit": UNIT, "h2d_bytes_per_step": 3 * cells * FT_B * world,
+           "d2h_bytes_per_step": 4 * cells * FT_B * world, "steps": e2e_steps}
+
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            rate, sps = cpu_oracle_rate(args.ref_size, 3)
+            cpu = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port",
+                   "sample": f"oracle (NumPy/SciPy port of the reference CPU path) on {args.ref_size}^3 x 3 steps, {sps:.2f} s/step"}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic",
+                "config": {"workload": f"3D triply-periodic NonhydrostaticModel {N}^3 Float64 WENO5 RK3 FFTBasedPoissonSolver"
+                           + (" per GPU" if world > 1 else ""),
+                           "l2_policy": "working set (>= 10 fields x %.0f MB) exceeds the 126 MB L2" % (cells * FT_B / 1e6),
+                           "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (no exchange)"},
+                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
