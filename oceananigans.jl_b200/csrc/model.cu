@@ -72,7 +72,61 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   rk_z2 = (FT)-17 / (FT)60; rk_z3 = (FT)-5 / (FT)12;
   chi = (FT)d.ab2_chi;
   clock.time = 0; clock.iteration = 0; clock.stage = 1; clock.last_dt = INFINITY; clock.last_stage_dt = INFINITY;
+  fast = ntr == 0 && !gh.z_stretched && d.buoyancy_kind == NH_BUOYANCY_NONE && !d.has_coriolis && !d.has_closure && !pHY;
+  for (int e = 0; e < 3; ++e)
+    fast = fast && gh.g.topo[e] == NH_PERIODIC && adv[e].kind == NH_ADV_WENO && adv[e].B == 3 && gh.g.N[e] >= 2 * gh.g.H[e] && gh.g.H[e] >= 3;
+  if (getenv("NHSTEP_NO_FAST")) fast = false;
+  if (fast) {
+    for (int a = 0; a < 3; ++a) F2[a] = alloc_field();
+    CUDA_CHECK(cudaFuncSetAttribute(tendency_fast_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TF_SMEM_ELEMS * sizeof(FT))));
+  }
   update_state(0);
+}
+
+template <typename FT>
+void Model<FT>::ensure_tendencies() {
+  if (!gn_stale) return;
+  gn_stale = false;
+  compute_tendencies();
+}
+
+template <typename FT>
+void Model<FT>::ensure_p_halo() {
+  if (!p_halo_stale) return;
+  p_halo_stale = false;
+  fill_halo_regions(1u << NH_FIELD_PNHS, 1);
+}
+
+// One fused stage: Gⁿ = G(U), U* = U + Δt(…) into the ping-pong buffer, then the pressure correction.
+template <typename FT>
+void Model<FT>::fast_stage(int mode, FT dt, FT c1, FT c2, double stage_dt) {
+  FastTendJob<FT> J;
+  J.g = gh.g; J.tab = tab; J.dt = dt; J.gamma = c1; J.zeta = c2; J.mode = mode;
+  for (int a = 0; a < 3; ++a) { J.U[a] = F[a]; J.Unew[a] = F2[a]; J.Gn[a] = Gn[a]; J.Gm[a] = Gm[a]; }
+  dim3 grd(ceil_div(gh.g.N[0], TF_TX), ceil_div(gh.g.N[1], TF_TY), ceil_div(gh.g.N[2], TF_TZ));
+  tendency_fast_kernel<FT><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
+  KLAUNCH(lc);
+  for (int a = 0; a < 3; ++a) std::swap(F[a], F2[a]);
+  fast_pressure(stage_dt);
+}
+
+template <typename FT>
+void Model<FT>::fast_pressure(double stage_dt) {
+  const GridDev<FT>& g = gh.g;
+  FastHaloJob<FT> H; H.g = g; H.nf = 3; for (int a = 0; a < 3; ++a) H.p[a] = F[a];
+  dim3 hg(1, g.N[1] + 2 * g.H[1], g.N[2] + 2 * g.H[2]);
+  periodic_halo_all_kernel<FT><<<hg, 128, 0, stream>>>(H);
+  KLAUNCH(lc);
+  dim3 blk(64, 4, 1);
+  source_term_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], stage_dt, 0, solver.A.p);
+  KLAUNCH(lc);
+  CT* sol = solver.solve(0.0);
+  copy_real_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(g, sol, pNHS);
+  KLAUNCH(lc);
+  pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], pNHS, stage_dt);
+  KLAUNCH(lc);
+  p_halo_stale = true;
+  CUDA_CHECK(cudaGetLastError());
 }
 
 template <typename FT>
@@ -126,6 +180,8 @@ void Model<FT>::set_field(int field, int region, const void* data, int64_t count
 
 template <typename FT>
 void Model<FT>::get_field(int field, int region, void* data, int64_t count, int where) {
+  if (field >= NH_FIELD_GN0 && field < NH_FIELD_GM0) ensure_tendencies();
+  if (field == NH_FIELD_PNHS && region == NH_PARENT) ensure_p_halo();
   FT* p = field_ptr(field);
   int64_t sz[3]; field_size(field, region, sz);
   NH_REQUIRE(count == sz[0] * sz[1] * sz[2], "nh_get_field: element count does not match the field's size");
@@ -232,6 +288,7 @@ void Model<FT>::update_hydrostatic_pressure() {
 
 template <typename FT>
 void Model<FT>::compute_tendencies() {
+  gn_stale = false;
   TendParams<FT> P = tend_params();
   dim3 blk(32, 4, 1);
   for (int what = 0; what < nf; ++what) {
@@ -243,6 +300,7 @@ void Model<FT>::compute_tendencies() {
 
 template <typename FT>
 void Model<FT>::update_state(int compute) {
+  if (compute) gn_stale = false;
   uint32_t mask = 0; for (int f = 0; f < nf; ++f) mask |= 1u << f;
   fill_halo_regions(mask, 0);
   update_hydrostatic_pressure();
@@ -251,6 +309,7 @@ void Model<FT>::update_state(int compute) {
 
 template <typename FT>
 void Model<FT>::substep_launch(int mode, FT dt, FT c1, FT c2) {
+  ensure_tendencies();
   StepJob<FT> J;
   J.g = gh.g; J.nf = nf; J.dt = dt; J.c1 = c1; J.c2 = c2; J.mode = mode;
   for (int f = 0; f < nf; ++f) { J.U[f] = F[f]; J.Gn[f] = Gn[f]; J.Gm[f] = Gm[f]; J.face_dim[f] = f < 3 ? f : -1; }
@@ -302,6 +361,31 @@ void Model<FT>::pressure_correct_velocities(double dt) {
 // store_tendencies.jl is replaced by a pointer swap (Gⁿ is fully rewritten by the next compute_tendencies!).
 template <typename FT>
 void Model<FT>::time_step(double dt, int euler) {
+  if (fast) {
+    // same sequence as below with compute_tendencies! + the next substep fused and the halo fills folded into the
+    // pressure-correction kernel; Gⁿ of the final state is refreshed lazily (ensure_tendencies).
+    if (desc.timestepper == NH_RK3) {
+      double first = (double)rk_g1 * dt, second = (double)(FT)(rk_g2 + rk_z2) * dt, third = (double)(FT)(rk_g3 + rk_z3) * dt;
+      double t_next = clock.time + dt;
+      auto swapG = [&]() { for (int f = 0; f < nf; ++f) std::swap(Gn[f], Gm[f]); };
+      fast_stage(0, (FT)dt, rk_g1, FT(0), first);
+      clock.time += first; clock.stage += 1; clock.last_stage_dt = first;
+      swapG();
+      fast_stage(1, (FT)dt, rk_g2, rk_z2, second);
+      clock.time += second; clock.stage += 1; clock.last_stage_dt = second;
+      swapG();
+      fast_stage(1, (FT)dt, rk_g3, rk_z3, third);
+      double corrected = t_next - clock.time;
+      clock.time += third; clock.iteration += 1; clock.stage = 1; clock.last_stage_dt = corrected; clock.last_dt = dt;
+    } else {
+      bool eul = euler || (dt != clock.last_dt);
+      fast_stage(eul ? 3 : 2, (FT)dt, eul ? FT(-0.5) : chi, FT(0), dt);
+      clock.time += dt; clock.iteration += 1; clock.stage = 1; clock.last_dt = dt; clock.last_stage_dt = dt;
+      for (int f = 0; f < nf; ++f) std::swap(Gn[f], Gm[f]);
+    }
+    gn_stale = true;
+    return;
+  }
   if (clock.iteration == 0) update_state(1);
   auto swapG = [&]() { for (int f = 0; f < nf; ++f) std::swap(Gn[f], Gm[f]); };
   if (desc.timestepper == NH_RK3) {

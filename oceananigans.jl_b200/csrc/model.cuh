@@ -2,6 +2,7 @@
 #pragma once
 #include "kernels_basic.cuh"
 #include "fft_generic.cuh"
+#include "tendency_fast.cuh"
 #include "grid_host.h"
 #include <memory>
 #include <cstring>
@@ -113,6 +114,13 @@ struct Model : nh_model {
   DevBuf<FT> stage;        // staging for host <-> device field copies
   DevBuf<double> red;      // reduction scratch
   FT rk_g1, rk_g2, rk_g3, rk_z2, rk_z3, chi;
+  // fused fast path (triply periodic, regular, WENO5, no tracers): ping-pong state, lazily refreshed Gⁿ and p halos
+  bool fast = false, gn_stale = false, p_halo_stale = false;
+  FT* F2[3] = {nullptr, nullptr, nullptr};
+  void fast_stage(int mode, FT dt, FT c1, FT c2, double stage_dt);
+  void fast_pressure(double stage_dt);
+  void ensure_tendencies();
+  void ensure_p_halo();
 
   Model(const nh_grid& grid, const nh_model_desc& d);
   FT* alloc_field();

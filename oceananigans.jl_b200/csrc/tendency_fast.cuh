@@ -1,0 +1,187 @@
+// tendency_fast.cuh — fused momentum tendencies + RK3/AB2 substep for the headline configuration: triply periodic,
+// regular spacing, WENO5 in all directions (BASELINE.json configs[1]; optional tracers come through the complete path).
+//
+// One CTA owns a TX×TY×TZ tile of cells.  For each velocity component a, the CTA evaluates every face flux
+// F_{b,a} (b = x,y,z) of the tile exactly ONCE into shared memory (the reference evaluates each twice, once per adjacent
+// cell, in three separate kernels), then each thread differences the staged fluxes for its cells, finishes
+// Gⁿ = -div(𝐯u_a) and applies U* = U + Δt(γGⁿ + ζG⁻) into the ping-pong state buffer in the same pass, so the step's
+// traffic is: read u,v,w (+G⁻), write Gⁿ and U* (SURVEY.md §8d phase A: 9w / 12w bytes per cell).
+// Arithmetic follows the reference's expression order (recon.cuh), so results are bit-identical to the complete path.
+#pragma once
+#include "recon.cuh"
+
+#define TF_TX 32
+#define TF_TY 8
+#define TF_TZ 8
+#define TF_THREADS 256
+#define TF_SMEM_ELEMS (TF_TZ * TF_TY * (TF_TX + 1) + TF_TZ * (TF_TY + 1) * TF_TX + (TF_TZ + 1) * TF_TY * TF_TX)
+
+template <typename FT>
+struct FastTendJob {
+  GridDev<FT> g;
+  const FT* U[3];      // state with filled halos
+  FT* Unew[3];         // ping-pong target (interior written)
+  FT* Gn[3];
+  const FT* Gm[3];
+  SchemeTables<FT> tab;
+  FT dt, gamma, zeta;
+  int mode;            // 0: U* = U + Δt·γ·Gⁿ, 1: U* = U + Δt(γGⁿ + ζG⁻), 2: AB2, 3: AB2-Euler, -1: tendencies only
+};
+
+// face flux F_{b,a} at flux-location index n (linear), strides sa (dim a) and sb (dim b)
+template <typename FT, bool SAME>
+__device__ __forceinline__ FT fast_flux(const SchemeTables<FT>& T, const FT* __restrict__ ua, const FT* __restrict__ ub,
+                                        long long n, long long sa, long long sb, FT Ab) {
+  // advecting velocity: Centered(4) interpolation of A_b·U_b along dim b onto a Centre (SAME) or along dim a onto a Face
+  const long long ss = SAME ? sb : sa;
+  const int s0 = SAME ? 1 : 0;
+  FT ut = T.sym[2][3] * (Ab * ub[n + (-2 + s0) * ss]);
+  ut = ut + T.sym[2][2] * (Ab * ub[n + (-1 + s0) * ss]);
+  ut = ut + T.sym[2][1] * (Ab * ub[n + (0 + s0) * ss]);
+  ut = ut + T.sym[2][0] * (Ab * ub[n + (1 + s0) * ss]);
+  const bool left = ut > FT(0);
+  const FT* p = ua + n + s0 * sb;
+  FT q0, q1, q2, q3, q4;
+  if (left) { q0 = p[-3 * sb]; q1 = p[-2 * sb]; q2 = p[-sb]; q3 = p[0]; q4 = p[sb]; }
+  else      { q0 = p[2 * sb]; q1 = p[sb]; q2 = p[0]; q3 = p[-sb]; q4 = p[-2 * sb]; }
+  return ut * weno5_from_q<FT>(T, q0, q1, q2, q3, q4);
+}
+
+template <typename FT>
+__global__ void __launch_bounds__(TF_THREADS, 2) tendency_fast_kernel(const __grid_constant__ FastTendJob<FT> J) {
+  extern __shared__ __align__(16) unsigned char tf_smem[];
+  typedef FT (*FxT)[TF_TY][TF_TX + 1];
+  typedef FT (*FyT)[TF_TY + 1][TF_TX];
+  typedef FT (*FzT)[TF_TY][TF_TX];
+  FxT Fx = reinterpret_cast<FxT>(tf_smem);
+  FyT Fy = reinterpret_cast<FyT>(tf_smem + sizeof(FT) * TF_TZ * TF_TY * (TF_TX + 1));
+  FzT Fz = reinterpret_cast<FzT>(tf_smem + sizeof(FT) * (TF_TZ * TF_TY * (TF_TX + 1) + TF_TZ * (TF_TY + 1) * TF_TX));
+  const GridDev<FT>& g = J.g;
+  const int i0 = blockIdx.x * TF_TX + 1, j0 = blockIdx.y * TF_TY + 1, k0 = blockIdx.z * TF_TZ + 1;
+  const int tid = threadIdx.x;
+  const long long st[3] = {1, g.sy, g.sz};
+  const FT Ax = g.dy * g.dz, Ay = g.dx * g.dz, Az = g.dx * g.dy;
+  const FT Vinv = FT(1) / ((g.dx * g.dy) * g.dz);
+  const int nx = min(TF_TX, g.N[0] - i0 + 1), ny = min(TF_TY, g.N[1] - j0 + 1), nz = min(TF_TZ, g.N[2] - k0 + 1);
+
+#pragma unroll 1
+  for (int a = 0; a < 3; ++a) {
+    const FT* __restrict__ ua = J.U[a];
+    const long long sa = st[a];
+    // ---- x-direction fluxes F_{x,a}: a == 0 → centres i0-1 … i0+nx-1, else faces i0 … i0+nx
+    for (int t = tid; t < (TF_TX + 1) * TF_TY * TF_TZ; t += TF_THREADS) {
+      int li = t % (TF_TX + 1), lj = (t / (TF_TX + 1)) % TF_TY, lk = t / ((TF_TX + 1) * TF_TY);
+      if (li > nx || lj >= ny || lk >= nz) continue;
+      long long n = g.idx(i0 + li - (a == 0 ? 1 : 0), j0 + lj, k0 + lk);
+      Fx[lk][lj][li] = a == 0 ? fast_flux<FT, true>(J.tab, ua, J.U[0], n, sa, 1, Ax)
+                              : fast_flux<FT, false>(J.tab, ua, J.U[0], n, sa, 1, Ax);
+    }
+    for (int t = tid; t < TF_TX * (TF_TY + 1) * TF_TZ; t += TF_THREADS) {
+      int li = t % TF_TX, lj = (t / TF_TX) % (TF_TY + 1), lk = t / (TF_TX * (TF_TY + 1));
+      if (li >= nx || lj > ny || lk >= nz) continue;
+      long long n = g.idx(i0 + li, j0 + lj - (a == 1 ? 1 : 0), k0 + lk);
+      Fy[lk][lj][li] = a == 1 ? fast_flux<FT, true>(J.tab, ua, J.U[1], n, sa, g.sy, Ay)
+                              : fast_flux<FT, false>(J.tab, ua, J.U[1], n, sa, g.sy, Ay);
+    }
+    for (int t = tid; t < TF_TX * TF_TY * (TF_TZ + 1); t += TF_THREADS) {
+      int li = t % TF_TX, lj = (t / TF_TX) % TF_TY, lk = t / (TF_TX * TF_TY);
+      if (li >= nx || lj >= ny || lk > nz) continue;
+      long long n = g.idx(i0 + li, j0 + lj, k0 + lk - (a == 2 ? 1 : 0));
+      Fz[lk][lj][li] = a == 2 ? fast_flux<FT, true>(J.tab, ua, J.U[2], n, sa, g.sz, Az)
+                              : fast_flux<FT, false>(J.tab, ua, J.U[2], n, sa, g.sz, Az);
+    }
+    __syncthreads();
+    // ---- divergence, tendency, substep
+    for (int t = tid; t < TF_TX * TF_TY * TF_TZ; t += TF_THREADS) {
+      int li = t % TF_TX, lj = (t / TF_TX) % TF_TY, lk = t / (TF_TX * TF_TY);
+      if (li >= nx || lj >= ny || lk >= nz) continue;
+      FT total = (Fx[lk][lj][li + 1] - Fx[lk][lj][li]) + (Fy[lk][lj + 1][li] - Fy[lk][lj][li]);
+      total = total + (Fz[lk + 1][lj][li] - Fz[lk][lj][li]);
+      FT G = -(Vinv * total);
+      G = G + FT(0);
+      long long n = g.idx(i0 + li, j0 + lj, k0 + lk);
+      J.Gn[a][n] = G;
+      if (J.mode >= 0) {
+        FT u = ua[n];
+        if (J.mode == 0) u = u + J.dt * J.gamma * G;
+        else if (J.mode == 1) u = u + J.dt * (J.gamma * G + J.zeta * J.Gm[a][n]);
+        else if (J.mode == 2) u = u + J.dt * ((FT(1.5) + J.gamma) * G - (FT(0.5) + J.gamma) * J.Gm[a][n]);
+        else u = u + J.dt * ((FT(1.5) + J.gamma) * G - FT(0));
+        J.Unew[a][n] = u;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// Periodic halo fill of several fields in ONE launch: every halo cell reads its wrapped interior image directly
+// (equivalent to the reference's x → y → z sequence of fill_periodic_*_halo! kernels,
+// src/BoundaryConditions/fill_halo_regions_periodic.jl:40-111, corners included).
+template <typename FT>
+struct FastHaloJob { GridDev<FT> g; FT* p[NH_MAXTR + 3]; int nf; };
+
+template <typename FT>
+__global__ void __launch_bounds__(256) periodic_halo_all_kernel(const __grid_constant__ FastHaloJob<FT> J) {
+  const GridDev<FT>& g = J.g;
+  const int Ex = g.N[0] + 2 * g.H[0], Ey = g.N[1] + 2 * g.H[1], Ez = g.N[2] + 2 * g.H[2];
+  // enumerate the parent box plane by plane; skip interior cells quickly (only shells do work)
+  int pj = blockIdx.y, pk = blockIdx.z;
+  int j = pj + 1 - g.H[1], k = pk + 1 - g.H[2];
+  bool row_interior = (j >= 1 && j <= g.N[1] && k >= 1 && k <= g.N[2]);
+  int wj = j < 1 ? j + g.N[1] : (j > g.N[1] ? j - g.N[1] : j);
+  int wk = k < 1 ? k + g.N[2] : (k > g.N[2] ? k - g.N[2] : k);
+  (void)Ey; (void)Ez;
+  if (row_interior) {
+    // only the 2·Hx cells at the two ends of this row
+    int t = threadIdx.x;
+    if (t >= 2 * g.H[0]) return;
+    int i = t < g.H[0] ? t + 1 - g.H[0] : g.N[0] + 1 + (t - g.H[0]);
+    int wi = i < 1 ? i + g.N[0] : i - g.N[0];
+    long long dst = g.idx(i, j, k), src = g.idx(wi, j, k);
+    for (int f = 0; f < J.nf; ++f) J.p[f][dst] = J.p[f][src];
+    return;
+  }
+  for (int pi = threadIdx.x; pi < Ex; pi += blockDim.x) {
+    int i = pi + 1 - g.H[0];
+    int wi = i < 1 ? i + g.N[0] : (i > g.N[0] ? i - g.N[0] : i);
+    long long dst = g.idx(i, j, k), src = g.idx(wi, wj, wk);
+    for (int f = 0; f < J.nf; ++f) J.p[f][dst] = J.p[f][src];
+  }
+}
+
+// Pressure correction over the interior with periodic index wrap on p (no p halo needed), fused with the periodic halo
+// fill of the corrected velocities: a corrected interior value is also stored to each of its periodic images.
+// _pressure_correct_velocities! — src/Models/NonhydrostaticModels/pressure_correction.jl:31-37
+template <typename FT>
+__global__ void __launch_bounds__(256) pressure_correct_halo_kernel(GridDev<FT> g, FT* __restrict__ u, FT* __restrict__ v,
+                                                                    FT* __restrict__ w, const FT* __restrict__ p, double dt) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  int k = blockIdx.z + 1;
+  if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
+  long long n = g.idx(i, j, k);
+  FT p0 = p[n];
+  FT pxm = p[g.idx(i == 1 ? g.N[0] : i - 1, j, k)];
+  FT pym = p[g.idx(i, j == 1 ? g.N[1] : j - 1, k)];
+  FT pzm = p[g.idx(i, j, k == 1 ? g.N[2] : k - 1)];
+  FT gx = (p0 - pxm) / g.dx, gy = (p0 - pym) / g.dy, gz = (p0 - pzm) / g.dz;
+  FT un, vn, wn;
+  if (sizeof(FT) == 4) {
+    un = (FT)((double)u[n] - (double)gx * dt); vn = (FT)((double)v[n] - (double)gy * dt); wn = (FT)((double)w[n] - (double)gz * dt);
+  } else {
+    un = u[n] - gx * (FT)dt; vn = v[n] - gy * (FT)dt; wn = w[n] - gz * (FT)dt;
+  }
+  // periodic images: index sets {i, i±N} ∩ parent range, likewise j, k
+  int xi[2], nxi = 1; xi[0] = i;
+  if (i <= g.H[0]) xi[nxi++] = i + g.N[0]; else if (i > g.N[0] - g.H[0]) xi[nxi++] = i - g.N[0];
+  int yj[2], nyj = 1; yj[0] = j;
+  if (j <= g.H[1]) yj[nyj++] = j + g.N[1]; else if (j > g.N[1] - g.H[1]) yj[nyj++] = j - g.N[1];
+  int zk[2], nzk = 1; zk[0] = k;
+  if (k <= g.H[2]) zk[nzk++] = k + g.N[2]; else if (k > g.N[2] - g.H[2]) zk[nzk++] = k - g.N[2];
+  for (int c = 0; c < nzk; ++c)
+    for (int b = 0; b < nyj; ++b)
+      for (int a = 0; a < nxi; ++a) {
+        long long m = g.idx(xi[a], yj[b], zk[c]);
+        u[m] = un; v[m] = vn; w[m] = wn;
+      }
+}

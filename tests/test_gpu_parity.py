@@ -283,3 +283,27 @@ def test_thermal_bubble_regression_setup_ab2(oc):
     ics = dict(T=T0, S=np.full((N, N, N), 35.0))
     err, floor = _run_steps(oc, m1, m2, ics, 6.0, 10, m3)
     check_parity(err, 1e-12, floor)
+
+
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+@pytest.mark.parametrize("size", [(40, 24, 16), (33, 13, 9)])
+def test_fused_fast_path_is_bit_identical_to_complete_path(oc, FT, timestepper, size, monkeypatch):
+    """The fused tendency+substep / pressure-correction+halo kernels against the one-kernel-per-reference-kernel path."""
+    import os
+    rng = np.random.default_rng(8)
+    ics = {n: rng.uniform(-1, 1, size).astype(FT) for n in "uvw"}
+    out = []
+    for no_fast in (False, True):
+        if no_fast:
+            monkeypatch.setenv("NHSTEP_NO_FAST", "1")
+        else:
+            monkeypatch.delenv("NHSTEP_NO_FAST", raising=False)
+        g = oc.RectilinearGrid(FT, size=size, extent=(1, 2, 3), topology=(P, P, P))
+        m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), timestepper=timestepper)
+        oc.set_model(m, **ics)
+        oc.time_step(m, 2e-3, n_steps=3)
+        out.append([m.velocities[n].parent() for n in "uvw"] + [m.pressures.pNHS.parent()]
+                   + [m.timestepper.Gn[n].interior() for n in "uvw"] + [m.timestepper.Gm[n].interior() for n in "uvw"])
+    for a, b in zip(*out):
+        np.testing.assert_array_equal(a, b)
