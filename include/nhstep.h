@@ -123,6 +123,9 @@ int32_t nh_calculate_pressure_correction(nh_model* model, double dt);
 int32_t nh_pressure_correct_velocities(nh_model* model, double dt);
 /* time_step!(model, Δt; euler) — runge_kutta_3.jl:77-151 / quasi_adams_bashforth_2.jl:74-115; n_steps ≥ 1 repeats it */
 int32_t nh_time_step(nh_model* model, double dt, int32_t euler, int32_t n_steps);
+/* one time_step! with CUDA events between its phases on the model's stream; phase_ms = {tendencies + substep,
+ * pressure solve (halo fill, source term, transforms, real store), pressure correction (+ halo fill), remainder} */
+int32_t nh_time_step_profiled(nh_model* model, double dt, int32_t euler, double phase_ms[4]);
 int32_t nh_clock_get(const nh_model* model, nh_clock* out);
 int32_t nh_clock_set(nh_model* model, const nh_clock* in);
 /* max |div U| and other diagnostics used by the reference tests (test/utils_for_runtests.jl:125-151) */

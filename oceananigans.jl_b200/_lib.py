@@ -43,7 +43,7 @@ SYMBOLS = [
     "nh_grid_spacings", "nh_model_create", "nh_model_destroy", "nh_model_grid_info", "nh_field_size", "nh_set_field",
     "nh_get_field", "nh_set_state_finalize", "nh_fill_halo_regions", "nh_update_state", "nh_compute_tendencies",
     "nh_rk3_substep", "nh_ab2_step", "nh_cache_previous_tendencies", "nh_calculate_pressure_correction",
-    "nh_pressure_correct_velocities", "nh_time_step", "nh_clock_get", "nh_clock_set", "nh_max_abs_divergence",
+    "nh_pressure_correct_velocities", "nh_time_step", "nh_time_step_profiled", "nh_clock_get", "nh_clock_set", "nh_max_abs_divergence",
     "nh_synchronize", "nh_field_device_ptr", "nh_model_set_stream", "nh_launch_count", "nh_poisson_create",
     "nh_poisson_destroy", "nh_poisson_solve", "nh_poisson_synchronize", "nh_poisson_launch_count",
     "nh_poisson_time_solves", "nh_tridiag_create", "nh_tridiag_solve", "nh_tridiag_destroy",
@@ -87,6 +87,7 @@ def lib():
             "nh_calculate_pressure_correction": [p, C.c_double],
             "nh_pressure_correct_velocities": [p, C.c_double],
             "nh_time_step": [p, C.c_double, C.c_int32, C.c_int32],
+            "nh_time_step_profiled": [p, C.c_double, C.c_int32, C.POINTER(C.c_double)],
             "nh_clock_get": [p, C.POINTER(Clock)],
             "nh_clock_set": [p, C.POINTER(Clock)],
             "nh_max_abs_divergence": [p, C.POINTER(C.c_double)],

@@ -170,6 +170,7 @@ int32_t nh_cache_previous_tendencies(nh_model* m) { MODEL_CALL(m, m->cache_previ
 int32_t nh_calculate_pressure_correction(nh_model* m, double dt) { MODEL_CALL(m, m->calculate_pressure_correction(dt)) }
 int32_t nh_pressure_correct_velocities(nh_model* m, double dt) { MODEL_CALL(m, m->pressure_correct_velocities(dt)) }
 int32_t nh_time_step(nh_model* m, double dt, int32_t euler, int32_t n_steps) { MODEL_CALL(m, for (int q = 0; q < (n_steps < 1 ? 1 : n_steps); ++q) m->time_step(dt, euler)) }
+int32_t nh_time_step_profiled(nh_model* m, double dt, int32_t euler, double phase_ms[4]) { MODEL_CALL(m, m->profiled_step(dt, euler, phase_ms)) }
 int32_t nh_clock_get(const nh_model* m, nh_clock* out) { NH_TRY NH_REQUIRE(m && out, "null argument"); *out = m->clock; NH_CATCH }
 int32_t nh_clock_set(nh_model* m, const nh_clock* in) { NH_TRY NH_REQUIRE(m && in, "null argument"); m->clock = *in; NH_CATCH }
 int32_t nh_max_abs_divergence(nh_model* m, double* out) { MODEL_CALL(m, *out = m->max_abs_divergence()) }

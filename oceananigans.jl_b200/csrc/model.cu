@@ -106,6 +106,7 @@ void Model<FT>::fast_stage(int mode, FT dt, FT c1, FT c2, double stage_dt) {
   dim3 grd(ceil_div(gh.g.N[0], TF_TX), ceil_div(gh.g.N[1], TF_TY), ceil_div(gh.g.N[2], TF_TZ));
   tendency_fast_kernel<FT><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
   KLAUNCH(lc);
+  mark(0);
   for (int a = 0; a < 3; ++a) std::swap(F[a], F2[a]);
   fast_pressure(stage_dt);
 }
@@ -123,8 +124,10 @@ void Model<FT>::fast_pressure(double stage_dt) {
   CT* sol = solver.solve(0.0);
   copy_real_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(g, sol, pNHS);
   KLAUNCH(lc);
+  mark(1);
   pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], pNHS, stage_dt);
   KLAUNCH(lc);
+  mark(2);
   p_halo_stale = true;
   CUDA_CHECK(cudaGetLastError());
 }
@@ -393,34 +396,34 @@ void Model<FT>::time_step(double dt, int euler) {
     double second = (double)(FT)(rk_g2 + rk_z2) * dt;
     double third = (double)(FT)(rk_g3 + rk_z3) * dt;
     double t_next = clock.time + dt;
-    substep_launch(0, (FT)dt, rk_g1, FT(0));
+    substep_launch(0, (FT)dt, rk_g1, FT(0)); mark(0);
     clock.time += first; clock.stage += 1; clock.last_stage_dt = first;
-    calculate_pressure_correction(first);
-    pressure_correct_velocities(first);
+    calculate_pressure_correction(first); mark(1);
+    pressure_correct_velocities(first); mark(2);
     swapG();
-    update_state(1);
-    substep_launch(1, (FT)dt, rk_g2, rk_z2);
+    update_state(1); mark(0);
+    substep_launch(1, (FT)dt, rk_g2, rk_z2); mark(0);
     clock.time += second; clock.stage += 1; clock.last_stage_dt = second;
-    calculate_pressure_correction(second);
-    pressure_correct_velocities(second);
+    calculate_pressure_correction(second); mark(1);
+    pressure_correct_velocities(second); mark(2);
     swapG();
-    update_state(1);
-    substep_launch(1, (FT)dt, rk_g3, rk_z3);
+    update_state(1); mark(0);
+    substep_launch(1, (FT)dt, rk_g3, rk_z3); mark(0);
     double corrected = t_next - clock.time;
     clock.time += third; clock.iteration += 1; clock.stage = 1;
     clock.last_stage_dt = corrected; clock.last_dt = dt;
-    calculate_pressure_correction(third);
-    pressure_correct_velocities(third);
-    update_state(1);
+    calculate_pressure_correction(third); mark(1);
+    pressure_correct_velocities(third); mark(2);
+    update_state(1); mark(0);
   } else {
     bool eul = euler || (dt != clock.last_dt);
     FT c = eul ? FT(-0.5) : chi;
-    substep_launch(eul ? 3 : 2, (FT)dt, c, FT(0));
+    substep_launch(eul ? 3 : 2, (FT)dt, c, FT(0)); mark(0);
     clock.time += dt; clock.iteration += 1; clock.stage = 1; clock.last_dt = dt; clock.last_stage_dt = dt;
-    calculate_pressure_correction(dt);
-    pressure_correct_velocities(dt);
+    calculate_pressure_correction(dt); mark(1);
+    pressure_correct_velocities(dt); mark(2);
     swapG();
-    update_state(1);
+    update_state(1); mark(0);
   }
 }
 

@@ -95,6 +95,27 @@ struct nh_model {
   virtual double max_abs_divergence() = 0;
   virtual void field_device_ptr(int field, void** ptr, int64_t* off, int64_t strides[3]) = 0;
   virtual void set_stream(cudaStream_t s) { stream = s; }
+  // phase timing (nh_time_step_profiled): CUDA events on the model's stream between the phases of one step
+  bool profiling = false;
+  std::vector<std::pair<int, cudaEvent_t>> marks;
+  void mark(int phase) {
+    if (!profiling) return;
+    cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, stream); marks.emplace_back(phase, e);
+  }
+  void profiled_step(double dt, int euler, double ms[4]) {
+    profiling = true; marks.clear();
+    mark(-1);
+    time_step(dt, euler);
+    mark(3);
+    cudaStreamSynchronize(stream);
+    for (int q = 0; q < 4; ++q) ms[q] = 0;
+    for (size_t q = 1; q < marks.size(); ++q) {
+      float t = 0; cudaEventElapsedTime(&t, marks[q - 1].second, marks[q].second);
+      ms[marks[q].first] += t;
+    }
+    for (auto& m : marks) cudaEventDestroy(m.second);
+    marks.clear(); profiling = false;
+  }
 };
 
 template <typename FT>

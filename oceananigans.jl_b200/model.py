@@ -214,6 +214,13 @@ def time_step(model, dt, euler=False, n_steps=1):
     check(lib().nh_time_step(model._h, float(dt), int(euler), int(n_steps)))
 
 
+def time_step_profiled(model, dt, euler=False):
+    """One time_step! with per-phase CUDA-event times (ms): tendencies+substep, pressure solve, pressure correction, rest."""
+    ms = (C.c_double * 4)()
+    check(lib().nh_time_step_profiled(model._h, float(dt), int(euler), ms))
+    return dict(zip(("tendencies_substep", "pressure_solve", "pressure_correct", "other"), (float(v) for v in ms)))
+
+
 def set_model(model, enforce_incompressibility=True, **kwargs):
     """set!(model; u=…, v=…, w=…, T=…, …, enforce_incompressibility=true)."""
     names = ["u", "v", "w"] + list(model.tracer_names)
