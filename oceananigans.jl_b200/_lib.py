@@ -3,7 +3,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnhstep.so")
+LIB_PATH = os.environ.get("NHSTEP_LIB", os.path.join(_HERE, "libnhstep.so"))   # override: development A/B builds only
 
 NH_MAX_TRACERS = 8
 F32, F64 = 0, 1

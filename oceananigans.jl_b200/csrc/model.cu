@@ -78,6 +78,7 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   if (getenv("NHSTEP_NO_FAST")) fast = false;
   if (fast) {
     for (int a = 0; a < 3; ++a) F2[a] = alloc_field();
+    if (PoissonFast<FT>::supported(gh) && !getenv("NHSTEP_NO_FAST_POISSON")) pfast.create(gh);
     CUDA_CHECK(cudaFuncSetAttribute(tendency_fast_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TF_SMEM_ELEMS * sizeof(FT))));
   }
   update_state(0);
@@ -114,6 +115,18 @@ void Model<FT>::fast_stage(int mode, FT dt, FT c1, FT c2, double stage_dt) {
 template <typename FT>
 void Model<FT>::fast_pressure(double stage_dt) {
   const GridDev<FT>& g = gh.g;
+  if (pfast.ok) {
+    // fused solve: source term with periodic wrap inside the first FFT pass, no halo fill, 5 launches
+    dim3 blk(64, 4, 1);
+    pfast.solve(F[0], F[1], F[2], pNHS, stage_dt, stream, lc);
+    mark(1);
+    pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], pNHS, stage_dt);
+    KLAUNCH(lc);
+    mark(2);
+    p_halo_stale = true;
+    CUDA_CHECK(cudaGetLastError());
+    return;
+  }
   FastHaloJob<FT> H; H.g = g; H.nf = 3; for (int a = 0; a < 3; ++a) H.p[a] = F[a];
   dim3 hg(1, g.N[1] + 2 * g.H[1], g.N[2] + 2 * g.H[2]);
   periodic_halo_all_kernel<FT><<<hg, 128, 0, stream>>>(H);

@@ -3,6 +3,7 @@
 #include "kernels_basic.cuh"
 #include "fft_generic.cuh"
 #include "tendency_fast.cuh"
+#include "poisson_fast.cuh"
 #include "grid_host.h"
 #include <memory>
 #include <cstring>
@@ -69,6 +70,65 @@ struct PoissonGeneric {
   long long count() const { return (long long)N[0] * N[1] * N[2]; }
 };
 
+// ---- fused FFT solve for (Periodic, Periodic, Periodic), power-of-two sizes (poisson_fast.cuh) -------------------
+template <typename FT>
+struct PoissonFast {
+  typedef typename cx_of<FT>::type CT;
+  bool ok = false;
+  PFJob<FT, CT> J;
+  DevBuf<CT> S, twx, twy, twz;
+  DevBuf<double> lx, ly, lz;
+  size_t smem_x = 0, smem_y = 0, smem_z = 0;
+  static bool supported(const GridHost<FT>& gh) {
+    if (gh.z_stretched) return false;
+    for (int e = 0; e < 3; ++e) {
+      int N = gh.g.N[e];
+      if (gh.g.topo[e] != NH_PERIODIC || N < 16 || N > 1024 || (N & (N - 1))) return false;
+      if ((size_t)PF_L * ff_line_pitch(N) * sizeof(CT) > 200 * 1024) return false;
+    }
+    return true;
+  }
+  void create(const GridHost<FT>& gh) {
+    const GridDev<FT>& g = gh.g;
+    J.g = g; J.Nx = g.N[0]; J.Ny = g.N[1]; J.Nz = g.N[2]; J.Mx = J.Nx / 2 + 2;
+    J.px = ff_make_plan(J.Nx); J.py = ff_make_plan(J.Ny); J.pz = ff_make_plan(J.Nz);
+    S.alloc((size_t)J.Mx * J.Ny * J.Nz);
+    DevBuf<CT>* tws[3] = {&twx, &twy, &twz};
+    DevBuf<double>* ls[3] = {&lx, &ly, &lz};
+    for (int e = 0; e < 3; ++e) {
+      int N = g.N[e];
+      std::vector<double> a, b;
+      nhhost::twiddles(N, a, b);
+      std::vector<CT> t(N);
+      for (int q = 0; q < N; ++q) { t[q].x = (FT)a[2 * q]; t[q].y = (FT)a[2 * q + 1]; }
+      tws[e]->upload(t);
+      double h = (double)(FT)(gh.L[e] / (FT)N);
+      ls[e]->upload(nhhost::poisson_eigenvalues(N, h, NH_PERIODIC));
+    }
+    J.twx = twx.p; J.twy = twy.p; J.twz = twz.p; J.lx = lx.p; J.ly = ly.p; J.lz = lz.p; J.S = S.p;
+    smem_x = (size_t)PF_L * ff_line_pitch(J.Nx) * sizeof(CT);
+    smem_y = (size_t)PF_L * ff_line_pitch(J.Ny) * sizeof(CT);
+    smem_z = (size_t)PF_L * ff_line_pitch(J.Nz) * sizeof(CT);
+    CUDA_CHECK(cudaFuncSetAttribute(pf_x_forward_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_x));
+    CUDA_CHECK(cudaFuncSetAttribute(pf_x_inverse_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_x));
+    CUDA_CHECK(cudaFuncSetAttribute(pf_y_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_y));
+    CUDA_CHECK(cudaFuncSetAttribute(pf_z_solve_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_z));
+    ok = true;
+  }
+  // rhs = div(u,v,w)/dt → p (interior of the halo'd field); 5 launches on `stream`
+  void solve(const FT* u, const FT* v, const FT* w, FT* p, double dt, cudaStream_t stream, LaunchCounter& lc) {
+    J.dt = dt; J.m = 0.0;
+    dim3 gx(ceil_div(J.Ny, 2 * PF_L), J.Nz), gy(ceil_div(J.Nx / 2 + 1, PF_L), J.Nz), gz(ceil_div(J.Nx / 2 + 1, PF_L), J.Ny);
+    pf_x_forward_kernel<FT, CT><<<gx, J.Nx, smem_x, stream>>>(J, u, v, w);
+    pf_y_kernel<FT, CT><<<gy, J.Ny, smem_y, stream>>>(J, 0);
+    pf_z_solve_kernel<FT, CT><<<gz, J.Nz, smem_z, stream>>>(J);
+    pf_y_kernel<FT, CT><<<gy, J.Ny, smem_y, stream>>>(J, 1);
+    pf_x_inverse_kernel<FT, CT><<<gx, J.Nx, smem_x, stream>>>(J, p);
+    lc.n += 5;
+    CUDA_CHECK(cudaGetLastError());
+  }
+};
+
 // ---- model -----------------------------------------------------------------------------------------------------
 struct nh_model {
   virtual ~nh_model() {}
@@ -132,6 +192,7 @@ struct Model : nh_model {
   SchemeDev adv[3];
   SchemeTables<FT> tab;
   PoissonGeneric<FT> solver;
+  PoissonFast<FT> pfast;
   DevBuf<FT> stage;        // staging for host <-> device field copies
   DevBuf<double> red;      // reduction scratch
   FT rk_g1, rk_g2, rk_g3, rk_z2, rk_z3, chi;

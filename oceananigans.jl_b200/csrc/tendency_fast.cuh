@@ -14,6 +14,9 @@
 #define TF_TY 8
 #define TF_TZ 8
 #define TF_THREADS 256
+#ifndef TF_MINBLOCKS
+#define TF_MINBLOCKS 4
+#endif
 #define TF_SMEM_ELEMS (TF_TZ * TF_TY * (TF_TX + 1) + TF_TZ * (TF_TY + 1) * TF_TX + (TF_TZ + 1) * TF_TY * TF_TX)
 
 template <typename FT>
@@ -48,7 +51,7 @@ __device__ __forceinline__ FT fast_flux(const SchemeTables<FT>& T, const FT* __r
 }
 
 template <typename FT>
-__global__ void __launch_bounds__(TF_THREADS, 2) tendency_fast_kernel(const __grid_constant__ FastTendJob<FT> J) {
+__global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel(const __grid_constant__ FastTendJob<FT> J) {
   extern __shared__ __align__(16) unsigned char tf_smem[];
   typedef FT (*FxT)[TF_TY][TF_TX + 1];
   typedef FT (*FyT)[TF_TY + 1][TF_TX];

@@ -307,3 +307,36 @@ def test_fused_fast_path_is_bit_identical_to_complete_path(oc, FT, timestepper, 
                    + [m.timestepper.Gn[n].interior() for n in "uvw"] + [m.timestepper.Gm[n].interior() for n in "uvw"])
     for a, b in zip(*out):
         np.testing.assert_array_equal(a, b)
+
+
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+@pytest.mark.parametrize("size", [(32, 32, 32), (64, 16, 32)])
+def test_fused_poisson_path_100_steps_vs_oracle(oc, FT, tol, size):
+    """Power-of-two triply periodic grids take the fused real-to-complex FFT solve (poisson_fast.cuh)."""
+    m1, m2 = make_pair(oc, FT, size, (P, P, P), extent=(2 * np.pi,) * 3)
+    ics = smooth_ics(m2, np.random.default_rng(1234))
+    dt = 0.2 * (2 * np.pi / max(size)) / 2.0
+    err = _run_steps(oc, m1, m2, ics, dt, 100)
+    check_parity(err, tol)
+    oc.fill_halo_regions(list(m1.velocities.values()))
+    assert m1.max_abs_divergence() < (1e-11 if FT == np.float64 else 5e-3)
+
+
+def test_fused_poisson_matches_complete_solver(oc, monkeypatch):
+    """Same model with and without the fused solve: fields agree to rounding after 5 steps (different FFT factorisation)."""
+    size = (64, 32, 16)
+    rng = np.random.default_rng(8)
+    ics = {n: rng.uniform(-1, 1, size) for n in "uvw"}
+    out = []
+    for no_fast in (False, True):
+        if no_fast:
+            monkeypatch.setenv("NHSTEP_NO_FAST_POISSON", "1")
+        else:
+            monkeypatch.delenv("NHSTEP_NO_FAST_POISSON", raising=False)
+        g = oc.RectilinearGrid(np.float64, size=size, extent=(1, 2, 3), topology=(P, P, P))
+        m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5))
+        oc.set_model(m, **ics)
+        oc.time_step(m, 2e-3, n_steps=5)
+        out.append([m.velocities[n].interior() for n in "uvw"] + [m.pressures.pNHS.parent()])
+    for a, b in zip(*out):
+        assert rel_l2(a, b) < 1e-13
