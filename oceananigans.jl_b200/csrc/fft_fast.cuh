@@ -121,3 +121,109 @@ __device__ __forceinline__ void ff_block_fft(CT* Xl, const FFPlan& P, int t, int
   }
 }
 #endif
+
+// ---- compile-time-size variants: every index, radix and stride is a constant, direction is a template flag ---------
+// Radix schedule of an N-point line (product = N); 8 points per thread per stage.
+template <int N> struct FFRad;
+template <> struct FFRad<16>   { static constexpr int n = 2, r0 = 8, r1 = 2, r2 = 1, r3 = 1; };
+template <> struct FFRad<32>   { static constexpr int n = 2, r0 = 8, r1 = 4, r2 = 1, r3 = 1; };
+template <> struct FFRad<64>   { static constexpr int n = 2, r0 = 8, r1 = 8, r2 = 1, r3 = 1; };
+template <> struct FFRad<128>  { static constexpr int n = 3, r0 = 8, r1 = 4, r2 = 4, r3 = 1; };
+template <> struct FFRad<256>  { static constexpr int n = 3, r0 = 8, r1 = 8, r2 = 4, r3 = 1; };
+template <> struct FFRad<512>  { static constexpr int n = 3, r0 = 8, r1 = 8, r2 = 8, r3 = 1; };
+template <> struct FFRad<1024> { static constexpr int n = 4, r0 = 8, r1 = 8, r2 = 4, r3 = 4; };
+
+// padding for the lines-fastest thread mapping (8 lanes = 8 lines at the same point): one extra slot per 8 points
+FF_HD int ff_phys8(int n) { return n + (n >> 3); }
+template <int N> struct FFPitch8 { static constexpr int value = ((N + N / 8 + 1) | 1); };
+
+// twiddle + butterflies on the 8 register-resident points of thread t: v[q*R + r] holds input j + r*N/R, j = t + q*N/8
+template <typename CT, int N, int R, int Ns, bool INV>
+FF_HD void ff_regs_stage(CT* v, int t, const CT* __restrict__ tw) {
+  constexpr int PER = 8 / R;
+#pragma unroll
+  for (int q = 0; q < PER; ++q) {
+    CT* w = v + q * R;
+    if (Ns > 1) {
+      const int j = t + q * (N / 8);
+      const int k = j & (Ns - 1);
+      const int tstep = k * (N / (Ns * R));
+#pragma unroll
+      for (int r = 1; r < R; ++r) {
+        CT c = tw[r * tstep];
+        if (INV) c.y = -c.y;
+        w[r] = ff_mul(w[r], c);
+      }
+    }
+    if (R == 8) ff_fft8(w, INV); else if (R == 4) ff_fft4(w, INV); else ff_fft2(w);
+  }
+}
+// scatter the stage's outputs (natural Stockham position j0 + r*Ns) into the padded shared line
+// PAD = 0: lines-fastest thread mapping (ff_phys8); PAD = 1: points-fastest mapping (ff_phys)
+template <int PAD> FF_HD int ff_pad(int n) { return PAD ? ff_phys(n) : ff_phys8(n); }
+
+template <typename CT, int N, int R, int Ns, int PAD = 0>
+FF_HD void ff_regs_scatter(CT* Xl, const CT* v, int t) {
+  constexpr int PER = 8 / R;
+#pragma unroll
+  for (int q = 0; q < PER; ++q) {
+    const int j = t + q * (N / 8);
+    const int k = j & (Ns - 1);
+    const int j0 = (j - k) * R + k;
+#pragma unroll
+    for (int r = 0; r < R; ++r) Xl[ff_pad<PAD>(j0 + r * Ns)] = v[q * R + r];
+  }
+}
+// gather the next stage's inputs j + r*N/R
+template <typename CT, int N, int R, int PAD = 0>
+FF_HD void ff_regs_gather(const CT* Xl, CT* v, int t) {
+  constexpr int PER = 8 / R;
+#pragma unroll
+  for (int q = 0; q < PER; ++q) {
+    const int j = t + q * (N / 8);
+#pragma unroll
+    for (int r = 0; r < R; ++r) v[q * R + r] = Xl[ff_pad<PAD>(j + r * (N / R))];
+  }
+}
+
+#ifdef __CUDACC__
+// Full N-point transform of the line owned by this thread group.  On entry v[m] = x[t + m*N/8] (m = 0..7); on exit
+// v[m] = X[t + m*N/8] as well (natural order), so a second transform can start from the registers directly.
+// Xl: this line's padded shared-memory scratch.  Every thread of the CTA must call (barriers inside).
+template <typename CT, int N, bool INV, int PAD = 0>
+__device__ __forceinline__ void ff_line_fft_regs(CT* v, CT* Xl, int t, const CT* __restrict__ tw) {
+  typedef FFRad<N> RD;
+  ff_regs_stage<CT, N, RD::r0, 1, INV>(v, t, tw);
+  ff_regs_scatter<CT, N, RD::r0, 1, PAD>(Xl, v, t);
+  __syncthreads();
+  ff_regs_gather<CT, N, RD::r1, PAD>(Xl, v, t);
+  ff_regs_stage<CT, N, RD::r1, RD::r0, INV>(v, t, tw);
+  if (RD::n >= 3) {
+    __syncthreads();
+    ff_regs_scatter<CT, N, RD::r1, RD::r0, PAD>(Xl, v, t);
+    __syncthreads();
+    ff_regs_gather<CT, N, RD::r2, PAD>(Xl, v, t);
+    ff_regs_stage<CT, N, RD::r2, RD::r0 * RD::r1, INV>(v, t, tw);
+  }
+  if (RD::n >= 4) {
+    __syncthreads();
+    ff_regs_scatter<CT, N, RD::r2, RD::r0 * RD::r1, PAD>(Xl, v, t);
+    __syncthreads();
+    ff_regs_gather<CT, N, RD::r3, PAD>(Xl, v, t);
+    ff_regs_stage<CT, N, RD::r3, RD::r0 * RD::r1 * RD::r2, INV>(v, t, tw);
+  }
+  // last stage: output (q, r) sits at t + q*N/8 + r*N/RL = t + (q + r*(8/RL))*N/8 → reorder registers to m = q + r*PER
+  constexpr int RL = RD::n == 2 ? RD::r1 : (RD::n == 3 ? RD::r2 : RD::r3);
+  constexpr int PER = 8 / RL;
+  if (PER > 1) {
+    CT w[8];
+#pragma unroll
+    for (int q = 0; q < PER; ++q)
+#pragma unroll
+      for (int r = 0; r < RL; ++r) w[q + r * PER] = v[q * RL + r];
+#pragma unroll
+    for (int m = 0; m < 8; ++m) v[m] = w[m];
+  }
+  __syncthreads();   // the scratch line may be reused by the caller
+}
+#endif

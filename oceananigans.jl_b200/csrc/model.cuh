@@ -109,21 +109,59 @@ struct PoissonFast {
     smem_x = (size_t)PF_L * ff_line_pitch(J.Nx) * sizeof(CT);
     smem_y = (size_t)PF_L * ff_line_pitch(J.Ny) * sizeof(CT);
     smem_z = (size_t)PF_L * ff_line_pitch(J.Nz) * sizeof(CT);
-    CUDA_CHECK(cudaFuncSetAttribute(pf_x_forward_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_x));
-    CUDA_CHECK(cudaFuncSetAttribute(pf_x_inverse_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_x));
-    CUDA_CHECK(cudaFuncSetAttribute(pf_y_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_y));
-    CUDA_CHECK(cudaFuncSetAttribute(pf_z_solve_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_z));
+    yz_dispatch(0, 0, 0);
     ok = true;
+  }
+  // size-templated kernels: what = 0 set attributes, 1 y-forward, 2 z-solve, 3 y-inverse, 4 x-forward, 5 x-inverse
+  const FT *xu = nullptr, *xv = nullptr, *xw = nullptr; FT* xp = nullptr;
+  template <int N> void yz_launch(int what, dim3 grid, cudaStream_t stream) {
+    const int smem = PF_L * FFPitch8<N>::value * (int)sizeof(CT);
+    const int smemx = PF_L * ((N + N / 8 + N / 64 + 1) | 1) * (int)sizeof(CT);
+    if (what == 0) {
+      if (J.Ny == N) {
+        CUDA_CHECK(cudaFuncSetAttribute(pf_y_kernel<FT, CT, N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CUDA_CHECK(cudaFuncSetAttribute(pf_y_kernel<FT, CT, N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      }
+      if (J.Nz == N) CUDA_CHECK(cudaFuncSetAttribute(pf_z_solve_kernel<FT, CT, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      if (J.Nx == N) {
+        CUDA_CHECK(cudaFuncSetAttribute(pf_x_forward_kernel<FT, CT, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smemx));
+        CUDA_CHECK(cudaFuncSetAttribute(pf_x_inverse_kernel<FT, CT, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smemx));
+      }
+    } else if (what == 4) pf_x_forward_kernel<FT, CT, N><<<grid, N, smemx, stream>>>(J, xu, xv, xw);
+    else if (what == 5) pf_x_inverse_kernel<FT, CT, N><<<grid, N, smemx, stream>>>(J, xp);
+    else if (what == 1) pf_y_kernel<FT, CT, N, false><<<grid, N, smem, stream>>>(J);
+    else if (what == 2) pf_z_solve_kernel<FT, CT, N><<<grid, N, smem, stream>>>(J);
+    else pf_y_kernel<FT, CT, N, true><<<grid, N, smem, stream>>>(J);
+  }
+  void yz_size(int N, int what, dim3 grid, cudaStream_t stream) {
+    switch (N) {
+      case 16: yz_launch<16>(what, grid, stream); break;
+      case 32: yz_launch<32>(what, grid, stream); break;
+      case 64: yz_launch<64>(what, grid, stream); break;
+      case 128: yz_launch<128>(what, grid, stream); break;
+      case 256: yz_launch<256>(what, grid, stream); break;
+      case 512: yz_launch<512>(what, grid, stream); break;
+      case 1024: yz_launch<1024>(what, grid, stream); break;
+      default: throw NhError("unsupported FFT size on the fused path");
+    }
+  }
+  void yz_dispatch(int what, dim3 grid, cudaStream_t stream) {
+    if (what == 0) {
+      yz_size(J.Ny, 0, grid, stream);
+      if (J.Nz != J.Ny) yz_size(J.Nz, 0, grid, stream);
+      if (J.Nx != J.Ny && J.Nx != J.Nz) yz_size(J.Nx, 0, grid, stream);
+    } else yz_size(what >= 4 ? J.Nx : (what == 2 ? J.Nz : J.Ny), what, grid, stream);
   }
   // rhs = div(u,v,w)/dt → p (interior of the halo'd field); 5 launches on `stream`
   void solve(const FT* u, const FT* v, const FT* w, FT* p, double dt, cudaStream_t stream, LaunchCounter& lc) {
     J.dt = dt; J.m = 0.0;
     dim3 gx(ceil_div(J.Ny, 2 * PF_L), J.Nz), gy(ceil_div(J.Nx / 2 + 1, PF_L), J.Nz), gz(ceil_div(J.Nx / 2 + 1, PF_L), J.Ny);
-    pf_x_forward_kernel<FT, CT><<<gx, J.Nx, smem_x, stream>>>(J, u, v, w);
-    pf_y_kernel<FT, CT><<<gy, J.Ny, smem_y, stream>>>(J, 0);
-    pf_z_solve_kernel<FT, CT><<<gz, J.Nz, smem_z, stream>>>(J);
-    pf_y_kernel<FT, CT><<<gy, J.Ny, smem_y, stream>>>(J, 1);
-    pf_x_inverse_kernel<FT, CT><<<gx, J.Nx, smem_x, stream>>>(J, p);
+    xu = u; xv = v; xw = w; xp = p;
+    yz_dispatch(4, gx, stream);
+    yz_dispatch(1, gy, stream);
+    yz_dispatch(2, gz, stream);
+    yz_dispatch(3, gy, stream);
+    yz_dispatch(5, gx, stream);
     lc.n += 5;
     CUDA_CHECK(cudaGetLastError());
   }

@@ -27,159 +27,177 @@ struct PFJob {
   double dt, m;
 };
 
-// K1 — grid (Ny/16, Nz), block Nx threads
-template <typename FT, typename CT>
-__global__ void pf_x_forward_kernel(const __grid_constant__ PFJob<FT, CT> J, const FT* __restrict__ u, const FT* __restrict__ v,
-                                    const FT* __restrict__ w) {
+// K1 — grid (Ny/16, Nz), block N = Nx threads.  Thread (l, t): pair-line l (rows j, j+1), points i-1 = t + m·N/8.
+// The divergence is evaluated straight into the FFT's input registers; after the transform one shared-memory exchange
+// gives every thread the mirrored coefficient Z[N-kx] it needs for the Hermitian split.
+template <typename FT, typename CT, int N>
+__global__ void __launch_bounds__(N) pf_x_forward_kernel(const __grid_constant__ PFJob<FT, CT> J, const FT* __restrict__ u,
+                                                         const FT* __restrict__ v, const FT* __restrict__ w) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
   const GridDev<FT>& g = J.g;
-  const int Nx = J.Nx, pitch = ff_line_pitch(Nx), tid = threadIdx.x, nth = blockDim.x;
-  const int k = blockIdx.y + 1, jbase = blockIdx.x * (2 * PF_L) + 1;
+  constexpr int tpl = N / 8, pitch = ((N + N / 8 + N / 64 + 1) | 1);
+  const int tid = threadIdx.x, l = tid / tpl, t = tid - l * tpl;
+  const int k = blockIdx.y + 1, j = blockIdx.x * (2 * PF_L) + 2 * l + 1;
   const int kp = k == J.Nz ? 1 : k + 1;
   const FT Ax = g.dy * g.dz, Ay = g.dx * g.dz, Az = g.dx * g.dy;
   const FT Vinv = FT(1) / ((g.dx * g.dy) * g.dz);
-  // ---- source term: rhs = divᶜᶜᶜ(U*) / Δt for 16 rows, packed (row 2p → real, row 2p+1 → imaginary)
-  for (int e = tid; e < 2 * PF_L * Nx; e += nth) {
-    int row = e / Nx, i = e - row * Nx + 1;
-    int j = jbase + row;
-    FT r = FT(0);
-    if (j <= J.Ny) {
-      int ip = i == Nx ? 1 : i + 1, jp = j == J.Ny ? 1 : j + 1;
-      FT tx = Ax * u[g.idx(ip, j, k)] - Ax * u[g.idx(i, j, k)];
-      FT ty = Ay * v[g.idx(i, jp, k)] - Ay * v[g.idx(i, j, k)];
-      FT tz = Az * w[g.idx(i, j, kp)] - Az * w[g.idx(i, j, k)];
-      FT total = tx + ty;
-      total = total + tz;
+  const bool rowa = j <= J.Ny, rowb = j + 1 <= J.Ny;
+  const int jb = j + 1, jc = (j + 2 > J.Ny) ? j + 2 - J.Ny : j + 2;
+  const long long ra = g.idx(1, j, k), rb = g.idx(1, jb > J.Ny ? 1 : jb, k), rc = g.idx(1, jc, k);
+  const long long raz = g.idx(1, j, kp), rbz = g.idx(1, jb > J.Ny ? 1 : jb, kp);
+  CT z[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int i0 = t + m * tpl;                 // zero-based i
+    const int ip = i0 + 1 == N ? 0 : i0 + 1;
+    FT da = FT(0), db = FT(0);
+    if (rowa) {
+      FT vb = v[rb + i0];
+      FT tx = Ax * u[ra + ip] - Ax * u[ra + i0];
+      FT ty = Ay * vb - Ay * v[ra + i0];
+      FT tz = Az * w[raz + i0] - Az * w[ra + i0];
+      FT total = tx + ty; total = total + tz;
       FT d = Vinv * total;
-      if (sizeof(FT) == 4) r = (FT)((double)d / J.dt); else r = (FT)(d / (FT)J.dt);
+      if (sizeof(FT) == 4) da = (FT)((double)d / J.dt); else da = (FT)(d / (FT)J.dt);
+      if (rowb) {
+        tx = Ax * u[rb + ip] - Ax * u[rb + i0];
+        ty = Ay * v[rc + i0] - Ay * vb;
+        tz = Az * w[rbz + i0] - Az * w[rb + i0];
+        total = tx + ty; total = total + tz;
+        d = Vinv * total;
+        if (sizeof(FT) == 4) db = (FT)((double)d / J.dt); else db = (FT)(d / (FT)J.dt);
+      }
     }
-    CT* line = X + (row >> 1) * pitch;
-    if (row & 1) line[ff_phys(i - 1)].y = r; else line[ff_phys(i - 1)].x = r;
+    z[m].x = da; z[m].y = db;
   }
+  CT* Xl = X + l * pitch;
+  ff_line_fft_regs<CT, N, false, 1>(z, Xl, t, J.twx);
+  // exchange: natural-order spectrum into shared memory, then A = (Z[k] + conj Z[N-k])/2, B = (Z[k] - conj Z[N-k])/(2i)
+#pragma unroll
+  for (int m = 0; m < 8; ++m) Xl[ff_phys(t + m * tpl)] = z[m];
   __syncthreads();
-  const int tpl = Nx / 8, l = tid / tpl, t = tid - l * tpl;
-  ff_block_fft<CT>(X + l * pitch, J.px, t, tpl, J.twx, false, l < PF_L);
-  // ---- Hermitian split and store: A = (Z[k] + conj Z[N-k])/2, B = (Z[k] - conj Z[N-k])/(2i)
-  const int half = Nx / 2;
-  for (int e = tid; e < 2 * PF_L * J.Mx; e += nth) {
-    int row = e / J.Mx, kx = e - row * J.Mx;
-    int j = jbase + row;
-    if (j > J.Ny) continue;
-    CT out; out.x = 0; out.y = 0;
-    if (kx <= half) {
-      const CT* line = X + (row >> 1) * pitch;
-      CT a = line[ff_phys(kx)], b = line[ff_phys((Nx - kx) & (Nx - 1))];
-      if (row & 1) { out.x = FT(0.5) * (a.y + b.y); out.y = FT(0.5) * (b.x - a.x); }
-      else         { out.x = FT(0.5) * (a.x + b.x); out.y = FT(0.5) * (a.y - b.y); }
-    }
-    J.S[kx + (long long)J.Mx * ((j - 1) + (long long)J.Ny * (k - 1))] = out;
+  if (!rowa) return;
+  CT* Sa = J.S + (long long)J.Mx * ((j - 1) + (long long)J.Ny * (k - 1));
+#pragma unroll
+  for (int m = 0; m < 5; ++m) {
+    const int kx = t + m * tpl;
+    if (m == 4 && t > 1) break;                 // kx = N/2 (t = 0) and the zero pad slot kx = N/2 + 1 (t = 1)
+    CT a, b, oa, ob;
+    if (m < 4) a = z[m]; else a = Xl[ff_phys(N / 2)];
+    b = Xl[ff_phys((N - kx) & (N - 1))];
+    oa.x = FT(0.5) * (a.x + b.x); oa.y = FT(0.5) * (a.y - b.y);
+    ob.x = FT(0.5) * (a.y + b.y); ob.y = FT(0.5) * (b.x - a.x);
+    if (m == 4 && t == 1) { oa.x = oa.y = ob.x = ob.y = 0; }
+    Sa[kx] = oa;
+    if (rowb) Sa[kx + J.Mx] = ob;
   }
 }
 
-// K2 / K4 — in-place c2c along y.  grid (ceil((Nx/2+1)/8), Nz), block Ny threads
-template <typename FT, typename CT>
-__global__ void pf_y_kernel(const __grid_constant__ PFJob<FT, CT> J, int inverse) {
+// K2 / K4 — in-place c2c along y on an 8-column tile.  grid (ceil((Nx/2+1)/8), Nz), block N = Ny threads.
+// Lanes run across the 8 adjacent kx columns (128-byte segments); each thread moves its 8 points global → registers,
+// the first butterfly stage runs before anything touches shared memory and the last one writes straight back.
+template <typename FT, typename CT, int N, bool INV>
+__global__ void __launch_bounds__(N) pf_y_kernel(const __grid_constant__ PFJob<FT, CT> J) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
-  const int Ny = J.Ny, pitch = ff_line_pitch(Ny), tid = threadIdx.x, nth = blockDim.x;
-  const int kx0 = blockIdx.x * PF_L, ncol = min(PF_L, J.Nx / 2 + 1 - kx0);
-  CT* base = J.S + kx0 + (long long)J.Mx * Ny * blockIdx.y;
-  for (int e = tid; e < PF_L * Ny; e += nth) {
-    int c = e & (PF_L - 1), n = e >> 3;
-    if (c < ncol) X[c * pitch + ff_phys(n)] = base[c + (long long)J.Mx * n];
-  }
-  __syncthreads();
-  const int tpl = Ny / 8, l = tid / tpl, t = tid - l * tpl;
-  ff_block_fft<CT>(X + l * pitch, J.py, t, tpl, J.twy, inverse != 0, l < ncol);
-  const FT scale = inverse ? FT(1) / FT(Ny) : FT(1);
-  for (int e = tid; e < PF_L * Ny; e += nth) {
-    int c = e & (PF_L - 1), n = e >> 3;
-    if (c < ncol) {
-      CT val = X[c * pitch + ff_phys(n)];
-      if (inverse) { val.x *= scale; val.y *= scale; }
-      base[c + (long long)J.Mx * n] = val;
+  constexpr int pitch = FFPitch8<N>::value;
+  const int tid = threadIdx.x, c = tid & (PF_L - 1), t = tid >> 3;
+  const int kx = blockIdx.x * PF_L + c;
+  const bool active = kx <= J.Nx / 2;
+  CT* base = J.S + kx + (long long)J.Mx * N * blockIdx.y + (long long)J.Mx * t;
+  const long long step = (long long)J.Mx * (N / 8);
+  CT v[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) { if (active) v[m] = base[m * step]; else { v[m].x = 0; v[m].y = 0; } }
+  ff_line_fft_regs<CT, N, INV>(v, X + c * pitch, t, J.twy);
+  if (active) {
+    const FT scale = FT(1) / FT(N);
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      if (INV) { v[m].x *= scale; v[m].y *= scale; }
+      base[m * step] = v[m];
     }
   }
 }
 
-// K3 — forward c2c along z, spectral division, inverse c2c along z.  grid (ceil((Nx/2+1)/8), Ny), block Nz threads
-template <typename FT, typename CT>
-__global__ void pf_z_solve_kernel(const __grid_constant__ PFJob<FT, CT> J) {
+// K3 — forward c2c along z, spectral division in registers, inverse c2c along z.  grid (ceil((Nx/2+1)/8), Ny), block Nz
+template <typename FT, typename CT, int N>
+__global__ void __launch_bounds__(N) pf_z_solve_kernel(const __grid_constant__ PFJob<FT, CT> J) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
-  const int Nz = J.Nz, pitch = ff_line_pitch(Nz), tid = threadIdx.x, nth = blockDim.x;
-  const int kx0 = blockIdx.x * PF_L, ncol = min(PF_L, J.Nx / 2 + 1 - kx0), ky = blockIdx.y;
+  constexpr int pitch = FFPitch8<N>::value;
+  const int tid = threadIdx.x, c = tid & (PF_L - 1), t = tid >> 3;
+  const int kx = blockIdx.x * PF_L + c, ky = blockIdx.y;
+  const bool active = kx <= J.Nx / 2;
   const long long sz = (long long)J.Mx * J.Ny;
-  CT* base = J.S + kx0 + (long long)J.Mx * ky;
-  for (int e = tid; e < PF_L * Nz; e += nth) {
-    int c = e & (PF_L - 1), n = e >> 3;
-    if (c < ncol) X[c * pitch + ff_phys(n)] = base[c + sz * n];
-  }
-  __syncthreads();
-  const int tpl = Nz / 8, l = tid / tpl, t = tid - l * tpl;
-  ff_block_fft<CT>(X + l * pitch, J.pz, t, tpl, J.twz, false, l < ncol);
+  CT* base = J.S + kx + (long long)J.Mx * ky + sz * t;
+  const long long step = sz * (N / 8);
+  CT v[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) { if (active) v[m] = base[m * step]; else { v[m].x = 0; v[m].y = 0; } }
+  ff_line_fft_regs<CT, N, false>(v, X + c * pitch, t, J.twz);
   // ϕ̂ = -b̂ / (λx + λy + λz - m)  (λ are Float64; fft_based_poisson_solver.jl:110-115)
-  const double lyv = J.ly[ky];
-  for (int e = tid; e < PF_L * Nz; e += nth) {
-    int c = e & (PF_L - 1), n = e >> 3;
-    if (c < ncol) {
-      double den = J.lx[kx0 + c] + lyv + J.lz[n] - J.m;
-      CT b = X[c * pitch + ff_phys(n)], r;
-      r.x = (FT)((double)(-b.x) / den);
-      r.y = (FT)((double)(-b.y) / den);
-      if (J.m == 0.0 && kx0 + c == 0 && ky == 0 && n == 0) { r.x = 0; r.y = 0; }
-      X[c * pitch + ff_phys(n)] = r;
-    }
+  const double lxy = active ? J.lx[kx] + J.ly[ky] : 1.0;
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int n = t + m * (N / 8);
+    double den = lxy + J.lz[n] - J.m;
+    CT r;
+    r.x = (FT)((double)(-v[m].x) / den);
+    r.y = (FT)((double)(-v[m].y) / den);
+    if (J.m == 0.0 && kx == 0 && ky == 0 && n == 0) { r.x = 0; r.y = 0; }
+    v[m] = r;
   }
-  __syncthreads();
-  ff_block_fft<CT>(X + l * pitch, J.pz, t, tpl, J.twz, true, l < ncol);
-  const FT scale = FT(1) / FT(Nz);
-  for (int e = tid; e < PF_L * Nz; e += nth) {
-    int c = e & (PF_L - 1), n = e >> 3;
-    if (c < ncol) {
-      CT val = X[c * pitch + ff_phys(n)];
-      val.x *= scale; val.y *= scale;
-      base[c + sz * n] = val;
-    }
+  ff_line_fft_regs<CT, N, true>(v, X + c * pitch, t, J.twz);
+  if (active) {
+    const FT scale = FT(1) / FT(N);
+#pragma unroll
+    for (int m = 0; m < 8; ++m) { v[m].x *= scale; v[m].y *= scale; base[m * step] = v[m]; }
   }
 }
 
-// K5 — grid (Ny/16, Nz), block Nx threads: two spectral rows → one complex line → inverse FFT → two real rows of p
-template <typename FT, typename CT>
-__global__ void pf_x_inverse_kernel(const __grid_constant__ PFJob<FT, CT> J, FT* __restrict__ p) {
+// K5 — grid (Ny/16, Nz), block N = Nx threads: two spectral rows → one complex line → inverse FFT → two real rows of p
+template <typename FT, typename CT, int N>
+__global__ void __launch_bounds__(N) pf_x_inverse_kernel(const __grid_constant__ PFJob<FT, CT> J, FT* __restrict__ p) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
   const GridDev<FT>& g = J.g;
-  const int Nx = J.Nx, pitch = ff_line_pitch(Nx), tid = threadIdx.x, nth = blockDim.x, half = Nx / 2;
-  const int k = blockIdx.y + 1, jbase = blockIdx.x * (2 * PF_L) + 1;
+  constexpr int tpl = N / 8, pitch = ((N + N / 8 + N / 64 + 1) | 1), half = N / 2;
+  const int tid = threadIdx.x, l = tid / tpl, t = tid - l * tpl;
+  const int k = blockIdx.y + 1, j = blockIdx.x * (2 * PF_L) + 2 * l + 1;
+  const bool rowa = j <= J.Ny, rowb = j + 1 <= J.Ny;
+  CT* Xl = X + l * pitch;
   // Z[kx] = A[kx] + i·B[kx] (kx ≤ N/2);  Z[N-kx] = conj(A[kx]) + i·conj(B[kx]) (0 < kx < N/2)
-  for (int e = tid; e < PF_L * (half + 1); e += nth) {
-    int pr = e / (half + 1), kx = e - pr * (half + 1);
-    int j = jbase + 2 * pr;
-    CT z, zc; z.x = z.y = zc.x = zc.y = 0;
-    if (j <= J.Ny) {
-      long long o = kx + (long long)J.Mx * ((j - 1) + (long long)J.Ny * (k - 1));
-      CT a = J.S[o], b; b.x = b.y = 0;
-      if (j + 1 <= J.Ny) b = J.S[o + J.Mx];
-      z.x = a.x - b.y; z.y = a.y + b.x;
-      zc.x = a.x + b.y; zc.y = b.x - a.y;
-    }
-    // the kx = 0 and kx = N/2 modes of a real row are real: Z = Re A + i·Re B (drops rounding-level imaginary parts)
-    if (kx == 0 || kx == half) { z.x = FT(0.5) * (z.x + zc.x); z.y = FT(0.5) * (z.y + zc.y); }
-    CT* line = X + pr * pitch;
-    line[ff_phys(kx)] = z;
-    if (kx > 0 && kx < half) line[ff_phys(Nx - kx)] = zc;
+  const CT* Sa = J.S + (long long)J.Mx * ((j - 1) + (long long)J.Ny * (k - 1));
+#pragma unroll
+  for (int m = 0; m < 5; ++m) {
+    const int kx = t + m * tpl;
+    if (m == 4 && t > 0) break;
+    CT a, b; a.x = a.y = b.x = b.y = 0;
+    if (rowa) a = Sa[kx];
+    if (rowb) b = Sa[kx + J.Mx];
+    CT zz, zc;
+    zz.x = a.x - b.y; zz.y = a.y + b.x;
+    zc.x = a.x + b.y; zc.y = b.x - a.y;
+    // the kx = 0 and kx = N/2 modes of a real row are real: Z = Re A + i·Re B
+    if (kx == 0 || kx == half) { zz.x = a.x; zz.y = b.x; }
+    Xl[ff_phys(kx)] = zz;
+    if (kx > 0 && kx < half) Xl[ff_phys(N - kx)] = zc;
   }
   __syncthreads();
-  const int tpl = Nx / 8, l = tid / tpl, t = tid - l * tpl;
-  ff_block_fft<CT>(X + l * pitch, J.px, t, tpl, J.twx, true, l < PF_L);
-  const FT scale = FT(1) / FT(Nx);
-  for (int e = tid; e < 2 * PF_L * Nx; e += nth) {
-    int row = e / Nx, i = e - row * Nx + 1;
-    int j = jbase + row;
-    if (j > J.Ny) continue;
-    CT val = X[(row >> 1) * pitch + ff_phys(i - 1)];
-    p[g.idx(i, j, k)] = ((row & 1) ? val.y : val.x) * scale;
+  CT z[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) z[m] = Xl[ff_phys(t + m * tpl)];
+  __syncthreads();
+  ff_line_fft_regs<CT, N, true, 1>(z, Xl, t, J.twx);
+  if (!rowa) return;
+  const FT scale = FT(1) / FT(N);
+  const long long ra = g.idx(1, j, k), rb = g.idx(1, rowb ? j + 1 : j, k);
+#pragma unroll
+  for (int m = 0; m < 8; ++m) {
+    const int i0 = t + m * tpl;
+    p[ra + i0] = z[m].x * scale;
+    if (rowb) p[rb + i0] = z[m].y * scale;
   }
 }
