@@ -74,14 +74,31 @@ class ClockSampler:
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "-lms", "50"], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
+
+    def lines(self):
+        try:
+            with open(self.f.name) as f:
+                return sum(1 for _ in f)
+        except OSError:
+            return 0
+
+    def wait_first_sample(self, timeout=5.0):
+        t0 = time.time()
+        while self.p is not None and self.lines() == 0 and time.time() - t0 < timeout:
+            time.sleep(0.05)
+
+    def mark(self):
+        """Call at the start of the timed region: only samples taken after this point are reported."""
+        self.first = self.lines()
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
         if self.p is None:
             return out
+        time.sleep(0.12)          # let the sample covering the end of the timed region land
         self.p.terminate()
         try:
             self.p.wait(timeout=5)
@@ -91,7 +108,10 @@ class ClockSampler:
         self.f.seek(0)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self.f.read().splitlines():
+        all_lines = self.f.read().splitlines()
+        first = getattr(self, "first", 0)
+        use = all_lines[first:] if len(all_lines) > first else all_lines
+        for line in use:
             parts = [s.strip() for s in line.split(",")]
             if len(parts) < 7:
                 continue
@@ -127,8 +147,8 @@ def run_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--size", type=int, default=256)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--ref-size", type=int, default=64)
@@ -164,10 +184,13 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local_rank) if rank == 0 else None
     for _ in range(args.warmup):
         oc.time_step(model, dt)
     barrier()
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.wait_first_sample()
+        sampler.mark()
     l0 = model.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()

@@ -17,6 +17,10 @@
 #ifndef TF_MINBLOCKS
 #define TF_MINBLOCKS 4
 #endif
+#ifndef TF_UNROLL
+#define TF_UNROLL 1
+#endif
+constexpr int tf_unroll = TF_UNROLL;
 #define TF_SMEM_ELEMS (TF_TZ * TF_TY * (TF_TX + 1) + TF_TZ * (TF_TY + 1) * TF_TX + (TF_TZ + 1) * TF_TY * TF_TX)
 
 template <typename FT>
@@ -43,10 +47,10 @@ __device__ __forceinline__ FT fast_flux(const SchemeTables<FT>& T, const FT* __r
   ut = ut + T.sym[2][1] * (Ab * ub[n + (0 + s0) * ss]);
   ut = ut + T.sym[2][0] * (Ab * ub[n + (1 + s0) * ss]);
   const bool left = ut > FT(0);
-  const FT* p = ua + n + s0 * sb;
-  FT q0, q1, q2, q3, q4;
-  if (left) { q0 = p[-3 * sb]; q1 = p[-2 * sb]; q2 = p[-sb]; q3 = p[0]; q4 = p[sb]; }
-  else      { q0 = p[2 * sb]; q1 = p[sb]; q2 = p[0]; q3 = p[-sb]; q4 = p[-2 * sb]; }
+  // upwind stencil without a branch: left bias reads offsets -3…1, right bias 2…-2 (reversed), from the same pointer
+  const long long ds = left ? sb : -sb;
+  const FT* p = ua + n + s0 * sb + (left ? -3 * sb : 2 * sb);
+  FT q0 = p[0], q1 = p[ds], q2 = p[2 * ds], q3 = p[3 * ds], q4 = p[4 * ds];
   return ut * weno5_from_q<FT>(T, q0, q1, q2, q3, q4);
 }
 
@@ -72,24 +76,25 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
     const FT* __restrict__ ua = J.U[a];
     const long long sa = st[a];
     // ---- x-direction fluxes F_{x,a}: a == 0 → centres i0-1 … i0+nx-1, else faces i0 … i0+nx
+#pragma unroll tf_unroll
     for (int t = tid; t < (TF_TX + 1) * TF_TY * TF_TZ; t += TF_THREADS) {
       int li = t % (TF_TX + 1), lj = (t / (TF_TX + 1)) % TF_TY, lk = t / ((TF_TX + 1) * TF_TY);
-      if (li > nx || lj >= ny || lk >= nz) continue;
-      long long n = g.idx(i0 + li - (a == 0 ? 1 : 0), j0 + lj, k0 + lk);
+      // partial tiles: clamp to the last valid point (the value is computed but never used)
+      long long n = g.idx(i0 + min(li, nx) - (a == 0 ? 1 : 0), j0 + min(lj, ny - 1), k0 + min(lk, nz - 1));
       Fx[lk][lj][li] = a == 0 ? fast_flux<FT, true>(J.tab, ua, J.U[0], n, sa, 1, Ax)
                               : fast_flux<FT, false>(J.tab, ua, J.U[0], n, sa, 1, Ax);
     }
+#pragma unroll tf_unroll
     for (int t = tid; t < TF_TX * (TF_TY + 1) * TF_TZ; t += TF_THREADS) {
       int li = t % TF_TX, lj = (t / TF_TX) % (TF_TY + 1), lk = t / (TF_TX * (TF_TY + 1));
-      if (li >= nx || lj > ny || lk >= nz) continue;
-      long long n = g.idx(i0 + li, j0 + lj - (a == 1 ? 1 : 0), k0 + lk);
+      long long n = g.idx(i0 + min(li, nx - 1), j0 + min(lj, ny) - (a == 1 ? 1 : 0), k0 + min(lk, nz - 1));
       Fy[lk][lj][li] = a == 1 ? fast_flux<FT, true>(J.tab, ua, J.U[1], n, sa, g.sy, Ay)
                               : fast_flux<FT, false>(J.tab, ua, J.U[1], n, sa, g.sy, Ay);
     }
+#pragma unroll tf_unroll
     for (int t = tid; t < TF_TX * TF_TY * (TF_TZ + 1); t += TF_THREADS) {
       int li = t % TF_TX, lj = (t / TF_TX) % TF_TY, lk = t / (TF_TX * TF_TY);
-      if (li >= nx || lj >= ny || lk > nz) continue;
-      long long n = g.idx(i0 + li, j0 + lj, k0 + lk - (a == 2 ? 1 : 0));
+      long long n = g.idx(i0 + min(li, nx - 1), j0 + min(lj, ny - 1), k0 + min(lk, nz) - (a == 2 ? 1 : 0));
       Fz[lk][lj][li] = a == 2 ? fast_flux<FT, true>(J.tab, ua, J.U[2], n, sa, g.sz, Az)
                               : fast_flux<FT, false>(J.tab, ua, J.U[2], n, sa, g.sz, Az);
     }
