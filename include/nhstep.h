@@ -137,6 +137,29 @@ int32_t nh_model_set_stream(nh_model* model, void* cuda_stream);
 /* number of kernels launched by this model since creation (bench.py's gpu_launches) */
 int32_t nh_launch_count(const nh_model* model, int64_t* count);
 
+/* ---- y-slab multi-GPU time step (one process per GPU) ---------------------------------------------------------
+ * Replaces, for the triply periodic regular-grid WENO5 configuration on a Distributed(Partition(1, R, 1)) architecture:
+ *   fill_halo_regions! of distributed fields   — src/DistributedComputations/halo_communication.jl:114-366
+ *   DistributedFFTBasedPoissonSolver solve!    — src/DistributedComputations/distributed_fft_based_poisson_solver.jl:141-178
+ *   transpose_z_to_y! / transpose_y_to_z!      — src/DistributedComputations/distributed_transpose.jl:25-191
+ * The library packs, transforms and unpacks on the model's stream; the messages themselves (NCCL send/recv and
+ * all-to-all over NVLink, MPI in the reference) are issued by the host on the buffers of nh_dist_buffer().  Per stage:
+ *   nh_dist_tendency_substep → exchange(v, 1 row) → nh_dist_poisson(0) → all-to-all A→B → nh_dist_poisson(1)
+ *   → all-to-all B→A → nh_dist_poisson(2) → exchange(pNHS, 1 row) → nh_dist_pressure_correct → exchange(u,v,w, H rows)
+ * where exchange = nh_dist_halo(pack) → send_lo→previous rank's recv_hi, send_hi→next rank's recv_lo → nh_dist_halo(unpack).
+ * The spectral buffers hold R blocks of Cx·NyL·Nz complex values; block d of A goes to rank d (and back for B). */
+enum { NH_DIST_SEND_LO = 0, NH_DIST_SEND_HI = 1, NH_DIST_RECV_LO = 2, NH_DIST_RECV_HI = 3, NH_DIST_SPECTRAL_A = 4, NH_DIST_SPECTRAL_B = 5 };
+/* the model was created on this rank's LOCAL grid (Nx, Ny/R, Nz; y Periodic); y0, y1, Ny describe the global y extent */
+int32_t nh_dist_configure(nh_model* model, int32_t rank, int32_t nranks, double y0, double y1, int32_t Ny_global);
+int32_t nh_dist_buffer(nh_model* model, int32_t which, void** device_ptr, int64_t* bytes);
+/* field_mask as in nh_fill_halo_regions (u, v, w, pNHS; at most three); `elements` = values per side just packed/unpacked */
+int32_t nh_dist_halo(nh_model* model, uint32_t field_mask, int32_t width, int32_t unpack, int64_t* elements);
+/* stage 0…2 of RK3 (runge_kutta_3.jl:77-151) or 0 of AB2; compute_tendencies! fused with the substep; updates the clock */
+int32_t nh_dist_tendency_substep(nh_model* model, double dt, int32_t stage, int32_t euler, double* stage_dt);
+/* phase 0: div(U*)/Δt → FFT x → FFT z into A;  1: FFT y, ÷(λx+λy+λz), IFFT y in B;  2: IFFT z, IFFT x from A → pNHS */
+int32_t nh_dist_poisson(nh_model* model, int32_t phase, double stage_dt);
+int32_t nh_dist_pressure_correct(nh_model* model, double stage_dt);
+
 /* ---- standalone solvers ---------------------------------------------------------------------------------- */
 /* FFTBasedPoissonSolver(grid) — src/Solvers/fft_based_poisson_solver.jl:52-74;
  * FourierTridiagonalPoissonSolver(grid) — src/Solvers/fourier_tridiagonal_poisson_solver.jl:71-117 */

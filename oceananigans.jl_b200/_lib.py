@@ -47,7 +47,10 @@ SYMBOLS = [
     "nh_synchronize", "nh_field_device_ptr", "nh_model_set_stream", "nh_launch_count", "nh_poisson_create",
     "nh_poisson_destroy", "nh_poisson_solve", "nh_poisson_synchronize", "nh_poisson_launch_count",
     "nh_poisson_time_solves", "nh_tridiag_create", "nh_tridiag_solve", "nh_tridiag_destroy",
+    "nh_dist_configure", "nh_dist_buffer", "nh_dist_halo", "nh_dist_tendency_substep", "nh_dist_poisson",
+    "nh_dist_pressure_correct",
 ]
+DIST_SEND_LO, DIST_SEND_HI, DIST_RECV_LO, DIST_RECV_HI, DIST_SPECTRAL_A, DIST_SPECTRAL_B = range(6)
 
 _lib = None
 
@@ -95,6 +98,12 @@ def lib():
             "nh_field_device_ptr": [p, C.c_int32, C.POINTER(p), C.POINTER(C.c_int64), C.POINTER(C.c_int64)],
             "nh_model_set_stream": [p, p],
             "nh_launch_count": [p, C.POINTER(C.c_int64)],
+            "nh_dist_configure": [p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_int32],
+            "nh_dist_buffer": [p, C.c_int32, C.POINTER(p), C.POINTER(C.c_int64)],
+            "nh_dist_halo": [p, C.c_uint32, C.c_int32, C.c_int32, C.POINTER(C.c_int64)],
+            "nh_dist_tendency_substep": [p, C.c_double, C.c_int32, C.c_int32, C.POINTER(C.c_double)],
+            "nh_dist_poisson": [p, C.c_int32, C.c_double],
+            "nh_dist_pressure_correct": [p, C.c_double],
             "nh_poisson_create": [p, C.c_int32, C.POINTER(p)],
             "nh_poisson_destroy": [p],
             "nh_poisson_solve": [p, p, p, C.c_double, C.c_int32],

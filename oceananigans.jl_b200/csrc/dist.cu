@@ -1,0 +1,118 @@
+// dist.cu — Model<FT> pieces of the y-slab multi-GPU time step (one process per GPU).
+//   src/DistributedComputations/halo_communication.jl:114-366, distributed_fft_based_poisson_solver.jl:141-178,
+//   src/Models/NonhydrostaticModels/solve_for_pressure.jl:12-17, runge_kutta_3.jl:77-151
+// Each call enqueues kernels on the model's stream and returns; the host driver places the NCCL messages between them:
+//   tendency_substep → [v: 1 row] → poisson(0) → [all-to-all A→B] → poisson(1) → [all-to-all B→A] → poisson(2)
+//                    → [p: 1 row] → pressure_correct → [u,v,w: H rows]
+#include "model.cuh"
+
+template <typename FT>
+void Model<FT>::dist_configure(int rank, int nranks, double y0, double y1, int Ny) {
+  NH_REQUIRE(fast, "the distributed path needs the fused configuration (triply periodic, regular, WENO5, no tracers/forcing terms)");
+  NH_REQUIRE(!dist.on, "model is already configured for a distributed run");
+  FT dy;
+  dist.create(gh, rank, nranks, y0, y1, Ny, dy);
+  gh.g.dy = dy;                       // the global spacing, so every rank computes with the same metric bits
+  pfast.ok = false;                   // the single-GPU solve would wrap y locally
+}
+
+template <typename FT>
+void Model<FT>::dist_buffer(int which, void** ptr, int64_t* bytes) {
+  NH_REQUIRE(dist.on, "model is not configured for a distributed run");
+  switch (which) {
+    case NH_DIST_SEND_LO: *ptr = dist.send_lo.p; *bytes = (int64_t)(dist.halo_elems * sizeof(FT)); break;
+    case NH_DIST_SEND_HI: *ptr = dist.send_hi.p; *bytes = (int64_t)(dist.halo_elems * sizeof(FT)); break;
+    case NH_DIST_RECV_LO: *ptr = dist.recv_lo.p; *bytes = (int64_t)(dist.halo_elems * sizeof(FT)); break;
+    case NH_DIST_RECV_HI: *ptr = dist.recv_hi.p; *bytes = (int64_t)(dist.halo_elems * sizeof(FT)); break;
+    case NH_DIST_SPECTRAL_A: *ptr = dist.A.p; *bytes = (int64_t)(dist.spec_elems * sizeof(CT)); break;
+    case NH_DIST_SPECTRAL_B: *ptr = dist.B.p; *bytes = (int64_t)(dist.spec_elems * sizeof(CT)); break;
+    default: throw NhError("unknown distributed buffer");
+  }
+}
+
+// pack (unpack = 0): rows next to both y faces → send_lo / send_hi;  unpack = 1: recv_lo / recv_hi → y halo rows.
+// Returns the number of elements per side.
+template <typename FT>
+int64_t Model<FT>::dist_halo(uint32_t mask, int w, int unpack) {
+  NH_REQUIRE(dist.on, "model is not configured for a distributed run");
+  const GridDev<FT>& g = gh.g;
+  NH_REQUIRE(w >= 1 && w <= g.H[1], "halo width");
+  HaloPackJob<FT> J; J.g = g; J.w = w; J.nf = 0;
+  for (int f = 0; f < 3; ++f) if (mask & (1u << f)) J.f[J.nf++] = F[f];
+  if (mask & (1u << NH_FIELD_PNHS)) J.f[J.nf++] = pNHS;
+  NH_REQUIRE(J.nf >= 1 && J.nf <= 3, "between one and three of u, v, w, pNHS per exchange");
+  J.lo = unpack ? dist.recv_lo.p : dist.send_lo.p;
+  J.hi = unpack ? dist.recv_hi.p : dist.send_hi.p;
+  long long n = (long long)(g.N[0] + 2 * g.H[0]) * w * (g.N[2] + 2 * g.H[2]) * J.nf;
+  y_halo_pack_kernel<FT><<<(unsigned)ceil_div(n, 256), 256, 0, stream>>>(J, unpack);
+  lc.n++;
+  CUDA_CHECK(cudaGetLastError());
+  return n;
+}
+
+// Gⁿ = G(U) and U* = U + Δt(…) in one sweep (the velocities' halos must be current); returns the stage's Δt.
+template <typename FT>
+double Model<FT>::dist_tendency_substep(double dt, int stage, int euler) {
+  NH_REQUIRE(dist.on, "model is not configured for a distributed run");
+  int mode; FT c1, c2; double stage_dt;
+  if (desc.timestepper == NH_RK3) {
+    NH_REQUIRE(stage >= 0 && stage < 3, "RK3 stage");
+    if (stage == 0) { mode = 0; c1 = rk_g1; c2 = FT(0); stage_dt = (double)rk_g1 * dt; }
+    else if (stage == 1) { mode = 1; c1 = rk_g2; c2 = rk_z2; stage_dt = (double)(FT)(rk_g2 + rk_z2) * dt; }
+    else { mode = 1; c1 = rk_g3; c2 = rk_z3; stage_dt = (double)(FT)(rk_g3 + rk_z3) * dt; }
+  } else {
+    NH_REQUIRE(stage == 0, "AB2 has a single stage");
+    bool eul = euler || (dt != clock.last_dt);
+    mode = eul ? 3 : 2; c1 = eul ? FT(-0.5) : chi; c2 = FT(0); stage_dt = dt;
+  }
+  FastTendJob<FT> J;
+  J.g = gh.g; J.tab = tab; J.dt = (FT)dt; J.gamma = c1; J.zeta = c2; J.mode = mode;
+  for (int a = 0; a < 3; ++a) { J.U[a] = F[a]; J.Unew[a] = F2[a]; J.Gn[a] = Gn[a]; J.Gm[a] = Gm[a]; }
+  dim3 grd(ceil_div(gh.g.N[0], TF_TX), ceil_div(gh.g.N[1], TF_TY), ceil_div(gh.g.N[2], TF_TZ));
+  tendency_fast_kernel<FT><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
+  lc.n++;
+  CUDA_CHECK(cudaGetLastError());
+  for (int a = 0; a < 3; ++a) std::swap(F[a], F2[a]);
+  for (int f = 0; f < nf; ++f) std::swap(Gn[f], Gm[f]);
+  if (desc.timestepper == NH_RK3) {
+    if (stage == 0) dist.t_next = clock.time + dt;
+    if (stage < 2) { clock.time += stage_dt; clock.stage += 1; clock.last_stage_dt = stage_dt; }
+    else {
+      // runge_kutta_3.jl:128-136: the last stage's Δt is measured from tⁿ + Δt
+      double corrected = dist.t_next - clock.time;
+      clock.time += stage_dt; clock.iteration += 1; clock.stage = 1; clock.last_stage_dt = corrected; clock.last_dt = dt;
+    }
+  } else { clock.time += dt; clock.iteration += 1; clock.stage = 1; clock.last_dt = dt; clock.last_stage_dt = dt; }
+  gn_stale = true;
+  return stage_dt;
+}
+
+template <typename FT>
+void Model<FT>::dist_poisson(int phase, double stage_dt) {
+  NH_REQUIRE(dist.on, "model is not configured for a distributed run");
+  dist.J.g = gh.g;
+  if (phase == 0) dist.forward(F[0], F[1], F[2], stage_dt, stream, lc);
+  else if (phase == 1) dist.solve_y(stream, lc);
+  else if (phase == 2) dist.backward(pNHS, stream, lc);
+  else throw NhError("poisson phase must be 0 (forward), 1 (solve along y) or 2 (backward)");
+}
+
+template <typename FT>
+void Model<FT>::dist_pressure_correct(double stage_dt) {
+  NH_REQUIRE(dist.on, "model is not configured for a distributed run");
+  dim3 blk(64, 4, 1);
+  pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(gh.g, F[0], F[1], F[2], pNHS, stage_dt, 0);
+  lc.n++;
+  p_halo_stale = true;
+  CUDA_CHECK(cudaGetLastError());
+}
+
+#define NH_DIST_INSTANTIATE(FT)                                                          \
+  template void Model<FT>::dist_configure(int, int, double, double, int);                \
+  template void Model<FT>::dist_buffer(int, void**, int64_t*);                           \
+  template int64_t Model<FT>::dist_halo(uint32_t, int, int);                             \
+  template double Model<FT>::dist_tendency_substep(double, int, int);                    \
+  template void Model<FT>::dist_poisson(int, double);                                    \
+  template void Model<FT>::dist_pressure_correct(double);
+NH_DIST_INSTANTIATE(float)
+NH_DIST_INSTANTIATE(double)

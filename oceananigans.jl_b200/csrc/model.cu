@@ -120,7 +120,7 @@ void Model<FT>::fast_pressure(double stage_dt) {
     dim3 blk(64, 4, 1);
     pfast.solve(F[0], F[1], F[2], pNHS, stage_dt, stream, lc);
     mark(1);
-    pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], pNHS, stage_dt);
+    pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], pNHS, stage_dt, 1);
     KLAUNCH(lc);
     mark(2);
     p_halo_stale = true;
@@ -138,7 +138,7 @@ void Model<FT>::fast_pressure(double stage_dt) {
   copy_real_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(g, sol, pNHS);
   KLAUNCH(lc);
   mark(1);
-  pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], pNHS, stage_dt);
+  pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], pNHS, stage_dt, 1);
   KLAUNCH(lc);
   mark(2);
   p_halo_stale = true;
@@ -377,6 +377,7 @@ void Model<FT>::pressure_correct_velocities(double dt) {
 // store_tendencies.jl is replaced by a pointer swap (Gⁿ is fully rewritten by the next compute_tendencies!).
 template <typename FT>
 void Model<FT>::time_step(double dt, int euler) {
+  if (dist.on) throw NhError("a distributed model is stepped through nh_dist_* (see include/nhstep.h), not nh_time_step");
   if (fast) {
     // same sequence as below with compute_tendencies! + the next substep fused and the halo fills folded into the
     // pressure-correction kernel; Gⁿ of the final state is refreshed lazily (ensure_tendencies).

@@ -90,7 +90,7 @@ struct PoissonFast {
   }
   void create(const GridHost<FT>& gh) {
     const GridDev<FT>& g = gh.g;
-    J.g = g; J.Nx = g.N[0]; J.Ny = g.N[1]; J.Nz = g.N[2]; J.Mx = J.Nx / 2 + 2;
+    J.g = g; J.Nx = g.N[0]; J.Ny = g.N[1]; J.Nz = g.N[2]; J.Mx = J.Nx / 2 + 2; J.Cx = J.Mx; J.ywrap = 1;
     J.px = ff_make_plan(J.Nx); J.py = ff_make_plan(J.Ny); J.pz = ff_make_plan(J.Nz);
     S.alloc((size_t)J.Mx * J.Ny * J.Nz);
     DevBuf<CT>* tws[3] = {&twx, &twy, &twz};
@@ -167,6 +167,8 @@ struct PoissonFast {
   }
 };
 
+#include "dist_host.cuh"
+
 // ---- model -----------------------------------------------------------------------------------------------------
 struct nh_model {
   virtual ~nh_model() {}
@@ -193,6 +195,13 @@ struct nh_model {
   virtual double max_abs_divergence() = 0;
   virtual void field_device_ptr(int field, void** ptr, int64_t* off, int64_t strides[3]) = 0;
   virtual void set_stream(cudaStream_t s) { stream = s; }
+  // y-slab multi-GPU pieces (dist.cu); the messages between them are issued by the host driver
+  virtual void dist_configure(int rank, int nranks, double y0, double y1, int Ny) = 0;
+  virtual void dist_buffer(int which, void** ptr, int64_t* bytes) = 0;
+  virtual int64_t dist_halo(uint32_t mask, int w, int unpack) = 0;
+  virtual double dist_tendency_substep(double dt, int stage, int euler) = 0;
+  virtual void dist_poisson(int phase, double stage_dt) = 0;
+  virtual void dist_pressure_correct(double stage_dt) = 0;
   // phase timing (nh_time_step_profiled): CUDA events on the model's stream between the phases of one step
   bool profiling = false;
   std::vector<std::pair<int, cudaEvent_t>> marks;
@@ -268,6 +277,13 @@ struct Model : nh_model {
   void set_stream(cudaStream_t s) override { stream = s; solver.stream = s; }
   void substep_launch(int mode, FT dt, FT c1, FT c2);
   void update_hydrostatic_pressure();
+  DistState<FT> dist;
+  void dist_configure(int rank, int nranks, double y0, double y1, int Ny) override;
+  void dist_buffer(int which, void** ptr, int64_t* bytes) override;
+  int64_t dist_halo(uint32_t mask, int w, int unpack) override;
+  double dist_tendency_substep(double dt, int stage, int euler) override;
+  void dist_poisson(int phase, double stage_dt) override;
+  void dist_pressure_correct(double stage_dt) override;
 };
 
 struct nh_poisson {

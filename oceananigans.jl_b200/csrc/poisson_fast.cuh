@@ -19,7 +19,11 @@
 template <typename FT, typename CT>
 struct PFJob {
   GridDev<FT> g;
-  int Nx, Ny, Nz, Mx;            // Mx = Nx/2 + 2: pitch of the half spectrum (complex elements)
+  int Nx, Ny, Nz, Mx;            // Mx = Nx/2 + 2: pitch of the half spectrum (complex elements); Ny is the LOCAL extent
+  // blocked-kx layout shared with the multi-GPU transposes: element (kx, j, k) lives at
+  //   (kx % Cx) + Cx·(j + Ny·(k + Nz·(kx / Cx)));  one GPU: Cx = Mx (a single block)
+  int Cx;
+  int ywrap;                     // 1: y is locally periodic (index wrap); 0: y halos are filled by neighbour exchange
   FFPlan px, py, pz;
   const CT *twx, *twy, *twz;
   const double *lx, *ly, *lz;
@@ -43,9 +47,9 @@ __global__ void __launch_bounds__(N) pf_x_forward_kernel(const __grid_constant__
   const FT Ax = g.dy * g.dz, Ay = g.dx * g.dz, Az = g.dx * g.dy;
   const FT Vinv = FT(1) / ((g.dx * g.dy) * g.dz);
   const bool rowa = j <= J.Ny, rowb = j + 1 <= J.Ny;
-  const int jb = j + 1, jc = (j + 2 > J.Ny) ? j + 2 - J.Ny : j + 2;
-  const long long ra = g.idx(1, j, k), rb = g.idx(1, jb > J.Ny ? 1 : jb, k), rc = g.idx(1, jc, k);
-  const long long raz = g.idx(1, j, kp), rbz = g.idx(1, jb > J.Ny ? 1 : jb, kp);
+  const int jb = (J.ywrap && j + 1 > J.Ny) ? j + 1 - J.Ny : j + 1, jc = (J.ywrap && j + 2 > J.Ny) ? j + 2 - J.Ny : j + 2;
+  const long long ra = g.idx(1, j, k), rb = g.idx(1, jb, k), rc = g.idx(1, jc, k);
+  const long long raz = g.idx(1, j, kp), rbz = g.idx(1, jb, kp);
   CT z[8];
 #pragma unroll
   for (int m = 0; m < 8; ++m) {
@@ -78,7 +82,8 @@ __global__ void __launch_bounds__(N) pf_x_forward_kernel(const __grid_constant__
   for (int m = 0; m < 8; ++m) Xl[ff_phys(t + m * tpl)] = z[m];
   __syncthreads();
   if (!rowa) return;
-  CT* Sa = J.S + (long long)J.Mx * ((j - 1) + (long long)J.Ny * (k - 1));
+  CT* Sa = J.S + (long long)J.Cx * ((j - 1) + (long long)J.Ny * (k - 1));
+  const long long blk = (long long)J.Cx * J.Ny * J.Nz;
 #pragma unroll
   for (int m = 0; m < 5; ++m) {
     const int kx = t + m * tpl;
@@ -89,8 +94,10 @@ __global__ void __launch_bounds__(N) pf_x_forward_kernel(const __grid_constant__
     oa.x = FT(0.5) * (a.x + b.x); oa.y = FT(0.5) * (a.y - b.y);
     ob.x = FT(0.5) * (a.y + b.y); ob.y = FT(0.5) * (b.x - a.x);
     if (m == 4 && t == 1) { oa.x = oa.y = ob.x = ob.y = 0; }
-    Sa[kx] = oa;
-    if (rowb) Sa[kx + J.Mx] = ob;
+    if (m == 4 && t == 1) { if (J.Cx != J.Mx) break; }          // the pad slot exists only in the single-block layout
+    const long long o = (kx % J.Cx) + blk * (kx / J.Cx);
+    Sa[o] = oa;
+    if (rowb) Sa[o + J.Cx] = ob;
   }
 }
 
@@ -169,14 +176,16 @@ __global__ void __launch_bounds__(N) pf_x_inverse_kernel(const __grid_constant__
   const bool rowa = j <= J.Ny, rowb = j + 1 <= J.Ny;
   CT* Xl = X + l * pitch;
   // Z[kx] = A[kx] + i·B[kx] (kx ≤ N/2);  Z[N-kx] = conj(A[kx]) + i·conj(B[kx]) (0 < kx < N/2)
-  const CT* Sa = J.S + (long long)J.Mx * ((j - 1) + (long long)J.Ny * (k - 1));
+  const CT* Sa = J.S + (long long)J.Cx * ((j - 1) + (long long)J.Ny * (k - 1));
+  const long long blk = (long long)J.Cx * J.Ny * J.Nz;
 #pragma unroll
   for (int m = 0; m < 5; ++m) {
     const int kx = t + m * tpl;
     if (m == 4 && t > 0) break;
     CT a, b; a.x = a.y = b.x = b.y = 0;
-    if (rowa) a = Sa[kx];
-    if (rowb) b = Sa[kx + J.Mx];
+    const long long o = (kx % J.Cx) + blk * (kx / J.Cx);
+    if (rowa) a = Sa[o];
+    if (rowb) b = Sa[o + J.Cx];
     CT zz, zc;
     zz.x = a.x - b.y; zz.y = a.y + b.x;
     zc.x = a.x + b.y; zc.y = b.x - a.y;

@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(256) periodic_halo_all_kernel(const __grid_con
 // _pressure_correct_velocities! — src/Models/NonhydrostaticModels/pressure_correction.jl:31-37
 template <typename FT>
 __global__ void __launch_bounds__(256) pressure_correct_halo_kernel(GridDev<FT> g, FT* __restrict__ u, FT* __restrict__ v,
-                                                                    FT* __restrict__ w, const FT* __restrict__ p, double dt) {
+                                                                    FT* __restrict__ w, const FT* __restrict__ p, double dt, int ywrap) {
   int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
   int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
   int k = blockIdx.z + 1;
@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(256) pressure_correct_halo_kernel(GridDev<FT> 
   long long n = g.idx(i, j, k);
   FT p0 = p[n];
   FT pxm = p[g.idx(i == 1 ? g.N[0] : i - 1, j, k)];
-  FT pym = p[g.idx(i, j == 1 ? g.N[1] : j - 1, k)];
+  FT pym = p[g.idx(i, (ywrap && j == 1) ? g.N[1] : j - 1, k)];
   FT pzm = p[g.idx(i, j, k == 1 ? g.N[2] : k - 1)];
   FT gx = (p0 - pxm) / g.dx, gy = (p0 - pym) / g.dy, gz = (p0 - pzm) / g.dz;
   FT un, vn, wn;
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(256) pressure_correct_halo_kernel(GridDev<FT> 
   int xi[2], nxi = 1; xi[0] = i;
   if (i <= g.H[0]) xi[nxi++] = i + g.N[0]; else if (i > g.N[0] - g.H[0]) xi[nxi++] = i - g.N[0];
   int yj[2], nyj = 1; yj[0] = j;
-  if (j <= g.H[1]) yj[nyj++] = j + g.N[1]; else if (j > g.N[1] - g.H[1]) yj[nyj++] = j - g.N[1];
+  if (ywrap) { if (j <= g.H[1]) yj[nyj++] = j + g.N[1]; else if (j > g.N[1] - g.H[1]) yj[nyj++] = j - g.N[1]; }
   int zk[2], nzk = 1; zk[0] = k;
   if (k <= g.H[2]) zk[nzk++] = k + g.N[2]; else if (k > g.N[2] - g.H[2]) zk[nzk++] = k - g.N[2];
   for (int c = 0; c < nzk; ++c)

@@ -1,0 +1,230 @@
+"""Multi-GPU NonhydrostaticModel: one process per GPU, y-slab partition, NCCL over NVLink through ``torch.distributed``.
+
+Mirrors the reference's distributed architecture for the hot path:
+  Distributed(GPU(); partition = Partition(1, R, 1))    src/DistributedComputations/distributed_architectures.jl:12-118,182-285
+  fill_halo_regions! of distributed fields              src/DistributedComputations/halo_communication.jl:114-366
+  DistributedFFTBasedPoissonSolver + transposes         src/DistributedComputations/distributed_fft_based_poisson_solver.jl:141-178,
+                                                        src/DistributedComputations/distributed_transpose.jl:25-191
+The kernels (pack/unpack, FFT passes, fused tendencies, pressure correction) live in libnhstep.so (csrc/dist.cuh); this
+module only places the messages between them.  The index helpers below restate the buffer layouts of csrc/dist.cuh so
+that the host logic can be tested on CPU with the ``gloo`` backend (tests/test_distributed_cpu.py).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+from ._lib import lib, check
+
+
+# ---- partition arithmetic (pure host logic) ------------------------------------------------------------------------
+class Partition:
+    """Partition(x=1, y=R, z=1): only y-slabs are supported on the B200 path (§8e)."""
+
+    def __init__(self, x=1, y=1, z=1):
+        if x != 1 or z != 1:
+            raise NotImplementedError("the B200 path partitions in y only (slab decomposition)")
+        self.x, self.y, self.z = 1, int(y), 1
+
+
+def local_slab(Ny, R, rank):
+    """(first global row, zero-based; number of rows) owned by ``rank`` — equal slabs, as Partition(1, R, 1) with Ny % R == 0."""
+    if Ny % R:
+        raise ValueError(f"Ny = {Ny} is not divisible by the {R} ranks")
+    return rank * (Ny // R), Ny // R
+
+
+def neighbours(rank, R):
+    """(previous, next) rank along the periodic y direction (distributed_architectures.jl:182-285, RankConnectivity south/north)."""
+    return (rank - 1) % R, (rank + 1) % R
+
+
+def spectral_block_width(Nx, R):
+    """Cx: columns of the half spectrum (kx = 0…Nx/2) owned by one rank, rounded up to the kernels' 8-column tile."""
+    cols = Nx // 2 + 1
+    return ((cols + R - 1) // R + 7) // 8 * 8
+
+
+def blocked_index(kx, jl, kz, Cx, NyL, Nz):
+    """Offset of spectral element (kx, jl, kz) in the z-local buffer A: R blocks of Cx columns, block d goes to rank d."""
+    return (kx % Cx) + Cx * (jl + NyL * (kz + Nz * (kx // Cx)))
+
+
+def transposed_index(kxl, j, kz, Cx, NyL, Nz):
+    """Offset of (local column kxl, GLOBAL row j, kz) in the y-local buffer B after the all-to-all (block s = rows of rank s)."""
+    return kxl + Cx * ((j % NyL) + NyL * (kz + Nz * (j // NyL)))
+
+
+# ---- messages ------------------------------------------------------------------------------------------------------
+def exchange_y_halos(send_lo, send_hi, recv_lo, recv_hi, rank, R, group=None):
+    """send_lo → previous rank's recv_hi, send_hi → next rank's recv_lo (periodic).  1-D torch tensors of equal length."""
+    import torch.distributed as dist
+    if R == 1:
+        recv_hi.copy_(send_lo)
+        recv_lo.copy_(send_hi)
+        return
+    prev, nxt = neighbours(rank, R)
+    if dist.get_backend(group) == "gloo":
+        # gloo matches by (peer, tag)
+        reqs = [dist.isend(send_lo, prev, group=group, tag=0), dist.isend(send_hi, nxt, group=group, tag=1),
+                dist.irecv(recv_hi, nxt, group=group, tag=0), dist.irecv(recv_lo, prev, group=group, tag=1)]
+        for r in reqs:
+            r.wait()
+        return
+    # NCCL matches by order per peer: with R = 2 both messages go to the same peer, whose first send is its send_lo
+    ops = [dist.P2POp(dist.isend, send_lo, prev, group), dist.P2POp(dist.isend, send_hi, nxt, group),
+           dist.P2POp(dist.irecv, recv_hi, nxt, group), dist.P2POp(dist.irecv, recv_lo, prev, group)]
+    for r in dist.batch_isend_irecv(ops):
+        r.wait()            # stream-ordered for NCCL: the current stream waits, the host does not
+
+
+def transpose_blocks(dst, src, R, group=None):
+    """Block d of ``src`` → rank d, received as block (sender's rank) of ``dst``: transpose_z_to_y! / transpose_y_to_z!."""
+    import torch.distributed as dist
+    if R == 1:
+        dst.copy_(src)
+        return
+    dist.all_to_all_single(dst, src, group=group)
+
+
+class _DeviceMemory:
+    """A raw device allocation of the library, exposed to torch without a copy."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class Distributed:
+    """Distributed(partition=Partition(y=R)): rank and size come from the default ``torch.distributed`` group."""
+
+    def __init__(self, partition=None, group=None):
+        import torch.distributed as dist
+        self.group = group
+        if dist.is_available() and dist.is_initialized():
+            self.rank, self.size = dist.get_rank(group), dist.get_world_size(group)
+        else:
+            self.rank, self.size = 0, 1
+        self.partition = partition or Partition(y=self.size)
+        if self.partition.y != self.size:
+            raise ValueError(f"Partition(y={self.partition.y}) does not match the {self.size} ranks of the process group")
+
+
+class DistributedNonhydrostaticModel:
+    """NonhydrostaticModel on a (Periodic, Periodic, Periodic) RectilinearGrid split into y-slabs over the ranks of ``arch``.
+
+    ``size``, ``x``, ``y``, ``z`` describe the GLOBAL grid; each rank holds rows ``local_slab(Ny, R, rank)``.
+    """
+
+    def __init__(self, arch, FT=np.float64, size=None, x=None, y=None, z=None, halo=(3, 3, 3), advection=None,
+                 timestepper="RungeKutta3", device=0, **kw):
+        import torch
+        from . import RectilinearGrid, Periodic, WENO
+        from .model import NonhydrostaticModel
+        self.arch, self.rank, self.R = arch, arch.rank, arch.size
+        self.global_size = tuple(int(n) for n in size)
+        Nx, Ny, Nz = self.global_size
+        self.j0, self.NyL = local_slab(Ny, self.R, self.rank)
+        y0, y1 = float(y[0]), float(y[1])
+        ylo = y0 + (y1 - y0) * self.rank / self.R
+        yhi = y0 + (y1 - y0) * (self.rank + 1) / self.R
+        self.global_grid_spec = dict(FT=FT, size=self.global_size, x=x, y=y, z=z, halo=halo)
+        self.grid = RectilinearGrid(FT, size=(Nx, self.NyL, Nz), x=x, y=(ylo, yhi), z=z, halo=halo,
+                                    topology=(Periodic, Periodic, Periodic), device=device)
+        self.model = NonhydrostaticModel(self.grid, advection=advection or WENO(FT, 5), timestepper=timestepper, **kw)
+        self._h = self.model._h
+        check(lib().nh_dist_configure(self._h, self.rank, self.R, y0, y1, Ny))
+        self.device = torch.device("cuda", device)
+        self.FT = np.dtype(FT)
+        tdt = torch.float64 if self.FT == np.float64 else torch.float32
+        cdt = torch.complex128 if self.FT == np.float64 else torch.complex64
+        self._buf = {}
+        for which in range(6):
+            p, nb = C.c_void_p(), C.c_int64()
+            check(lib().nh_dist_buffer(self._h, which, C.byref(p), C.byref(nb)))
+            t = torch.as_tensor(_DeviceMemory(p.value, nb.value), device=self.device)
+            self._buf[which] = t.view(cdt if which >= L.DIST_SPECTRAL_A else tdt)
+        self.velocities, self.pressures = self.model.velocities, self.model.pressures
+        self.Cx = spectral_block_width(Nx, self.R)
+        self.halo = self.model.halo
+        self._uvw = (1 << L.FIELD_U) | (1 << L.FIELD_V) | (1 << L.FIELD_W)
+
+    # -- pieces ---------------------------------------------------------------------------------------------------
+    def exchange(self, mask, width):
+        """fill_halo_regions! in y for the fields of ``mask``: pack → NCCL send/recv → unpack."""
+        n = C.c_int64()
+        check(lib().nh_dist_halo(self._h, mask, width, 0, C.byref(n)))
+        b, n = self._buf, n.value
+        exchange_y_halos(b[L.DIST_SEND_LO][:n], b[L.DIST_SEND_HI][:n], b[L.DIST_RECV_LO][:n], b[L.DIST_RECV_HI][:n],
+                         self.rank, self.R, self.arch.group)
+        check(lib().nh_dist_halo(self._h, mask, width, 1, None))
+
+    def pressure_phase(self, stage_dt):
+        """calculate_pressure_correction! + pressure_correct_velocities! + fill_halo_regions!(velocities)."""
+        h, b = self._h, self._buf
+        self.exchange(1 << L.FIELD_V, 1)
+        check(lib().nh_dist_poisson(h, 0, stage_dt))
+        transpose_blocks(b[L.DIST_SPECTRAL_B], b[L.DIST_SPECTRAL_A], self.R, self.arch.group)
+        check(lib().nh_dist_poisson(h, 1, stage_dt))
+        transpose_blocks(b[L.DIST_SPECTRAL_A], b[L.DIST_SPECTRAL_B], self.R, self.arch.group)
+        check(lib().nh_dist_poisson(h, 2, stage_dt))
+        self.exchange(1 << L.FIELD_PNHS, 1)
+        check(lib().nh_dist_pressure_correct(h, stage_dt))
+        self.exchange(self._uvw, self.halo[1])
+
+    def time_step(self, dt, euler=False, n_steps=1):
+        """time_step!(model, Δt) — runge_kutta_3.jl:77-151 / quasi_adams_bashforth_2.jl:74-115 on the slab partition."""
+        stages = 3 if self.model.timestepper_name in ("RungeKutta3", "RK3") else 1
+        sdt = C.c_double()
+        for _ in range(n_steps):
+            for s in range(stages):
+                check(lib().nh_dist_tendency_substep(self._h, float(dt), s, int(euler), C.byref(sdt)))
+                self.pressure_phase(sdt.value)
+
+    # -- state ----------------------------------------------------------------------------------------------------
+    def set(self, enforce_incompressibility=True, **global_arrays):
+        """set!(model; u=…, v=…, w=…) from GLOBAL (Nx, Ny, Nz) arrays; every rank keeps its own rows."""
+        for name, a in global_arrays.items():
+            a = np.asarray(a)
+            if a.shape != self.global_size:
+                raise ValueError(f"{name} must have the global size {self.global_size}")
+            self.velocities[name].set(a[:, self.j0:self.j0 + self.NyL, :])
+        check(lib().nh_fill_halo_regions(self._h, self._uvw, 1))
+        self.exchange(self._uvw, self.halo[1])
+        if enforce_incompressibility:
+            self.pressure_phase(1.0)
+
+    def local_interior(self, name):
+        f = self.pressures[name] if name in self.pressures else self.velocities[name]
+        return f.interior()
+
+    def gather(self, name):
+        """Global (Nx, Ny, Nz) array of a field on every rank (diagnostics / tests only)."""
+        import torch
+        import torch.distributed as dist
+        loc = np.ascontiguousarray(self.local_interior(name).transpose(1, 0, 2))       # rows first
+        if self.R == 1:
+            return loc.transpose(1, 0, 2)
+        t = torch.from_numpy(loc).to(self.device)
+        out = [torch.empty_like(t) for _ in range(self.R)]
+        dist.all_gather(out, t, group=self.arch.group)
+        return torch.cat(out, dim=0).cpu().numpy().transpose(1, 0, 2)
+
+    def max_abs_divergence(self):
+        import torch
+        import torch.distributed as dist
+        v = self.model.max_abs_divergence()
+        if self.R == 1:
+            return v
+        t = torch.tensor([v], device=self.device, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.arch.group)
+        return float(t.item())
+
+    def synchronize(self):
+        self.model.synchronize()
+
+    def launch_count(self):
+        return self.model.launch_count()
+
+    @property
+    def clock(self):
+        return self.model.clock

@@ -1,0 +1,133 @@
+"""Multi-GPU (y-slab) time step against the single-GPU model and the oracle.
+
+R = 1 exercises every distributed kernel (blocked spectral layout, z/y passes, halo pack/unpack, ywrap = 0 paths) on one
+GPU with the messages degenerating to copies; R = 2, 4 need that many GPUs (``gpurun --gpus N``) and run one process per
+GPU over NCCL.  Tolerance: F64 relative L2 ≤ 1e-12 (the FFT passes run in a different order than on one GPU, so the
+results are not bit-identical), F32 ≤ 1e-5.
+"""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+pytestmark = pytest.mark.gpu
+
+
+def _ics(size, FT, seed=3):
+    rng = np.random.default_rng(seed)
+    Nx, Ny, Nz = size
+    x = (np.arange(Nx) + 0.5) / Nx
+    y = (np.arange(Ny) + 0.5) / Ny
+    z = (np.arange(Nz) + 0.5) / Nz
+    X, Y, Z = np.meshgrid(x, y, z, indexing="ij")
+    u = np.sin(2 * np.pi * X) * np.cos(2 * np.pi * Y) * np.cos(4 * np.pi * Z) + 0.1 * rng.standard_normal(size)
+    v = -np.cos(2 * np.pi * X) * np.sin(2 * np.pi * Y) * np.cos(2 * np.pi * Z) + 0.1 * rng.standard_normal(size)
+    w = 0.3 * np.sin(4 * np.pi * X) * np.sin(2 * np.pi * Y) + 0.1 * rng.standard_normal(size)
+    return {k: a.astype(FT) for k, a in (("u", u), ("v", v), ("w", w))}
+
+
+def _single_gpu(size, FT, timestepper, steps, dt):
+    import oceananigans_jl_b200 as oc
+    g = oc.RectilinearGrid(FT, size=size, x=(0, 1), y=(0, 2), z=(0, 1), halo=(3, 3, 3),
+                           topology=(oc.Periodic, oc.Periodic, oc.Periodic))
+    m = oc.NonhydrostaticModel(g, advection=oc.WENO(FT, 5), timestepper=timestepper)
+    oc.set_model(m, **_ics(size, FT))
+    oc.time_step(m, dt, n_steps=steps)
+    return {n: m.velocities[n].interior() for n in "uvw"} | {"pNHS": m.pressures.pNHS.interior(), "time": m.clock.time}
+
+
+def _distributed(rank, world, size, FT, timestepper, steps, dt, out):
+    import oceananigans_jl_b200 as oc
+    from oceananigans_jl_b200 import distributed as D
+    arch = D.Distributed(D.Partition(y=world))
+    m = D.DistributedNonhydrostaticModel(arch, FT, size=size, x=(0, 1), y=(0, 2), z=(0, 1), halo=(3, 3, 3),
+                                         advection=oc.WENO(FT, 5), timestepper=timestepper, device=rank)
+    m.set(**_ics(size, FT))
+    div0 = m.max_abs_divergence()
+    m.time_step(dt, n_steps=steps)
+    res = {n: m.gather(n) for n in ("u", "v", "w", "pNHS")}
+    res["div0"], res["div"] = div0, m.max_abs_divergence()
+    res["time"], res["iteration"] = m.clock.time, m.clock.iteration
+    if rank == 0:
+        out.update(res)
+    return res
+
+
+def _rel(a, b):
+    return float(np.linalg.norm((a.astype(np.float64) - b.astype(np.float64)).ravel()) / max(np.linalg.norm(b.astype(np.float64).ravel()), 1e-300))
+
+
+def _check(res, ref, FT, steps, dt):
+    tol = 1e-12 if FT == np.float64 else 1e-5
+    for n in ("u", "v", "w", "pNHS"):
+        assert _rel(res[n], ref[n]) <= tol, (n, _rel(res[n], ref[n]))
+    scale = 1e-13 if FT == np.float64 else 1e-4
+    assert res["div0"] < scale * 100 and res["div"] < scale * 100
+    assert res["iteration"] == steps and res["time"] == ref["time"]
+
+
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+@pytest.mark.parametrize("size", [(32, 32, 16), (16, 64, 32)])
+def test_one_rank_distributed_path_matches_single_gpu(FT, timestepper, size):
+    steps, dt = 10, 2e-3
+    ref = _single_gpu(size, FT, timestepper, steps, dt)
+    out = {}
+    _distributed(0, 1, size, FT, timestepper, steps, dt, out)
+    _check(out, ref, FT, steps, dt)
+
+
+def test_one_rank_distributed_path_matches_oracle():
+    import oracle as o
+    size, steps, dt, FT = (16, 32, 16), 10, 2e-3, np.float64
+    grid = o.RectilinearGrid(FT, size=size, x=(0, 1), y=(0, 2), z=(0, 1), halo=(3, 3, 3),
+                             topology=(o.Periodic, o.Periodic, o.Periodic))
+    m = o.NonhydrostaticModel(grid, advection=o.WENO(FT, 5), timestepper="RungeKutta3")
+    o.set_model(m, **_ics(size, FT))
+    for _ in range(steps):
+        o.time_step(m, dt)
+    ref = {n: m.velocities[n].interior for n in "uvw"} | {"pNHS": m.pNHS.interior}
+    out = {}
+    _distributed(0, 1, size, FT, "RungeKutta3", steps, dt, out)
+    for n in ("u", "v", "w", "pNHS"):
+        assert _rel(out[n], ref[n]) <= 1e-12, (n, _rel(out[n], ref[n]))
+
+
+def _worker(rank, world, port, size, FT, timestepper, steps, dt, path):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        out = {}
+        _distributed(rank, world, size, FT, timestepper, steps, dt, out)
+        if rank == 0:
+            np.savez(path, **out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("FT,timestepper,size", [(np.float64, "RungeKutta3", (32, 64, 16)),
+                                                 (np.float64, "QuasiAdamsBashforth2", (64, 32, 32)),
+                                                 (np.float32, "RungeKutta3", (32, 64, 32))])
+def test_multi_gpu_matches_single_gpu(world, FT, timestepper, size, tmp_path):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    steps, dt = 10, 2e-3
+    ref = _single_gpu(size, FT, timestepper, steps, dt)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    path = str(tmp_path / "dist.npz")
+    mp.spawn(_worker, args=(world, port, size, FT, timestepper, steps, dt, path), nprocs=world, join=True)
+    res = dict(np.load(path))
+    _check(res, ref, FT, steps, dt)
