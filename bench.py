@@ -34,19 +34,22 @@ def peaks():
         return 6650.0, "fallback"
 
 
-def smooth_ics(N, seed):
-    """Σ of random-phase low-wavenumber sinusoids + 1e-3 noise, built per axis to stay cheap."""
+def smooth_ics(N, seed, size=None, rows=None):
+    """Σ of random-phase low-wavenumber sinusoids + 1e-3 noise, built per axis to stay cheap.
+    ``size`` = global (Nx, Ny, Nz) (default N³); ``rows`` = (first row, count) restricts y to one rank's slab."""
     rng = np.random.default_rng(seed)
-    x = np.arange(N) / N
+    Nx, Ny, Nz = size or (N, N, N)
+    j0, nj = rows or (0, Ny)
+    x, y, z = np.arange(Nx) / Nx, (j0 + np.arange(nj)) / Ny, np.arange(Nz) / Nz
     out = {}
     for name in "uvw":
-        v = np.zeros((N, N, N))
+        v = np.zeros((Nx, nj, Nz))
         for _ in range(4):
             k = rng.integers(0, 4, 3)
             ph = rng.uniform(0, 2 * np.pi, 3)
-            v += (np.cos(2 * np.pi * k[0] * x + ph[0])[:, None, None] * np.cos(2 * np.pi * k[1] * x + ph[1])[None, :, None]
-                  * np.cos(2 * np.pi * k[2] * x + ph[2])[None, None, :])
-        v += 1e-3 * rng.uniform(-1, 1, (N, N, N))
+            v += (np.cos(2 * np.pi * k[0] * x + ph[0])[:, None, None] * np.cos(2 * np.pi * k[1] * y + ph[1])[None, :, None]
+                  * np.cos(2 * np.pi * k[2] * z + ph[2])[None, None, :])
+        v += 1e-3 * np.random.default_rng(seed + 1000 + j0).uniform(-1, 1, (Nx, nj, Nz))
         out[name] = v
     return out
 
@@ -171,13 +174,30 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     N = args.size
-    topo = (oc.Periodic,) * 3
-    grid = oc.RectilinearGrid(np.float64, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=topo, device=local_rank)
-    model = oc.NonhydrostaticModel(grid, advection=oc.WENO(order=5), timestepper="RungeKutta3")
-    ics = smooth_ics(N, 1234 + rank)
-    oc.set_model(model, **ics)
     dt = 0.2 * (2 * np.pi / N) / 2.0
-    cells = N ** 3
+    if world == 1:
+        gsize = (N, N, N)
+        grid = oc.RectilinearGrid(np.float64, size=gsize, extent=(2 * np.pi,) * 3, topology=(oc.Periodic,) * 3, device=local_rank)
+        model = oc.NonhydrostaticModel(grid, advection=oc.WENO(order=5), timestepper="RungeKutta3")
+        oc.set_model(model, **smooth_ics(N, 1234))
+        step = lambda n=1: oc.time_step(model, dt, n_steps=n)                              # noqa: E731
+        profiled = lambda: oc.time_step_profiled(model, dt)                                # noqa: E731
+    else:
+        # weak scaling: N³ cells per GPU, the global grid grows in x and y at constant spacing; y-slabs over the ranks
+        from oceananigans_jl_b200 import distributed as D
+        factors = {2: (1, 2), 4: (2, 2), 8: (2, 4), 16: (4, 4)}
+        if world not in factors:
+            raise SystemExit("--gpus must be 1, 2, 4, 8 or 16")
+        fx, fy = factors[world]
+        gsize = (N * fx, N * fy, N)
+        arch = D.Distributed(D.Partition(y=world))
+        model = D.DistributedNonhydrostaticModel(arch, np.float64, size=gsize, x=(0, 2 * np.pi * fx), y=(0, 2 * np.pi * fy),
+                                                 z=(-2 * np.pi, 0), advection=oc.WENO(order=5), timestepper="RungeKutta3",
+                                                 device=local_rank)
+        model.set_local(**smooth_ics(N, 1234, gsize, (model.j0, model.NyL)))
+        step = lambda n=1: model.time_step(dt, n_steps=n)                                  # noqa: E731
+        profiled = lambda: model.time_step_profiled(dt)                                    # noqa: E731
+    cells = gsize[0] * gsize[1] * gsize[2] // world                                        # per GPU
 
     def barrier():
         if world > 1:
@@ -186,7 +206,7 @@ def main():
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
     for _ in range(args.warmup):
-        oc.time_step(model, dt)
+        step()
     barrier()
     if sampler:
         sampler.wait_first_sample()
@@ -195,7 +215,7 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        oc.time_step(model, dt)
+        step()
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
@@ -215,8 +235,8 @@ def main():
     phases = {"tendencies_substep": 0.0, "pressure_solve": 0.0, "pressure_correct": 0.0, "other": 0.0}
     nprof = max(1, min(args.steps, 5))
     for _ in range(nprof):
-        for k, v in oc.time_step_profiled(model, dt).items():
-            phases[k] += v
+        for k, v in profiled().items():
+            phases[k] = phases.get(k, 0.0) + v
     for k in phases:
         phases[k] /= nprof            # ms per step (3 substeps)
     # algorithmic bytes per step and phase (w = 8, F = 3): tendencies+substep A = 9w + 2·12w,
@@ -239,19 +259,28 @@ def main():
                 "phase_ms_per_step": phases}
 
     # ---- e2e: HOST buffers through the C ABI; H2D of u,v,w and D2H of u,v,w,p inside the timed region ----
-    host_in = {n: torch.from_numpy(np.asfortranarray(model.velocities[n].interior())).pin_memory() for n in "uvw"}
-    host_np = {n: host_in[n].numpy() for n in "uvw"}
-    e2e_steps = max(1, min(args.steps, 5))
+    from oceananigans_jl_b200.model import pinned_empty
+    shape = model.velocities["u"].size
+    host_np = {n: pinned_empty(shape) for n in "uvw"}            # the step's inputs, page-locked
+    host_out = {n: pinned_empty(shape) for n in ("u", "v", "w", "p")}
+    for n in "uvw":
+        model.velocities[n].interior(out=host_np[n])
+    e2e_steps = max(1, min(args.steps, 10))
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
+        if world == 1:
+            for n in "uvw":
+                model.velocities[n].set(host_np[n])
+            oc.fill_halo_regions(model.prognostic_fields())
+        else:
+            model.set_local(enforce_incompressibility=False, **host_np)
+        step()
         for n in "uvw":
-            model.velocities[n].set(host_np[n])
-        oc.fill_halo_regions(model.prognostic_fields())
-        oc.time_step(model, dt)
-        outs = [model.velocities[n].interior() for n in "uvw"] + [model.pressures.pNHS.interior()]
-        for n, a in zip("uvw", outs):
-            host_np[n][...] = a
+            model.velocities[n].interior(out=host_out[n])
+        model.pressures.pNHS.interior(out=host_out["p"])
+        for n in "uvw":                                          # next step's inputs = this step's result (no copy)
+            host_np[n], host_out[n] = host_out[n], host_np[n]
     barrier()
     e2e_t = time.perf_counter() - t0
     if world > 1:
@@ -271,9 +300,10 @@ def main():
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": f"3D triply-periodic NonhydrostaticModel {N}^3 Float64 WENO5 RK3 FFTBasedPoissonSolver"
-                           + (" per GPU" if world > 1 else ""),
+                           + (f" per GPU (global {gsize[0]}x{gsize[1]}x{gsize[2]})" if world > 1 else ""),
                            "l2_policy": "working set (>= 10 fields x %.0f MB) exceeds the 126 MB L2" % (cells * FT_B / 1e6),
-                           "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (no exchange)"},
+                           "parallelism": "single GPU" if world == 1 else
+                           f"y-slabs over {world} GPUs: NCCL halo exchange + 2 all-to-all transposes per pressure solve"},
                 "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:

@@ -180,14 +180,64 @@ class DistributedNonhydrostaticModel:
                 check(lib().nh_dist_tendency_substep(self._h, float(dt), s, int(euler), C.byref(sdt)))
                 self.pressure_phase(sdt.value)
 
+    def time_step_profiled(self, dt, euler=False):
+        """One time_step! with CUDA events between its pieces (ms per step): the three kernel phases of the single-GPU
+        profile plus the two kinds of messages (each including its pack/unpack kernels and the NCCL call)."""
+        import torch
+        h, b, g = self._h, self._buf, self.arch.group
+        ev, keys = [torch.cuda.Event(enable_timing=True)], []
+
+        def mark(key):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            ev.append(e)
+            keys.append(key)
+
+        stages = 3 if self.model.timestepper_name in ("RungeKutta3", "RK3") else 1
+        sdt = C.c_double()
+        ev[0].record()
+        for s in range(stages):
+            check(lib().nh_dist_tendency_substep(h, float(dt), s, int(euler), C.byref(sdt)))
+            mark("tendencies_substep")
+            self.exchange(1 << L.FIELD_V, 1)
+            mark("halo_exchange")
+            check(lib().nh_dist_poisson(h, 0, sdt.value))
+            mark("pressure_solve")
+            transpose_blocks(b[L.DIST_SPECTRAL_B], b[L.DIST_SPECTRAL_A], self.R, g)
+            mark("transpose")
+            check(lib().nh_dist_poisson(h, 1, sdt.value))
+            mark("pressure_solve")
+            transpose_blocks(b[L.DIST_SPECTRAL_A], b[L.DIST_SPECTRAL_B], self.R, g)
+            mark("transpose")
+            check(lib().nh_dist_poisson(h, 2, sdt.value))
+            mark("pressure_solve")
+            self.exchange(1 << L.FIELD_PNHS, 1)
+            mark("halo_exchange")
+            check(lib().nh_dist_pressure_correct(h, sdt.value))
+            mark("pressure_correct")
+            self.exchange(self._uvw, self.halo[1])
+            mark("halo_exchange")
+        torch.cuda.synchronize()
+        out = {"tendencies_substep": 0.0, "pressure_solve": 0.0, "pressure_correct": 0.0, "halo_exchange": 0.0, "transpose": 0.0}
+        for q, key in enumerate(keys):
+            out[key] += ev[q].elapsed_time(ev[q + 1])
+        return out
+
     # -- state ----------------------------------------------------------------------------------------------------
     def set(self, enforce_incompressibility=True, **global_arrays):
         """set!(model; u=…, v=…, w=…) from GLOBAL (Nx, Ny, Nz) arrays; every rank keeps its own rows."""
+        rows = {}
         for name, a in global_arrays.items():
             a = np.asarray(a)
             if a.shape != self.global_size:
                 raise ValueError(f"{name} must have the global size {self.global_size}")
-            self.velocities[name].set(a[:, self.j0:self.j0 + self.NyL, :])
+            rows[name] = a[:, self.j0:self.j0 + self.NyL, :]
+        self.set_local(enforce_incompressibility, **rows)
+
+    def set_local(self, enforce_incompressibility=True, **local_arrays):
+        """As ``set`` with this rank's own (Nx, Ny/R, Nz) rows."""
+        for name, a in local_arrays.items():
+            self.velocities[name].set(a)
         check(lib().nh_fill_halo_regions(self._h, self._uvw, 1))
         self.exchange(self._uvw, self.halo[1])
         if enforce_incompressibility:

@@ -28,17 +28,21 @@ class Field:
     def size(self):
         return self._size(L.INTERIOR)
 
-    def _get(self, region):
+    def _get(self, region, out=None):
         shape = self._size(region)
-        out = np.empty(shape, dtype=self.model.grid.FT, order="F")
+        if out is None:
+            out = np.empty(shape, dtype=self.model.grid.FT, order="F")
+        elif out.shape != shape or out.dtype != self.model.grid.FT or not out.flags.f_contiguous:
+            raise ValueError(f"out must be a Fortran-ordered {shape} array of the grid's float type")
         check(lib().nh_get_field(self.model._h, self.id, region, _ptr(out), out.size, L.HOST))
         return out
 
-    def interior(self):
-        return self._get(L.INTERIOR)
+    def interior(self, out=None):
+        """interior(field) copied to the host; ``out`` (e.g. from ``pinned_empty``) avoids the allocation."""
+        return self._get(L.INTERIOR, out)
 
-    def parent(self):
-        return self._get(L.PARENT)
+    def parent(self, out=None):
+        return self._get(L.PARENT, out)
 
     def _put(self, values, region):
         shape = self._size(region)
@@ -57,6 +61,16 @@ class Field:
 
     def set_parent(self, values):
         self._put(values, L.PARENT)
+
+
+def pinned_empty(shape, FT=np.float64):
+    """Fortran-ordered host array in page-locked memory (full-rate PCIe copies through nh_set_field / nh_get_field)."""
+    import torch
+    t = torch.empty(tuple(reversed(shape)), dtype=torch.float64 if np.dtype(FT) == np.float64 else torch.float32,
+                    pin_memory=True)
+    a = t.numpy().T
+    assert a.flags.f_contiguous
+    return a
 
 
 class _Namespace(dict):

@@ -92,7 +92,7 @@ def test_one_rank_distributed_path_matches_oracle():
     o.set_model(m, **_ics(size, FT))
     for _ in range(steps):
         o.time_step(m, dt)
-    ref = {n: m.velocities[n].interior for n in "uvw"} | {"pNHS": m.pNHS.interior}
+    ref = {n: m.velocities[a].interior for a, n in enumerate("uvw")} | {"pNHS": m.pNHS.interior}
     out = {}
     _distributed(0, 1, size, FT, "RungeKutta3", steps, dt, out)
     for n in ("u", "v", "w", "pNHS"):
