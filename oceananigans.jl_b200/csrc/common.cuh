@@ -38,6 +38,10 @@ struct GridDev {
   __host__ __device__ __forceinline__ long long idx(int i, int j, int k) const {
     return (long long)(i - 1 + ox) + sy * (j - 1 + oy) + sz * (k - 1 + oz);
   }
+  // 32-bit variant for kernels that are only used while the parent volume is below 2^31 elements
+  __host__ __device__ __forceinline__ int idx32(int i, int j, int k) const {
+    return (i - 1 + ox) + px * ((j - 1 + oy) + py * (k - 1 + oz));
+  }
   __device__ __forceinline__ FT Dzc(int k) const { return dzc[k + zoff]; }
   __device__ __forceinline__ FT Dzf(int k) const { return dzf[k + zoff]; }
 };

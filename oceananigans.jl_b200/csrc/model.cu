@@ -75,6 +75,7 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   fast = ntr == 0 && !gh.z_stretched && d.buoyancy_kind == NH_BUOYANCY_NONE && !d.has_coriolis && !d.has_closure && !pHY;
   for (int e = 0; e < 3; ++e)
     fast = fast && gh.g.topo[e] == NH_PERIODIC && adv[e].kind == NH_ADV_WENO && adv[e].B == 3 && gh.g.N[e] >= 2 * gh.g.H[e] && gh.g.H[e] >= 3;
+  fast = fast && gh.volume() < (1ll << 31);        // the fused kernel uses 32-bit element offsets
   if (getenv("NHSTEP_NO_FAST")) fast = false;
   if (fast) {
     for (int a = 0; a < 3; ++a) F2[a] = alloc_field();

@@ -38,9 +38,9 @@ struct FastTendJob {
 // face flux F_{b,a} at flux-location index n (linear), strides sa (dim a) and sb (dim b)
 template <typename FT, bool SAME>
 __device__ __forceinline__ FT fast_flux(const SchemeTables<FT>& T, const FT* __restrict__ ua, const FT* __restrict__ ub,
-                                        long long n, long long sa, long long sb, FT Ab) {
+                                        int n, int sa, int sb, FT Ab) {
   // advecting velocity: Centered(4) interpolation of A_b·U_b along dim b onto a Centre (SAME) or along dim a onto a Face
-  const long long ss = SAME ? sb : sa;
+  const int ss = SAME ? sb : sa;
   const int s0 = SAME ? 1 : 0;
   FT ut = T.sym[2][3] * (Ab * ub[n + (-2 + s0) * ss]);
   ut = ut + T.sym[2][2] * (Ab * ub[n + (-1 + s0) * ss]);
@@ -48,7 +48,7 @@ __device__ __forceinline__ FT fast_flux(const SchemeTables<FT>& T, const FT* __r
   ut = ut + T.sym[2][0] * (Ab * ub[n + (1 + s0) * ss]);
   const bool left = ut > FT(0);
   // upwind stencil without a branch: left bias reads offsets -3…1, right bias 2…-2 (reversed), from the same pointer
-  const long long ds = left ? sb : -sb;
+  const int ds = left ? sb : -sb;
   const FT* p = ua + n + s0 * sb + (left ? -3 * sb : 2 * sb);
   FT q0 = p[0], q1 = p[ds], q2 = p[2 * ds], q3 = p[3 * ds], q4 = p[4 * ds];
   return ut * weno5_from_q<FT>(T, q0, q1, q2, q3, q4);
@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
   const GridDev<FT>& g = J.g;
   const int i0 = blockIdx.x * TF_TX + 1, j0 = blockIdx.y * TF_TY + 1, k0 = blockIdx.z * TF_TZ + 1;
   const int tid = threadIdx.x;
-  const long long st[3] = {1, g.sy, g.sz};
+  const int st[3] = {1, (int)g.sy, (int)g.sz};   // 32-bit element offsets: the parent volume is < 2^31 elements
   const FT Ax = g.dy * g.dz, Ay = g.dx * g.dz, Az = g.dx * g.dy;
   const FT Vinv = FT(1) / ((g.dx * g.dy) * g.dz);
   const int nx = min(TF_TX, g.N[0] - i0 + 1), ny = min(TF_TY, g.N[1] - j0 + 1), nz = min(TF_TZ, g.N[2] - k0 + 1);
@@ -74,29 +74,29 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
 #pragma unroll 1
   for (int a = 0; a < 3; ++a) {
     const FT* __restrict__ ua = J.U[a];
-    const long long sa = st[a];
+    const int sa = st[a];
     // ---- x-direction fluxes F_{x,a}: a == 0 → centres i0-1 … i0+nx-1, else faces i0 … i0+nx
 #pragma unroll tf_unroll
     for (int t = tid; t < (TF_TX + 1) * TF_TY * TF_TZ; t += TF_THREADS) {
       int li = t % (TF_TX + 1), lj = (t / (TF_TX + 1)) % TF_TY, lk = t / ((TF_TX + 1) * TF_TY);
       // partial tiles: clamp to the last valid point (the value is computed but never used)
-      long long n = g.idx(i0 + min(li, nx) - (a == 0 ? 1 : 0), j0 + min(lj, ny - 1), k0 + min(lk, nz - 1));
+      int n = g.idx32(i0 + min(li, nx) - (a == 0 ? 1 : 0), j0 + min(lj, ny - 1), k0 + min(lk, nz - 1));
       Fx[lk][lj][li] = a == 0 ? fast_flux<FT, true>(J.tab, ua, J.U[0], n, sa, 1, Ax)
                               : fast_flux<FT, false>(J.tab, ua, J.U[0], n, sa, 1, Ax);
     }
 #pragma unroll tf_unroll
     for (int t = tid; t < TF_TX * (TF_TY + 1) * TF_TZ; t += TF_THREADS) {
       int li = t % TF_TX, lj = (t / TF_TX) % (TF_TY + 1), lk = t / (TF_TX * (TF_TY + 1));
-      long long n = g.idx(i0 + min(li, nx - 1), j0 + min(lj, ny) - (a == 1 ? 1 : 0), k0 + min(lk, nz - 1));
-      Fy[lk][lj][li] = a == 1 ? fast_flux<FT, true>(J.tab, ua, J.U[1], n, sa, g.sy, Ay)
-                              : fast_flux<FT, false>(J.tab, ua, J.U[1], n, sa, g.sy, Ay);
+      int n = g.idx32(i0 + min(li, nx - 1), j0 + min(lj, ny) - (a == 1 ? 1 : 0), k0 + min(lk, nz - 1));
+      Fy[lk][lj][li] = a == 1 ? fast_flux<FT, true>(J.tab, ua, J.U[1], n, sa, st[1], Ay)
+                              : fast_flux<FT, false>(J.tab, ua, J.U[1], n, sa, st[1], Ay);
     }
 #pragma unroll tf_unroll
     for (int t = tid; t < TF_TX * TF_TY * (TF_TZ + 1); t += TF_THREADS) {
       int li = t % TF_TX, lj = (t / TF_TX) % TF_TY, lk = t / (TF_TX * TF_TY);
-      long long n = g.idx(i0 + min(li, nx - 1), j0 + min(lj, ny - 1), k0 + min(lk, nz) - (a == 2 ? 1 : 0));
-      Fz[lk][lj][li] = a == 2 ? fast_flux<FT, true>(J.tab, ua, J.U[2], n, sa, g.sz, Az)
-                              : fast_flux<FT, false>(J.tab, ua, J.U[2], n, sa, g.sz, Az);
+      int n = g.idx32(i0 + min(li, nx - 1), j0 + min(lj, ny - 1), k0 + min(lk, nz) - (a == 2 ? 1 : 0));
+      Fz[lk][lj][li] = a == 2 ? fast_flux<FT, true>(J.tab, ua, J.U[2], n, sa, st[2], Az)
+                              : fast_flux<FT, false>(J.tab, ua, J.U[2], n, sa, st[2], Az);
     }
     __syncthreads();
     // ---- divergence, tendency, substep
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
       total = total + (Fz[lk + 1][lj][li] - Fz[lk][lj][li]);
       FT G = -(Vinv * total);
       G = G + FT(0);
-      long long n = g.idx(i0 + li, j0 + lj, k0 + lk);
+      int n = g.idx32(i0 + li, j0 + lj, k0 + lk);
       J.Gn[a][n] = G;
       if (J.mode >= 0) {
         FT u = ua[n];
