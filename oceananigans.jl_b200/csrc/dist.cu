@@ -68,8 +68,7 @@ double Model<FT>::dist_tendency_substep(double dt, int stage, int euler) {
   FastTendJob<FT> J;
   J.g = gh.g; J.tab = tab; J.dt = (FT)dt; J.gamma = c1; J.zeta = c2; J.mode = mode;
   for (int a = 0; a < 3; ++a) { J.U[a] = F[a]; J.Unew[a] = F2[a]; J.Gn[a] = Gn[a]; J.Gm[a] = Gm[a]; }
-  dim3 grd(ceil_div(gh.g.N[0], TF_TX), ceil_div(gh.g.N[1], TF_TY), ceil_div(gh.g.N[2], TF_TZ));
-  tendency_fast_kernel<FT><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
+  launch_fused_tendency<FT>(J, stream);
   lc.n++;
   CUDA_CHECK(cudaGetLastError());
   for (int a = 0; a < 3; ++a) std::swap(F[a], F2[a]);

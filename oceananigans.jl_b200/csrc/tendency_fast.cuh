@@ -11,8 +11,12 @@
 #include "recon.cuh"
 
 #define TF_TX 32
+#ifndef TF_TY
 #define TF_TY 8
+#endif
+#ifndef TF_TZ
 #define TF_TZ 8
+#endif
 #define TF_THREADS 256
 #ifndef TF_MINBLOCKS
 #define TF_MINBLOCKS 4
@@ -120,6 +124,14 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
     }
     __syncthreads();
   }
+}
+
+// host launch of the fused tendency + substep sweep
+template <typename FT>
+inline void launch_fused_tendency(const FastTendJob<FT>& J, cudaStream_t stream) {
+  const GridDev<FT>& g = J.g;
+  dim3 grd(ceil_div(g.N[0], TF_TX), ceil_div(g.N[1], TF_TY), ceil_div(g.N[2], TF_TZ));
+  tendency_fast_kernel<FT><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
 }
 
 // Periodic halo fill of several fields in ONE launch: every halo cell reads its wrapped interior image directly
