@@ -34,6 +34,16 @@ def peaks():
         return 6650.0, "fallback"
 
 
+def measured_traffic(phase, N):
+    """DRAM bytes per launch of the phase's kernel(s) from the committed ncu capture, if it was taken at this size."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            t = json.load(f)
+        return t["dram_bytes_per_launch"][phase] if t["size"] == N else None
+    except Exception:
+        return None
+
+
 def smooth_ics(N, seed, size=None, rows=None):
     """Σ of random-phase low-wavenumber sinusoids + 1e-3 noise, built per axis to stay cheap.
     ``size`` = global (Nx, Ny, Nz) (default N³); ``rows`` = (first row, count) restricts y to one rank's slab."""
@@ -253,10 +263,18 @@ def main():
     roofline = {"bound": "hbm", "kernel": kernel_names[dom], "launches_per_step": 3,
                 "algorithmic_bytes_per_launch": alg[dom] / 3, "ms_per_launch": phases[dom] / 3,
                 "achieved": achieved, "peak": peak, "peak_source": peak_kind, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None,
+                "frac": achieved / peak, "traffic": measured_traffic(dom, N),
                 "whole_step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms_per_step * 1e-3) / 1e9,
                                "frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak},
                 "phase_ms_per_step": phases}
+    if dom == "tendencies_substep":
+        # the sweep is FP64-issue bound, not HBM bound: ≈ 1290 FP64 instructions per cell (ncu opcode mix,
+        # profiles/r1_tendency_sass_mix.md) against 64 FP64 instr/clk/SM × 148 SMs at the sampled SM clock
+        mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        fp64_peak = 64 * 148 * mhz * 1e6
+        fp64_rate = 1290.0 * cells / (phases[dom] / 3 * 1e-3)
+        roofline["fp64_pipe"] = {"instr_per_cell": 1290, "achieved_instr_per_s": fp64_rate, "peak_instr_per_s": fp64_peak,
+                                 "frac": fp64_rate / fp64_peak}
 
     # ---- e2e: HOST buffers through the C ABI; H2D of u,v,w and D2H of u,v,w,p inside the timed region ----
     from oceananigans_jl_b200.model import pinned_empty
