@@ -99,8 +99,7 @@ void Model<FT>::dist_poisson(int phase, double stage_dt) {
 template <typename FT>
 void Model<FT>::dist_pressure_correct(double stage_dt) {
   NH_REQUIRE(dist.on, "model is not configured for a distributed run");
-  dim3 blk(64, 4, 1);
-  pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(gh.g, F[0], F[1], F[2], pNHS, stage_dt, 0);
+  launch_pressure_correct_halo<FT>(gh.g, F[0], F[1], F[2], pNHS, stage_dt, 0, stream);
   lc.n++;
   p_halo_stale = true;
   CUDA_CHECK(cudaGetLastError());

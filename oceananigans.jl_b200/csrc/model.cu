@@ -120,7 +120,7 @@ void Model<FT>::fast_pressure(double stage_dt) {
     dim3 blk(64, 4, 1);
     pfast.solve(F[0], F[1], F[2], pNHS, stage_dt, stream, lc);
     mark(1);
-    pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], pNHS, stage_dt, 1);
+    launch_pressure_correct_halo<FT>(g, F[0], F[1], F[2], pNHS, stage_dt, 1, stream);
     KLAUNCH(lc);
     mark(2);
     p_halo_stale = true;
@@ -138,7 +138,7 @@ void Model<FT>::fast_pressure(double stage_dt) {
   copy_real_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(g, sol, pNHS);
   KLAUNCH(lc);
   mark(1);
-  pressure_correct_halo_kernel<FT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], pNHS, stage_dt, 1);
+  launch_pressure_correct_halo<FT>(g, F[0], F[1], F[2], pNHS, stage_dt, 1, stream);
   KLAUNCH(lc);
   mark(2);
   p_halo_stale = true;

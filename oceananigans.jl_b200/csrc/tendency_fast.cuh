@@ -172,36 +172,74 @@ __global__ void __launch_bounds__(256) periodic_halo_all_kernel(const __grid_con
 // Pressure correction over the interior with periodic index wrap on p (no p halo needed), fused with the periodic halo
 // fill of the corrected velocities: a corrected interior value is also stored to each of its periodic images.
 // _pressure_correct_velocities! — src/Models/NonhydrostaticModels/pressure_correction.jl:31-37
+// Each thread corrects two x-adjacent cells (16-byte loads/stores; i = 1 starts a 128-byte line, pitches are multiples of 16).
 template <typename FT>
 __global__ void __launch_bounds__(256) pressure_correct_halo_kernel(GridDev<FT> g, FT* __restrict__ u, FT* __restrict__ v,
                                                                     FT* __restrict__ w, const FT* __restrict__ p, double dt, int ywrap) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
-  int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
-  int k = blockIdx.z + 1;
+  typedef typename cx_of<FT>::type V2;
+  const int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x) + 1;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  const int k = blockIdx.z + 1;
   if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
-  long long n = g.idx(i, j, k);
-  FT p0 = p[n];
-  FT pxm = p[g.idx(i == 1 ? g.N[0] : i - 1, j, k)];
-  FT pym = p[g.idx(i, (ywrap && j == 1) ? g.N[1] : j - 1, k)];
-  FT pzm = p[g.idx(i, j, k == 1 ? g.N[2] : k - 1)];
-  FT gx = (p0 - pxm) / g.dx, gy = (p0 - pym) / g.dy, gz = (p0 - pzm) / g.dz;
-  FT un, vn, wn;
-  if (sizeof(FT) == 4) {
-    un = (FT)((double)u[n] - (double)gx * dt); vn = (FT)((double)v[n] - (double)gy * dt); wn = (FT)((double)w[n] - (double)gz * dt);
+  const bool two = i + 1 <= g.N[0];
+  const long long n = g.idx(i, j, k);
+  const long long nym = g.idx(i, (ywrap && j == 1) ? g.N[1] : j - 1, k), nzm = g.idx(i, j, k == 1 ? g.N[2] : k - 1);
+  FT p0[2], pym[2], pzm[2], uu[2], vv[2], ww[2];
+  if (two) {
+    V2 t;
+    t = *reinterpret_cast<const V2*>(p + n); p0[0] = t.x; p0[1] = t.y;
+    t = *reinterpret_cast<const V2*>(p + nym); pym[0] = t.x; pym[1] = t.y;
+    t = *reinterpret_cast<const V2*>(p + nzm); pzm[0] = t.x; pzm[1] = t.y;
+    t = *reinterpret_cast<const V2*>(u + n); uu[0] = t.x; uu[1] = t.y;
+    t = *reinterpret_cast<const V2*>(v + n); vv[0] = t.x; vv[1] = t.y;
+    t = *reinterpret_cast<const V2*>(w + n); ww[0] = t.x; ww[1] = t.y;
   } else {
-    un = u[n] - gx * (FT)dt; vn = v[n] - gy * (FT)dt; wn = w[n] - gz * (FT)dt;
+    p0[0] = p0[1] = p[n]; pym[0] = pym[1] = p[nym]; pzm[0] = pzm[1] = p[nzm];
+    uu[0] = uu[1] = u[n]; vv[0] = vv[1] = v[n]; ww[0] = ww[1] = w[n];
   }
-  // periodic images: index sets {i, i±N} ∩ parent range, likewise j, k
-  int xi[2], nxi = 1; xi[0] = i;
-  if (i <= g.H[0]) xi[nxi++] = i + g.N[0]; else if (i > g.N[0] - g.H[0]) xi[nxi++] = i - g.N[0];
+  const FT pxm0 = p[i == 1 ? g.idx(g.N[0], j, k) : n - 1];
+  FT un[2], vn[2], wn[2];
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    const FT pxm = c == 0 ? pxm0 : p0[0];
+    const FT gx = (p0[c] - pxm) / g.dx, gy = (p0[c] - pym[c]) / g.dy, gz = (p0[c] - pzm[c]) / g.dz;
+    if (sizeof(FT) == 4) {
+      un[c] = (FT)((double)uu[c] - (double)gx * dt); vn[c] = (FT)((double)vv[c] - (double)gy * dt); wn[c] = (FT)((double)ww[c] - (double)gz * dt);
+    } else {
+      un[c] = uu[c] - gx * (FT)dt; vn[c] = vv[c] - gy * (FT)dt; wn[c] = ww[c] - gz * (FT)dt;
+    }
+  }
+  if (two) {
+    V2 t;
+    t.x = un[0]; t.y = un[1]; *reinterpret_cast<V2*>(u + n) = t;
+    t.x = vn[0]; t.y = vn[1]; *reinterpret_cast<V2*>(v + n) = t;
+    t.x = wn[0]; t.y = wn[1]; *reinterpret_cast<V2*>(w + n) = t;
+  } else { u[n] = un[0]; v[n] = vn[0]; w[n] = wn[0]; }
+  // periodic images: index sets {i, i±N} ∩ parent range, likewise j, k; only cells within a halo width of a face have any
+  const bool xedge = i <= g.H[0] || i + 1 > g.N[0] - g.H[0];
+  const bool yedge = ywrap && (j <= g.H[1] || j > g.N[1] - g.H[1]);
+  const bool zedge = k <= g.H[2] || k > g.N[2] - g.H[2];
+  if (!(xedge || yedge || zedge)) return;
   int yj[2], nyj = 1; yj[0] = j;
   if (ywrap) { if (j <= g.H[1]) yj[nyj++] = j + g.N[1]; else if (j > g.N[1] - g.H[1]) yj[nyj++] = j - g.N[1]; }
   int zk[2], nzk = 1; zk[0] = k;
   if (k <= g.H[2]) zk[nzk++] = k + g.N[2]; else if (k > g.N[2] - g.H[2]) zk[nzk++] = k - g.N[2];
-  for (int c = 0; c < nzk; ++c)
-    for (int b = 0; b < nyj; ++b)
-      for (int a = 0; a < nxi; ++a) {
-        long long m = g.idx(xi[a], yj[b], zk[c]);
-        u[m] = un; v[m] = vn; w[m] = wn;
-      }
+  for (int c = 0; c < (two ? 2 : 1); ++c) {
+    const int ii = i + c;
+    int xi[2], nxi = 1; xi[0] = ii;
+    if (ii <= g.H[0]) xi[nxi++] = ii + g.N[0]; else if (ii > g.N[0] - g.H[0]) xi[nxi++] = ii - g.N[0];
+    for (int cz = 0; cz < nzk; ++cz)
+      for (int b = 0; b < nyj; ++b)
+        for (int a = (cz == 0 && b == 0) ? 1 : 0; a < nxi; ++a) {
+          const long long m = g.idx(xi[a], yj[b], zk[cz]);
+          u[m] = un[c]; v[m] = vn[c]; w[m] = wn[c];
+        }
+  }
+}
+
+template <typename FT>
+inline void launch_pressure_correct_halo(const GridDev<FT>& g, FT* u, FT* v, FT* w, const FT* p, double dt, int ywrap,
+                                         cudaStream_t stream) {
+  dim3 blk(64, 4, 1), grd(ceil_div(ceil_div(g.N[0], 2), 64), ceil_div(g.N[1], 4), g.N[2]);
+  pressure_correct_halo_kernel<FT><<<grd, blk, 0, stream>>>(g, u, v, w, p, dt, ywrap);
 }
