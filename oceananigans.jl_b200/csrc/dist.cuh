@@ -15,7 +15,7 @@
 
 // in-place c2c along z on the blocked layout.  grid (R·Cx/8, NyL), block N = Nz
 template <typename FT, typename CT, int N, bool INV>
-__global__ void __launch_bounds__(N) pd_z_kernel(const __grid_constant__ PFJob<FT, CT> J, int R) {
+__global__ void __launch_bounds__(N, pf_min_ctas(N)) pd_z_kernel(const __grid_constant__ PFJob<FT, CT> J, int R) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
   constexpr int pitch = FFPitch8<N>::value;
@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(N) pd_z_kernel(const __grid_constant__ PFJob<F
 // forward c2c along the GLOBAL y, spectral division, inverse c2c along y, on the transposed buffer T (this rank's Cx
 // columns, all Ny rows).  grid (Cx/8, Nz), block N = Ny (global)
 template <typename FT, typename CT, int N>
-__global__ void __launch_bounds__(N) pd_y_solve_kernel(const __grid_constant__ PFJob<FT, CT> J, CT* __restrict__ T, int rank) {
+__global__ void __launch_bounds__(N, pf_min_ctas(N)) pd_y_solve_kernel(const __grid_constant__ PFJob<FT, CT> J, CT* __restrict__ T, int rank) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
   constexpr int pitch = FFPitch8<N>::value;
@@ -67,9 +67,11 @@ __global__ void __launch_bounds__(N) pd_y_solve_kernel(const __grid_constant__ P
     const int j = t + m * (N / 8);
     // same association as the single-GPU kernel and the reference: ((λx + λy) + λz) - m
     double den = ((lamx + J.ly[j]) + lamz) - J.m;
+    const bool den_ok = nh_den_ok(den);
+    const double yr = nh_rcp_refined(den);
     CT r;
-    r.x = (FT)((double)(-v[m].x) / den);
-    r.y = (FT)((double)(-v[m].y) / den);
+    r.x = (FT)nh_div_checked((double)(-v[m].x), den, yr, den_ok);
+    r.y = (FT)nh_div_checked((double)(-v[m].y), den, yr, den_ok);
     if (J.m == 0.0 && kx == 0 && j == 0 && kz == 0) { r.x = 0; r.y = 0; }
     v[m] = r;
   }

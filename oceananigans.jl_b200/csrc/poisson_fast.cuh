@@ -12,9 +12,13 @@
 // FFT lines are staged in shared memory and transformed with the register-radix butterflies of fft_fast.cuh.
 #pragma once
 #include "common.cuh"
+#include "recon.cuh"
 #include "fft_fast.cuh"
 
 #define PF_L 8   // lines per CTA
+// Every FFT kernel asks for 1024 resident threads per SM (a 64-register cap): these passes are latency bound, and the
+// measured gain from the extra warps outweighs the few spilled values (x-forward 85 → 64 registers: 233 → 170 µs at 256³).
+__host__ __device__ constexpr int pf_min_ctas(int n) { return n >= 1024 ? 1 : (1024 / n > 16 ? 16 : 1024 / n); }
 
 template <typename FT, typename CT>
 struct PFJob {
@@ -35,7 +39,7 @@ struct PFJob {
 // The divergence is evaluated straight into the FFT's input registers; after the transform one shared-memory exchange
 // gives every thread the mirrored coefficient Z[N-kx] it needs for the Hermitian split.
 template <typename FT, typename CT, int N>
-__global__ void __launch_bounds__(N) pf_x_forward_kernel(const __grid_constant__ PFJob<FT, CT> J, const FT* __restrict__ u,
+__global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_x_forward_kernel(const __grid_constant__ PFJob<FT, CT> J, const FT* __restrict__ u,
                                                          const FT* __restrict__ v, const FT* __restrict__ w) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
@@ -105,7 +109,7 @@ __global__ void __launch_bounds__(N) pf_x_forward_kernel(const __grid_constant__
 // Lanes run across the 8 adjacent kx columns (128-byte segments); each thread moves its 8 points global → registers,
 // the first butterfly stage runs before anything touches shared memory and the last one writes straight back.
 template <typename FT, typename CT, int N, bool INV>
-__global__ void __launch_bounds__(N) pf_y_kernel(const __grid_constant__ PFJob<FT, CT> J) {
+__global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_y_kernel(const __grid_constant__ PFJob<FT, CT> J) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
   constexpr int pitch = FFPitch8<N>::value;
@@ -130,7 +134,7 @@ __global__ void __launch_bounds__(N) pf_y_kernel(const __grid_constant__ PFJob<F
 
 // K3 — forward c2c along z, spectral division in registers, inverse c2c along z.  grid (ceil((Nx/2+1)/8), Ny), block Nz
 template <typename FT, typename CT, int N>
-__global__ void __launch_bounds__(N) pf_z_solve_kernel(const __grid_constant__ PFJob<FT, CT> J) {
+__global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_z_solve_kernel(const __grid_constant__ PFJob<FT, CT> J) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
   constexpr int pitch = FFPitch8<N>::value;
@@ -150,9 +154,11 @@ __global__ void __launch_bounds__(N) pf_z_solve_kernel(const __grid_constant__ P
   for (int m = 0; m < 8; ++m) {
     const int n = t + m * (N / 8);
     double den = lxy + J.lz[n] - J.m;
+    const bool den_ok = nh_den_ok(den);
+    const double yr = nh_rcp_refined(den);          // shared by the two components (recon.cuh: same bits as `/`)
     CT r;
-    r.x = (FT)((double)(-v[m].x) / den);
-    r.y = (FT)((double)(-v[m].y) / den);
+    r.x = (FT)nh_div_checked((double)(-v[m].x), den, yr, den_ok);
+    r.y = (FT)nh_div_checked((double)(-v[m].y), den, yr, den_ok);
     if (J.m == 0.0 && kx == 0 && ky == 0 && n == 0) { r.x = 0; r.y = 0; }
     v[m] = r;
   }
@@ -166,7 +172,7 @@ __global__ void __launch_bounds__(N) pf_z_solve_kernel(const __grid_constant__ P
 
 // K5 — grid (Ny/16, Nz), block N = Nx threads: two spectral rows → one complex line → inverse FFT → two real rows of p
 template <typename FT, typename CT, int N>
-__global__ void __launch_bounds__(N) pf_x_inverse_kernel(const __grid_constant__ PFJob<FT, CT> J, FT* __restrict__ p) {
+__global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_x_inverse_kernel(const __grid_constant__ PFJob<FT, CT> J, FT* __restrict__ p) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
   const GridDev<FT>& g = J.g;
