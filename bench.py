@@ -203,7 +203,7 @@ def main():
         arch = D.Distributed(D.Partition(y=world))
         model = D.DistributedNonhydrostaticModel(arch, np.float64, size=gsize, x=(0, 2 * np.pi * fx), y=(0, 2 * np.pi * fy),
                                                  z=(-2 * np.pi, 0), advection=oc.WENO(order=5), timestepper="RungeKutta3",
-                                                 device=local_rank)
+                                                 device=local_rank, p2p=not os.environ.get("NHSTEP_NO_P2P"))
         model.set_local(**smooth_ics(N, 1234, gsize, (model.j0, model.NyL)))
         step = lambda n=1: model.time_step(dt, n_steps=n)                                  # noqa: E731
         profiled = lambda: model.time_step_profiled(dt)                                    # noqa: E731
@@ -321,7 +321,10 @@ def main():
                            + (f" per GPU (global {gsize[0]}x{gsize[1]}x{gsize[2]})" if world > 1 else ""),
                            "l2_policy": "working set (>= 10 fields x %.0f MB) exceeds the 126 MB L2" % (cells * FT_B / 1e6),
                            "parallelism": "single GPU" if world == 1 else
-                           f"y-slabs over {world} GPUs: NCCL halo exchange + 2 all-to-all transposes per pressure solve"},
+                           (f"y-slabs over {world} GPUs: kernels store halo rows and FFT transpose blocks into the peers' "
+                            "buffers over NVLink (CUDA IPC), 5 one-element NCCL all-reduces per stage as barriers"
+                            if getattr(model, "p2p", False) else
+                            f"y-slabs over {world} GPUs: NCCL halo exchange + 2 all-to-all transposes per pressure solve")},
                 "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
         print(json.dumps(line))
     if world > 1:

@@ -159,6 +159,16 @@ int32_t nh_dist_tendency_substep(nh_model* model, double dt, int32_t stage, int3
 /* phase 0: div(U*)/Δt → FFT x → FFT z into A;  1: FFT y, ÷(λx+λy+λz), IFFT y in B;  2: IFFT z, IFFT x from A → pNHS */
 int32_t nh_dist_poisson(nh_model* model, int32_t phase, double stage_dt);
 int32_t nh_dist_pressure_correct(nh_model* model, double stage_dt);
+/* Peer-to-peer mode (NVLink / NVSwitch peer memory; one process per GPU on ONE node).  After every rank has passed the
+ * concatenation of all ranks' export blobs (rank order) to nh_dist_ipc_import, the kernels store their transpose blocks
+ * and halo rows straight into the destination rank's buffers: nh_dist_poisson(0) scatters into the peers' y-local
+ * buffers, nh_dist_poisson(1) scatters back, nh_dist_poisson(2) also writes the next rank's p[j = 0],
+ * nh_dist_tendency_substep the previous rank's v*[j = Ny+1], nh_dist_pressure_correct the neighbours' u, v, w halo rows.
+ * The host then issues ONE stream-ordered barrier (e.g. a one-element NCCL all-reduce) after each of those five calls
+ * instead of the exchanges / all-to-alls listed above.  Must be called before the first step, at the same point on
+ * every rank.  blob = NULL returns the required size in *nbytes. */
+int32_t nh_dist_ipc_export(nh_model* model, unsigned char* blob, int64_t capacity, int64_t* nbytes);
+int32_t nh_dist_ipc_import(nh_model* model, const unsigned char* all_blobs, int64_t nbytes);
 
 /* ---- standalone solvers ---------------------------------------------------------------------------------- */
 /* FFTBasedPoissonSolver(grid) — src/Solvers/fft_based_poisson_solver.jl:52-74;

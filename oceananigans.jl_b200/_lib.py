@@ -48,7 +48,7 @@ SYMBOLS = [
     "nh_poisson_destroy", "nh_poisson_solve", "nh_poisson_synchronize", "nh_poisson_launch_count",
     "nh_poisson_time_solves", "nh_tridiag_create", "nh_tridiag_solve", "nh_tridiag_destroy",
     "nh_dist_configure", "nh_dist_buffer", "nh_dist_halo", "nh_dist_tendency_substep", "nh_dist_poisson",
-    "nh_dist_pressure_correct",
+    "nh_dist_pressure_correct", "nh_dist_ipc_export", "nh_dist_ipc_import",
 ]
 DIST_SEND_LO, DIST_SEND_HI, DIST_RECV_LO, DIST_RECV_HI, DIST_SPECTRAL_A, DIST_SPECTRAL_B = range(6)
 
@@ -104,6 +104,8 @@ def lib():
             "nh_dist_tendency_substep": [p, C.c_double, C.c_int32, C.c_int32, C.POINTER(C.c_double)],
             "nh_dist_poisson": [p, C.c_int32, C.c_double],
             "nh_dist_pressure_correct": [p, C.c_double],
+            "nh_dist_ipc_export": [p, p, C.c_int64, C.POINTER(C.c_int64)],
+            "nh_dist_ipc_import": [p, p, C.c_int64],
             "nh_poisson_create": [p, C.c_int32, C.POINTER(p)],
             "nh_poisson_destroy": [p],
             "nh_poisson_solve": [p, p, p, C.c_double, C.c_int32],

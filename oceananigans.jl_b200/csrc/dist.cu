@@ -68,10 +68,11 @@ double Model<FT>::dist_tendency_substep(double dt, int stage, int euler) {
   FastTendJob<FT> J;
   J.g = gh.g; J.tab = tab; J.dt = (FT)dt; J.gamma = c1; J.zeta = c2; J.mode = mode;
   for (int a = 0; a < 3; ++a) { J.U[a] = F[a]; J.Unew[a] = F2[a]; J.Gn[a] = Gn[a]; J.Gm[a] = Gm[a]; }
+  if (dist.p2p) J.v_prev = dist.prevF2[1];
   launch_fused_tendency<FT>(J, stream);
   lc.n++;
   CUDA_CHECK(cudaGetLastError());
-  for (int a = 0; a < 3; ++a) std::swap(F[a], F2[a]);
+  for (int a = 0; a < 3; ++a) { std::swap(F[a], F2[a]); std::swap(dist.prevF[a], dist.prevF2[a]); std::swap(dist.nextF[a], dist.nextF2[a]); }
   for (int f = 0; f < nf; ++f) std::swap(Gn[f], Gm[f]);
   if (desc.timestepper == NH_RK3) {
     if (stage == 0) dist.t_next = clock.time + dt;
@@ -99,10 +100,64 @@ void Model<FT>::dist_poisson(int phase, double stage_dt) {
 template <typename FT>
 void Model<FT>::dist_pressure_correct(double stage_dt) {
   NH_REQUIRE(dist.on, "model is not configured for a distributed run");
-  launch_pressure_correct_halo<FT>(gh.g, F[0], F[1], F[2], pNHS, stage_dt, 0, stream);
+  YPeers<FT> peers;
+  if (dist.p2p) for (int a = 0; a < 3; ++a) { peers.prev[a] = dist.prevF[a]; peers.next[a] = dist.nextF[a]; }
+  launch_pressure_correct_halo<FT>(gh.g, F[0], F[1], F[2], pNHS, stage_dt, 0, stream, peers);
   lc.n++;
   p_halo_stale = true;
   CUDA_CHECK(cudaGetLastError());
+}
+
+// ---- peer-to-peer mode: CUDA IPC handles of the buffers other ranks write into -------------------------------------
+// blob = 9 handles: spectral A, spectral B, u, v, w (current state), u, v, w (ping-pong target), pNHS
+static const int kIpcHandles = 9;
+
+template <typename FT>
+int64_t Model<FT>::dist_ipc_export(unsigned char* blob, int64_t capacity) {
+  NH_REQUIRE(dist.on, "model is not configured for a distributed run");
+  const int64_t need = (int64_t)kIpcHandles * sizeof(cudaIpcMemHandle_t);
+  if (!blob) return need;
+  NH_REQUIRE(capacity >= need, "nh_dist_ipc_export: buffer too small");
+  void* ptrs[kIpcHandles] = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS};
+  for (int q = 0; q < kIpcHandles; ++q) {
+    cudaIpcMemHandle_t h;
+    CUDA_CHECK(cudaIpcGetMemHandle(&h, ptrs[q]));
+    std::memcpy(blob + q * sizeof(h), &h, sizeof(h));
+  }
+  return need;
+}
+
+// blobs: the export of every rank, in rank order.  Opens what this rank writes into: every rank's spectral buffers and
+// the fields of the previous / next rank; with one rank (or for this rank's own buffers) the local pointers are used.
+template <typename FT>
+void Model<FT>::dist_ipc_import(const unsigned char* blobs, int64_t nbytes) {
+  NH_REQUIRE(dist.on, "model is not configured for a distributed run");
+  NH_REQUIRE(!dist.p2p, "peer buffers are already open");
+  const int R = dist.R, rank = dist.rank;
+  NH_REQUIRE(R <= PF_MAXR, "peer-to-peer mode supports at most 16 ranks");
+  const int64_t per = (int64_t)kIpcHandles * sizeof(cudaIpcMemHandle_t);
+  NH_REQUIRE(nbytes == per * R, "nh_dist_ipc_import: expected one export blob per rank");
+  void* own[kIpcHandles] = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS};
+  std::vector<std::vector<void*>> ptr(R, std::vector<void*>(kIpcHandles, nullptr));
+  auto open = [&](int r, int q) -> void* {
+    if (r == rank) return own[q];
+    if (ptr[r][q]) return ptr[r][q];
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, blobs + r * per + q * sizeof(h), sizeof(h));
+    void* out = nullptr;
+    CUDA_CHECK(cudaIpcOpenMemHandle(&out, h, cudaIpcMemLazyEnablePeerAccess));
+    dist.opened.push_back(out);
+    ptr[r][q] = out;
+    return out;
+  };
+  for (int r = 0; r < R; ++r) { dist.peerA[r] = (CT*)open(r, 0); dist.peerB[r] = (CT*)open(r, 1); }
+  const int prev = (rank + R - 1) % R, next = (rank + 1) % R;
+  for (int a = 0; a < 3; ++a) {
+    dist.prevF[a] = (FT*)open(prev, 2 + a); dist.prevF2[a] = (FT*)open(prev, 5 + a);
+    dist.nextF[a] = (FT*)open(next, 2 + a); dist.nextF2[a] = (FT*)open(next, 5 + a);
+  }
+  dist.next_p = (FT*)open(next, 8);
+  dist.p2p = true;
 }
 
 #define NH_DIST_INSTANTIATE(FT)                                                          \
@@ -111,6 +166,8 @@ void Model<FT>::dist_pressure_correct(double stage_dt) {
   template int64_t Model<FT>::dist_halo(uint32_t, int, int);                             \
   template double Model<FT>::dist_tendency_substep(double, int, int);                    \
   template void Model<FT>::dist_poisson(int, double);                                    \
-  template void Model<FT>::dist_pressure_correct(double);
+  template void Model<FT>::dist_pressure_correct(double);                                \
+  template int64_t Model<FT>::dist_ipc_export(unsigned char*, int64_t);                  \
+  template void Model<FT>::dist_ipc_import(const unsigned char*, int64_t);
 NH_DIST_INSTANTIATE(float)
 NH_DIST_INSTANTIATE(double)

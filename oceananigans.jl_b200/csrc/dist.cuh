@@ -39,6 +39,32 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pd_z_kernel(const __grid_co
   }
 }
 
+// forward z pass with the transpose folded in: block d of the result is stored straight into rank d's y-local buffer
+// (block `rank` of it) through its peer pointer, so no all-to-all follows — only a barrier.  grid (R·Cx/8, NyL), block Nz
+template <typename FT, typename CT, int N>
+__global__ void __launch_bounds__(N, pf_min_ctas(N)) pd_z_scatter_kernel(const __grid_constant__ PFJob<FT, CT> J, int rank) {
+  extern __shared__ __align__(16) unsigned char pf_smem[];
+  CT* X = reinterpret_cast<CT*>(pf_smem);
+  constexpr int pitch = FFPitch8<N>::value;
+  const int tid = threadIdx.x, c = tid & (PF_L - 1), t = tid >> 3;
+  const int kx = blockIdx.x * PF_L + c, jl = blockIdx.y;
+  const bool active = kx <= J.Nx / 2;
+  const long long plane = (long long)J.Cx * J.Ny;
+  const long long inner = (kx % J.Cx) + (long long)J.Cx * jl + plane * t;
+  const int d = kx / J.Cx;
+  const CT* src = J.S + inner + plane * J.Nz * d;
+  CT* dst = J.peer[d] + inner + plane * J.Nz * rank;
+  const long long step = plane * (N / 8);
+  CT v[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) { if (active) v[m] = src[m * step]; else { v[m].x = 0; v[m].y = 0; } }
+  ff_line_fft_regs<CT, N, false>(v, X + c * pitch, t, J.twz);
+  if (active) {
+#pragma unroll
+    for (int m = 0; m < 8; ++m) dst[m * step] = v[m];
+  }
+}
+
 // forward c2c along the GLOBAL y, spectral division, inverse c2c along y, on the transposed buffer T (this rank's Cx
 // columns, all Ny rows).  grid (Cx/8, Nz), block N = Ny (global)
 template <typename FT, typename CT, int N>
@@ -79,7 +105,15 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pd_y_solve_kernel(const __g
   if (active) {
     const FT scale = FT(1) / FT(N);
 #pragma unroll
-    for (int m = 0; m < 8; ++m) { v[m].x *= scale; v[m].y *= scale; base[off[m]] = v[m]; }
+    for (int m = 0; m < 8; ++m) {
+      v[m].x *= scale; v[m].y *= scale;
+      if (J.peer[0] == nullptr) base[off[m]] = v[m];
+      else {
+        // transpose back folded in: rows of rank s go to block `rank` of rank s's z-local buffer
+        const int j = t + m * (N / 8), s = j / NyL;
+        J.peer[s][kxl + (long long)J.Cx * (j - s * NyL) + plane * kz + plane * J.Nz * rank] = v[m];
+      }
+    }
   }
 }
 

@@ -25,6 +25,13 @@ struct DistState {
   DevBuf<FT> send_lo, send_hi, recv_lo, recv_hi;
   size_t halo_elems = 0, spec_elems = 0;
   double t_next = 0;
+  // peer-to-peer mode (nh_dist_ipc_*): NVLink peer pointers of every rank's spectral buffers and of the neighbours' fields
+  bool p2p = false;
+  CT* peerA[PF_MAXR];
+  CT* peerB[PF_MAXR];
+  FT *prevF[3], *prevF2[3], *nextF[3], *nextF2[3], *next_p = nullptr;
+  std::vector<void*> opened;
+  ~DistState() { for (void* q : opened) cudaIpcCloseMemHandle(q); }
 
   void create(const GridHost<FT>& gh, int rank_, int R_, double y0, double y1, int Ny_global, FT& dy_out) {
     const GridDev<FT>& g = gh.g;
@@ -57,6 +64,8 @@ struct DistState {
       ls[e]->upload(nhhost::poisson_eigenvalues(Ns[e], h, NH_PERIODIC));
     }
     J.twx = twx.p; J.twy = twy.p; J.twz = twz.p; J.lx = lx.p; J.ly = ly.p; J.lz = lz.p;
+    for (int d = 0; d < PF_MAXR; ++d) { J.peer[d] = nullptr; peerA[d] = peerB[d] = nullptr; }
+    J.p_next = nullptr;
     halo_elems = (size_t)(g.N[0] + 2 * g.H[0]) * g.H[1] * (g.N[2] + 2 * g.H[2]) * 3;
     send_lo.alloc(halo_elems); send_hi.alloc(halo_elems); recv_lo.alloc(halo_elems); recv_hi.alloc(halo_elems);
     PD_SWITCH_N(J.Nx, (set_attr_x<NN>()));
@@ -73,6 +82,7 @@ struct DistState {
     const int smem = PF_L * FFPitch8<N>::value * (int)sizeof(CT);
     CUDA_CHECK(cudaFuncSetAttribute(pd_z_kernel<FT, CT, N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     CUDA_CHECK(cudaFuncSetAttribute(pd_z_kernel<FT, CT, N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CUDA_CHECK(cudaFuncSetAttribute(pd_z_scatter_kernel<FT, CT, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   }
   template <int N> void set_attr_y() {
     const int smem = PF_L * FFPitch8<N>::value * (int)sizeof(CT);
@@ -88,6 +98,7 @@ struct DistState {
     const int smem = PF_L * FFPitch8<N>::value * (int)sizeof(CT);
     dim3 gz(R * J.Cx / PF_L, J.Ny);
     if (inv) pd_z_kernel<FT, CT, N, true><<<gz, N, smem, s>>>(J, R);
+    else if (p2p) pd_z_scatter_kernel<FT, CT, N><<<gz, N, smem, s>>>(J, rank);
     else pd_z_kernel<FT, CT, N, false><<<gz, N, smem, s>>>(J, R);
   }
   template <int N> void launch_y(cudaStream_t s) {
@@ -97,7 +108,8 @@ struct DistState {
   }
   // div(U*)/Δt → x-FFT → z-FFT, result in A (the all-to-all send buffer)
   void forward(const FT* u, const FT* v, const FT* w, double dt, cudaStream_t s, LaunchCounter& lc) {
-    J.dt = dt; J.m = 0.0; J.S = A.p;
+    J.dt = dt; J.m = 0.0; J.S = A.p; J.p_next = nullptr;
+    for (int d = 0; d < PF_MAXR; ++d) J.peer[d] = p2p ? peerB[d] : nullptr;      // the scatter targets the y-local buffers
     PD_SWITCH_N(J.Nx, (launch_x<NN>(true, u, v, w, nullptr, s)));
     PD_SWITCH_N(J.Nz, (launch_z<NN>(false, s)));
     lc.n += 2;
@@ -105,13 +117,15 @@ struct DistState {
   }
   // after all_to_all(A → B): y-FFT, division, y-IFFT in B
   void solve_y(cudaStream_t s, LaunchCounter& lc) {
+    for (int d = 0; d < PF_MAXR; ++d) J.peer[d] = p2p ? peerA[d] : nullptr;      // … and back into the z-local ones
     PD_SWITCH_N(Ny, (launch_y<NN>(s)));
     lc.n += 1;
     CUDA_CHECK(cudaGetLastError());
   }
   // after all_to_all(B → A): z-IFFT, x-IFFT, real store into p
   void backward(FT* p, cudaStream_t s, LaunchCounter& lc) {
-    J.S = A.p;
+    J.S = A.p; J.p_next = p2p ? next_p : nullptr;
+    for (int d = 0; d < PF_MAXR; ++d) J.peer[d] = nullptr;
     PD_SWITCH_N(J.Nz, (launch_z<NN>(true, s)));
     PD_SWITCH_N(J.Nx, (launch_x<NN>(false, nullptr, nullptr, nullptr, p, s)));
     lc.n += 2;

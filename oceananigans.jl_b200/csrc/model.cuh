@@ -91,6 +91,8 @@ struct PoissonFast {
   void create(const GridHost<FT>& gh) {
     const GridDev<FT>& g = gh.g;
     J.g = g; J.Nx = g.N[0]; J.Ny = g.N[1]; J.Nz = g.N[2]; J.Mx = J.Nx / 2 + 2; J.Cx = J.Mx; J.ywrap = 1;
+    for (int d = 0; d < PF_MAXR; ++d) J.peer[d] = nullptr;
+    J.p_next = nullptr;
     J.px = ff_make_plan(J.Nx); J.py = ff_make_plan(J.Ny); J.pz = ff_make_plan(J.Nz);
     S.alloc((size_t)J.Mx * J.Ny * J.Nz);
     DevBuf<CT>* tws[3] = {&twx, &twy, &twz};
@@ -202,6 +204,8 @@ struct nh_model {
   virtual double dist_tendency_substep(double dt, int stage, int euler) = 0;
   virtual void dist_poisson(int phase, double stage_dt) = 0;
   virtual void dist_pressure_correct(double stage_dt) = 0;
+  virtual int64_t dist_ipc_export(unsigned char* blob, int64_t capacity) = 0;
+  virtual void dist_ipc_import(const unsigned char* blobs, int64_t nbytes) = 0;
   // phase timing (nh_time_step_profiled): CUDA events on the model's stream between the phases of one step
   bool profiling = false;
   std::vector<std::pair<int, cudaEvent_t>> marks;
@@ -284,6 +288,8 @@ struct Model : nh_model {
   double dist_tendency_substep(double dt, int stage, int euler) override;
   void dist_poisson(int phase, double stage_dt) override;
   void dist_pressure_correct(double stage_dt) override;
+  int64_t dist_ipc_export(unsigned char* blob, int64_t capacity) override;
+  void dist_ipc_import(const unsigned char* blobs, int64_t nbytes) override;
 };
 
 struct nh_poisson {

@@ -16,6 +16,7 @@
 #include "fft_fast.cuh"
 
 #define PF_L 8   // lines per CTA
+#define PF_MAXR 16   // ranks of a y-slab run addressable through peer pointers
 // Every FFT kernel asks for 1024 resident threads per SM (a 64-register cap): these passes are latency bound, and the
 // measured gain from the extra warps outweighs the few spilled values (x-forward 85 → 64 registers: 233 → 170 µs at 256³).
 __host__ __device__ constexpr int pf_min_ctas(int n) { return n >= 1024 ? 1 : (1024 / n > 16 ? 16 : 1024 / n); }
@@ -33,6 +34,10 @@ struct PFJob {
   const double *lx, *ly, *lz;
   CT* S;
   double dt, m;
+  // y-slab runs with peer-to-peer transfers (csrc/dist.cuh): the spectral buffers of every rank and the next rank's
+  // pressure field as NVLink peer pointers; all nullptr on one GPU or when the messages go through NCCL
+  CT* peer[PF_MAXR];
+  FT* p_next;
 };
 
 // K1 — grid (Ny/16, Nz), block N = Nx threads.  Thread (l, t): pair-line l (rows j, j+1), points i-1 = t + m·N/8.
@@ -214,5 +219,11 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_x_inverse_kernel(const _
     const int i0 = t + m * tpl;
     p[ra + i0] = z[m].x * scale;
     if (rowb) p[rb + i0] = z[m].y * scale;
+  }
+  // the last local row is row 0 of the next rank's pressure (its v-correction reads p[j-1])
+  if (J.p_next != nullptr && (j == J.Ny || (rowb && j + 1 == J.Ny))) {
+    const long long r0 = g.idx(1, 0, k);
+#pragma unroll
+    for (int m = 0; m < 8; ++m) J.p_next[r0 + t + m * tpl] = (j == J.Ny ? z[m].x : z[m].y) * scale;
   }
 }

@@ -37,6 +37,9 @@ struct FastTendJob {
   SchemeTables<FT> tab;
   FT dt, gamma, zeta;
   int mode;            // 0: U* = U + Δt·γ·Gⁿ, 1: U* = U + Δt(γGⁿ + ζG⁻), 2: AB2, 3: AB2-Euler, -1: tendencies only
+  // y-slab runs with peer-to-peer halos: row j = 1 of v* is also stored into row Ny+1 of the previous rank's v* (NVLink
+  // peer pointer), which is all the divergence of that rank needs from here; nullptr otherwise
+  FT* v_prev = nullptr;
 };
 
 // face flux F_{b,a} at flux-location index n (linear), strides sa (dim a) and sb (dim b)
@@ -120,6 +123,7 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
         else if (J.mode == 2) u = u + J.dt * ((FT(1.5) + J.gamma) * G - (FT(0.5) + J.gamma) * J.Gm[a][n]);
         else u = u + J.dt * ((FT(1.5) + J.gamma) * G - FT(0));
         J.Unew[a][n] = u;
+        if (a == 1 && J.v_prev != nullptr && j0 + lj == 1) J.v_prev[n + g.N[1] * (int)g.sy] = u;
       }
     }
     __syncthreads();
@@ -174,8 +178,12 @@ __global__ void __launch_bounds__(256) periodic_halo_all_kernel(const __grid_con
 // _pressure_correct_velocities! — src/Models/NonhydrostaticModels/pressure_correction.jl:31-37
 // Each thread corrects two x-adjacent cells (16-byte loads/stores; i = 1 starts a 128-byte line, pitches are multiples of 16).
 template <typename FT>
+struct YPeers { FT* prev[3] = {nullptr, nullptr, nullptr}; FT* next[3] = {nullptr, nullptr, nullptr}; };   // peers' u, v, w (y-slab runs)
+
+template <typename FT>
 __global__ void __launch_bounds__(256) pressure_correct_halo_kernel(GridDev<FT> g, FT* __restrict__ u, FT* __restrict__ v,
-                                                                    FT* __restrict__ w, const FT* __restrict__ p, double dt, int ywrap) {
+                                                                    FT* __restrict__ w, const FT* __restrict__ p, double dt, int ywrap,
+                                                                    YPeers<FT> peers) {
   typedef typename cx_of<FT>::type V2;
   const int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x) + 1;
   const int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
@@ -217,7 +225,8 @@ __global__ void __launch_bounds__(256) pressure_correct_halo_kernel(GridDev<FT> 
   } else { u[n] = un[0]; v[n] = vn[0]; w[n] = wn[0]; }
   // periodic images: index sets {i, i±N} ∩ parent range, likewise j, k; only cells within a halo width of a face have any
   const bool xedge = i <= g.H[0] || i + 1 > g.N[0] - g.H[0];
-  const bool yedge = ywrap && (j <= g.H[1] || j > g.N[1] - g.H[1]);
+  const bool remote = !ywrap && peers.prev[0] != nullptr;
+  const bool yedge = (ywrap || remote) && (j <= g.H[1] || j > g.N[1] - g.H[1]);
   const bool zedge = k <= g.H[2] || k > g.N[2] - g.H[2];
   if (!(xedge || yedge || zedge)) return;
   int yj[2], nyj = 1; yj[0] = j;
@@ -234,12 +243,23 @@ __global__ void __launch_bounds__(256) pressure_correct_halo_kernel(GridDev<FT> 
           const long long m = g.idx(xi[a], yj[b], zk[cz]);
           u[m] = un[c]; v[m] = vn[c]; w[m] = wn[c];
         }
+    if (remote && (j <= g.H[1] || j > g.N[1] - g.H[1])) {
+      // the neighbour's y halo row that mirrors this row (all x / z images of it too), written over NVLink
+      const bool lo = j <= g.H[1];
+      FT* const* dst = lo ? peers.prev : peers.next;
+      const int jr = lo ? j + g.N[1] : j - g.N[1];
+      for (int cz = 0; cz < nzk; ++cz)
+        for (int a = 0; a < nxi; ++a) {
+          const long long m = g.idx(xi[a], jr, zk[cz]);
+          dst[0][m] = un[c]; dst[1][m] = vn[c]; dst[2][m] = wn[c];
+        }
+    }
   }
 }
 
 template <typename FT>
 inline void launch_pressure_correct_halo(const GridDev<FT>& g, FT* u, FT* v, FT* w, const FT* p, double dt, int ywrap,
-                                         cudaStream_t stream) {
+                                         cudaStream_t stream, const YPeers<FT>& peers = YPeers<FT>()) {
   dim3 blk(64, 4, 1), grd(ceil_div(ceil_div(g.N[0], 2), 64), ceil_div(g.N[1], 4), g.N[2]);
-  pressure_correct_halo_kernel<FT><<<grd, blk, 0, stream>>>(g, u, v, w, p, dt, ywrap);
+  pressure_correct_halo_kernel<FT><<<grd, blk, 0, stream>>>(g, u, v, w, p, dt, ywrap, peers);
 }

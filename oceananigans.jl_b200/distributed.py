@@ -116,7 +116,7 @@ class DistributedNonhydrostaticModel:
     """
 
     def __init__(self, arch, FT=np.float64, size=None, x=None, y=None, z=None, halo=(3, 3, 3), advection=None,
-                 timestepper="RungeKutta3", device=0, **kw):
+                 timestepper="RungeKutta3", device=0, p2p=False, **kw):
         import torch
         from . import RectilinearGrid, Periodic, WENO
         from .model import NonhydrostaticModel
@@ -147,6 +147,36 @@ class DistributedNonhydrostaticModel:
         self.Cx = spectral_block_width(Nx, self.R)
         self.halo = self.model.halo
         self._uvw = (1 << L.FIELD_U) | (1 << L.FIELD_V) | (1 << L.FIELD_W)
+        self.p2p = False
+        if p2p:
+            self._enable_peer_to_peer()
+
+    def _enable_peer_to_peer(self):
+        """Exchange CUDA IPC handles so that the kernels store transposes and halo rows straight into the peers' buffers
+        (NVLink peer memory); the messages then shrink to one stream-ordered barrier per piece."""
+        import torch
+        import torch.distributed as dist
+        n = C.c_int64()
+        check(lib().nh_dist_ipc_export(self._h, None, 0, C.byref(n)))
+        blob = (C.c_ubyte * n.value)()
+        check(lib().nh_dist_ipc_export(self._h, blob, n.value, C.byref(n)))
+        mine = torch.frombuffer(bytearray(blob), dtype=torch.uint8)
+        if self.R > 1:
+            allb = torch.empty(self.R * n.value, dtype=torch.uint8, device=self.device)
+            dist.all_gather_into_tensor(allb, mine.to(self.device), group=self.arch.group)
+            allb = allb.cpu()
+        else:
+            allb = mine
+        raw = (C.c_ubyte * allb.numel()).from_buffer_copy(allb.numpy().tobytes())
+        check(lib().nh_dist_ipc_import(self._h, raw, allb.numel()))
+        self._flag = torch.zeros(1, device=self.device)
+        self.p2p = True
+
+    def _barrier(self):
+        """All ranks' kernels issued so far have completed before anything issued after it starts (stream-ordered)."""
+        if self.R > 1:
+            import torch.distributed as dist
+            dist.all_reduce(self._flag, group=self.arch.group)
 
     # -- pieces ---------------------------------------------------------------------------------------------------
     def exchange(self, mask, width):
@@ -161,6 +191,18 @@ class DistributedNonhydrostaticModel:
     def pressure_phase(self, stage_dt):
         """calculate_pressure_correction! + pressure_correct_velocities! + fill_halo_regions!(velocities)."""
         h, b = self._h, self._buf
+        if self.p2p:
+            # the kernels have already stored into the peers' buffers: only barriers remain
+            self._barrier()                                   # v*[Ny+1] written by the next rank's tendency sweep
+            check(lib().nh_dist_poisson(h, 0, stage_dt))      # … scatters its z-FFT output into the peers' B
+            self._barrier()
+            check(lib().nh_dist_poisson(h, 1, stage_dt))      # … scatters the solution back into the peers' A
+            self._barrier()
+            check(lib().nh_dist_poisson(h, 2, stage_dt))      # … also writes p[0] of the next rank
+            self._barrier()
+            check(lib().nh_dist_pressure_correct(h, stage_dt))   # … also writes the neighbours' u, v, w halo rows
+            self._barrier()
+            return
         self.exchange(1 << L.FIELD_V, 1)
         check(lib().nh_dist_poisson(h, 0, stage_dt))
         transpose_blocks(b[L.DIST_SPECTRAL_B], b[L.DIST_SPECTRAL_A], self.R, self.arch.group)
@@ -199,6 +241,18 @@ class DistributedNonhydrostaticModel:
         for s in range(stages):
             check(lib().nh_dist_tendency_substep(h, float(dt), s, int(euler), C.byref(sdt)))
             mark("tendencies_substep")
+            if self.p2p:
+                for phase, key in ((0, "pressure_solve"), (1, "pressure_solve"), (2, "pressure_solve"), (3, "pressure_correct")):
+                    self._barrier()
+                    mark("halo_exchange")               # barrier only: the data moved inside the kernels
+                    if phase < 3:
+                        check(lib().nh_dist_poisson(h, phase, sdt.value))
+                    else:
+                        check(lib().nh_dist_pressure_correct(h, sdt.value))
+                    mark(key)
+                self._barrier()
+                mark("halo_exchange")
+                continue
             self.exchange(1 << L.FIELD_V, 1)
             mark("halo_exchange")
             check(lib().nh_dist_poisson(h, 0, sdt.value))

@@ -42,12 +42,12 @@ def _single_gpu(size, FT, timestepper, steps, dt):
     return {n: m.velocities[n].interior() for n in "uvw"} | {"pNHS": m.pressures.pNHS.interior(), "time": m.clock.time}
 
 
-def _distributed(rank, world, size, FT, timestepper, steps, dt, out):
+def _distributed(rank, world, size, FT, timestepper, steps, dt, out, p2p=False):
     import oceananigans_jl_b200 as oc
     from oceananigans_jl_b200 import distributed as D
     arch = D.Distributed(D.Partition(y=world))
     m = D.DistributedNonhydrostaticModel(arch, FT, size=size, x=(0, 1), y=(0, 2), z=(0, 1), halo=(3, 3, 3),
-                                         advection=oc.WENO(FT, 5), timestepper=timestepper, device=rank)
+                                         advection=oc.WENO(FT, 5), timestepper=timestepper, device=rank, p2p=p2p)
     m.set(**_ics(size, FT))
     div0 = m.max_abs_divergence()
     m.time_step(dt, n_steps=steps)
@@ -72,14 +72,15 @@ def _check(res, ref, FT, steps, dt):
     assert res["iteration"] == steps and res["time"] == ref["time"]
 
 
+@pytest.mark.parametrize("p2p", [False, True], ids=["nccl", "p2p"])
 @pytest.mark.parametrize("FT", [np.float64, np.float32])
 @pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
 @pytest.mark.parametrize("size", [(32, 32, 16), (16, 64, 32)])
-def test_one_rank_distributed_path_matches_single_gpu(FT, timestepper, size):
+def test_one_rank_distributed_path_matches_single_gpu(FT, timestepper, size, p2p):
     steps, dt = 10, 2e-3
     ref = _single_gpu(size, FT, timestepper, steps, dt)
     out = {}
-    _distributed(0, 1, size, FT, timestepper, steps, dt, out)
+    _distributed(0, 1, size, FT, timestepper, steps, dt, out, p2p)
     _check(out, ref, FT, steps, dt)
 
 
@@ -99,7 +100,7 @@ def test_one_rank_distributed_path_matches_oracle():
         assert _rel(out[n], ref[n]) <= 1e-12, (n, _rel(out[n], ref[n]))
 
 
-def _worker(rank, world, port, size, FT, timestepper, steps, dt, path):
+def _worker(rank, world, port, size, FT, timestepper, steps, dt, path, p2p):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -107,18 +108,19 @@ def _worker(rank, world, port, size, FT, timestepper, steps, dt, path):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
         out = {}
-        _distributed(rank, world, size, FT, timestepper, steps, dt, out)
+        _distributed(rank, world, size, FT, timestepper, steps, dt, out, p2p)
         if rank == 0:
             np.savez(path, **out)
     finally:
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("p2p", [False, True], ids=["nccl", "p2p"])
 @pytest.mark.parametrize("world", [2, 4])
 @pytest.mark.parametrize("FT,timestepper,size", [(np.float64, "RungeKutta3", (32, 64, 16)),
                                                  (np.float64, "QuasiAdamsBashforth2", (64, 32, 32)),
                                                  (np.float32, "RungeKutta3", (32, 64, 32))])
-def test_multi_gpu_matches_single_gpu(world, FT, timestepper, size, tmp_path):
+def test_multi_gpu_matches_single_gpu(world, FT, timestepper, size, p2p, tmp_path):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
@@ -128,6 +130,6 @@ def test_multi_gpu_matches_single_gpu(world, FT, timestepper, size, tmp_path):
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     path = str(tmp_path / "dist.npz")
-    mp.spawn(_worker, args=(world, port, size, FT, timestepper, steps, dt, path), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, size, FT, timestepper, steps, dt, path, p2p), nprocs=world, join=True)
     res = dict(np.load(path))
     _check(res, ref, FT, steps, dt)

@@ -25,7 +25,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     arch = D.Distributed(D.Partition(y=world))
     m = D.DistributedNonhydrostaticModel(arch, FT, size=(Nx, Ny, Nz), x=(0, 2 * np.pi), y=(0, 2 * np.pi), z=(0, 2 * np.pi),
-                                         advection=oc.WENO(FT, 5), device=local)
+                                         advection=oc.WENO(FT, 5), device=local, p2p="p2p" in sys.argv)
     rng = np.random.default_rng(1)
     x, y, z = (np.arange(n) / n for n in (Nx, Ny, Nz))
     ics = {}
@@ -68,6 +68,7 @@ def main():
 
     sdt = C.c_double()
     timed("tendency_substep", lambda: check(lib().nh_dist_tendency_substep(h, dt, 1, 0, C.byref(sdt))))
+    timed("barrier", m._barrier if m.p2p else (lambda: None))
     timed("exchange_v_1row", lambda: m.exchange(1 << L.FIELD_V, 1))
     timed("poisson_forward(x,z)", lambda: check(lib().nh_dist_poisson(h, 0, dt)))
     timed("all_to_all", lambda: D.transpose_blocks(b[L.DIST_SPECTRAL_B], b[L.DIST_SPECTRAL_A], world, arch.group))
@@ -78,7 +79,7 @@ def main():
     timed("exchange_uvw_3rows", lambda: m.exchange(m._uvw, 3))
     if rank == 0:
         cells = Nx * Ny * Nz
-        print(f"R={world} global {Nx}x{Ny}x{Nz} {np.dtype(FT).name}: {ms.item():.3f} ms/step, "
+        print(f"p2p={m.p2p} R={world} global {Nx}x{Ny}x{Nz} {np.dtype(FT).name}: {ms.item():.3f} ms/step, "
               f"{cells / (ms.item() * 1e-3):.3e} cell-updates/s; per stage pieces (ms):")
         for k, v in pieces.items():
             print(f"   {k:24s} {v:8.3f}")
