@@ -20,8 +20,12 @@ struct PoissonStandalone : nh_poisson {
     gh.build(grid.desc, grid.zfaces, grid.desc.H);
     s.stream = stream;
     s.create(gh, kind);
+    // fused passes for (Periodic, Periodic, Periodic | Bounded) power-of-two grids; everything else takes the complete path
+    if (kind == NH_SOLVER_FFT && PoissonFast<FT>::supported(gh, true) && !getenv("NHSTEP_NO_FAST_POISSON")) fast.create(gh);
   }
+  PoissonFast<FT> fast;
   void run(const FT* rhs_dev, FT* phi_dev, double m) {
+    if (fast.ok) { fast.solve_rhs(rhs_dev, phi_dev, m, stream, *s.lc); return; }
     long long n = s.count();
     int blocks = (int)((n + 255) / 256);
     real_to_complex_kernel<FT, CT><<<blocks, 256, 0, stream>>>(rhs_dev, s.A.p, n, (long long)s.N[0] * s.N[1], s.dzc1.p,

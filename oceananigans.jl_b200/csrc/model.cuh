@@ -79,17 +79,27 @@ struct PoissonFast {
   DevBuf<CT> S, twx, twy, twz;
   DevBuf<double> lx, ly, lz;
   size_t smem_x = 0, smem_y = 0, smem_z = 0;
-  static bool supported(const GridHost<FT>& gh) {
+  bool zdct = false;                 // z is Bounded: DCT-II/III along z inside the z-solve kernel
+  DevBuf<CT> tw4z;
+  GridDev<FT> gdense;                // the reference's dense (Nx, Ny, Nz) array layout, for standalone solves
+  // x, y Periodic; z Periodic (model fast path and standalone) or Bounded (standalone); power-of-two sizes 16 … 1024
+  static bool supported(const GridHost<FT>& gh, bool allow_bounded_z = false) {
     if (gh.z_stretched) return false;
     for (int e = 0; e < 3; ++e) {
       int N = gh.g.N[e];
-      if (gh.g.topo[e] != NH_PERIODIC || N < 16 || N > 1024 || (N & (N - 1))) return false;
+      bool topo_ok = gh.g.topo[e] == NH_PERIODIC || (e == 2 && allow_bounded_z && gh.g.topo[e] == NH_BOUNDED);
+      if (!topo_ok || N < 16 || N > 1024 || (N & (N - 1))) return false;
       if ((size_t)PF_L * ff_line_pitch(N) * sizeof(CT) > 200 * 1024) return false;
     }
     return true;
   }
   void create(const GridHost<FT>& gh) {
     const GridDev<FT>& g = gh.g;
+    zdct = g.topo[2] == NH_BOUNDED;
+    gdense = g;
+    for (int e = 0; e < 3; ++e) gdense.H[e] = 0;
+    gdense.ox = gdense.oy = gdense.oz = 0; gdense.px = g.N[0]; gdense.py = g.N[1]; gdense.pz = g.N[2];
+    gdense.sy = g.N[0]; gdense.sz = (long long)g.N[0] * g.N[1];
     J.g = g; J.Nx = g.N[0]; J.Ny = g.N[1]; J.Nz = g.N[2]; J.Mx = J.Nx / 2 + 2; J.Cx = J.Mx; J.ywrap = 1;
     for (int d = 0; d < PF_MAXR; ++d) J.peer[d] = nullptr;
     J.p_next = nullptr;
@@ -105,8 +115,14 @@ struct PoissonFast {
       for (int q = 0; q < N; ++q) { t[q].x = (FT)a[2 * q]; t[q].y = (FT)a[2 * q + 1]; }
       tws[e]->upload(t);
       double h = (double)(FT)(gh.L[e] / (FT)N);
-      ls[e]->upload(nhhost::poisson_eigenvalues(N, h, NH_PERIODIC));
+      ls[e]->upload(nhhost::poisson_eigenvalues(N, h, g.topo[e]));
+      if (e == 2 && zdct) {
+        std::vector<CT> t4(N);
+        for (int q = 0; q < N; ++q) { t4[q].x = (FT)b[2 * q]; t4[q].y = (FT)b[2 * q + 1]; }
+        tw4z.upload(t4);
+      }
     }
+    J.tw4z = tw4z.p;
     J.twx = twx.p; J.twy = twy.p; J.twz = twz.p; J.lx = lx.p; J.ly = ly.p; J.lz = lz.p; J.S = S.p;
     smem_x = (size_t)PF_L * ff_line_pitch(J.Nx) * sizeof(CT);
     smem_y = (size_t)PF_L * ff_line_pitch(J.Ny) * sizeof(CT);
@@ -124,15 +140,21 @@ struct PoissonFast {
         CUDA_CHECK(cudaFuncSetAttribute(pf_y_kernel<FT, CT, N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         CUDA_CHECK(cudaFuncSetAttribute(pf_y_kernel<FT, CT, N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       }
-      if (J.Nz == N) CUDA_CHECK(cudaFuncSetAttribute(pf_z_solve_kernel<FT, CT, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      if (J.Nz == N) {
+        CUDA_CHECK(cudaFuncSetAttribute(pf_z_solve_kernel<FT, CT, N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CUDA_CHECK(cudaFuncSetAttribute(pf_z_solve_kernel<FT, CT, N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      }
       if (J.Nx == N) {
-        CUDA_CHECK(cudaFuncSetAttribute(pf_x_forward_kernel<FT, CT, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smemx));
+        CUDA_CHECK(cudaFuncSetAttribute(pf_x_forward_kernel<FT, CT, N, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smemx));
+        CUDA_CHECK(cudaFuncSetAttribute(pf_x_forward_kernel<FT, CT, N, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smemx));
         CUDA_CHECK(cudaFuncSetAttribute(pf_x_inverse_kernel<FT, CT, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smemx));
       }
-    } else if (what == 4) pf_x_forward_kernel<FT, CT, N><<<grid, N, smemx, stream>>>(J, xu, xv, xw);
+    } else if (what == 4) pf_x_forward_kernel<FT, CT, N, false><<<grid, N, smemx, stream>>>(J, xu, xv, xw);
+    else if (what == 6) pf_x_forward_kernel<FT, CT, N, true><<<grid, N, smemx, stream>>>(J, xu, nullptr, nullptr);
     else if (what == 5) pf_x_inverse_kernel<FT, CT, N><<<grid, N, smemx, stream>>>(J, xp);
     else if (what == 1) pf_y_kernel<FT, CT, N, false><<<grid, N, smem, stream>>>(J);
-    else if (what == 2) pf_z_solve_kernel<FT, CT, N><<<grid, N, smem, stream>>>(J);
+    else if (what == 2 && zdct) pf_z_solve_kernel<FT, CT, N, true><<<grid, N, smem, stream>>>(J);
+    else if (what == 2) pf_z_solve_kernel<FT, CT, N, false><<<grid, N, smem, stream>>>(J);
     else pf_y_kernel<FT, CT, N, true><<<grid, N, smem, stream>>>(J);
   }
   void yz_size(int N, int what, dim3 grid, cudaStream_t stream) {
@@ -152,7 +174,7 @@ struct PoissonFast {
       yz_size(J.Ny, 0, grid, stream);
       if (J.Nz != J.Ny) yz_size(J.Nz, 0, grid, stream);
       if (J.Nx != J.Ny && J.Nx != J.Nz) yz_size(J.Nx, 0, grid, stream);
-    } else yz_size(what >= 4 ? J.Nx : (what == 2 ? J.Nz : J.Ny), what, grid, stream);
+    } else yz_size(what >= 4 ? J.Nx : (what == 2 ? J.Nz : J.Ny), what, grid, stream);   // 4, 5, 6 are x passes
   }
   // rhs = div(u,v,w)/dt → p (interior of the halo'd field); 5 launches on `stream`
   void solve(const FT* u, const FT* v, const FT* w, FT* p, double dt, cudaStream_t stream, LaunchCounter& lc) {
@@ -164,6 +186,21 @@ struct PoissonFast {
     yz_dispatch(2, gz, stream);
     yz_dispatch(3, gy, stream);
     yz_dispatch(5, gx, stream);
+    lc.n += 5;
+    CUDA_CHECK(cudaGetLastError());
+  }
+  // solve!(ϕ, solver, b, m) on dense device arrays (fft_based_poisson_solver.jl:95-125): ϕ = Re(𝓕⁻¹[-𝓕b / (λ - m)])
+  void solve_rhs(const FT* rhs, FT* phi, double m, cudaStream_t stream, LaunchCounter& lc) {
+    const GridDev<FT> keep = J.g;
+    J.g = gdense; J.dt = 1.0; J.m = m;
+    dim3 gx(ceil_div(J.Ny, 2 * PF_L), J.Nz), gy(ceil_div(J.Nx / 2 + 1, PF_L), J.Nz), gz(ceil_div(J.Nx / 2 + 1, PF_L), J.Ny);
+    xu = rhs; xv = xw = nullptr; xp = phi;
+    yz_dispatch(6, gx, stream);
+    yz_dispatch(1, gy, stream);
+    yz_dispatch(2, gz, stream);
+    yz_dispatch(3, gy, stream);
+    yz_dispatch(5, gx, stream);
+    J.g = keep;
     lc.n += 5;
     CUDA_CHECK(cudaGetLastError());
   }

@@ -31,6 +31,7 @@ struct PFJob {
   int ywrap;                     // 1: y is locally periodic (index wrap); 0: y halos are filled by neighbour exchange
   FFPlan px, py, pz;
   const CT *twx, *twy, *twz;
+  const CT* tw4z;                // exp(-iπk/(2Nz)): DCT-II/III post/pre-twiddles for a Bounded z (nullptr when z is Periodic)
   const double *lx, *ly, *lz;
   CT* S;
   double dt, m;
@@ -43,7 +44,8 @@ struct PFJob {
 // K1 — grid (Ny/16, Nz), block N = Nx threads.  Thread (l, t): pair-line l (rows j, j+1), points i-1 = t + m·N/8.
 // The divergence is evaluated straight into the FFT's input registers; after the transform one shared-memory exchange
 // gives every thread the mirrored coefficient Z[N-kx] it needs for the Hermitian split.
-template <typename FT, typename CT, int N>
+// RHS = true: the right-hand side is given (u = a real array laid out by J.g, standalone solve!(ϕ, solver, b)); v, w unused.
+template <typename FT, typename CT, int N, bool RHS = false>
 __global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_x_forward_kernel(const __grid_constant__ PFJob<FT, CT> J, const FT* __restrict__ u,
                                                          const FT* __restrict__ v, const FT* __restrict__ w) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
@@ -65,7 +67,10 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_x_forward_kernel(const _
     const int i0 = t + m * tpl;                 // zero-based i
     const int ip = i0 + 1 == N ? 0 : i0 + 1;
     FT da = FT(0), db = FT(0);
-    if (rowa) {
+    if (RHS) {
+      if (rowa) da = u[ra + i0];
+      if (rowb) db = u[rb + i0];
+    } else if (rowa) {
       FT vb = v[rb + i0];
       FT tx = Ax * u[ra + ip] - Ax * u[ra + i0];
       FT ty = Ay * vb - Ay * v[ra + i0];
@@ -138,7 +143,12 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_y_kernel(const __grid_co
 }
 
 // K3 — forward c2c along z, spectral division in registers, inverse c2c along z.  grid (ceil((Nx/2+1)/8), Ny), block Nz
-template <typename FT, typename CT, int N>
+// DCT = true: z is Bounded.  The reference's REDFT10 / REDFT01 along z (discrete_transforms.jl, index_permutations.jl:18-90)
+// become a complex FFT of the even/odd-permuted column (Makhoul) with the twiddles ω_k = exp(-iπk/(2N)):
+//   forward  Y[k] = ω_k V[k] + conj(ω_k) V[N-k];   backward  V[k] = conj(ω_k)(Y[k] - i·Y[N-k])/2, Y[N] := 0
+// The permutation is folded into the global load/store index (position p of the FFT line ↔ plane 2p or 2(N-1-p)+1); the
+// mirrored coefficient comes from the other half of the line through one shared-memory exchange each way.
+template <typename FT, typename CT, int N, bool DCT = false>
 __global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_z_solve_kernel(const __grid_constant__ PFJob<FT, CT> J) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
@@ -147,12 +157,31 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_z_solve_kernel(const __g
   const int kx = blockIdx.x * PF_L + c, ky = blockIdx.y;
   const bool active = kx <= J.Nx / 2;
   const long long sz = (long long)J.Mx * J.Ny;
-  CT* base = J.S + kx + (long long)J.Mx * ky + sz * t;
-  const long long step = sz * (N / 8);
+  CT* base = J.S + kx + (long long)J.Mx * ky;
+  CT* Xl = X + c * pitch;
+  long long off[8];
   CT v[8];
 #pragma unroll
-  for (int m = 0; m < 8; ++m) { if (active) v[m] = base[m * step]; else { v[m].x = 0; v[m].y = 0; } }
-  ff_line_fft_regs<CT, N, false>(v, X + c * pitch, t, J.twz);
+  for (int m = 0; m < 8; ++m) {
+    const int p = t + m * (N / 8);
+    off[m] = sz * (DCT ? (p < N / 2 ? 2 * p : 2 * (N - 1 - p) + 1) : p);
+    if (active) v[m] = base[off[m]]; else { v[m].x = 0; v[m].y = 0; }
+  }
+  ff_line_fft_regs<CT, N, false>(v, Xl, t, J.twz);
+  if (DCT) {
+#pragma unroll
+    for (int m = 0; m < 8; ++m) Xl[ff_phys8(t + m * (N / 8))] = v[m];
+    __syncthreads();
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const int p = t + m * (N / 8);
+      const CT w = J.tw4z[p], b = Xl[ff_phys8((N - p) & (N - 1))];
+      CT wc; wc.x = w.x; wc.y = -w.y;
+      const CT a1 = ff_mul(w, v[m]), a2 = ff_mul(wc, b);
+      v[m].x = a1.x + a2.x; v[m].y = a1.y + a2.y;
+    }
+    __syncthreads();
+  }
   // ϕ̂ = -b̂ / (λx + λy + λz - m)  (λ are Float64; fft_based_poisson_solver.jl:110-115)
   const double lxy = active ? J.lx[kx] + J.ly[ky] : 1.0;
 #pragma unroll
@@ -167,11 +196,27 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_z_solve_kernel(const __g
     if (J.m == 0.0 && kx == 0 && ky == 0 && n == 0) { r.x = 0; r.y = 0; }
     v[m] = r;
   }
-  ff_line_fft_regs<CT, N, true>(v, X + c * pitch, t, J.twz);
+  if (DCT) {
+#pragma unroll
+    for (int m = 0; m < 8; ++m) Xl[ff_phys8(t + m * (N / 8))] = v[m];
+    __syncthreads();
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const int p = t + m * (N / 8);
+      CT b; b.x = 0; b.y = 0;
+      if (p > 0) b = Xl[ff_phys8(N - p)];
+      CT s; s.x = v[m].x + b.y; s.y = v[m].y - b.x;               // Y[k] - i·Y[N-k]
+      CT wc = J.tw4z[p]; wc.y = -wc.y;
+      const CT r = ff_mul(wc, s);
+      v[m].x = r.x * FT(0.5); v[m].y = r.y * FT(0.5);
+    }
+    __syncthreads();
+  }
+  ff_line_fft_regs<CT, N, true>(v, Xl, t, J.twz);
   if (active) {
     const FT scale = FT(1) / FT(N);
 #pragma unroll
-    for (int m = 0; m < 8; ++m) { v[m].x *= scale; v[m].y *= scale; base[m * step] = v[m]; }
+    for (int m = 0; m < 8; ++m) { v[m].x *= scale; v[m].y *= scale; base[off[m]] = v[m]; }
   }
 }
 

@@ -140,3 +140,27 @@ def test_fft_poisson_large_roundtrip_property(oc):
     d = 1.0 / N
     lap = sum((np.roll(phi, -1, ax) - 2 * phi + np.roll(phi, 1, ax)) for ax in range(3)) / d ** 2
     assert np.linalg.norm((lap - rhs).ravel()) <= 1e-9 * np.linalg.norm(rhs.ravel())
+
+
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 3e-5)])
+@pytest.mark.parametrize("topo", [(P, P, P), (P, P, B)])
+@pytest.mark.parametrize("size3", [(32, 16, 64), (64, 32, 16), (16, 64, 32), (128, 128, 128)])
+def test_fused_standalone_solver_vs_oracle_and_complete_path(oc, topo, size3, FT, tol, monkeypatch):
+    """The fused FFT / DCT passes (power-of-two (P,P,P|B) grids) against the oracle and against the complete path, with and
+    without a Helmholtz shift m (fft_based_poisson_solver.jl:95-125)."""
+    rng = np.random.default_rng(5)
+    g, og = grids(oc, FT, topo, size3)
+    rhs = rng.standard_normal(size3).astype(FT)
+    rhs -= rhs.mean(dtype=np.float64).astype(FT)
+    fused = oc.FFTBasedPoissonSolver(g)
+    monkeypatch.setenv("NHSTEP_NO_FAST_POISSON", "1")
+    complete = oc.FFTBasedPoissonSolver(g)
+    monkeypatch.delenv("NHSTEP_NO_FAST_POISSON")
+    assert fused.launch_count() == 0
+    for m in (0.0, -3.5):
+        phi = fused.solve(rhs, m)
+        ref = o.FFTBasedPoissonSolver(og).solve(None, rhs, m)
+        scale = np.abs(ref).max()
+        assert np.abs(phi - ref).max() <= tol * scale, (topo, size3, m)
+        assert np.abs(phi - complete.solve(rhs, m)).max() <= tol * scale
+    assert fused.launch_count() == 10 and complete.launch_count() > 10      # 5 fused launches per solve
