@@ -21,10 +21,13 @@ struct PoissonStandalone : nh_poisson {
     s.stream = stream;
     s.create(gh, kind);
     // fused passes for (Periodic, Periodic, Periodic | Bounded) power-of-two grids; everything else takes the complete path
-    if (kind == NH_SOLVER_FFT && PoissonFast<FT>::supported(gh, true) && !getenv("NHSTEP_NO_FAST_POISSON")) fast.create(gh);
+    if (getenv("NHSTEP_NO_FAST_POISSON")) return;
+    if (kind == NH_SOLVER_FFT && PoissonFast<FT>::supported(gh, true)) fast.create(gh);
+    if (kind == NH_SOLVER_FOURIER_TRIDIAGONAL && PoissonFast<FT>::supported_tridiagonal(gh)) fast.create(gh, true);
   }
   PoissonFast<FT> fast;
   void run(const FT* rhs_dev, FT* phi_dev, double m) {
+    if (fast.ok && fast.tri) { fast.solve_tridiagonal(rhs_dev, phi_dev, stream, *s.lc); return; }
     if (fast.ok) { fast.solve_rhs(rhs_dev, phi_dev, m, stream, *s.lc); return; }
     long long n = s.count();
     int blocks = (int)((n + 255) / 256);

@@ -65,7 +65,7 @@ struct DistState {
     }
     J.twx = twx.p; J.twy = twy.p; J.twz = twz.p; J.lx = lx.p; J.ly = ly.p; J.lz = lz.p;
     for (int d = 0; d < PF_MAXR; ++d) { J.peer[d] = nullptr; peerA[d] = peerB[d] = nullptr; }
-    J.p_next = nullptr;
+    J.p_next = nullptr; J.tw4z = nullptr; J.dzscale = nullptr;
     halo_elems = (size_t)(g.N[0] + 2 * g.H[0]) * g.H[1] * (g.N[2] + 2 * g.H[2]) * 3;
     send_lo.alloc(halo_elems); send_hi.alloc(halo_elems); recv_lo.alloc(halo_elems); recv_hi.alloc(halo_elems);
     PD_SWITCH_N(J.Nx, (set_attr_x<NN>()));

@@ -93,9 +93,23 @@ struct PoissonFast {
     }
     return true;
   }
-  void create(const GridHost<FT>& gh) {
+  // Fourier-tridiagonal variant (standalone): x, y Periodic power-of-two; z Bounded with any spacing, any Nz ≥ 2 —
+  // FFT passes in x and y around a Thomas sweep along z on the half spectrum (pf_thomas_kernel)
+  bool tri = false;
+  DevBuf<PFStale<FT>> stale;
+  DevBuf<FT> tt, lower, dzc1;
+  DevBuf<double> dA, dC;
+  static bool supported_tridiagonal(const GridHost<FT>& gh) {
+    for (int e = 0; e < 2; ++e) {
+      int N = gh.g.N[e];
+      if (gh.g.topo[e] != NH_PERIODIC || N < 16 || N > 1024 || (N & (N - 1))) return false;
+    }
+    return gh.g.topo[2] == NH_BOUNDED && gh.g.N[2] >= 2;
+  }
+  void create(const GridHost<FT>& gh, bool tridiagonal = false) {
     const GridDev<FT>& g = gh.g;
-    zdct = g.topo[2] == NH_BOUNDED;
+    tri = tridiagonal;
+    zdct = !tri && g.topo[2] == NH_BOUNDED;
     gdense = g;
     for (int e = 0; e < 3; ++e) gdense.H[e] = 0;
     gdense.ox = gdense.oy = gdense.oz = 0; gdense.px = g.N[0]; gdense.py = g.N[1]; gdense.pz = g.N[2];
@@ -103,11 +117,28 @@ struct PoissonFast {
     J.g = g; J.Nx = g.N[0]; J.Ny = g.N[1]; J.Nz = g.N[2]; J.Mx = J.Nx / 2 + 2; J.Cx = J.Mx; J.ywrap = 1;
     for (int d = 0; d < PF_MAXR; ++d) J.peer[d] = nullptr;
     J.p_next = nullptr;
-    J.px = ff_make_plan(J.Nx); J.py = ff_make_plan(J.Ny); J.pz = ff_make_plan(J.Nz);
+    J.px = ff_make_plan(J.Nx); J.py = ff_make_plan(J.Ny); J.pz = ff_make_plan(tri ? 16 : J.Nz);
     S.alloc((size_t)J.Mx * J.Ny * J.Nz);
     DevBuf<CT>* tws[3] = {&twx, &twy, &twz};
     DevBuf<double>* ls[3] = {&lx, &ly, &lz};
-    for (int e = 0; e < 3; ++e) {
+    if (tri) {
+      // grid-only parts of the main diagonal and the off-diagonals, in the reference's expression and precision
+      // (compute_main_diagonal!, fourier_tridiagonal_poisson_solver.jl:41-51,88-96)
+      const int Nz = J.Nz;
+      auto Dzf = [&](int k) { return gh.dzf_h[k + g.zoff]; };
+      auto Dzc = [&](int k) { return gh.dzc_h[k + g.zoff]; };
+      std::vector<double> a(Nz), c(Nz);
+      std::vector<FT> low, dz1(Nz);
+      a[0] = (double)(FT(-1) / Dzf(2));
+      for (int k = 2; k <= Nz - 1; ++k) a[k - 1] = (double)(-(FT(1) / Dzf(k + 1) + FT(1) / Dzf(k)));
+      a[Nz - 1] = (double)(FT(-1) / Dzf(Nz));
+      for (int k = 1; k <= Nz; ++k) { c[k - 1] = (double)Dzc(k); dz1[k - 1] = Dzc(k); }
+      for (int q = 2; q <= Nz; ++q) low.push_back(FT(1) / Dzf(q));
+      dA.upload(a); dC.upload(c); lower.upload(low); dzc1.upload(dz1);
+      tt.alloc((size_t)J.Mx * J.Ny * J.Nz);
+      stale.alloc(1);
+    }
+    for (int e = 0; e < (tri ? 2 : 3); ++e) {
       int N = g.N[e];
       std::vector<double> a, b;
       nhhost::twiddles(N, a, b);
@@ -122,7 +153,7 @@ struct PoissonFast {
         tw4z.upload(t4);
       }
     }
-    J.tw4z = tw4z.p;
+    J.tw4z = tw4z.p; J.dzscale = nullptr;
     J.twx = twx.p; J.twy = twy.p; J.twz = twz.p; J.lx = lx.p; J.ly = ly.p; J.lz = lz.p; J.S = S.p;
     smem_x = (size_t)PF_L * ff_line_pitch(J.Nx) * sizeof(CT);
     smem_y = (size_t)PF_L * ff_line_pitch(J.Ny) * sizeof(CT);
@@ -172,8 +203,8 @@ struct PoissonFast {
   void yz_dispatch(int what, dim3 grid, cudaStream_t stream) {
     if (what == 0) {
       yz_size(J.Ny, 0, grid, stream);
-      if (J.Nz != J.Ny) yz_size(J.Nz, 0, grid, stream);
-      if (J.Nx != J.Ny && J.Nx != J.Nz) yz_size(J.Nx, 0, grid, stream);
+      if (J.Nz != J.Ny && !tri) yz_size(J.Nz, 0, grid, stream);
+      if (J.Nx != J.Ny && (tri || J.Nx != J.Nz)) yz_size(J.Nx, 0, grid, stream);
     } else yz_size(what >= 4 ? J.Nx : (what == 2 ? J.Nz : J.Ny), what, grid, stream);   // 4, 5, 6 are x passes
   }
   // rhs = div(u,v,w)/dt → p (interior of the halo'd field); 5 launches on `stream`
@@ -202,6 +233,23 @@ struct PoissonFast {
     yz_dispatch(5, gx, stream);
     J.g = keep;
     lc.n += 5;
+    CUDA_CHECK(cudaGetLastError());
+  }
+  // FourierTridiagonalPoissonSolver: set_source_term! (b·Δz) + solve! (fourier_tridiagonal_poisson_solver.jl:119-147)
+  void solve_tridiagonal(const FT* rhs, FT* phi, cudaStream_t stream, LaunchCounter& lc) {
+    const GridDev<FT> keep = J.g;
+    J.g = gdense; J.dt = 1.0; J.m = 0.0; J.dzscale = dzc1.p; J.S = S.p;
+    dim3 gx(ceil_div(J.Ny, 2 * PF_L), J.Nz), gy(ceil_div(J.Nx / 2 + 1, PF_L), J.Nz);
+    xu = rhs; xv = xw = nullptr; xp = phi;
+    yz_dispatch(6, gx, stream);
+    yz_dispatch(1, gy, stream);
+    dim3 gt(ceil_div(J.Nx / 2 + 1, 128), J.Ny);
+    pf_thomas_kernel<FT, CT><<<gt, 128, 0, stream>>>(J, lower.p, dA.p, dC.p, S.p, tt.p, stale.p);
+    yz_dispatch(3, gy, stream);
+    yz_dispatch(5, gx, stream);
+    pf_stale_gather_kernel<FT><<<1, PF_STALE_MAX, 0, stream>>>(stale.p, phi, J.Nx, J.Ny);
+    J.dzscale = nullptr; J.g = keep;
+    lc.n += 6;
     CUDA_CHECK(cudaGetLastError());
   }
 };

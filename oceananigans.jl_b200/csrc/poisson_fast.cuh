@@ -32,6 +32,7 @@ struct PFJob {
   FFPlan px, py, pz;
   const CT *twx, *twy, *twz;
   const CT* tw4z;                // exp(-iπk/(2Nz)): DCT-II/III post/pre-twiddles for a Bounded z (nullptr when z is Periodic)
+  const FT* dzscale;             // Δzᵃᵃᶜ[k-1]: the Fourier-tridiagonal solver's set_source_term! multiplies b by it (else nullptr)
   const double *lx, *ly, *lz;
   CT* S;
   double dt, m;
@@ -70,6 +71,7 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_x_forward_kernel(const _
     if (RHS) {
       if (rowa) da = u[ra + i0];
       if (rowb) db = u[rb + i0];
+      if (J.dzscale != nullptr) { const FT dzk = J.dzscale[k - 1]; da = da * dzk; db = db * dzk; }
     } else if (rowa) {
       FT vb = v[rb + i0];
       FT tx = Ax * u[ra + ip] - Ax * u[ra + i0];
@@ -270,5 +272,78 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pf_x_inverse_kernel(const _
     const long long r0 = g.idx(1, 0, k);
 #pragma unroll
     for (int m = 0; m < 8; ++m) J.p_next[r0 + t + m * tpl] = (j == J.Ny ? z[m].x : z[m].y) * scale;
+  }
+}
+
+// Fourier-tridiagonal solve on the half spectrum: one thread per (kx, ky) column, lanes across kx (coalesced planes).
+//   solve_batched_tridiagonal_system_z! — src/Solvers/batched_tridiagonal_solver.jl:209-235 (Thomas sweep with the
+//   |β| > 10·eps guard: where it fails ϕ keeps what the previous solve left there — `Phi` persists between solves);
+//   main diagonal D = dA[k] - dC[k]·(λx + λy) in Float64 — compute_main_diagonal!, fourier_tridiagonal_poisson_solver.jl:41-51
+//   (dA, dC are the grid-only parts, tabulated on the host with the reference's expression);
+//   ϕ .= ϕ .- mean(ϕ) — fourier_tridiagonal_poisson_solver.jl:140-147: a real-space constant lives in the (0,0) column, so
+//   the thread that owns it subtracts the column's k-average there, before the inverse transforms.
+// The positions where the guard fails depend only on the matrix, not on the right-hand side (in practice the single
+// singular entry (kx, ky, k) = (0, 0, Nz)).  The reference's ϕ array holds the previous solve's REAL-SPACE solution at
+// that moment, so what it "keeps" there is ϕ_prev[i = kx+1, j = ky+1, k]: PFStale lists those positions (filled by the
+// first solve) and pf_stale_gather_kernel refreshes their values from the real-space output after every solve.
+// f = ϕ̂ = J.S in place (forward-transformed source in, spectral solution out), grid (ceil((Nx/2+1)/128), Ny), block 128
+#define PF_STALE_MAX 64
+template <typename FT>
+struct PFStale { int n; int pos[PF_STALE_MAX][3]; FT val[PF_STALE_MAX]; };
+
+template <typename FT>
+__global__ void pf_stale_gather_kernel(PFStale<FT>* st, const FT* __restrict__ phi, int Nx, int Ny) {
+  const int q = threadIdx.x;
+  if (q < min(st->n, PF_STALE_MAX)) st->val[q] = phi[st->pos[q][0] + (long long)Nx * (st->pos[q][1] + (long long)Ny * st->pos[q][2])];
+}
+
+template <typename FT, typename CT>
+__global__ void __launch_bounds__(128) pf_thomas_kernel(const __grid_constant__ PFJob<FT, CT> J, const FT* __restrict__ lower,
+                                                        const double* __restrict__ dA, const double* __restrict__ dC,
+                                                        CT* __restrict__ Phi, FT* __restrict__ tt, PFStale<FT>* st) {
+  const int kx = blockIdx.x * blockDim.x + threadIdx.x, ky = blockIdx.y;
+  if (kx > J.Nx / 2) return;
+  const int Nz = J.Nz;
+  const long long sz = (long long)J.Mx * J.Ny, col = kx + (long long)J.Mx * ky;
+  const double lam = J.lx[kx] + J.ly[ky];
+  const double guard = 10.0 * (sizeof(FT) == 4 ? 1.1920928955078125e-07 : 2.220446049250313e-16);
+  double beta = dA[0] - dC[0] * lam;
+  const CT f1 = J.S[col];
+  CT prev; prev.x = (FT)((double)f1.x / beta); prev.y = (FT)((double)f1.y / beta);
+  Phi[col] = prev;
+  for (int k = 2; k <= Nz; ++k) {
+    const FT ak = lower[k - 2];
+    const FT tk = (FT)((double)ak / beta);
+    tt[col + sz * (k - 1)] = tk;
+    beta = (dA[k - 1] - dC[k - 1] * lam) - (double)(ak * tk);
+    const CT fk = J.S[col + sz * (k - 1)];
+    CT num; num.x = fk.x - ak * prev.x; num.y = fk.y - ak * prev.y;
+    if (fabs(beta) > guard) { prev.x = (FT)((double)num.x / beta); prev.y = (FT)((double)num.y / beta); }
+    else {
+      // keep what the previous solve left at this index (zero before the first solve)
+      prev.x = FT(0); prev.y = FT(0);
+      const int n = min(st->n, PF_STALE_MAX);
+      int found = -1;
+      for (int q = 0; q < n; ++q) if (st->pos[q][0] == kx && st->pos[q][1] == ky && st->pos[q][2] == k - 1) found = q;
+      if (found >= 0) prev.x = st->val[found];
+      else {
+        const int q = atomicAdd(&st->n, 1);
+        if (q < PF_STALE_MAX) { st->pos[q][0] = kx; st->pos[q][1] = ky; st->pos[q][2] = k - 1; st->val[q] = FT(0); }
+      }
+    }
+    Phi[col + sz * (k - 1)] = prev;
+  }
+  double sx = prev.x, sy = prev.y;
+  for (int k = Nz - 1; k >= 1; --k) {
+    CT here = Phi[col + sz * (k - 1)];
+    const FT tk = tt[col + sz * k];
+    here.x = here.x - tk * prev.x; here.y = here.y - tk * prev.y;
+    Phi[col + sz * (k - 1)] = here;
+    prev = here;
+    sx += here.x; sy += here.y;
+  }
+  if (kx == 0 && ky == 0) {
+    const FT mx = (FT)(sx / Nz), my = (FT)(sy / Nz);
+    for (int k = 0; k < Nz; ++k) { CT h = Phi[col + sz * k]; h.x -= mx; h.y -= my; Phi[col + sz * k] = h; }
   }
 }

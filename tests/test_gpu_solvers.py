@@ -164,3 +164,32 @@ def test_fused_standalone_solver_vs_oracle_and_complete_path(oc, topo, size3, FT
         assert np.abs(phi - ref).max() <= tol * scale, (topo, size3, m)
         assert np.abs(phi - complete.solve(rhs, m)).max() <= tol * scale
     assert fused.launch_count() == 10 and complete.launch_count() > 10      # 5 fused launches per solve
+
+
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-11), (np.float32, 1e-4)])
+@pytest.mark.parametrize("size3", [(16, 16, 8), (32, 16, 21), (64, 32, 40), (128, 128, 64)])
+def test_fused_fourier_tridiagonal_vs_oracle_and_complete_path(oc, size3, FT, tol, monkeypatch):
+    """FFT x/y passes around the Thomas sweep on the half spectrum (stretched Bounded z, any Nz) against the oracle and the
+    complete path; two solves in a row exercise the storage that persists between solves
+    (fourier_tridiagonal_poisson_solver.jl:119-147, batched_tridiagonal_solver.jl:209-235)."""
+    rng = np.random.default_rng(11)
+    Nz = size3[2]
+    faces = np.cumsum(np.concatenate([[0.0], 0.5 + rng.random(Nz)]))
+    g, og = grids(oc, FT, (P, P, B), size3, z=faces)
+    fused = oc.FourierTridiagonalPoissonSolver(g)
+    monkeypatch.setenv("NHSTEP_NO_FAST_POISSON", "1")
+    complete = oc.FourierTridiagonalPoissonSolver(g)
+    monkeypatch.delenv("NHSTEP_NO_FAST_POISSON")
+    ref_solver = o.FourierTridiagonalPoissonSolver(og)
+    base = fused.launch_count()
+    for trial in range(2):
+        rhs = random_rhs(og, rng)
+        phi = fused.solve(rhs)
+        ref_solver.set_source_term(rhs)
+        ref = np.array(ref_solver.solve()).real.astype(FT)
+        scale = np.abs(ref).max()
+        assert np.abs(phi - ref).max() <= tol * scale, (size3, trial, np.abs(phi - ref).max() / scale)
+        assert np.abs(phi - complete.solve(rhs)).max() <= tol * scale
+        if FT == np.float64:                   # in Float32 the 1/Δ² of the residual check swamps √eps at these sizes
+            assert residual_ok(og, phi, rhs)
+    assert fused.launch_count() - base == 12   # x, y, Thomas, y, x + the one-block stale-value gather, per solve
