@@ -122,6 +122,21 @@ __global__ void __launch_bounds__(256) source_term_kernel(GridDev<FT> g, const F
   rhs[(long long)(i - 1) + (long long)g.N[0] * ((j - 1) + (long long)g.N[1] * (k - 1))] = out;
 }
 
+// the same source term as a dense real (Nx, Ny, Nz) array: input of the fused solver passes (poisson_fast.cuh, RHS mode)
+template <typename FT>
+__global__ void __launch_bounds__(256) source_term_real_kernel(GridDev<FT> g, const FT* u, const FT* v, const FT* w, double dt,
+                                                               int times_dz, FT* rhs) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  int k = blockIdx.z + 1;
+  if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
+  FT d = div_ccc(g, u, v, w, i, j, k);
+  if (times_dz) d = g.Dzc(k) * d;
+  FT r;
+  if (sizeof(FT) == 4) r = (FT)((double)d / dt); else r = (FT)(d / (FT)dt);
+  rhs[(long long)(i - 1) + (long long)g.N[0] * ((j - 1) + (long long)g.N[1] * (k - 1))] = r;
+}
+
 // _pressure_correct_velocities! — pressure_correction.jl:31-37 (∂p·Δt evaluated in Float64 for Float32 grids)
 template <typename FT>
 __global__ void __launch_bounds__(256) pressure_correct_kernel(GridDev<FT> g, FT* u, FT* v, FT* w, const FT* p, double dt) {

@@ -77,9 +77,13 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
     fast = fast && gh.g.topo[e] == NH_PERIODIC && adv[e].kind == NH_ADV_WENO && adv[e].B == 3 && gh.g.N[e] >= 2 * gh.g.H[e] && gh.g.H[e] >= 3;
   fast = fast && gh.volume() < (1ll << 31);        // the fused kernel uses 32-bit element offsets
   if (getenv("NHSTEP_NO_FAST")) fast = false;
+  if (!getenv("NHSTEP_NO_FAST_POISSON")) {
+    // fused FFT / DCT / Thomas passes for (Periodic, Periodic, Periodic | Bounded) power-of-two grids, any model physics
+    if (!gh.z_stretched && PoissonFast<FT>::supported(gh, true)) pfast.create(gh);
+    else if (gh.z_stretched && PoissonFast<FT>::supported_tridiagonal(gh)) pfast.create(gh, true);
+  }
   if (fast) {
     for (int a = 0; a < 3; ++a) F2[a] = alloc_field();
-    if (PoissonFast<FT>::supported(gh) && !getenv("NHSTEP_NO_FAST_POISSON")) pfast.create(gh);
     CUDA_CHECK(cudaFuncSetAttribute(tendency_fast_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TF_SMEM_ELEMS * sizeof(FT))));
   }
   update_state(0);
@@ -354,6 +358,19 @@ template <typename FT>
 void Model<FT>::calculate_pressure_correction(double dt) {
   fill_halo_regions(0x7u, 1);
   dim3 blk(64, 4, 1);
+  if (pfast.ok) {
+    // fused passes: real source term (same expression as below) → x/y FFT + z FFT | DCT | Thomas → interior of pNHS
+    const long long n = (long long)gh.g.N[0] * gh.g.N[1] * gh.g.N[2];
+    if (prhs.n < (size_t)n) prhs.alloc(n, false);
+    source_term_real_kernel<FT><<<grid3(blk), blk, 0, stream>>>(gh.g, F[0], F[1], F[2], dt, pfast.tri ? 1 : 0, prhs.p);
+    KLAUNCH(lc);
+    if (pfast.tri) pfast.solve_tridiagonal(prhs.p, pNHS, stream, lc, false, &gh.g);
+    else pfast.solve_rhs(prhs.p, pNHS, 0.0, stream, lc, &gh.g);
+    fill_halo_regions(1u << NH_FIELD_PNHS, 1);
+    p_halo_stale = false;
+    CUDA_CHECK(cudaGetLastError());
+    return;
+  }
   CT* rhs = solver.A.p;
   source_term_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(gh.g, F[0], F[1], F[2], dt,
                                                             solver.kind == NH_SOLVER_FOURIER_TRIDIAGONAL ? 1 : 0, rhs);

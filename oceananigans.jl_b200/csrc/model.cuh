@@ -221,7 +221,8 @@ struct PoissonFast {
     CUDA_CHECK(cudaGetLastError());
   }
   // solve!(ϕ, solver, b, m) on dense device arrays (fft_based_poisson_solver.jl:95-125): ϕ = Re(𝓕⁻¹[-𝓕b / (λ - m)])
-  void solve_rhs(const FT* rhs, FT* phi, double m, cudaStream_t stream, LaunchCounter& lc) {
+  // `out` = layout of ϕ (nullptr: dense like b; a model passes its halo'd field geometry and gets the interior written)
+  void solve_rhs(const FT* rhs, FT* phi, double m, cudaStream_t stream, LaunchCounter& lc, const GridDev<FT>* out = nullptr) {
     const GridDev<FT> keep = J.g;
     J.g = gdense; J.dt = 1.0; J.m = m;
     dim3 gx(ceil_div(J.Ny, 2 * PF_L), J.Nz), gy(ceil_div(J.Nx / 2 + 1, PF_L), J.Nz), gz(ceil_div(J.Nx / 2 + 1, PF_L), J.Ny);
@@ -230,15 +231,18 @@ struct PoissonFast {
     yz_dispatch(1, gy, stream);
     yz_dispatch(2, gz, stream);
     yz_dispatch(3, gy, stream);
+    if (out) J.g = *out;
     yz_dispatch(5, gx, stream);
     J.g = keep;
     lc.n += 5;
     CUDA_CHECK(cudaGetLastError());
   }
   // FourierTridiagonalPoissonSolver: set_source_term! (b·Δz) + solve! (fourier_tridiagonal_poisson_solver.jl:119-147)
-  void solve_tridiagonal(const FT* rhs, FT* phi, cudaStream_t stream, LaunchCounter& lc) {
+  // times_dz = false: b already carries the Δz factor (the model's _fourier_tridiagonal_source_term!)
+  void solve_tridiagonal(const FT* rhs, FT* phi, cudaStream_t stream, LaunchCounter& lc, bool times_dz = true,
+                         const GridDev<FT>* out = nullptr) {
     const GridDev<FT> keep = J.g;
-    J.g = gdense; J.dt = 1.0; J.m = 0.0; J.dzscale = dzc1.p; J.S = S.p;
+    J.g = gdense; J.dt = 1.0; J.m = 0.0; J.dzscale = times_dz ? dzc1.p : nullptr; J.S = S.p;
     dim3 gx(ceil_div(J.Ny, 2 * PF_L), J.Nz), gy(ceil_div(J.Nx / 2 + 1, PF_L), J.Nz);
     xu = rhs; xv = xw = nullptr; xp = phi;
     yz_dispatch(6, gx, stream);
@@ -246,8 +250,9 @@ struct PoissonFast {
     dim3 gt(ceil_div(J.Nx / 2 + 1, 128), J.Ny);
     pf_thomas_kernel<FT, CT><<<gt, 128, 0, stream>>>(J, lower.p, dA.p, dC.p, S.p, tt.p, stale.p);
     yz_dispatch(3, gy, stream);
+    if (out) J.g = *out;
     yz_dispatch(5, gx, stream);
-    pf_stale_gather_kernel<FT><<<1, PF_STALE_MAX, 0, stream>>>(stale.p, phi, J.Nx, J.Ny);
+    pf_stale_gather_kernel<FT><<<1, PF_STALE_MAX, 0, stream>>>(stale.p, phi, J.g);
     J.dzscale = nullptr; J.g = keep;
     lc.n += 6;
     CUDA_CHECK(cudaGetLastError());
@@ -328,7 +333,8 @@ struct Model : nh_model {
   SchemeDev adv[3];
   SchemeTables<FT> tab;
   PoissonGeneric<FT> solver;
-  PoissonFast<FT> pfast;
+  PoissonFast<FT> pfast;   // fused solver passes where the grid allows (else the complete `solver` does the work)
+  DevBuf<FT> prhs;         // dense real source term for them on the complete path
   DevBuf<FT> stage;        // staging for host <-> device field copies
   DevBuf<double> red;      // reduction scratch
   FT rk_g1, rk_g2, rk_g3, rk_z2, rk_z3, chi;

@@ -292,9 +292,9 @@ template <typename FT>
 struct PFStale { int n; int pos[PF_STALE_MAX][3]; FT val[PF_STALE_MAX]; };
 
 template <typename FT>
-__global__ void pf_stale_gather_kernel(PFStale<FT>* st, const FT* __restrict__ phi, int Nx, int Ny) {
+__global__ void pf_stale_gather_kernel(PFStale<FT>* st, const FT* __restrict__ phi, GridDev<FT> g) {
   const int q = threadIdx.x;
-  if (q < min(st->n, PF_STALE_MAX)) st->val[q] = phi[st->pos[q][0] + (long long)Nx * (st->pos[q][1] + (long long)Ny * st->pos[q][2])];
+  if (q < min(st->n, PF_STALE_MAX)) st->val[q] = phi[g.idx(st->pos[q][0] + 1, st->pos[q][1] + 1, st->pos[q][2] + 1)];
 }
 
 template <typename FT, typename CT>

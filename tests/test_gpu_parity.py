@@ -339,4 +339,35 @@ def test_fused_poisson_matches_complete_solver(oc, monkeypatch):
         oc.time_step(m, 2e-3, n_steps=5)
         out.append([m.velocities[n].interior() for n in "uvw"] + [m.pressures.pNHS.parent()])
     for a, b in zip(*out):
-        assert rel_l2(a, b) < 1e-13
+        assert rel_l2(a, b) < 1e-12
+
+
+@pytest.mark.parametrize("stretched", [False, True], ids=["dct", "tridiagonal"])
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+def test_bounded_z_models_on_fused_solver_passes(oc, stretched, timestepper, monkeypatch):
+    """(Periodic, Periodic, Bounded) models with power-of-two horizontal sizes take the fused solver passes (DCT along a
+    regular z, Thomas sweep along a stretched z) inside the complete path: against the oracle and against the complete
+    solver, Centered + closure + Coriolis physics, 30 steps."""
+    Nz = 16 if not stretched else 12
+    k = np.arange(1, Nz + 2)
+    z = np.tanh(1.3 * (2 * (k - 1) / Nz - 1)) / np.tanh(1.3) if stretched else (0, 1)
+    kw = dict(z=z, timestepper=timestepper, advection=("Centered", 4), coriolis=1e-2, closure=(1e-3, 1e-3))
+    size = (32, 16, Nz)
+    m1, m2 = make_pair(oc, np.float64, size, (P, P, B), **kw)
+    monkeypatch.setenv("NHSTEP_NO_FAST_POISSON", "1")
+    m3, _ = make_pair(oc, np.float64, size, (P, P, B), **kw)
+    monkeypatch.delenv("NHSTEP_NO_FAST_POISSON")
+    counts = []
+    for m in (m1, m3):
+        base = m.launch_count()
+        oc.calculate_pressure_correction(m, 1.0)
+        counts.append(m.launch_count() - base)
+    assert counts[0] < counts[1], f"the fused passes were not taken: {counts}"
+    ics = smooth_ics(m2, np.random.default_rng(21), amp=0.5)
+    err = _run_steps(oc, m1, m2, ics, 5e-3, 30)
+    check_parity(err, 1e-12)
+    oc.set_model(m3, **ics)
+    oc.time_step(m3, 5e-3, n_steps=30)
+    for n in "uvw":
+        assert rel_l2(m1.velocities[n].interior(), m3.velocities[n].interior()) < 1e-12
+    assert rel_l2(m1.pressures.pNHS.interior(), m3.pressures.pNHS.interior()) < 1e-11
