@@ -1,4 +1,6 @@
-"""Quick phase timing of one model configuration (development aid): python tools/time_phases.py [N] [steps]"""
+"""Quick phase timing of one model configuration (development aid):
+   python tools/time_phases.py [N] [steps] [f32] [ppb | les]
+   ppb: (Periodic, Periodic, Bounded) WENO5, no tracers;  les: ppb + buoyancy tracer b + ScalarDiffusivity + FPlane"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -7,10 +9,20 @@ from bench import smooth_ics
 
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
-FT = np.float32 if (len(sys.argv) > 3 and sys.argv[3] == "f32") else np.float64
-g = oc.RectilinearGrid(FT, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=(oc.Periodic,) * 3)
-m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5))
-oc.set_model(m, **smooth_ics(N, 1234))
+FT = np.float32 if "f32" in sys.argv else np.float64
+bounded = "ppb" in sys.argv or "les" in sys.argv
+topo = (oc.Periodic, oc.Periodic, oc.Bounded if bounded else oc.Periodic)
+g = oc.RectilinearGrid(FT, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=topo)
+kw = {}
+if "les" in sys.argv:
+    kw = dict(buoyancy=oc.BuoyancyTracer(), tracers=("b",), closure=oc.ScalarDiffusivity(1e-4, 1e-4), coriolis=oc.FPlane(1e-4))
+m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), **kw)
+ics = smooth_ics(N, 1234)
+if bounded:
+    ics["w"] = np.concatenate([ics["w"], ics["w"][:, :, :1]], axis=2)
+    ics["w"][:, :, 0] = 0
+    ics["w"][:, :, -1] = 0
+oc.set_model(m, **ics)
 dt = 0.2 * (2 * np.pi / N) / 2.0
 oc.time_step(m, dt, n_steps=3)
 acc = {}
