@@ -27,13 +27,13 @@ def main():
     m = D.DistributedNonhydrostaticModel(arch, FT, size=(Nx, Ny, Nz), x=(0, 2 * np.pi), y=(0, 2 * np.pi), z=(0, 2 * np.pi),
                                          advection=oc.WENO(FT, 5), device=local, p2p="p2p" in sys.argv)
     rng = np.random.default_rng(1)
-    x, y, z = (np.arange(n) / n for n in (Nx, Ny, Nz))
+    x, y, z = np.arange(Nx) / Nx, (m.j0 + np.arange(m.NyL)) / Ny, np.arange(Nz) / Nz     # this rank's rows only
     ics = {}
     for name in "uvw":
         k, ph = rng.integers(1, 4, 3), rng.uniform(0, 6.28, 3)
         ics[name] = (np.cos(6.28 * k[0] * x + ph[0])[:, None, None] * np.cos(6.28 * k[1] * y + ph[1])[None, :, None]
                      * np.cos(6.28 * k[2] * z + ph[2])[None, None, :]).astype(FT)
-    m.set(**ics)
+    m.set_local(**ics)
     dt = 0.2 * (2 * np.pi / Nx) / 2.0
 
     def sync():
