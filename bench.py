@@ -24,6 +24,8 @@ sys.path.insert(0, ROOT)
 
 METRIC = "cell-updates/s (NonhydrostaticModel WENO step)"
 UNIT = "cell-updates/s"
+# FP64-pipe instructions per cell of tendency_fast_kernel (ncu opcode mix, profiles/r1_tendency_sass_mix.md)
+FP64_INSTR_PER_CELL = {"exact": 1290.0, "contracted": 750.0}
 
 
 def peaks():
@@ -228,7 +230,11 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--ref-size", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    # contracted: FMA contraction in the tendency sweep (what a GPU build of the reference computes; within the north_star
+    # tolerance of the CPU reference); exact: bit-identical to the reference's CPU arithmetic.  Both are reported at N = 1.
+    ap.add_argument("--arithmetic", choices=["contracted", "exact"], default="contracted")
     args = ap.parse_args()
+    exact = args.arithmetic == "exact"
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -250,7 +256,7 @@ def main():
     if world == 1:
         gsize = (N, N, N)
         grid = oc.RectilinearGrid(np.float64, size=gsize, extent=(2 * np.pi,) * 3, topology=(oc.Periodic,) * 3, device=local_rank)
-        model = oc.NonhydrostaticModel(grid, advection=oc.WENO(order=5), timestepper="RungeKutta3")
+        model = oc.NonhydrostaticModel(grid, advection=oc.WENO(order=5), timestepper="RungeKutta3", exact_arithmetic=exact)
         oc.set_model(model, **smooth_ics(N, 1234))
         step = lambda n=1: oc.time_step(model, dt, n_steps=n)                              # noqa: E731
         profiled = lambda: oc.time_step_profiled(model, dt)                                # noqa: E731
@@ -265,7 +271,8 @@ def main():
         arch = D.Distributed(D.Partition(y=world))
         model = D.DistributedNonhydrostaticModel(arch, np.float64, size=gsize, x=(0, 2 * np.pi * fx), y=(0, 2 * np.pi * fy),
                                                  z=(-2 * np.pi, 0), advection=oc.WENO(order=5), timestepper="RungeKutta3",
-                                                 device=local_rank, p2p=not os.environ.get("NHSTEP_NO_P2P"))
+                                                 device=local_rank, p2p=not os.environ.get("NHSTEP_NO_P2P"),
+                                                 exact_arithmetic=exact)
         model.set_local(**smooth_ics(N, 1234, gsize, (model.j0, model.NyL)))
         step = lambda n=1: model.time_step(dt, n_steps=n)                                  # noqa: E731
         profiled = lambda: model.time_step_profiled(dt)                                    # noqa: E731
@@ -330,13 +337,31 @@ def main():
                                "frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak},
                 "phase_ms_per_step": phases}
     if dom == "tendencies_substep":
-        # the sweep is FP64-issue bound, not HBM bound: ≈ 1290 FP64 instructions per cell (ncu opcode mix,
+        # the sweep is FP64-issue bound, not HBM bound: FP64 instructions per cell (ncu opcode mix,
         # profiles/r1_tendency_sass_mix.md) against 64 FP64 instr/clk/SM × 148 SMs at the sampled SM clock
         mhz = (clocks or {}).get("sm_mhz") or 1965.0
         fp64_peak = 64 * 148 * mhz * 1e6
-        fp64_rate = 1290.0 * cells / (phases[dom] / 3 * 1e-3)
-        roofline["fp64_pipe"] = {"instr_per_cell": 1290, "achieved_instr_per_s": fp64_rate, "peak_instr_per_s": fp64_peak,
+        per_cell = FP64_INSTR_PER_CELL[args.arithmetic]
+        fp64_rate = per_cell * cells / (phases[dom] / 3 * 1e-3)
+        roofline["fp64_pipe"] = {"instr_per_cell": per_cell, "achieved_instr_per_s": fp64_rate, "peak_instr_per_s": fp64_peak,
                                  "frac": fp64_rate / fp64_peak}
+
+    # ---- the other arithmetic mode, same workload (N = 1 only): a shorter timed run for the record ----
+    other = None
+    if world == 1:
+        m2 = oc.NonhydrostaticModel(grid, advection=oc.WENO(order=5), timestepper="RungeKutta3", exact_arithmetic=not exact)
+        oc.set_model(m2, **smooth_ics(N, 1234))
+        n2 = max(1, min(args.steps, 20))
+        oc.time_step(m2, dt, n_steps=max(3, args.warmup))
+        torch.cuda.synchronize()
+        e0.record()
+        oc.time_step(m2, dt, n_steps=n2)
+        e1.record()
+        torch.cuda.synchronize()
+        ms2 = e0.elapsed_time(e1) / n2
+        other = {"arithmetic": "contracted" if exact else "exact", "ms_per_step": ms2, "value": cells / (ms2 * 1e-3),
+                 "unit": UNIT, "steps": n2}
+        del m2
 
     # ---- e2e: HOST buffers through the C ABI; H2D of u,v,w and D2H of u,v,w,p inside the timed region ----
     from oceananigans_jl_b200.model import pinned_empty
@@ -381,6 +406,10 @@ def main():
                 "data": "synthetic",
                 "config": {"workload": f"3D triply-periodic NonhydrostaticModel {N}^3 Float64 WENO5 RK3 FFTBasedPoissonSolver"
                            + (f" per GPU (global {gsize[0]}x{gsize[1]}x{gsize[2]})" if world > 1 else ""),
+                           "arithmetic": ("exact: bit-identical to the reference's CPU arithmetic (no FMA contraction)" if exact else
+                                          "contracted: FMA contraction + regrouped WENO5 weights in the tendency sweep, "
+                                          "rel. L2 <= 1e-12 vs the oracle after 100 steps (tests/test_gpu_parity.py)"),
+                           "other_arithmetic": other,
                            "l2_policy": "working set (>= 10 fields x %.0f MB) exceeds the 126 MB L2" % (cells * FT_B / 1e6),
                            "parallelism": "single GPU" if world == 1 else
                            (f"y-slabs over {world} GPUs: kernels store halo rows and FFT transpose blocks into the peers' "

@@ -84,7 +84,7 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   }
   if (fast) {
     for (int a = 0; a < 3; ++a) F2[a] = alloc_field();
-    CUDA_CHECK(cudaFuncSetAttribute(tendency_fast_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TF_SMEM_ELEMS * sizeof(FT))));
+    CUDA_CHECK(cudaFuncSetAttribute(tendency_fast_kernel<FT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TF_SMEM_ELEMS * sizeof(FT))));
   }
   update_state(0);
 }
@@ -109,7 +109,7 @@ void Model<FT>::fast_stage(int mode, FT dt, FT c1, FT c2, double stage_dt) {
   FastTendJob<FT> J;
   J.g = gh.g; J.tab = tab; J.dt = dt; J.gamma = c1; J.zeta = c2; J.mode = mode;
   for (int a = 0; a < 3; ++a) { J.U[a] = F[a]; J.Unew[a] = F2[a]; J.Gn[a] = Gn[a]; J.Gm[a] = Gm[a]; }
-  launch_fused_tendency<FT>(J, stream);
+  launch_fused_tendency<FT>(J, stream, desc.exact_arithmetic != 0);
   KLAUNCH(lc);
   mark(0);
   for (int a = 0; a < 3; ++a) std::swap(F[a], F2[a]);

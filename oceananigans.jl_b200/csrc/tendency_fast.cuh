@@ -43,25 +43,74 @@ struct FastTendJob {
 };
 
 // face flux F_{b,a} at flux-location index n (linear), strides sa (dim a) and sb (dim b)
-template <typename FT, bool SAME>
+template <typename FT, bool SAME, int VARIANT = 0>
 __device__ __forceinline__ FT fast_flux(const SchemeTables<FT>& T, const FT* __restrict__ ua, const FT* __restrict__ ub,
                                         int n, int sa, int sb, FT Ab) {
   // advecting velocity: Centered(4) interpolation of A_b·U_b along dim b onto a Centre (SAME) or along dim a onto a Face
   const int ss = SAME ? sb : sa;
   const int s0 = SAME ? 1 : 0;
-  FT ut = T.sym[2][3] * (Ab * ub[n + (-2 + s0) * ss]);
-  ut = ut + T.sym[2][2] * (Ab * ub[n + (-1 + s0) * ss]);
-  ut = ut + T.sym[2][1] * (Ab * ub[n + (0 + s0) * ss]);
-  ut = ut + T.sym[2][0] * (Ab * ub[n + (1 + s0) * ss]);
+  FT ut;
+  if (VARIANT == 0) {
+    ut = T.sym[2][3] * (Ab * ub[n + (-2 + s0) * ss]);
+    ut = ut + T.sym[2][2] * (Ab * ub[n + (-1 + s0) * ss]);
+    ut = ut + T.sym[2][1] * (Ab * ub[n + (0 + s0) * ss]);
+    ut = ut + T.sym[2][0] * (Ab * ub[n + (1 + s0) * ss]);
+  } else {
+    // contracted build: the constant face area factored out of the four-point sum
+    ut = T.sym[2][3] * ub[n + (-2 + s0) * ss] + T.sym[2][2] * ub[n + (-1 + s0) * ss];
+    ut = (ut + T.sym[2][1] * ub[n + (0 + s0) * ss]) + T.sym[2][0] * ub[n + (1 + s0) * ss];
+    ut = Ab * ut;
+  }
   const bool left = ut > FT(0);
   // upwind stencil without a branch: left bias reads offsets -3…1, right bias 2…-2 (reversed), from the same pointer
   const int ds = left ? sb : -sb;
   const FT* p = ua + n + s0 * sb + (left ? -3 * sb : 2 * sb);
   FT q0 = p[0], q1 = p[ds], q2 = p[2 * ds], q3 = p[3 * ds], q4 = p[4 * ds];
-  return ut * weno5_from_q<FT>(T, q0, q1, q2, q3, q4);
+  if (VARIANT == 0) return ut * weno5_from_q<FT>(T, q0, q1, q2, q3, q4);
+  return ut * weno5_contracted<FT>(T, q0, q1, q2, q3, q4);
 }
 
-template <typename FT>
+// `count` consecutive face fluxes F_{b,a} along direction b (stride sb), starting at flux location n: the same arithmetic
+// as fast_flux, with the stencil S[m] = U_a[n + (s0-3+m)·sb], m = 0…5, carried in registers from one face to the next
+// (left bias uses S[0…4], right bias S[5…1]); when a == b the advecting velocity reads the same window (S[1…4]).
+template <typename FT, int VARIANT>
+__device__ __forceinline__ void march_fluxes(const SchemeTables<FT>& T, const FT* __restrict__ ua, const FT* __restrict__ ub,
+                                             bool same, int n, int sb, int sa, FT Ab, int count, FT* out, int ostride) {
+  static_assert(TF_THREADS == TF_TX * TF_TY && TF_THREADS == TF_TX * TF_TZ, "one thread per line of faces");
+  const FT* p = ua + (n + ((same ? 1 : 0) - 3) * sb);
+  FT S0 = p[0], S1 = p[sb], S2 = p[2 * sb], S3 = p[3 * sb], S4 = p[4 * sb];
+  p += 5 * sb;
+  const FT* pb = ub + (n - 2 * sa);
+#pragma unroll 1
+  for (int c = 0; c < count; ++c) {
+    const FT S5 = *p;
+    FT u0, u1, u2, u3;
+    if (same) { u0 = S1; u1 = S2; u2 = S3; u3 = S4; }
+    else { u0 = pb[0]; u1 = pb[sa]; u2 = pb[2 * sa]; u3 = pb[3 * sa]; }
+    FT ut;
+    if (VARIANT == 0) {
+      ut = T.sym[2][3] * (Ab * u0);
+      ut = ut + T.sym[2][2] * (Ab * u1);
+      ut = ut + T.sym[2][1] * (Ab * u2);
+      ut = ut + T.sym[2][0] * (Ab * u3);
+    } else {
+      ut = T.sym[2][3] * u0 + T.sym[2][2] * u1;
+      ut = (ut + T.sym[2][1] * u2) + T.sym[2][0] * u3;
+      ut = Ab * ut;
+    }
+    const bool left = ut > FT(0);
+    const FT q0 = left ? S0 : S5, q1 = left ? S1 : S4, q2 = left ? S2 : S3, q3 = left ? S3 : S2, q4 = left ? S4 : S1;
+    *out = ut * (VARIANT == 0 ? weno5_from_q<FT>(T, q0, q1, q2, q3, q4) : weno5_contracted<FT>(T, q0, q1, q2, q3, q4));
+    out += ostride;
+    S0 = S1; S1 = S2; S2 = S3; S3 = S4; S4 = S5;
+    p += sb; pb += sb;
+  }
+}
+
+// VARIANT only gives the two builds of this kernel different symbols: 0 is compiled with -fmad=false like the rest of the
+// library (bit-identical to the reference's CPU arithmetic), 1 lives in tendency_fma.cu, compiled with FMA contraction
+// (nh_model_desc.exact_arithmetic = 0: ≈ ⅓ fewer FP64 instructions, results within rounding of the exact build).
+template <typename FT, int VARIANT = 0>
 __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel(const __grid_constant__ FastTendJob<FT> J) {
   extern __shared__ __align__(16) unsigned char tf_smem[];
   typedef FT (*FxT)[TF_TY][TF_TX + 1];
@@ -88,22 +137,17 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
       int li = t % (TF_TX + 1), lj = (t / (TF_TX + 1)) % TF_TY, lk = t / ((TF_TX + 1) * TF_TY);
       // partial tiles: clamp to the last valid point (the value is computed but never used)
       int n = g.idx32(i0 + min(li, nx) - (a == 0 ? 1 : 0), j0 + min(lj, ny - 1), k0 + min(lk, nz - 1));
-      Fx[lk][lj][li] = a == 0 ? fast_flux<FT, true>(J.tab, ua, J.U[0], n, sa, 1, Ax)
-                              : fast_flux<FT, false>(J.tab, ua, J.U[0], n, sa, 1, Ax);
+      Fx[lk][lj][li] = a == 0 ? fast_flux<FT, true, VARIANT>(J.tab, ua, J.U[0], n, sa, 1, Ax)
+                              : fast_flux<FT, false, VARIANT>(J.tab, ua, J.U[0], n, sa, 1, Ax);
     }
-#pragma unroll tf_unroll
-    for (int t = tid; t < TF_TX * (TF_TY + 1) * TF_TZ; t += TF_THREADS) {
-      int li = t % TF_TX, lj = (t / TF_TX) % (TF_TY + 1), lk = t / (TF_TX * (TF_TY + 1));
-      int n = g.idx32(i0 + min(li, nx - 1), j0 + min(lj, ny) - (a == 1 ? 1 : 0), k0 + min(lk, nz - 1));
-      Fy[lk][lj][li] = a == 1 ? fast_flux<FT, true>(J.tab, ua, J.U[1], n, sa, st[1], Ay)
-                              : fast_flux<FT, false>(J.tab, ua, J.U[1], n, sa, st[1], Ay);
-    }
-#pragma unroll tf_unroll
-    for (int t = tid; t < TF_TX * TF_TY * (TF_TZ + 1); t += TF_THREADS) {
-      int li = t % TF_TX, lj = (t / TF_TX) % TF_TY, lk = t / (TF_TX * TF_TY);
-      int n = g.idx32(i0 + min(li, nx - 1), j0 + min(lj, ny - 1), k0 + min(lk, nz) - (a == 2 ? 1 : 0));
-      Fz[lk][lj][li] = a == 2 ? fast_flux<FT, true>(J.tab, ua, J.U[2], n, sa, st[2], Az)
-                              : fast_flux<FT, false>(J.tab, ua, J.U[2], n, sa, st[2], Az);
+    // ---- y- and z-direction fluxes: one thread per line of faces, marching along the flux direction with the six
+    // stencil values in registers (each row / plane of U_a is loaded once per line instead of five times)
+    {
+      const int li = tid & (TF_TX - 1), lo = tid / TF_TX, ci = i0 + min(li, nx - 1);
+      march_fluxes<FT, VARIANT>(J.tab, ua, J.U[1], a == 1, g.idx32(ci, j0 - (a == 1 ? 1 : 0), k0 + min(lo, nz - 1)),
+                                st[1], sa, Ay, ny + 1, &Fy[lo][0][li], TF_TX);
+      march_fluxes<FT, VARIANT>(J.tab, ua, J.U[2], a == 2, g.idx32(ci, j0 + min(lo, ny - 1), k0 - (a == 2 ? 1 : 0)),
+                                st[2], sa, Az, nz + 1, &Fz[0][lo][li], TF_TY * TF_TX);
     }
     __syncthreads();
     // ---- divergence, tendency, substep
@@ -130,12 +174,15 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
   }
 }
 
-// host launch of the fused tendency + substep sweep
+// host launch of the fused tendency + substep sweep; the contracted build is defined in tendency_fma.cu
+template <typename FT> void launch_fused_tendency_fma(const FastTendJob<FT>& J, cudaStream_t stream);
+
 template <typename FT>
-inline void launch_fused_tendency(const FastTendJob<FT>& J, cudaStream_t stream) {
+inline void launch_fused_tendency(const FastTendJob<FT>& J, cudaStream_t stream, bool exact = true) {
+  if (!exact) { launch_fused_tendency_fma<FT>(J, stream); return; }
   const GridDev<FT>& g = J.g;
   dim3 grd(ceil_div(g.N[0], TF_TX), ceil_div(g.N[1], TF_TY), ceil_div(g.N[2], TF_TZ));
-  tendency_fast_kernel<FT><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
+  tendency_fast_kernel<FT, 0><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
 }
 
 // Periodic halo fill of several fields in ONE launch: every halo cell reads its wrapped interior image directly

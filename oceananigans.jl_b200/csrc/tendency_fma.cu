@@ -1,0 +1,23 @@
+// tendency_fma.cu — the fused tendency + substep sweep compiled WITH floating-point contraction (the Makefile builds this
+// one translation unit with -fmad=true).  Selected by nh_model_desc.exact_arithmetic = 0: the same source as the exact
+// kernel, so every a·b + c of the reference's expressions becomes one FMA (one rounding instead of two).  Results are not
+// bit-identical to the reference's CPU code any more but stay within the north_star tolerance (tests/test_gpu_parity.py
+// test_contracted_arithmetic_*), with roughly a third fewer FP64 instructions per cell.
+#include "fft_generic.cuh"      // cx_of (two-element vector types)
+#include "tendency_fast.cuh"
+
+template <typename FT>
+void launch_fused_tendency_fma(const FastTendJob<FT>& J, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    CUDA_CHECK(cudaFuncSetAttribute(tendency_fast_kernel<FT, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)(TF_SMEM_ELEMS * sizeof(FT))));
+    attr_set = true;
+  }
+  const GridDev<FT>& g = J.g;
+  dim3 grd(ceil_div(g.N[0], TF_TX), ceil_div(g.N[1], TF_TY), ceil_div(g.N[2], TF_TZ));
+  tendency_fast_kernel<FT, 1><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
+}
+
+template void launch_fused_tendency_fma<float>(const FastTendJob<float>&, cudaStream_t);
+template void launch_fused_tendency_fma<double>(const FastTendJob<double>&, cudaStream_t);

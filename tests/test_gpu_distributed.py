@@ -42,12 +42,13 @@ def _single_gpu(size, FT, timestepper, steps, dt):
     return {n: m.velocities[n].interior() for n in "uvw"} | {"pNHS": m.pressures.pNHS.interior(), "time": m.clock.time}
 
 
-def _distributed(rank, world, size, FT, timestepper, steps, dt, out, p2p=False):
+def _distributed(rank, world, size, FT, timestepper, steps, dt, out, p2p=False, exact=True):
     import oceananigans_jl_b200 as oc
     from oceananigans_jl_b200 import distributed as D
     arch = D.Distributed(D.Partition(y=world))
     m = D.DistributedNonhydrostaticModel(arch, FT, size=size, x=(0, 1), y=(0, 2), z=(0, 1), halo=(3, 3, 3),
-                                         advection=oc.WENO(FT, 5), timestepper=timestepper, device=rank, p2p=p2p)
+                                         advection=oc.WENO(FT, 5), timestepper=timestepper, device=rank, p2p=p2p,
+                                         exact_arithmetic=exact)
     m.set(**_ics(size, FT))
     div0 = m.max_abs_divergence()
     m.time_step(dt, n_steps=steps)
@@ -84,7 +85,8 @@ def test_one_rank_distributed_path_matches_single_gpu(FT, timestepper, size, p2p
     _check(out, ref, FT, steps, dt)
 
 
-def test_one_rank_distributed_path_matches_oracle():
+@pytest.mark.parametrize("exact", [True, False], ids=["exact", "contracted"])
+def test_one_rank_distributed_path_matches_oracle(exact):
     import oracle as o
     size, steps, dt, FT = (16, 32, 16), 10, 2e-3, np.float64
     grid = o.RectilinearGrid(FT, size=size, x=(0, 1), y=(0, 2), z=(0, 1), halo=(3, 3, 3),
@@ -95,7 +97,7 @@ def test_one_rank_distributed_path_matches_oracle():
         o.time_step(m, dt)
     ref = {n: m.velocities[a].interior for a, n in enumerate("uvw")} | {"pNHS": m.pNHS.interior}
     out = {}
-    _distributed(0, 1, size, FT, "RungeKutta3", steps, dt, out)
+    _distributed(0, 1, size, FT, "RungeKutta3", steps, dt, out, exact=exact)
     for n in ("u", "v", "w", "pNHS"):
         assert _rel(out[n], ref[n]) <= 1e-12, (n, _rel(out[n], ref[n]))
 

@@ -33,7 +33,7 @@ def rel_l2(a, b):
 
 
 def make_pair(oc, FT, size, topo, z=None, advection=("WENO", 5), timestepper="RungeKutta3", buoyancy=None, coriolis=None,
-              closure=None, tracers=(), extent=None, x=None, y=None):
+              closure=None, tracers=(), extent=None, x=None, y=None, exact_arithmetic=True):
     """The same model twice: (CUDA, oracle)."""
     kw = {}
     if extent is not None:
@@ -63,7 +63,7 @@ def make_pair(oc, FT, size, topo, z=None, advection=("WENO", 5), timestepper="Ru
     k1 = oc.ScalarDiffusivity(*closure) if closure else None
     k2 = o.ScalarDiffusivity(*closure) if closure else None
     m1 = oc.NonhydrostaticModel(g1, advection=adv(oc, None), timestepper=timestepper, buoyancy=b1, coriolis=c1, closure=k1,
-                                tracers=tracers)
+                                tracers=tracers, exact_arithmetic=exact_arithmetic)
     m2 = o.NonhydrostaticModel(g2, advection=adv(o, FT), timestepper=timestepper, buoyancy=b2, coriolis=c2, closure=k2,
                                tracers=tracers)
     return m1, m2
@@ -320,6 +320,39 @@ def test_fused_poisson_path_100_steps_vs_oracle(oc, FT, tol, size):
     check_parity(err, tol)
     oc.fill_halo_regions(list(m1.velocities.values()))
     assert m1.max_abs_divergence() < (1e-11 if FT == np.float64 else 5e-3)
+
+
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+@pytest.mark.parametrize("size", [(24, 24, 24), (64, 16, 32), (40, 24, 16)])
+def test_contracted_arithmetic_100_steps_vs_oracle(oc, FT, tol, timestepper, size):
+    """exact_arithmetic=False (tendency_fma.cu: FMA contraction, regrouped WENO5 weights, the arithmetic a GPU build of the
+    reference produces) stays within the north_star tolerance of the oracle after 100 steps."""
+    m1, m2 = make_pair(oc, FT, size, (P, P, P), extent=(2 * np.pi,) * 3, timestepper=timestepper, exact_arithmetic=False)
+    _, m3 = make_pair(oc, FT, size, (P, P, P), extent=(2 * np.pi,) * 3, timestepper=timestepper)
+    ics = smooth_ics(m2, np.random.default_rng(1234))
+    dt = 0.2 * (2 * np.pi / max(size)) / 2.0
+    err, floor = _run_steps(oc, m1, m2, ics, dt, 100, m3)
+    check_parity(err, tol, floor)
+    oc.fill_halo_regions(list(m1.velocities.values()))
+    assert m1.max_abs_divergence() < (1e-11 if FT == np.float64 else 5e-3)
+
+
+def test_contracted_arithmetic_is_a_different_kernel_within_rounding(oc):
+    """One tendency evaluation in both modes: not bit-identical (the contracted build really ran), equal to ~1e-13."""
+    size = (40, 24, 16)
+    rng = np.random.default_rng(8)
+    ics = {n: rng.uniform(-1, 1, size) for n in "uvw"}
+    G = []
+    for exact in (True, False):
+        g = oc.RectilinearGrid(np.float64, size=size, extent=(1, 2, 3), topology=(P, P, P))
+        m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), exact_arithmetic=exact)
+        oc.set_model(m, **ics)
+        oc.time_step(m, 1e-3)
+        G.append([m.timestepper.Gn[n].interior() for n in "uvw"])
+    for a, b in zip(*G):
+        assert not np.array_equal(a, b)
+        assert rel_l2(b, a) < 1e-13
 
 
 def test_fused_poisson_matches_complete_solver(oc, monkeypatch):

@@ -16,7 +16,7 @@ g = oc.RectilinearGrid(FT, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=top
 kw = {}
 if "les" in sys.argv:
     kw = dict(buoyancy=oc.BuoyancyTracer(), tracers=("b",), closure=oc.ScalarDiffusivity(1e-4, 1e-4), coriolis=oc.FPlane(1e-4))
-m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), **kw)
+m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), exact_arithmetic="fma" not in sys.argv, **kw)
 ics = smooth_ics(N, 1234)
 if bounded:
     ics["w"] = np.concatenate([ics["w"], ics["w"][:, :, :1]], axis=2)
