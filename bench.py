@@ -7,7 +7,8 @@ A "step" is one time_step!(model, Δt) (3 RK3 substeps incl. 3 pressure solves) 
 one cell-update = one grid cell advanced by one step.  Prints ONE JSON line (see the task contract): `value` is the
 device-resident throughput (CUDA events), `e2e` the same step driven through the C ABI with HOST buffers (u, v, w copied
 host→device before and u, v, w, p device→host after every step), `roofline` the dominant phase against measured HBM
-bandwidth, `cpu_baseline` the oracle (NumPy port of the reference's CPU path) on a bounded sample.
+bandwidth, `cpu_baseline` the compiled C / OpenMP restatement of the reference's CPU path (oracle/cpu_step.c) on a bounded sample,
+all host threads.
 """
 import argparse
 import json
@@ -66,19 +67,24 @@ def smooth_ics(N, seed, size=None, rows=None):
     return out
 
 
-def cpu_oracle_rate(N, steps):
-    """The oracle (CPU restatement of the reference's CPU path) on an N³ sample of the same workload."""
-    import oracle as o
-    g = o.RectilinearGrid(np.float64, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=("Periodic",) * 3)
-    m = o.NonhydrostaticModel(g, advection=o.WENO(np.float64, 5))
-    o.set_model(m, **smooth_ics(N, 1234))
+def cpu_oracle_rate(N, steps, warmup=1):
+    """The compiled C / OpenMP restatement of the reference's CPU() path (oracle/cpu_step.c: one pass per reference
+    kernel, every face flux evaluated twice, full complex FFT — pinned against the NumPy oracle in tests/test_cpu_step.py)
+    on an N³ sample of the same workload, on all host threads OpenMP gives it.  Returns (rate, s/step, threads)."""
+    from oracle.cpu_step import CpuStepModel
+    m = CpuStepModel((N, N, N), (2 * np.pi,) * 3)
+    ics = smooth_ics(N, 1234)
+    m.set(ics["u"], ics["v"], ics["w"])
     dt = 0.2 * (2 * np.pi / N) / 2.0
-    o.time_step(m, dt)
+    m.time_step(dt, max(1, warmup))
     t0 = time.perf_counter()
-    for _ in range(steps):
-        o.time_step(m, dt)
+    m.time_step(dt, steps)
     t = time.perf_counter() - t0
-    return N ** 3 * steps / t, t / steps
+    return N ** 3 * steps / t, t / steps, m.threads()
+
+
+CPU_SAMPLE = ("oracle/cpu_step.c (C / OpenMP restatement of the reference CPU() path; Julia is absent on this box), "
+              "{n}^3 cells x {k} steps on {c} threads, {s:.3f} s/step")
 
 
 class NvmlSampler:
@@ -209,14 +215,14 @@ def run_reference(args, rank):
     if rank != 0:
         return
     N = args.ref_size
-    rate, sps = cpu_oracle_rate(N, max(1, args.steps))
+    rate, sps, cores = cpu_oracle_rate(N, max(1, args.steps), max(1, args.warmup))
     line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"3D triply-periodic NonhydrostaticModel {args.size}^3 Float64 WENO5 RK3 FFTBasedPoissonSolver",
                        "sample": f"{N}^3 cells per step"},
-            "cpu_baseline": {"value": rate, "unit": UNIT, "cores": 1, "kind": "port",
-                             "sample": f"oracle (NumPy/SciPy restatement of the reference CPU path; Julia is absent), {N}^3 x {args.steps} steps"},
+            "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": CPU_SAMPLE.format(n=N, k=args.steps, c=cores, s=sps)},
             "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -228,7 +234,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--size", type=int, default=256)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--ref-size", type=int, default=64)
+    ap.add_argument("--ref-size", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     # contracted: FMA contraction in the tendency sweep (what a GPU build of the reference computes; within the north_star
     # tolerance of the CPU reference); exact: bit-identical to the reference's CPU arithmetic.  Both are reported at N = 1.
@@ -398,9 +404,9 @@ def main():
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            rate, sps = cpu_oracle_rate(args.ref_size, 3)
-            cpu = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port",
-                   "sample": f"oracle (NumPy/SciPy port of the reference CPU path) on {args.ref_size}^3 x 3 steps, {sps:.2f} s/step"}
+            rate, sps, cores = cpu_oracle_rate(args.ref_size, 10)
+            cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": CPU_SAMPLE.format(n=args.ref_size, k=10, c=cores, s=sps)}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
