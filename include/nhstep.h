@@ -105,6 +105,16 @@ int32_t nh_get_field(nh_model* model, int32_t field, int32_t region, void* data,
  * this call = update_state!(compute_tendencies=false) [+ pressure solve and correction with Δt = 1 + update_state!] */
 int32_t nh_set_state_finalize(nh_model* model, int32_t enforce_incompressibility);
 
+/* FieldBoundaryConditions(west|east|south|north|bottom|top = Value/Gradient/FluxBoundaryCondition(number)) passed as
+ * NonhydrostaticModel(; boundary_conditions = (name = …,)) — src/BoundaryConditions/boundary_condition.jl:90-122 (number
+ * conditions), field_boundary_conditions.jl:199-201 (converted to eltype(grid)), fill_halo_regions_value_gradient.jl:7-99
+ * (Value / Gradient: linear extrapolation into the first halo cell), apply_flux_bcs.jl:50-160 (Flux: Gc[1] += q·A/V,
+ * Gc[N] -= q·A/V inside compute_tendencies!).  `field` is a prognostic field id, `dim` a Bounded direction in which the
+ * field sits at Centers (a wall-normal velocity keeps the impenetrable condition), `side` 0 = west/south/bottom,
+ * 1 = east/north/top.  NH_BC_DEFAULT restores the no-flux default.  Call before nh_set_field / nh_set_state_finalize. */
+enum { NH_BC_DEFAULT = 0, NH_BC_FLUX = 1, NH_BC_VALUE = 2, NH_BC_GRADIENT = 3 };
+int32_t nh_model_set_boundary_condition(nh_model* model, int32_t field, int32_t dim, int32_t side, int32_t kind, double value);
+
 /* fill_halo_regions!(fields…; fill_boundary_normal_velocities) — src/Fields/field_tuples.jl:56-119,
  * src/BoundaryConditions/fill_halo_regions.jl:50-82.  field_mask bit f = field id f (ids < 32). */
 int32_t nh_fill_halo_regions(nh_model* model, uint32_t field_mask, int32_t fill_boundary_normal_velocities);

@@ -177,4 +177,5 @@ class ScalarDiffusivity:
 from .model import (Field, NonhydrostaticModel, fill_halo_regions, update_state, compute_tendencies,  # noqa: E402,F401
                     calculate_pressure_correction, pressure_correct_velocities, rk3_substep, ab2_step,
                     cache_previous_tendencies, time_step, time_step_profiled, set_model, FFTBasedPoissonSolver,
-                    FourierTridiagonalPoissonSolver, BatchedTridiagonalSolver)
+                    FourierTridiagonalPoissonSolver, BatchedTridiagonalSolver, BoundaryCondition,
+                    FieldBoundaryConditions, ValueBoundaryCondition, GradientBoundaryCondition, FluxBoundaryCondition)

@@ -48,8 +48,9 @@ SYMBOLS = [
     "nh_poisson_destroy", "nh_poisson_solve", "nh_poisson_synchronize", "nh_poisson_launch_count",
     "nh_poisson_time_solves", "nh_tridiag_create", "nh_tridiag_solve", "nh_tridiag_destroy",
     "nh_dist_configure", "nh_dist_buffer", "nh_dist_halo", "nh_dist_tendency_substep", "nh_dist_poisson",
-    "nh_dist_pressure_correct", "nh_dist_ipc_export", "nh_dist_ipc_import",
+    "nh_dist_pressure_correct", "nh_dist_ipc_export", "nh_dist_ipc_import", "nh_model_set_boundary_condition",
 ]
+BC_DEFAULT, BC_FLUX, BC_VALUE, BC_GRADIENT = range(4)
 DIST_SEND_LO, DIST_SEND_HI, DIST_RECV_LO, DIST_RECV_HI, DIST_SPECTRAL_A, DIST_SPECTRAL_B = range(6)
 
 _lib = None
@@ -82,6 +83,7 @@ def lib():
             "nh_get_field": [p, C.c_int32, C.c_int32, p, C.c_int64, C.c_int32],
             "nh_set_state_finalize": [p, C.c_int32],
             "nh_fill_halo_regions": [p, C.c_uint32, C.c_int32],
+            "nh_model_set_boundary_condition": [p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double],
             "nh_update_state": [p, C.c_int32],
             "nh_compute_tendencies": [p],
             "nh_rk3_substep": [p, C.c_double, C.c_double, C.c_double, C.c_int32],

@@ -8,13 +8,15 @@
 
 // ---- halo fill ------------------------------------------------------------------------------------------------
 // src/BoundaryConditions/fill_halo_regions_periodic.jl:40-111, fill_halo_regions_flux.jl:14-33,
-// fill_halo_regions_open.jl:65-70.  One launch fills one direction of up to NH_MAXF fields (the tupled fill of
-// src/Fields/field_tuples.jl:88-101).
+// fill_halo_regions_open.jl:65-70, fill_halo_regions_value_gradient.jl:7-99.  One launch fills one direction of up to
+// NH_MAXF fields (the tupled fill of src/Fields/field_tuples.jl:88-101).
 template <typename FT>
 struct HaloJob {
   GridDev<FT> g;
   FT* p[NH_MAXF];
-  int mode[NH_MAXF];      // 0 skip, 1 periodic, 2 flux (mirror), 3 open (wall-normal velocity := 0)
+  int mode[NH_MAXF];      // 0 skip, 1 periodic, 2 wall (per-side kind below), 3 open (wall-normal velocity := 0)
+  int side_kind[NH_MAXF][2];   // mode 2: NH_BC_DEFAULT / NH_BC_FLUX (mirror), NH_BC_VALUE, NH_BC_GRADIENT at the left / right wall
+  FT side_val[NH_MAXF][2];
   int nf;
   int d;                  // direction being filled
   int lo[3], hi[3];       // transverse logical index range (inclusive); entry d unused
@@ -43,11 +45,63 @@ __global__ void halo_fill_kernel(const __grid_constant__ HaloJob<FT> J) {
       at(N + h) = at(h);               // east halo  ← west end of the interior
     }
   } else if (mode == 2) {
-    at(0) = at(1);
-    at(N + 1) = at(N);
+    // Δ between the first interior and the first halo point: the Face spacing at index 1 / N+1
+    for (int side = 0; side < 2; ++side) {
+      const int kind = J.side_kind[f][side];
+      const int iI = side ? N : 1, iH = side ? N + 1 : 0, iB = side ? N + 1 : 1;
+      const FT cI = at(iI);
+      if (kind != NH_BC_VALUE && kind != NH_BC_GRADIENT) { at(iH) = cI; continue; }
+      const FT D = d == 0 ? g.dx : d == 1 ? g.dy : g.Dzf(iB);
+      const FT v = J.side_val[f][side];
+      FT grad;
+      if (kind == NH_BC_GRADIENT) grad = v;
+      else grad = side ? (v - cI) / (D / FT(2)) : (cI - v) / (D / FT(2));
+      at(iH) = cI + grad * (side ? D : -D);
+    }
   } else {
     at(1) = FT(0);
     at(N + 1) = FT(0);
+  }
+}
+
+// ---- flux boundary conditions ------------------------------------------------------------------------------------
+// apply_{x,y,z}_bcs! — src/BoundaryConditions/apply_flux_bcs.jl:50-160: Gc[1] += q·A/V, Gc[N] -= q·A/V over the
+// grid-interior transverse range (`:yz`, `:xz`, `:xy`), A at the boundary face, V at the field's own location.
+template <typename FT>
+struct FluxBcJob {
+  GridDev<FT> g;
+  FT* G;
+  int d;                  // direction of the wall pair
+  int zloc_face;          // the field sits at Faces in z (w): Δz of its volume / transverse areas is Δzᶠ
+  int has[2];
+  FT q[2];
+};
+
+template <typename FT>
+__global__ void flux_bc_kernel(const __grid_constant__ FluxBcJob<FT> J) {
+  const GridDev<FT>& g = J.g;
+  const int d = J.d;
+  const int e1 = d == 0 ? 1 : 0, e2 = d == 2 ? 1 : 2;
+  const int n1 = g.N[e1], n2 = g.N[e2];
+  long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= (long long)n1 * n2) return;
+  int c[3];
+  c[e1] = 1 + (int)(t % n1); c[e2] = 1 + (int)(t / n1);
+  const int N = g.N[d];
+  for (int side = 0; side < 2; ++side) {
+    if (!J.has[side]) continue;
+    c[d] = side ? N : 1;
+    const int k = c[2];
+    // Δz at the field's own vertical location (index k), and at the flipped location on the wall for d == 2
+    const FT dzl = J.zloc_face ? g.Dzf(k) : g.Dzc(k);
+    FT A;
+    if (d == 0) A = g.dy * dzl;             // Ax = Δy·Δz
+    else if (d == 1) A = g.dx * dzl;        // Ay = Δx·Δz
+    else A = g.dx * g.dy;                   // Az = Δx·Δy
+    const FT V = (g.dx * g.dy) * dzl;       // V = Az·Δz
+    FT& G = J.G[g.idx(c[0], c[1], c[2])];
+    const FT inc = J.q[side] * A / V;
+    if (side == 0) G += inc; else G -= inc;
   }
 }
 

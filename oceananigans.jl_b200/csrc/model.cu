@@ -224,6 +224,21 @@ void Model<FT>::field_device_ptr(int field, void** ptr, int64_t* off, int64_t st
   strides[0] = 1; strides[1] = gh.g.sy; strides[2] = gh.g.sz;
 }
 
+// FieldBoundaryConditions with number conditions (include/nhstep.h: nh_model_set_boundary_condition)
+template <typename FT>
+void Model<FT>::set_boundary_condition(int field, int dim, int side, int kind, double value) {
+  NH_REQUIRE(field >= 0 && field < nf, "boundary conditions can be set on prognostic fields (u, v, w, tracers) only");
+  NH_REQUIRE(dim >= 0 && dim < 3 && (side == 0 || side == 1), "bad dim / side");
+  NH_REQUIRE(kind >= NH_BC_DEFAULT && kind <= NH_BC_GRADIENT, "unknown boundary condition kind");
+  NH_REQUIRE(gh.g.topo[dim] == NH_BOUNDED, "Value / Gradient / Flux boundary conditions need a Bounded direction");
+  NH_REQUIRE(field_face_dim(field) != dim, "a wall-normal velocity component keeps the impenetrable (Open) condition");
+  bc_kind[field][dim][side] = kind;
+  bc_val[field][dim][side] = kind == NH_BC_DEFAULT ? FT(0) : (FT)value;
+  has_flux_bcs = false;
+  for (int f = 0; f < nf; ++f) for (int d = 0; d < 3; ++d) for (int s2 = 0; s2 < 2; ++s2)
+    if (bc_kind[f][d][s2] == NH_BC_FLUX) has_flux_bcs = true;
+}
+
 // fill_halo_regions! — open fill, then the three directions sorted so that Periodic runs after the others
 // (fill_halo_regions.jl:50-67,121-123,159-196; field_tuples.jl:56-101)
 template <typename FT>
@@ -269,7 +284,13 @@ void Model<FT>::fill_halo_regions(uint32_t mask, int fill_normal) {
       for (int e = 0; e < 3; ++e) { J.lo[e] = 1; J.hi[e] = g.N[e]; }
       for (int id : ids) {
         if (field_face_dim(id) == d) continue;        // Face field on a wall: open / no boundary condition
-        J.p[J.nf] = field_ptr(id); J.mode[J.nf] = 2; J.nf++;
+        J.p[J.nf] = field_ptr(id); J.mode[J.nf] = 2;
+        for (int side = 0; side < 2; ++side) {
+          const bool prog = id >= 0 && id < nf;
+          J.side_kind[J.nf][side] = prog ? bc_kind[id][d][side] : NH_BC_DEFAULT;
+          J.side_val[J.nf][side] = prog ? bc_val[id][d][side] : FT(0);
+        }
+        J.nf++;
       }
       if (!J.nf) continue;
     }
@@ -314,6 +335,18 @@ void Model<FT>::compute_tendencies() {
   for (int what = 0; what < nf; ++what) {
     tendency_generic_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, what);
     KLAUNCH(lc);
+  }
+  // compute_boundary_tendency_contributions! (compute_nonhydrostatic_tendencies.jl:202-207): x, then y, then z walls
+  if (has_flux_bcs) {
+    for (int d = 0; d < 3; ++d) for (int f = 0; f < nf; ++f) {
+      if (bc_kind[f][d][0] != NH_BC_FLUX && bc_kind[f][d][1] != NH_BC_FLUX) continue;
+      FluxBcJob<FT> J; J.g = gh.g; J.G = Gn[f]; J.d = d; J.zloc_face = f == 2;
+      for (int side = 0; side < 2; ++side) { J.has[side] = bc_kind[f][d][side] == NH_BC_FLUX; J.q[side] = bc_val[f][d][side]; }
+      const int e1 = d == 0 ? 1 : 0, e2 = d == 2 ? 1 : 2;
+      long long n = (long long)gh.g.N[e1] * gh.g.N[e2];
+      flux_bc_kernel<FT><<<ceil_div(n, 128), 128, 0, stream>>>(J);
+      KLAUNCH(lc);
+    }
   }
   CUDA_CHECK(cudaGetLastError());
 }

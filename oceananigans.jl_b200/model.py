@@ -81,11 +81,49 @@ class _Namespace(dict):
             raise AttributeError(k) from e
 
 
+class BoundaryCondition:
+    """BoundaryCondition(classification, number) — src/BoundaryConditions/boundary_condition.jl:17-60 with a number
+    condition (converted to eltype(grid), field_boundary_conditions.jl:199-201)."""
+
+    def __init__(self, kind, condition):
+        self.kind, self.condition = kind, float(condition)
+
+
+def ValueBoundaryCondition(val):
+    return BoundaryCondition(L.BC_VALUE, val)
+
+
+def GradientBoundaryCondition(val):
+    return BoundaryCondition(L.BC_GRADIENT, val)
+
+
+def FluxBoundaryCondition(val):
+    return BoundaryCondition(L.BC_FLUX, val)
+
+
+_SIDES = {"west": (0, 0), "east": (0, 1), "south": (1, 0), "north": (1, 1), "bottom": (2, 0), "top": (2, 1)}
+
+
+class FieldBoundaryConditions:
+    """FieldBoundaryConditions(; west, east, south, north, bottom, top) — field_boundary_conditions.jl:60-110; sides that
+    are not given keep the defaults of :13-37 (periodic / no-flux / impenetrable)."""
+
+    def __init__(self, **sides):
+        for k, bc in sides.items():
+            if k not in _SIDES:
+                raise ValueError(f"unknown side {k}")
+            if not isinstance(bc, BoundaryCondition):
+                raise ValueError("only Value/Gradient/FluxBoundaryCondition(number) cross the C ABI")
+        self.sides = sides
+
+
 class NonhydrostaticModel:
-    """NonhydrostaticModel(; grid, advection, buoyancy, coriolis, closure, tracers, timestepper, hydrostatic_pressure_anomaly)."""
+    """NonhydrostaticModel(; grid, advection, buoyancy, coriolis, closure, tracers, timestepper, hydrostatic_pressure_anomaly,
+    boundary_conditions)."""
 
     def __init__(self, grid, advection="default", buoyancy=None, coriolis=None, closure=None, tracers=(),
-                 timestepper="RungeKutta3", hydrostatic_pressure_anomaly="default", chi=0.1, exact_arithmetic=True):
+                 timestepper="RungeKutta3", hydrostatic_pressure_anomaly="default", chi=0.1, exact_arithmetic=True,
+                 boundary_conditions=None):
         if advection == "default":
             advection = Centered(order=2)
         tracers = (tracers,) if isinstance(tracers, str) else tuple(tracers)
@@ -137,6 +175,13 @@ class NonhydrostaticModel:
         self.timestepper_name = timestepper
         self._h = C.c_void_p()
         check(lib().nh_model_create(grid._h, C.byref(d), C.byref(self._h)))
+        for name, fbcs in (boundary_conditions or {}).items():
+            names_ = ["u", "v", "w"] + list(tracers)
+            if name not in names_:
+                raise ValueError(f"boundary_conditions: {name} is not a prognostic field of this model")
+            for side, bc in fbcs.sides.items():
+                dim, s_ = _SIDES[side]
+                check(lib().nh_model_set_boundary_condition(self._h, names_.index(name), dim, s_, bc.kind, bc.condition))
         gi = L.GridDesc()
         check(lib().nh_model_grid_info(self._h, C.byref(gi)))
         self.halo = tuple(gi.H)

@@ -8,6 +8,8 @@ Follows the reference's
   src/BoundaryConditions/fill_halo_regions_flux.jl:14-33      (no-flux: mirror the first interior cell, one halo cell)
   src/BoundaryConditions/fill_halo_regions_open.jl:9-70       (impenetrable: wall-normal velocity := 0 at 1 and N+1)
   src/Fields/field_tuples.jl:56-101                           (tupled fill: one task list for all ordinary fields)
+  src/BoundaryConditions/fill_halo_regions_value_gradient.jl:7-99  (Value / Gradient: linear extrapolation into one halo cell)
+  src/BoundaryConditions/field_boundary_conditions.jl:199-201  (Number conditions are converted to eltype(grid))
 """
 import numpy as np
 
@@ -39,6 +41,8 @@ class Field:
         self.H = grid.H
         self.data = np.zeros(tuple(self.size[d] + 2 * self.H[d] for d in range(3)), dtype=grid.FT)
         self.bcs = default_bcs(grid, self.loc, prognostic)
+        # non-default conditions with a constant: side_bcs[d][side] = None | ("value" | "gradient" | "flux", number)
+        self.side_bcs = [[None, None], [None, None], [None, None]]
 
     # 1-based inclusive ranges → parent view
     def at(self, ri, rj, rk):
@@ -62,7 +66,16 @@ class Field:
         f.__dict__.update(self.__dict__)
         f.data = self.data.copy()
         f.bcs = list(self.bcs)
+        f.side_bcs = [list(x) for x in self.side_bcs]
         return f
+
+    def set_boundary_condition(self, d, side, kind, value):
+        """FieldBoundaryConditions(west/east/south/north/bottom/top = Value/Gradient/FluxBoundaryCondition(number))."""
+        if self.bcs[d] != FBC:
+            raise ValueError(f"{kind} boundary condition needs a Bounded direction in which '{self.name}' sits at Centers")
+        if kind not in ("value", "gradient", "flux"):
+            raise ValueError(kind)
+        self.side_bcs[d][side] = (kind, self.grid.FT(value))
 
 
 # ---------------------------------------------------------------------------------------------
@@ -115,8 +128,24 @@ def _fill_flux_dir(f, d):
     lo_dst, lo_src, hi_dst, hi_src = list(rng), list(rng), list(rng), list(rng)
     lo_dst[d], lo_src[d] = (0, 0), (1, 1)
     hi_dst[d], hi_src[d] = (N + 1, N + 1), (N, N)
-    f.at(*lo_dst)[...] = f.at(*lo_src)
-    f.at(*hi_dst)[...] = f.at(*hi_src)
+    c = g.coords[d]
+    for side, dst, src, bidx, sign in ((0, lo_dst, lo_src, 1, -1), (1, hi_dst, hi_src, N + 1, +1)):
+        bc = f.side_bcs[d][side]
+        if bc is None or bc[0] == "flux":
+            f.at(*dst)[...] = f.at(*src)
+            continue
+        # fill_halo_regions_value_gradient.jl: Δ at the boundary face (flip(loc) = Face index 1 or N+1)
+        FT = g.FT
+        D = c.df if (c.topo == Flat or c.regular) else c.df[bidx]
+        D = FT(D)
+        cI = f.at(*src)
+        if bc[0] == "gradient":
+            grad = bc[1]
+        elif side == 0:
+            grad = (cI - bc[1]) / (D / FT(2))
+        else:
+            grad = (bc[1] - cI) / (D / FT(2))
+        f.at(*dst)[...] = cI + grad * (D if sign > 0 else -D)
 
 
 def _fill_periodic_dir(fields, d):

@@ -20,10 +20,13 @@ import numpy as np
 from .grid import Bounded, Flat, round_fraction
 from .fields import Field, fill_halo_regions
 from .advection import Centered, adapt_advection_order
-from .operators import divergence_ccc, deriv, delta, interior_region
+from .operators import divergence_ccc, deriv, delta, interior_region, area, volume
 from .solvers import FFTBasedPoissonSolver, FourierTridiagonalPoissonSolver
 from .tendencies import (VEL_LOC, CCC, momentum_tendency, tracer_tendency, tendency_region,
                          update_hydrostatic_pressure)
+
+
+SIDES = {"west": (0, 0), "east": (0, 1), "south": (1, 0), "north": (1, 1), "bottom": (2, 0), "top": (2, 1)}
 
 
 class FPlane:
@@ -65,7 +68,7 @@ class Clock:
 
 class NonhydrostaticModel:
     def __init__(self, grid, advection="default", buoyancy=None, coriolis=None, closure=None, tracers=(),
-                 timestepper="RungeKutta3", hydrostatic_pressure_anomaly="default", chi=0.1):
+                 timestepper="RungeKutta3", hydrostatic_pressure_anomaly="default", chi=0.1, boundary_conditions=None):
         FT = grid.FT
         if advection == "default":
             advection = Centered(FT, 2)
@@ -90,6 +93,13 @@ class NonhydrostaticModel:
         self.buoyancy, self.coriolis, self.closure = buoyancy, coriolis, closure
         self.velocities = tuple(Field(grid, VEL_LOC[a], name="uvw"[a]) for a in range(3))
         self.tracers = {n: Field(grid, CCC, name=n) for n in tracers}
+        # boundary_conditions = {field name: {"west"|"east"|"south"|"north"|"bottom"|"top": (kind, number)}} —
+        # FieldBoundaryConditions with Value / Gradient / FluxBoundaryCondition(number) entries
+        for name, sides in (boundary_conditions or {}).items():
+            f = dict(zip(["u", "v", "w"] + list(tracers), list(self.velocities) + list(self.tracers.values())))[name]
+            for side, (kind, value) in sides.items():
+                d, s = SIDES[side]
+                f.set_boundary_condition(d, s, kind, value)
         self.pNHS = Field(grid, CCC, prognostic=False, name="pNHS")
         if hydrostatic_pressure_anomaly == "default":
             self.pHY = Field(grid, CCC, prognostic=False, name="pHY") if buoyancy is not None else None
@@ -142,6 +152,33 @@ def compute_tendencies_(model):
     for n in model.tracers:
         R, G = tracer_tendency(model, n)
         model.Gn[n].at(*R)[...] = G
+    apply_flux_bcs(model)
+
+
+def apply_flux_bcs(model):
+    """compute_boundary_tendency_contributions! (compute_nonhydrostatic_tendencies.jl:202-207) with
+    apply_{x,y,z}_bcs! of src/BoundaryConditions/apply_flux_bcs.jl:50-160: Gc[1] += q·A/V, Gc[N] -= q·A/V over the
+    grid-interior transverse range; A at the boundary face (flip(loc)), V at the field's own location."""
+    grid = model.grid
+    for n, f in zip(model.prognostic_names(), model.prognostic_fields()):
+        G = model.Gn[n]
+        for d in range(3):
+            for side in (0, 1):
+                bc = f.side_bcs[d][side]
+                if bc is None or bc[0] != "flux":
+                    continue
+                N = grid.N[d]
+                r = [(1, grid.N[e]) for e in range(3)]
+                rf = list(r)
+                r[d] = (1, 1) if side == 0 else (N, N)
+                rf[d] = (1, 1) if side == 0 else (N + 1, N + 1)
+                floc = list(f.loc)
+                floc[d] = "f" if f.loc[d] == "c" else "c"
+                inc = bc[1] * area(grid, d, tuple(floc), rf) / volume(grid, f.loc, r)
+                if side == 0:
+                    G.at(*r)[...] += inc
+                else:
+                    G.at(*r)[...] -= inc
 
 
 def compute_source_term(model, dt):

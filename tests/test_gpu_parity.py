@@ -33,8 +33,8 @@ def rel_l2(a, b):
 
 
 def make_pair(oc, FT, size, topo, z=None, advection=("WENO", 5), timestepper="RungeKutta3", buoyancy=None, coriolis=None,
-              closure=None, tracers=(), extent=None, x=None, y=None, exact_arithmetic=True):
-    """The same model twice: (CUDA, oracle)."""
+              closure=None, tracers=(), extent=None, x=None, y=None, exact_arithmetic=True, bcs=None):
+    """The same model twice: (CUDA, oracle).  bcs = {field: {side: (kind, number)}} (Value / Gradient / Flux)."""
     kw = {}
     if extent is not None:
         kw["extent"] = extent
@@ -62,10 +62,13 @@ def make_pair(oc, FT, size, topo, z=None, advection=("WENO", 5), timestepper="Ru
     c2 = o.FPlane(coriolis) if coriolis is not None else None
     k1 = oc.ScalarDiffusivity(*closure) if closure else None
     k2 = o.ScalarDiffusivity(*closure) if closure else None
+    mk = {"value": oc.ValueBoundaryCondition, "gradient": oc.GradientBoundaryCondition, "flux": oc.FluxBoundaryCondition}
+    bcs1 = {n: oc.FieldBoundaryConditions(**{side: mk[k](v) for side, (k, v) in sides.items()})
+            for n, sides in (bcs or {}).items()}
     m1 = oc.NonhydrostaticModel(g1, advection=adv(oc, None), timestepper=timestepper, buoyancy=b1, coriolis=c1, closure=k1,
-                                tracers=tracers, exact_arithmetic=exact_arithmetic)
+                                tracers=tracers, exact_arithmetic=exact_arithmetic, boundary_conditions=bcs1)
     m2 = o.NonhydrostaticModel(g2, advection=adv(o, FT), timestepper=timestepper, buoyancy=b2, coriolis=c2, closure=k2,
-                               tracers=tracers)
+                               tracers=tracers, boundary_conditions=bcs)
     return m1, m2
 
 
@@ -82,6 +85,16 @@ def names_fields(m1, m2):
         yield n, f1, f2
 
 
+BCS_LES = {"u": {"top": ("flux", -1e-4), "bottom": ("value", 0.0)}, "v": {"bottom": ("value", 0.1)},
+           "T": {"top": ("flux", 1e-3), "bottom": ("gradient", 0.01)}, "S": {"top": ("flux", -2e-4)}}
+BCS_BOX = {"b": {"west": ("value", 1.0), "east": ("gradient", -0.5), "south": ("flux", 0.2), "north": ("value", 0.0),
+                 "bottom": ("gradient", 0.3), "top": ("flux", -0.1)},
+           "u": {"south": ("value", 0.5), "north": ("flux", 0.05), "top": ("gradient", 0.2)},
+           "v": {"west": ("value", -0.25), "bottom": ("flux", 0.01)},
+           "w": {"west": ("flux", 0.02), "east": ("value", 0.0), "north": ("gradient", 1.0)}}
+BCS_STRETCHED = {"c": {"bottom": ("value", 2.0), "top": ("gradient", -1.0)}, "u": {"bottom": ("value", 0.0), "top": ("flux", 1e-3)},
+                 "v": {"top": ("value", 0.2), "bottom": ("flux", -1e-3)}}
+
 CONFIGS = [
     # size, topo, z, advection, kwargs
     ((12, 10, 9), (P, P, P), None, ("WENO", 5), {}),
@@ -96,6 +109,10 @@ CONFIGS = [
     ((16, 12), (P, F, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",))),
     ((10, 9, 8), (P, P, B), "stretched", ("WENO", 5), dict(buoyancy="seawater", tracers=("T", "S"), closure=(1e-3, 1e-3))),
     ((9, 8, 2), (P, P, B), None, ("WENO", 5), {}),     # order adapted in z (N < buffer)
+    # Value / Gradient / Flux boundary conditions with number conditions (the ocean-LES style set, then every wall pair)
+    ((12, 10, 9), (P, P, B), None, ("WENO", 5), dict(buoyancy="seawater", tracers=("T", "S"), coriolis=1e-2, closure=(1e-2, 2e-2), bcs=BCS_LES)),
+    ((9, 8, 10), (B, B, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=(1e-2, 1e-2), bcs=BCS_BOX)),
+    ((10, 9, 8), (P, P, B), "stretched", ("Centered", 2), dict(tracers=("c",), closure=(1e-3, 1e-3), bcs=BCS_STRETCHED)),
 ]
 
 
@@ -108,7 +125,7 @@ def _z(zkind, size):
 
 
 @pytest.mark.parametrize("FT", [np.float64, np.float32])
-@pytest.mark.parametrize("cfg", CONFIGS, ids=[f"{c[1]}-{c[3]}-{c[2]}-{c[0]}" for c in CONFIGS])
+@pytest.mark.parametrize("cfg", CONFIGS, ids=[f"{c[1]}-{c[3]}-{c[2]}-{c[0]}" + ("-bcs" if "bcs" in c[4] else "") for c in CONFIGS])
 def test_tendencies_and_halos_bit_exact(oc, FT, cfg):
     size, topo, zkind, adv, kw = cfg
     m1, m2 = make_pair(oc, FT, size, topo, z=_z(zkind, size), advection=adv, **kw)
@@ -253,6 +270,31 @@ def test_100_steps_full_physics_bounded_z(oc, FT, tol):
     ics = smooth_ics(m2, np.random.default_rng(1234), amp=0.5)
     err, floor = _run_steps(oc, m1, m2, ics, 1e-2, 100, m3)
     check_parity(err, tol, floor)
+
+
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+def test_100_steps_with_value_gradient_flux_boundary_conditions(oc, FT, tol, timestepper):
+    """Ocean-LES style walls (test/regression_tests/ocean_large_eddy_simulation_regression_test.jl:20-40: wind-stress
+    flux on u, cooling flux on T, bottom T gradient; plus no-slip bottom) on (P,P,B) — 100 steps against the oracle."""
+    kw = dict(extent=(1, 1, 1), buoyancy="seawater", tracers=("T", "S"), coriolis=1e-4, closure=(1e-3, 1e-3),
+              timestepper=timestepper, bcs=BCS_LES)
+    m1, m2 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
+    _, m3 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
+    ics = smooth_ics(m2, np.random.default_rng(99), amp=0.5)
+    err, floor = _run_steps(oc, m1, m2, ics, 1e-2, 100, m3)
+    check_parity(err, tol, floor)
+
+
+def test_boundary_condition_errors(oc):
+    """Construction-time errors like the reference's: walls only in Bounded directions, wall-normal velocity stays Open."""
+    g = oc.RectilinearGrid(np.float64, size=(8, 8, 8), extent=(1, 1, 1), topology=(P, P, B))
+    with pytest.raises(oc.NhError):
+        oc.NonhydrostaticModel(g, boundary_conditions={"u": oc.FieldBoundaryConditions(west=oc.ValueBoundaryCondition(0))})
+    with pytest.raises(oc.NhError):
+        oc.NonhydrostaticModel(g, boundary_conditions={"w": oc.FieldBoundaryConditions(top=oc.ValueBoundaryCondition(0))})
+    with pytest.raises(ValueError):
+        oc.NonhydrostaticModel(g, boundary_conditions={"T": oc.FieldBoundaryConditions(top=oc.FluxBoundaryCondition(1))})
 
 
 @pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])

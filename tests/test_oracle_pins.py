@@ -252,3 +252,71 @@ def test_taylor_green_vortex(timestepper):
     ve = np.broadcast_to(va(xC, t)[:, None, None], (N, N, 2))
     assert np.max(np.abs((m.velocities[0].interior - ue) / ue)) < 5e-6
     assert np.max(np.abs((m.velocities[1].interior - ve) / ve)) < 5e-6
+
+
+# ---------------------------------------------------------------------------------------------
+# Flux / Value / Gradient boundary conditions — test/test_boundary_conditions_integration.jl:28-54,384-433
+# ---------------------------------------------------------------------------------------------
+
+_BUDGET = ([((P, B, B), n, side) for n in ("u", "c") for side in ("north", "south", "top", "bottom")]
+           + [((B, P, B), n, side) for n in ("v", "c") for side in ("east", "west", "top", "bottom")]
+           + [((B, B, P), n, side) for n in ("w", "c") for side in ("east", "west", "north", "south")])
+
+
+@pytest.mark.parametrize("topo,name,side", _BUDGET, ids=[f"{''.join(x[0] for x in t)}-{n}-{s}" for t, n, s in _BUDGET])
+def test_nonhydrostatic_flux_budget(topo, name, side):
+    """test_nonhydrostatic_flux_budget: a constant boundary flux π into a field at rest raises its mean by flux·t/L."""
+    FT = np.float64
+    Lx, Ly, Lz = 0.3, 0.4, 0.5
+    L = {"west": Lx, "east": Lx, "south": Ly, "north": Ly, "bottom": Lz, "top": Lz}[side]
+    flux = FT(np.pi)
+    direction = 1 if side in ("west", "south", "bottom") else -1
+    g = o.RectilinearGrid(FT, size=(2, 2, 2), x=(0, Lx), y=(0, Ly), z=(0, Lz), topology=topo)
+    m = o.NonhydrostaticModel(g, tracers=("c",), boundary_conditions={name: {side: ("flux", flux * direction)}})
+    o.time_step(m, 1.0)
+    f = dict(zip(m.prognostic_names(), m.prognostic_fields()))[name]
+    assert np.isclose(f.interior.mean(), flux * m.clock.time / L, rtol=np.sqrt(np.finfo(FT).eps), atol=0)
+
+
+@pytest.mark.parametrize("kind", ["value", "gradient", "flux"])
+def test_value_gradient_halo_definitions(kind):
+    """fill_halo_regions_value_gradient.jl:10-15: the wall value is the mean of halo and first interior cell; the wall
+    gradient is their difference over Δ; Flux leaves the no-flux mirror (the flux enters the tendency instead)."""
+    FT = np.float64
+    g = o.RectilinearGrid(FT, size=(4, 4, 4), extent=(1, 1, 2), topology=(P, P, B))
+    m = o.NonhydrostaticModel(g, tracers=("c",), boundary_conditions={"c": {"bottom": (kind, 0.7), "top": (kind, -0.3)}})
+    rng = np.random.default_rng(3)
+    c = m.tracers["c"]
+    c.set(rng.uniform(-1, 1, (4, 4, 4)))
+    fill_halo_regions(c)
+    lo_h, lo_i = c.at((1, 4), (1, 4), (0, 0)), c.at((1, 4), (1, 4), (1, 1))
+    hi_h, hi_i = c.at((1, 4), (1, 4), (5, 5)), c.at((1, 4), (1, 4), (4, 4))
+    dz = 0.5
+    if kind == "value":
+        np.testing.assert_allclose((lo_h + lo_i) / 2, 0.7, rtol=1e-14)
+        np.testing.assert_allclose((hi_h + hi_i) / 2, -0.3, rtol=1e-14)
+    elif kind == "gradient":
+        np.testing.assert_allclose((lo_i - lo_h) / dz, 0.7, rtol=1e-13)
+        np.testing.assert_allclose((hi_h - hi_i) / dz, -0.3, rtol=1e-13)
+    else:
+        np.testing.assert_array_equal(lo_h, lo_i)
+        np.testing.assert_array_equal(hi_h, hi_i)
+
+
+def test_diffusive_flux_through_a_gradient_wall_matches_the_budget():
+    """fluxes_with_diffusivity_boundary_conditions_are_correct (test_boundary_conditions_integration.jl:56-108) with a
+    constant κ instead of the AMD closure: b = z·bz with a bottom Gradient(bz) condition loses κ·bz·t/Lz of its mean
+    through the (insulated by default) top, to 1e-6."""
+    FT = np.float64
+    Lz, kappa, bz = 1.0, FT(np.exp(-3)), FT(np.pi)
+    g = o.RectilinearGrid(FT, size=(16, 16, 16), extent=(1, 1, Lz), topology=(P, P, B))
+    m = o.NonhydrostaticModel(g, tracers=("b",), buoyancy=o.BuoyancyTracer(), closure=o.ScalarDiffusivity(kappa, kappa),
+                              timestepper="QuasiAdamsBashforth2", boundary_conditions={"b": {"bottom": ("gradient", bz)}})
+    zc = (np.arange(16) + 0.5) / 16 * Lz - Lz
+    o.set_model(m, b=np.broadcast_to(zc * bz, (16, 16, 16)))
+    b = m.tracers["b"]
+    mean0 = b.interior.mean()
+    dt = 1e-6 * Lz ** 2 / kappa
+    for n in range(10):
+        o.time_step(m, dt, euler=(n == 0))
+    assert abs((b.interior.mean() - mean0) - (-kappa * bz) * m.clock.time / Lz) < 1e-6
