@@ -166,7 +166,29 @@ class SeawaterBuoyancy:
         self.g, self.alpha, self.beta = gravitational_acceleration, thermal_expansion, haline_contraction
 
 
+class SmagorinskyLilly:
+    """SmagorinskyLilly(FT; C = 0.16, Cb = 1, Pr = 1) — Smagorinskys/lilly_coefficient.jl:108-113; Pr a number or a
+    dict by tracer name."""
+    kind = L.CLOSURE_SMAGORINSKY_LILLY
+
+    def __init__(self, C=0.16, Cb=1.0, Pr=1.0):
+        self.C, self.Cb, self.Pr = C, Cb, Pr
+
+    def Pr_for(self, name):
+        return self.Pr[name] if isinstance(self.Pr, dict) else self.Pr
+
+
+class Smagorinsky(SmagorinskyLilly):
+    """Smagorinsky(FT; coefficient = 0.16, Pr = 1) with a number coefficient — Smagorinskys/smagorinsky.jl:78-84,105."""
+    kind = L.CLOSURE_SMAGORINSKY
+
+    def __init__(self, coefficient=0.16, Pr=1.0):
+        self.C, self.Cb, self.Pr = coefficient, 0.0, Pr
+
+
 class ScalarDiffusivity:
+    kind = L.CLOSURE_SCALAR
+
     def __init__(self, nu=0.0, kappa=0.0):
         self.nu, self.kappa = nu, kappa
 

@@ -77,6 +77,8 @@ struct TendParams {
   int w_buoyancy;             // buoyancy acts on w directly (pHY′ is nothing)
   int has_coriolis; FT fcor;
   int has_closure; FT nu; FT kappa[NH_MAXTR];
+  const FT* nue;              // eddy viscosity νₑ at ccc (Smagorinsky closures); nullptr ⇒ the constants above
+  FT Pr[NH_MAXTR];            // κₑ = ℑ(νₑ) / Pr
 };
 
 struct FieldExtent { int n[3]; };   // interior size of a field (N, or N+1 on a Bounded Face dim)

@@ -172,4 +172,53 @@ void twiddles(int N, std::vector<double>& tw, std::vector<double>& tw4) {
   }
 }
 
+// ---- correctly rounded cube root ------------------------------------------------------------------------------------
+// x = m·2^(E-P) with m a P-bit integer; E = 3q + rem; g = m·2^(rem-P) ∈ [1/2, 4).  r = ⌊cbrt(g)·2^S⌋ with S = P when
+// g ≥ 1 (cbrt(g) ∈ [1, 1.59)) and P+1 otherwise (cbrt(g) ∈ [0.79, 1)) has one bit more than the result's mantissa, so
+// the rounded mantissa is (r+1)>>1 (no ties: an odd (P+1)-bit integer cubed is never m·2^s).  r is found by bisection on
+// r³ ≤ X = m·2^(rem-P+3S) with 192-bit integers.
+namespace {
+struct U192 { unsigned long long hi, mid, lo; };
+inline bool le(const U192& a, const U192& b) {
+  if (a.hi != b.hi) return a.hi < b.hi;
+  if (a.mid != b.mid) return a.mid < b.mid;
+  return a.lo <= b.lo;
+}
+inline U192 cube(unsigned long long r) {          // r < 2^55
+  typedef unsigned __int128 u128;
+  u128 r2 = (u128)r * r;
+  unsigned long long a = (unsigned long long)(r2 >> 64), b = (unsigned long long)r2;
+  u128 br = (u128)b * r, ar = (u128)a * r + (br >> 64);
+  return U192{(unsigned long long)(ar >> 64), (unsigned long long)ar, (unsigned long long)br};
+}
+inline U192 shifted(unsigned long long m, int sh) {   // m·2^sh, m < 2^53, sh < 128
+  typedef unsigned __int128 u128;
+  if (sh < 64) { u128 v = (u128)m << sh; return U192{0, (unsigned long long)(v >> 64), (unsigned long long)v}; }
+  u128 v = (u128)m << (sh - 64);
+  return U192{(unsigned long long)(v >> 64), (unsigned long long)v, 0};
+}
+}  // namespace
+
+template <typename FT>
+FT cbrt_correctly_rounded(FT x) {
+  if (!(x > FT(0)) || !std::isfinite((double)x)) return std::cbrt(x);
+  const int P = sizeof(FT) == 8 ? 53 : 24;
+  int E;
+  double f = std::frexp((double)x, &E);                       // x = f·2^E, f ∈ [1/2, 1)
+  unsigned long long m = (unsigned long long)std::ldexp(f, P);   // exact: x has P significant bits
+  int q = E >= 0 ? E / 3 : -((-E + 2) / 3);                  // floor division
+  int rem = E - 3 * q;
+  const int S = ((m << rem) >= (1ull << P)) ? P : P + 1;
+  const U192 X = shifted(m, rem - P + 3 * S);
+  unsigned long long lo = 0, hi = 1ull << 55;                 // invariant: lo³ ≤ X < hi³
+  while (hi - lo > 1) {
+    unsigned long long mid = lo + (hi - lo) / 2;
+    if (le(cube(mid), X)) lo = mid; else hi = mid;
+  }
+  unsigned long long y = (lo + 1) >> 1;
+  return (FT)std::ldexp((double)y, q - (S - 1));
+}
+template float cbrt_correctly_rounded<float>(float);
+template double cbrt_correctly_rounded<double>(double);
+
 }  // namespace nhhost

@@ -62,6 +62,20 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   pNHS = alloc_field();
   bool want_phy = d.hydrostatic_pressure_anomaly < 0 ? d.buoyancy_kind != NH_BUOYANCY_NONE : d.hydrostatic_pressure_anomaly != 0;
   if (want_phy) pHY = alloc_field();
+  NH_REQUIRE(d.has_closure >= NH_CLOSURE_NONE && d.has_closure <= NH_CLOSURE_SMAGORINSKY_LILLY, "unknown closure kind");
+  if (d.has_closure >= NH_CLOSURE_SMAGORINSKY) {
+    // build_diffusivity_fields (smagorinsky.jl:123-133); filter width Δᶠ = cbrt(Δx·Δy·Δz), correctly rounded on the host
+    nue = alloc_field();
+    std::vector<FT> t(gh.g.N[2]);
+    for (int k = 1; k <= gh.g.N[2]; ++k) {
+      FT dz = gh.g.topo[2] == NH_FLAT ? FT(1) : gh.dzc_h[k + gh.g.zoff];
+      FT d3 = gh.g.dx * gh.g.dy * dz;
+      FT df = nhhost::cbrt_correctly_rounded<FT>(d3);
+      t[k - 1] = df * df;
+    }
+    df2.upload(t);
+    for (int n = 0; n < ntr; ++n) NH_REQUIRE(d.smagorinsky_Pr[n] != 0, "Smagorinsky: Pr must be non-zero for every tracer");
+  }
 
   solver.lc = &lc;
   solver.stream = stream;
@@ -162,6 +176,7 @@ FT* Model<FT>::field_ptr(int field) {
   if (field >= 0 && field < nf) return F[field];
   if (field == NH_FIELD_PNHS) return pNHS;
   if (field == NH_FIELD_PHY) { NH_REQUIRE(pHY, "model has no hydrostatic pressure anomaly"); return pHY; }
+  if (field == NH_FIELD_NUE) { NH_REQUIRE(nue, "model has no eddy viscosity (closure is not a Smagorinsky)"); return nue; }
   if (field >= NH_FIELD_GN0 && field < NH_FIELD_GN0 + nf) return Gn[field - NH_FIELD_GN0];
   if (field >= NH_FIELD_GM0 && field < NH_FIELD_GM0 + nf) return Gm[field - NH_FIELD_GM0];
   throw NhError("unknown field id");
@@ -315,7 +330,22 @@ TendParams<FT> Model<FT>::tend_params() const {
   P.w_buoyancy = (desc.buoyancy_kind != NH_BUOYANCY_NONE && !pHY) ? 1 : 0;
   P.has_coriolis = desc.has_coriolis; P.fcor = (FT)desc.coriolis_f;
   P.has_closure = desc.has_closure; P.nu = (FT)desc.nu;
+  P.nue = nue;
+  for (int t = 0; t < ntr; ++t) P.Pr[t] = (FT)desc.smagorinsky_Pr[t];
   return P;
+}
+
+// compute_diffusivities! (smagorinsky.jl:107-119) over :xyz; the halo of νₑ is filled afterwards by update_state
+template <typename FT>
+void Model<FT>::compute_diffusivities() {
+  if (!nue) return;
+  SmagJob<FT> J;
+  J.P = tend_params(); J.nue = nue; J.df2 = df2.p;
+  J.lilly = desc.has_closure == NH_CLOSURE_SMAGORINSKY_LILLY;
+  J.C = (FT)desc.smagorinsky_C; J.Cb = (FT)desc.smagorinsky_Cb; J.C64 = desc.smagorinsky_C;
+  dim3 blk(32, 4, 1);
+  smagorinsky_kernel<FT><<<grid3(blk), blk, 0, stream>>>(J);
+  KLAUNCH(lc);
 }
 
 template <typename FT>
@@ -356,7 +386,9 @@ void Model<FT>::update_state(int compute) {
   if (compute) gn_stale = false;
   uint32_t mask = 0; for (int f = 0; f < nf; ++f) mask |= 1u << f;
   fill_halo_regions(mask, 0);
+  compute_diffusivities();                       // compute_auxiliaries!: diffusivities, then hydrostatic pressure
   update_hydrostatic_pressure();
+  if (nue) fill_halo_regions(1u << NH_FIELD_NUE, 1);
   if (compute) compute_tendencies();
 }
 

@@ -331,6 +331,9 @@ struct Model : nh_model {
   FT* Gm[NH_MAXF];
   FT* pNHS = nullptr;
   FT* pHY = nullptr;
+  FT* nue = nullptr;       // νₑ of the Smagorinsky closures (diffusivity_fields.νₑ)
+  DevBuf<FT> df2;          // Δᶠ² = cbrt(ΔxΔyΔz)² per k
+  void compute_diffusivities();
   SchemeDev adv[3];
   SchemeTables<FT> tab;
   PoissonGeneric<FT> solver;

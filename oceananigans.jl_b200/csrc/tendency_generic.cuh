@@ -189,10 +189,30 @@ __device__ __forceinline__ FT strain(const TendParams<FT>& P, int i, int j, int 
   return FT(0.5) * (deriv<FT, hi>(g, P.U[lo], 0, zc, i, j, k) + deriv<FT, lo>(g, P.U[hi], 0, zc, i, j, k));
 }
 
+// ν at the location of Σ_ab: the constant, or the eddy viscosity νₑ[i,j,k] at ccc / ℑ_hi(ℑ_lo νₑ) on the edge
+// (abstract_scalar_diffusivity_closure.jl:60-75 with a Center-located viscosity field; interpolation_operators.jl:45-53)
+template <typename FT, int d>
+__device__ __forceinline__ FT interp_to_face(const GridDev<FT>& g, const FT* q, int i, int j, int k) {
+  if (g.topo[d] == NH_FLAT) return q[g.idx(i, j, k)];
+  constexpr int di = d == 0, dj = d == 1, dk = d == 2;
+  return FT(0.5) * (q[g.idx(i - di, j - dj, k - dk)] + q[g.idx(i, j, k)]);
+}
+
+template <typename FT, int a, int b>
+__device__ __forceinline__ FT nu_at(const TendParams<FT>& P, int i, int j, int k) {
+  if (!P.nue) return P.nu;
+  const GridDev<FT>& g = P.g;
+  if (a == b) return P.nue[g.idx(i, j, k)];
+  constexpr int lo = a < b ? a : b, hi = a < b ? b : a;
+  if (g.topo[hi] == NH_FLAT) return interp_to_face<FT, lo>(g, P.nue, i, j, k);
+  constexpr int di = hi == 0, dj = hi == 1, dk = hi == 2;
+  return FT(0.5) * (interp_to_face<FT, lo>(g, P.nue, i - di, j - dj, k - dk) + interp_to_face<FT, lo>(g, P.nue, i, j, k));
+}
+
 template <typename FT, int a, int b>
 __device__ __forceinline__ FT viscous_Aflux(const TendParams<FT>& P, int i, int j, int k) {
   constexpr int zc = (a != b && (a == 2 || b == 2)) ? 0 : 1;
-  return area_at(P.g, b, zc, k) * (FT(-2) * (P.nu * strain<FT, a, b>(P, i, j, k)));
+  return area_at(P.g, b, zc, k) * (FT(-2) * (nu_at<FT, a, b>(P, i, j, k) * strain<FT, a, b>(P, i, j, k)));
 }
 
 template <typename FT, int a, int b>
@@ -210,14 +230,16 @@ __device__ __forceinline__ FT div_viscous_flux(const TendParams<FT>& P, int i, i
   return FT(1) / volume_at(P.g, a == 2 ? 0 : 1, k) * total;
 }
 
+// diffusive_flux = -κ·∂c with κ the constant, or ℑ_b(νₑ) / Pr (Smagorinskys/smagorinsky.jl:135-137)
 template <typename FT, int b>
-__device__ __forceinline__ FT diffusive_Aflux(const TendParams<FT>& P, const FT* c, FT kappa, int i, int j, int k) {
+__device__ __forceinline__ FT diffusive_Aflux(const TendParams<FT>& P, const FT* c, int n, int i, int j, int k) {
   constexpr int zc = b == 2 ? 0 : 1;
+  const FT kappa = P.nue ? interp_to_face<FT, b>(P.g, P.nue, i, j, k) / P.Pr[n] : P.kappa[n];
   return area_at(P.g, b, zc, k) * (-kappa * deriv<FT, b>(P.g, c, 0, zc, i, j, k));
 }
 
 template <typename FT>
-__device__ __forceinline__ FT div_diffusive_flux(const TendParams<FT>& P, const FT* c, FT kappa, int i, int j, int k) {
+__device__ __forceinline__ FT div_diffusive_flux(const TendParams<FT>& P, const FT* c, int kappa, int i, int j, int k) {
   const GridDev<FT>& g = P.g;
   FT tx = g.topo[0] == NH_FLAT ? FT(0) : diffusive_Aflux<FT, 0>(P, c, kappa, i + 1, j, k) - diffusive_Aflux<FT, 0>(P, c, kappa, i, j, k);
   FT ty = g.topo[1] == NH_FLAT ? FT(0) : diffusive_Aflux<FT, 1>(P, c, kappa, i, j + 1, k) - diffusive_Aflux<FT, 1>(P, c, kappa, i, j, k);
@@ -225,6 +247,71 @@ __device__ __forceinline__ FT div_diffusive_flux(const TendParams<FT>& P, const 
   FT total = tx + ty;
   total = total + tz;
   return FT(1) / volume_at(g, 1, k) * total;
+}
+
+// ---- Smagorinsky / Smagorinsky-Lilly eddy viscosity ---------------------------------------------------------------
+// _compute_smagorinsky_viscosity! over :xyz — Smagorinskys/smagorinsky.jl:88-105, lilly_coefficient.jl:125-139,
+// scale_invariant_operators.jl:10-13 (ΣᵢⱼΣᵢⱼᶜᶜᶜ), BuoyancyFormulations ∂z_b.  Δᶠ² = cbrt(ΔxΔyΔz)² comes from a host
+// table (one entry per k) with a correctly rounded cube root (grid_host.cpp), the same bits as the oracle's.
+template <typename FT, int lo, int hi>
+__device__ __forceinline__ FT strain_sq_to_center(const TendParams<FT>& P, int i, int j, int k) {
+  // ℑ_hi(ℑ_lo Σ_lohi²) onto Centers: 0.5·(X(q) + X(q+1)) along hi of X = 0.5·(Σ²(p) + Σ²(p+1)) along lo; identity if Flat
+  const GridDev<FT>& g = P.g;
+  constexpr int li = lo == 0, lj = lo == 1, lk = lo == 2, hi_i = hi == 0, hi_j = hi == 1, hi_k = hi == 2;
+  auto sq = [&](int i2, int j2, int k2) { FT x = strain<FT, lo, hi>(P, i2, j2, k2); return x * x; };
+  auto X = [&](int i2, int j2, int k2) {
+    if (g.topo[lo] == NH_FLAT) return sq(i2, j2, k2);
+    return FT(0.5) * (sq(i2, j2, k2) + sq(i2 + li, j2 + lj, k2 + lk));
+  };
+  if (g.topo[hi] == NH_FLAT) return X(i, j, k);
+  return FT(0.5) * (X(i, j, k) + X(i + hi_i, j + hi_j, k + hi_k));
+}
+
+template <typename FT>
+__device__ __forceinline__ FT dz_b_at(const TendParams<FT>& P, int i, int j, int k) {
+  if (P.buoy_kind == NH_BUOYANCY_NONE) return FT(0);
+  if (P.buoy_kind == NH_BUOYANCY_TRACER) return deriv<FT, 2>(P.g, P.c[P.iT], 0, 0, i, j, k);
+  return P.grav * (P.alpha * deriv<FT, 2>(P.g, P.c[P.iT], 0, 0, i, j, k) - P.beta * deriv<FT, 2>(P.g, P.c[P.iS], 0, 0, i, j, k));
+}
+
+template <typename FT>
+struct SmagJob {
+  TendParams<FT> P;
+  FT* nue;
+  const FT* df2;          // Δᶠ·Δᶠ at k (index k-1)
+  int lilly;
+  FT C, Cb;               // SmagorinskyLilly: converted to FT
+  double C64;             // Smagorinsky(coefficient = number): NOT converted (the product is formed in Float64)
+};
+
+template <typename FT>
+__global__ void __launch_bounds__(128) smagorinsky_kernel(const __grid_constant__ SmagJob<FT> J) {
+  const TendParams<FT>& P = J.P;
+  const GridDev<FT>& g = P.g;
+  int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
+  int j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  int k = blockIdx.z + 1;
+  if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
+  const FT s11 = strain<FT, 0, 0>(P, i, j, k), s22 = strain<FT, 1, 1>(P, i, j, k), s33 = strain<FT, 2, 2>(P, i, j, k);
+  FT S2 = s11 * s11 + s22 * s22 + s33 * s33;
+  S2 = S2 + FT(2) * strain_sq_to_center<FT, 0, 1>(P, i, j, k);
+  S2 = S2 + FT(2) * strain_sq_to_center<FT, 0, 2>(P, i, j, k);
+  S2 = S2 + FT(2) * strain_sq_to_center<FT, 1, 2>(P, i, j, k);
+  const FT df2 = J.df2[k - 1];
+  const FT root = sqrt(FT(2) * S2);
+  FT nu;
+  if (J.lilly) {
+    const FT N2 = g.topo[2] == NH_FLAT ? dz_b_at(P, i, j, k) : FT(0.5) * (dz_b_at(P, i, j, k) + dz_b_at(P, i, j, k + 1));
+    const FT N2p = N2 > FT(0) ? N2 : FT(0);            // max(zero(FT), N²)
+    const FT ratio = J.Cb * N2p / S2;
+    const FT sig2 = FT(1) - (ratio < FT(1) ? ratio : (ratio != ratio ? ratio : FT(1)));   // min(1, NaN) is NaN in Julia
+    const FT sig = S2 == FT(0) ? FT(0) : sqrt(sig2);
+    const FT cs2 = sig * (J.C * J.C);
+    nu = cs2 * df2 * root;
+  } else {
+    nu = (FT)((J.C64 * J.C64) * (double)df2 * (double)root);
+  }
+  J.nue[g.idx(i, j, k)] = nu;
 }
 
 // ---- the tendencies ---------------------------------------------------------------------------------------
@@ -252,7 +339,7 @@ __device__ __forceinline__ FT velocity_tendency(const TendParams<FT>& P, int i, 
 template <typename FT>
 __device__ __forceinline__ FT tracer_tendency(const TendParams<FT>& P, int n, int i, int j, int k) {
   FT G = -div_Uc<FT>(P, P.c[n], i, j, k);
-  if (P.has_closure) G = G - div_diffusive_flux<FT>(P, P.c[n], P.kappa[n], i, j, k);
+  if (P.has_closure) G = G - div_diffusive_flux<FT>(P, P.c[n], n, i, j, k);
   else G = G - FT(0);
   return G;
 }

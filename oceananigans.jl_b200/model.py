@@ -164,10 +164,14 @@ class NonhydrostaticModel:
             raise ValueError("unsupported buoyancy formulation")
         if coriolis is not None:
             d.has_coriolis, d.coriolis_f = 1, coriolis.f
-        if closure is not None:
-            d.has_closure, d.nu = 1, closure.nu
+        if closure is not None and closure.kind == L.CLOSURE_SCALAR:
+            d.has_closure, d.nu = L.CLOSURE_SCALAR, closure.nu
             for n, name in enumerate(tracers):
                 d.kappa[n] = closure.kappa_for(name)
+        elif closure is not None:
+            d.has_closure, d.smagorinsky_C, d.smagorinsky_Cb = closure.kind, closure.C, closure.Cb
+            for n, name in enumerate(tracers):
+                d.smagorinsky_Pr[n] = closure.Pr_for(name)
         d.hydrostatic_pressure_anomaly = -1 if hydrostatic_pressure_anomaly == "default" else int(bool(hydrostatic_pressure_anomaly))
         d.exact_arithmetic = int(bool(exact_arithmetic))
         self.grid = grid
@@ -192,6 +196,9 @@ class NonhydrostaticModel:
         self.pressures = _Namespace(pNHS=Field(self, L.FIELD_PNHS, "pNHS", ("c", "c", "c")))
         if (buoyancy is not None) if hydrostatic_pressure_anomaly == "default" else hydrostatic_pressure_anomaly:
             self.pressures["pHY"] = Field(self, L.FIELD_PHY, "pHY", ("c", "c", "c"))
+        self.diffusivity_fields = _Namespace()
+        if closure is not None and closure.kind != L.CLOSURE_SCALAR:
+            self.diffusivity_fields["nu_e"] = Field(self, L.FIELD_NUE, "nu_e", ("c", "c", "c"))
         self.timestepper = _Namespace(
             Gn=_Namespace((n, Field(self, L.FIELD_GN0 + i, "Gn_" + n, locs[i])) for i, n in enumerate(names)),
             Gm=_Namespace((n, Field(self, L.FIELD_GM0 + i, "Gm_" + n, locs[i])) for i, n in enumerate(names)))

@@ -31,6 +31,28 @@ def round_fraction(fr, FT):
     return FT(best)
 
 
+def cbrt_correctly_rounded(x, FT):
+    """Correctly rounded cube root of a positive FT number by exact integer arithmetic (implementation-independent: the
+    CUDA library's host code computes the same bits; the reference's Base.cbrt is accurate to < 1 ulp)."""
+    import math
+    FT = np.dtype(FT).type
+    P = 53 if FT == np.float64 else 24
+    if not (FT(x) > 0) or not np.isfinite(FT(x)):
+        return FT(np.cbrt(FT(x)))
+    f, E = math.frexp(float(FT(x)))
+    m = int(math.ldexp(f, P))
+    q, rem = divmod(E, 3)
+    S = P if (m << rem) >= (1 << P) else P + 1
+    X = m << (rem - P + 3 * S)
+    r = 1 << ((X.bit_length() + 2) // 3)
+    while True:                                  # integer Newton: ⌊cbrt(X)⌋
+        nr = (2 * r + X // (r * r)) // 3
+        if nr >= r:
+            break
+        r = nr
+    return FT(math.ldexp((r + 1) >> 1, q - (S - 1)))
+
+
 class OffsetVec:
     """Dense vector with an arbitrary first index (mirrors OffsetArrays.OffsetVector)."""
 

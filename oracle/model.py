@@ -23,7 +23,7 @@ from .advection import Centered, adapt_advection_order
 from .operators import divergence_ccc, deriv, delta, interior_region, area, volume
 from .solvers import FFTBasedPoissonSolver, FourierTridiagonalPoissonSolver
 from .tendencies import (VEL_LOC, CCC, momentum_tendency, tracer_tendency, tendency_region,
-                         update_hydrostatic_pressure)
+                         update_hydrostatic_pressure, compute_smagorinsky_viscosity)
 
 
 SIDES = {"west": (0, 0), "east": (0, 1), "south": (1, 0), "north": (1, 1), "bottom": (2, 0), "top": (2, 1)}
@@ -50,11 +50,32 @@ class SeawaterBuoyancy:
 
 
 class ScalarDiffusivity:
+    kind = "scalar"
+
     def __init__(self, nu=0.0, kappa=0.0):
         self.nu, self.kappa = nu, kappa
 
     def kappa_for(self, name):
         return self.kappa[name] if isinstance(self.kappa, dict) else self.kappa
+
+
+class SmagorinskyLilly:
+    """SmagorinskyLilly(FT; C = 0.16, Cb = 1, Pr = 1) — Smagorinskys/lilly_coefficient.jl:108-113 (C, Cb, Pr → FT)."""
+    kind = "smagorinsky_lilly"
+
+    def __init__(self, C=0.16, Cb=1.0, Pr=1.0):
+        self.C, self.Cb, self.Pr = C, Cb, Pr
+
+    def Pr_for(self, name):
+        return self.Pr[name] if isinstance(self.Pr, dict) else self.Pr
+
+
+class Smagorinsky(SmagorinskyLilly):
+    """Smagorinsky(FT; coefficient = 0.16, Pr = 1) — Smagorinskys/smagorinsky.jl:78-84,105 (constant coefficient)."""
+    kind = "smagorinsky"
+
+    def __init__(self, coefficient=0.16, Pr=1.0):
+        self.C, self.Cb, self.Pr = coefficient, 0.0, Pr
 
 
 class Clock:
@@ -101,6 +122,8 @@ class NonhydrostaticModel:
                 d, s = SIDES[side]
                 f.set_boundary_condition(d, s, kind, value)
         self.pNHS = Field(grid, CCC, prognostic=False, name="pNHS")
+        # build_diffusivity_fields (smagorinsky.jl:123-133): νₑ at ccc with default boundary conditions
+        self.nu_e = Field(grid, CCC, prognostic=False, name="nu_e") if (closure is not None and closure.kind != "scalar") else None
         if hydrostatic_pressure_anomaly == "default":
             self.pHY = Field(grid, CCC, prognostic=False, name="pHY") if buoyancy is not None else None
         else:
@@ -139,7 +162,11 @@ class NonhydrostaticModel:
 def update_state(model, compute_tendencies=True):
     """update_state!: halo fill (normal velocities not re-imposed) → hydrostatic pressure → tendencies."""
     fill_halo_regions(model.prognostic_fields(), fill_boundary_normal_velocities=False)
+    if model.nu_e is not None:                     # compute_auxiliaries!: diffusivities, then hydrostatic pressure
+        compute_smagorinsky_viscosity(model)
     update_hydrostatic_pressure(model.grid, model.pHY, model.buoyancy, model.tracers)
+    if model.nu_e is not None:
+        fill_halo_regions(model.nu_e)
     if compute_tendencies:
         compute_tendencies_(model)
 

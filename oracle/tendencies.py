@@ -14,7 +14,7 @@ Follows the reference's
 """
 import numpy as np
 
-from .grid import Bounded, Flat
+from .grid import Bounded, Flat, cbrt_correctly_rounded
 from .advection import (is_upwind, symmetric_interpolate, biased_interpolate, shift)
 from .operators import area, volume, delta, diff, interp, deriv
 
@@ -230,17 +230,85 @@ def _strain(grid, U, a, b, R):
     return grid.FT(0.5) * (deriv(grid, U[lo].at, hi, loc, R) + deriv(grid, U[hi].at, lo, loc, R))
 
 
-def div_viscous_flux(grid, nu, U, a, R):
-    """∂ⱼ_τ_aⱼ (closure_kernel_operators.jl:22-41) with viscous_flux = -2·(ν·Σ)."""
+def strain_dot_strain_ccc(grid, U, R):
+    """ΣᵢⱼΣᵢⱼᶜᶜᶜ (Smagorinskys/scale_invariant_operators.jl:10-13; velocity_tracer_gradients.jl:44-46,78):
+    tr_Σ² + 2·ℑxyᶜᶜᵃ(Σ₁₂²) + 2·ℑxzᶜᵃᶜ(Σ₁₃²) + 2·ℑyzᵃᶜᶜ(Σ₂₃²), ℑ_ab = ℑ_b(ℑ_a ·) (interpolation_operators.jl:45-53)."""
     FT = grid.FT
-    nu = FT(nu)
+    s = [_strain(grid, U, a, a, R) for a in range(3)]
+    total = s[0] * s[0] + s[1] * s[1] + s[2] * s[2]
+    for lo, hi in ((0, 1), (0, 2), (1, 2)):
+        def sq(*r, lo=lo, hi=hi):
+            x = _strain(grid, U, lo, hi, list(r))
+            return x * x
+
+        def inner(*r, lo=lo, sq=sq):
+            return interp(grid, sq, lo, "c", list(r))
+        total = total + FT(2) * interp(grid, inner, hi, "c", R)
+    return total
+
+
+def dz_b(grid, buoyancy, tracers):
+    """getter for ∂z_b at (c,c,f) — buoyancy_tracer.jl:16, seawater_buoyancy.jl:219-224, no_buoyancy.jl:9."""
+    FT = grid.FT
+    ccf = ("c", "c", "f")
+    if buoyancy is None:
+        return lambda *r: FT(0)
+    if buoyancy.kind == "tracer":
+        return lambda *r: deriv(grid, tracers["b"].at, 2, ccf, list(r))
+    g, al, be = FT(buoyancy.g), FT(buoyancy.alpha), FT(buoyancy.beta)
+    return lambda *r: g * (al * deriv(grid, tracers["T"].at, 2, ccf, list(r)) - be * deriv(grid, tracers["S"].at, 2, ccf, list(r)))
+
+
+def compute_smagorinsky_viscosity(model):
+    """_compute_smagorinsky_viscosity! over :xyz (Smagorinskys/smagorinsky.jl:88-103) with the constant coefficient
+    (:105) or the Lilly stability correction (lilly_coefficient.jl:125-139): νₑ = cˢ²·Δᶠ²·√(2Σ²), Δᶠ = cbrt(ΔxΔyΔz)."""
+    grid, FT, cl = model.grid, model.grid.FT, model.closure
+    R = [(1, grid.N[0]), (1, grid.N[1]), (1, grid.N[2])]
+    S2 = np.asarray(strain_dot_strain_ccc(grid, model.velocities, R), dtype=FT)
+    D3 = delta(grid, 0, "c", R) * delta(grid, 1, "c", R) * delta(grid, 2, "c", R)
+    D3 = np.asarray(D3, dtype=FT)
+    Df = np.vectorize(lambda v: cbrt_correctly_rounded(v, FT), otypes=[FT])(D3)      # a few distinct values (one per k)
+    if cl.kind == "smagorinsky_lilly":
+        N2 = interp(grid, dz_b(grid, model.buoyancy, model.tracers), 2, "c", R)
+        N2p = np.maximum(FT(0), N2)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            ratio = FT(cl.Cb) * N2p / S2
+            # Julia's min(1, NaN) is NaN; the ifelse below discards it
+            sig2 = FT(1) - np.where(np.isnan(ratio), ratio, np.minimum(FT(1), ratio))
+            sig = np.where(S2 == 0, FT(0), np.sqrt(sig2))
+        cs2 = sig * (FT(cl.C) * FT(cl.C))
+    else:
+        cs2 = np.float64(cl.C) * np.float64(cl.C)      # the constant coefficient is NOT converted to eltype(grid)
+    nu = cs2 * (Df * Df) * np.sqrt(FT(2) * S2)
+    model.nu_e.at(*R)[...] = np.broadcast_to(nu, model.nu_e.at(*R).shape).astype(FT)
+
+
+def _nu_getter(grid, nu, a, b):
+    """ν at the location of Σ_ab: a number, or the field νₑ at ccc (a == b) / ℑ_hi(ℑ_lo νₑ) at the edge
+    (abstract_scalar_diffusivity_closure.jl:60-75 with a Center-located viscosity field)."""
+    if not hasattr(nu, "at"):
+        c = grid.FT(nu)
+        return lambda RR: c
+    if a == b:
+        return lambda RR: nu.at(*RR)
+    lo, hi = min(a, b), max(a, b)
+
+    def inner(*r):
+        return interp(grid, nu.at, lo, "f", list(r))
+    return lambda RR: interp(grid, inner, hi, "f", RR)
+
+
+def div_viscous_flux(grid, nu, U, a, R):
+    """∂ⱼ_τ_aⱼ (closure_kernel_operators.jl:22-41) with viscous_flux = -2·(ν·Σ); ν a number or the eddy-viscosity field."""
+    FT = grid.FT
     total = None
     for b in range(3):
         target = "f" if a == b else "c"
         floc = flux_location(a, b)
+        nu_at = _nu_getter(grid, nu, a, b)
 
-        def Aq(RR, b=b, floc=floc):
-            return area(grid, b, floc, RR) * (FT(-2) * (nu * _strain(grid, U, a, b, RR)))
+        def Aq(RR, b=b, floc=floc, nu_at=nu_at):
+            return area(grid, b, floc, RR) * (FT(-2) * (nu_at(RR) * _strain(grid, U, a, b, RR)))
         if grid.topology[b] == Flat:
             t = FT(0)
         else:
@@ -249,16 +317,21 @@ def div_viscous_flux(grid, nu, U, a, R):
     return FT(1) / volume(grid, VEL_LOC[a], R) * total
 
 
-def div_diffusive_flux(grid, kappa, c, R):
-    """∇_dot_qᶜ (closure_kernel_operators.jl:43-48) with diffusive_flux = -κ·∂c."""
+def div_diffusive_flux(grid, kappa, c, R, Pr=None):
+    """∇_dot_qᶜ (closure_kernel_operators.jl:43-48) with diffusive_flux = -κ·∂c; κ a number, or (Pr given) the field νₑ:
+    κ at the face = ℑ_b(νₑ) / Pr (Smagorinskys/smagorinsky.jl:135-137)."""
     FT = grid.FT
-    kappa = FT(kappa)
     total = None
     for b in range(3):
         floc = VEL_LOC[b]
+        if Pr is None:
+            kc = FT(kappa)
+            k_at = lambda RR, kc=kc: kc
+        else:
+            k_at = lambda RR, b=b: interp(grid, kappa.at, b, "f", RR) / FT(Pr)
 
-        def Aq(RR, b=b, floc=floc):
-            return area(grid, b, floc, RR) * (-kappa * deriv(grid, c.at, b, floc, RR))
+        def Aq(RR, b=b, floc=floc, k_at=k_at):
+            return area(grid, b, floc, RR) * (-k_at(RR) * deriv(grid, c.at, b, floc, RR))
         if grid.topology[b] == Flat:
             t = FT(0)
         else:
@@ -292,7 +365,8 @@ def momentum_tendency(model, a):
         else:
             G = G - FT(0)
     if model.closure is not None:
-        G = G - div_viscous_flux(grid, model.closure.nu, U, a, R)
+        nu = model.nu_e if model.closure.kind != "scalar" else model.closure.nu
+        G = G - div_viscous_flux(grid, nu, U, a, R)
     else:
         G = G - FT(0)
     return R, G
@@ -303,7 +377,9 @@ def tracer_tendency(model, name):
     c = model.tracers[name]
     R = tendency_region(grid, CCC)
     G = -div_Uc(grid, model.advection, model.velocities, c, R)
-    if model.closure is not None:
+    if model.closure is not None and model.closure.kind != "scalar":
+        G = G - div_diffusive_flux(grid, model.nu_e, c, R, Pr=model.closure.Pr_for(name))
+    elif model.closure is not None:
         G = G - div_diffusive_flux(grid, model.closure.kappa_for(name), c, R)
     else:
         G = G - FT(0)

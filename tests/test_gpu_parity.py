@@ -60,8 +60,13 @@ def make_pair(oc, FT, size, topo, z=None, advection=("WENO", 5), timestepper="Ru
         b1, b2 = oc.BuoyancyTracer(), o.BuoyancyTracer()
     c1 = oc.FPlane(coriolis) if coriolis is not None else None
     c2 = o.FPlane(coriolis) if coriolis is not None else None
-    k1 = oc.ScalarDiffusivity(*closure) if closure else None
-    k2 = o.ScalarDiffusivity(*closure) if closure else None
+    if closure and closure[0] == "lilly":          # ("lilly", C, Cb, Pr)
+        k1, k2 = oc.SmagorinskyLilly(*closure[1:]), o.SmagorinskyLilly(*closure[1:])
+    elif closure and closure[0] == "smagorinsky":  # ("smagorinsky", coefficient, Pr)
+        k1, k2 = oc.Smagorinsky(*closure[1:]), o.Smagorinsky(*closure[1:])
+    else:
+        k1 = oc.ScalarDiffusivity(*closure) if closure else None
+        k2 = o.ScalarDiffusivity(*closure) if closure else None
     mk = {"value": oc.ValueBoundaryCondition, "gradient": oc.GradientBoundaryCondition, "flux": oc.FluxBoundaryCondition}
     bcs1 = {n: oc.FieldBoundaryConditions(**{side: mk[k](v) for side, (k, v) in sides.items()})
             for n, sides in (bcs or {}).items()}
@@ -113,6 +118,13 @@ CONFIGS = [
     ((12, 10, 9), (P, P, B), None, ("WENO", 5), dict(buoyancy="seawater", tracers=("T", "S"), coriolis=1e-2, closure=(1e-2, 2e-2), bcs=BCS_LES)),
     ((9, 8, 10), (B, B, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=(1e-2, 1e-2), bcs=BCS_BOX)),
     ((10, 9, 8), (P, P, B), "stretched", ("Centered", 2), dict(tracers=("c",), closure=(1e-3, 1e-3), bcs=BCS_STRETCHED)),
+    # Smagorinsky closures: eddy viscosity field νₑ, variable-coefficient viscous / diffusive fluxes
+    ((12, 10, 9), (P, P, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=("lilly", 0.16, 1.0, 1.0))),
+    ((10, 9, 8), (P, P, B), "stretched", ("WENO", 5), dict(buoyancy="seawater", tracers=("T", "S"), coriolis=1e-2,
+                                                           closure=("lilly", 0.23, 1.0, {"T": 1.0, "S": 2.0}), bcs=BCS_LES)),
+    ((9, 8, 10), (B, B, B), None, ("Centered", 2), dict(tracers=("c",), closure=("smagorinsky", 0.16, 0.7))),
+    ((12, 10, 9), (P, P, P), None, ("WENO", 5), dict(closure=("lilly", 0.16, 1.0, 1.0))),
+    ((16, 12), (P, F, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=("lilly", 0.16, 1.0, 1.0))),
 ]
 
 
@@ -136,6 +148,8 @@ def test_tendencies_and_halos_bit_exact(oc, FT, cfg):
         f2.set(ics[n])
     oc.update_state(m1, compute_tendencies=True)
     o_update_state(m2, compute_tendencies=True)
+    if m2.nu_e is not None:
+        np.testing.assert_array_equal(m1.diffusivity_fields.nu_e.parent(), m2.nu_e.data, err_msg="nu_e")
     for n, f1, f2 in names_fields(m1, m2):
         np.testing.assert_array_equal(f1.parent(), f2.data, err_msg=f"parent({n}) after halo fill")
         G1 = m1.timestepper.Gn[n].interior()
@@ -282,6 +296,20 @@ def test_100_steps_with_value_gradient_flux_boundary_conditions(oc, FT, tol, tim
     m1, m2 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
     _, m3 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
     ics = smooth_ics(m2, np.random.default_rng(99), amp=0.5)
+    err, floor = _run_steps(oc, m1, m2, ics, 1e-2, 100, m3)
+    check_parity(err, tol, floor)
+
+
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+def test_100_steps_smagorinsky_lilly_les(oc, FT, tol, timestepper):
+    """The ocean-LES regression set-up's physics (ocean_large_eddy_simulation_regression_test.jl:20-60: SmagorinskyLilly
+    C = 0.23, wind stress + cooling + bottom gradient, SeawaterBuoyancy, FPlane) on 16³ — 100 steps against the oracle."""
+    kw = dict(extent=(1, 1, 1), buoyancy="seawater", tracers=("T", "S"), coriolis=1e-4, closure=("lilly", 0.23, 1.0, 1.0),
+              timestepper=timestepper, bcs=BCS_LES)
+    m1, m2 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
+    _, m3 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
+    ics = smooth_ics(m2, np.random.default_rng(5), amp=0.5)
     err, floor = _run_steps(oc, m1, m2, ics, 1e-2, 100, m3)
     check_parity(err, tol, floor)
 

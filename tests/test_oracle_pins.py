@@ -320,3 +320,55 @@ def test_diffusive_flux_through_a_gradient_wall_matches_the_budget():
     for n in range(10):
         o.time_step(m, dt, euler=(n == 0))
     assert abs((b.interior.mean() - mean0) - (-kappa * bz) * m.clock.time / Lz) < 1e-6
+
+
+# ---------------------------------------------------------------------------------------------
+# Smagorinsky closures — analytic eddy viscosity (the reference only smoke-tests these closures:
+# test_time_stepping.jl:244-257, test_turbulence_closures.jl:300-320; its golden LES files are remote DataDeps)
+# ---------------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+def test_smagorinsky_viscosity_of_a_linear_shear(FT):
+    """u = S·z: Σ₁₃ = S/2, 2ΣᵢⱼΣᵢⱼ = S², so νₑ = (C·Δᶠ)²·|S| (smagorinsky.jl:46-50); with b = N²·z the Lilly factor is
+    √(1 - Cb·N²/Σ²) = √(1 - 2·Cb·N²/S²) (lilly_coefficient.jl:13-16,125-130), clipped at 0 and unity for N² ≤ 0."""
+    from oracle.model import update_state
+    S, C = 3.0, 0.16
+    N = (8, 8, 16)
+    g = o.RectilinearGrid(FT, size=N, extent=(1, 1, 2), topology=(P, P, B))
+    zc = -2 + (np.arange(16) + 0.5) * 2 / 16
+    u = np.broadcast_to(S * zc, N)
+    delta_f = np.cbrt((1 / 8) * (1 / 8) * (2 / 16))
+    rtol = 1e-12 if FT == np.float64 else 2e-6
+    for Cb, N2, expect in ((1.0, 0.0, 1.0), (1.0, 2.0, np.sqrt(1 - 2 * 2.0 / S ** 2)), (1.0, 100.0, 0.0), (1.0, -5.0, 1.0),
+                           (0.0, 2.0, 1.0)):
+        m = o.NonhydrostaticModel(g, tracers=("b",), buoyancy=o.BuoyancyTracer(), closure=o.SmagorinskyLilly(C=C, Cb=Cb))
+        m.velocities[0].set(u)
+        m.tracers["b"].set(np.broadcast_to(N2 * zc, N))
+        update_state(m, compute_tendencies=False)
+        nu = m.nu_e.interior[:, :, 2:-2]                  # away from the walls (mirror halos flatten the profiles there)
+        np.testing.assert_allclose(nu, (C * delta_f) ** 2 * S * expect, rtol=rtol, atol=1e-30)
+    m = o.NonhydrostaticModel(g, closure=o.Smagorinsky(coefficient=C))
+    m.velocities[0].set(u)
+    update_state(m, compute_tendencies=False)
+    np.testing.assert_allclose(m.nu_e.interior[:, :, 2:-2], (C * delta_f) ** 2 * S, rtol=rtol)
+
+
+def test_smagorinsky_time_stepping_stays_incompressible_and_dissipates():
+    """time_stepping_works_with_closure (test_time_stepping.jl:36-49) for ConstantSmagorinsky and SmagorinskyLilly, plus
+    the physics the closure is there for: kinetic energy of a random field decays faster than without it."""
+    rng = np.random.default_rng(11)
+    N = (8, 8, 8)
+    ics = {n: rng.uniform(-1, 1, N) for n in "uvw"}
+    ke = {}
+    for name, cl in (("none", None), ("smag", o.Smagorinsky()), ("lilly", o.SmagorinskyLilly())):
+        g = o.RectilinearGrid(np.float64, size=N, extent=(1, 1, 1), topology=(P, P, P))
+        m = o.NonhydrostaticModel(g, advection=o.Centered(np.float64, 2), closure=cl, tracers=("b",) if cl else (),
+                                  buoyancy=o.BuoyancyTracer() if cl else None)
+        o.set_model(m, **ics)
+        for _ in range(5):
+            o.time_step(m, 1e-3)
+        u, v, w = m.velocities
+        R = interior_region(g)
+        assert np.abs(divergence_ccc(g, u, v, w, R)).max() < 1e-10
+        ke[name] = sum((f.interior ** 2).sum() for f in m.velocities)
+    assert ke["smag"] < ke["none"] and ke["lilly"] < ke["none"]
