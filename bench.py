@@ -72,6 +72,7 @@ def cpu_oracle_rate(N, steps, warmup=1):
     kernel, every face flux evaluated twice, full complex FFT — pinned against the NumPy oracle in tests/test_cpu_step.py)
     on an N³ sample of the same workload, on all host threads OpenMP gives it.  Returns (rate, s/step, threads)."""
     from oracle.cpu_step import CpuStepModel
+    CpuStepModel.use_all_cores()
     m = CpuStepModel((N, N, N), (2 * np.pi,) * 3)
     ics = smooth_ics(N, 1234)
     m.set(ics["u"], ics["v"], ics["w"])

@@ -416,6 +416,15 @@ void cpu_model_time_step(cpu_model *m, double dt) {
     m->iteration += 1;
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to its ranks; the baseline is meant to use every host core it may run on */
+void cpu_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int cpu_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -35,6 +35,7 @@ def lib():
         L.cpu_model_compute_tendencies.argtypes = [ctypes.c_void_p]
         L.cpu_model_time_step.argtypes = [ctypes.c_void_p, ctypes.c_double]
         L.cpu_threads.restype = ctypes.c_int
+        L.cpu_set_threads.argtypes = [ctypes.c_int]
         _LIB = L
     return _LIB
 
@@ -93,3 +94,10 @@ class CpuStepModel:
     @staticmethod
     def threads():
         return int(lib().cpu_threads())
+
+    @staticmethod
+    def use_all_cores():
+        """All cores this process may run on, whatever OMP_NUM_THREADS says (torchrun sets it to 1 for its ranks)."""
+        n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        lib().cpu_set_threads(n)
+        return n
