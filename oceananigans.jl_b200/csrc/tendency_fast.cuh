@@ -33,6 +33,11 @@
 #ifndef TF_PREFETCH
 #define TF_PREFETCH 0    // L2 prefetch of the tiles the next phase reads: measured slower (1.27 vs 1.16 ms at 256³), kept off
 #endif
+#ifndef TF_PIPELINE
+#define TF_PIPELINE 0    // marching loops load the next face's stencil value and advecting velocities right after the current
+                         // face's upwind selection (into the registers that selection just freed) instead of at the top of
+                         // the next step: the loads fly during the WENO arithmetic
+#endif
 constexpr int tf_unroll = TF_UNROLL;
 #define TF_SMEM_ELEMS (TF_TZ * TF_TY * (TF_TX + 1) + TF_TZ * (TF_TY + 1) * TF_TX + (TF_TZ + 1) * TF_TY * TF_TX)
 
@@ -103,6 +108,26 @@ __device__ __forceinline__ FT march_one(const SchemeTables<FT>& T, FT S0, FT S1,
   return ut * (VARIANT == 0 ? weno5_from_q<FT>(T, q0, q1, q2, q3, q4) : weno5_contracted<FT>(T, q0, q1, q2, q3, q4));
 }
 
+// march_one with the advecting-velocity inputs passed in registers (pipelined loops)
+template <typename FT, int VARIANT, bool SAME>
+__device__ __forceinline__ FT march_ut(const SchemeTables<FT>& T, FT S1, FT S2, FT S3, FT S4, FT v0, FT v1, FT v2, FT v3, FT Ab) {
+  FT u0, u1, u2, u3;
+  if (SAME) { u0 = S1; u1 = S2; u2 = S3; u3 = S4; }
+  else { u0 = v0; u1 = v1; u2 = v2; u3 = v3; }
+  FT ut;
+  if (VARIANT == 0) {
+    ut = T.sym[2][3] * (Ab * u0);
+    ut = ut + T.sym[2][2] * (Ab * u1);
+    ut = ut + T.sym[2][1] * (Ab * u2);
+    ut = ut + T.sym[2][0] * (Ab * u3);
+  } else {
+    ut = T.sym[2][3] * u0 + T.sym[2][2] * u1;
+    ut = (ut + T.sym[2][1] * u2) + T.sym[2][0] * u3;
+    ut = Ab * ut;
+  }
+  return ut;
+}
+
 // `count` consecutive face fluxes F_{b,a} along direction b (stride sb), starting at flux location n, with the stencil
 // window carried in registers from one face to the next.  The loop body is written out for the six rotations of the
 // window's register names, so advancing one face costs one load and no register moves.
@@ -114,6 +139,38 @@ __device__ __forceinline__ void march_fluxes(const SchemeTables<FT>& T, const FT
   FT S0 = p[0], S1 = p[sb], S2 = p[2 * sb], S3 = p[3 * sb], S4 = p[4 * sb], S5;
   p += 5 * sb;
   const FT* pb = ub + (n - 2 * sa);
+#if TF_PIPELINE
+  if ((VARIANT == 0 ? TF_ROTATE_EXACT : TF_ROTATE) != 0) {
+    // software-pipelined: window value S5 and the four advecting-velocity inputs of step c are loaded during step c-1
+    FT v0 = FT(0), v1 = FT(0), v2 = FT(0), v3 = FT(0);
+    S5 = *p;
+    if (!SAME) { v0 = pb[0]; v1 = pb[sa]; v2 = pb[2 * sa]; v3 = pb[3 * sa]; }
+#define TF_PIPE_STEP(A, B, C, D, E, F, LAST)                                                         \
+    {                                                                                                \
+      const FT ut = march_ut<FT, VARIANT, SAME>(T, B, C, D, E, v0, v1, v2, v3, Ab);                   \
+      const bool left = ut > FT(0);                                                                  \
+      const FT q0 = left ? A : F, q1 = left ? B : E, q2 = left ? C : D, q3 = left ? D : C, q4 = left ? E : B; \
+      if (!(LAST)) {                                                                                 \
+        p += sb; pb += sb;                                                                           \
+        A = *p;                                                                                      \
+        if (!SAME) { v0 = pb[0]; v1 = pb[sa]; v2 = pb[2 * sa]; v3 = pb[3 * sa]; }                    \
+      }                                                                                              \
+      *out = ut * (VARIANT == 0 ? weno5_from_q<FT>(T, q0, q1, q2, q3, q4) : weno5_contracted<FT>(T, q0, q1, q2, q3, q4)); \
+      out += ostride;                                                                                \
+    }
+#pragma unroll 1
+    for (int c = count; c > 0; c -= 6) {
+      TF_PIPE_STEP(S0, S1, S2, S3, S4, S5, c == 1) if (c == 1) break;
+      TF_PIPE_STEP(S1, S2, S3, S4, S5, S0, c == 2) if (c == 2) break;
+      TF_PIPE_STEP(S2, S3, S4, S5, S0, S1, c == 3) if (c == 3) break;
+      TF_PIPE_STEP(S3, S4, S5, S0, S1, S2, c == 4) if (c == 4) break;
+      TF_PIPE_STEP(S4, S5, S0, S1, S2, S3, c == 5) if (c == 5) break;
+      TF_PIPE_STEP(S5, S0, S1, S2, S3, S4, c == 6)
+    }
+#undef TF_PIPE_STEP
+    return;
+  }
+#endif
 #define TF_MARCH_STEP(A, B, C, D, E, F)                                                \
   F = *p;                                                                              \
   *out = march_one<FT, VARIANT, SAME>(T, A, B, C, D, E, F, pb, sa, Ab);                \

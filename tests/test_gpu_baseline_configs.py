@@ -29,7 +29,7 @@ def test_config0_2d_turbulence_128_readme_example(oc):
     rounding difference is measured by the oracle's own 1-ulp sensitivity and the bound is 10× that where larger)."""
     N = 128
     rng = np.random.default_rng(1234)
-    ics = {n: rng.uniform(-1, 1, (N, N)) for n in "uv"}
+    ics = {n: rng.uniform(-1, 1, (N, N, 1)) for n in "uv"}      # fields of a Flat-z grid are N×N×1
     kw = dict(size=(N, N), x=(0, 2 * np.pi), y=(0, 2 * np.pi), topology=(P, P, F))
     m1 = oc.NonhydrostaticModel(oc.RectilinearGrid(np.float64, **kw), advection=oc.WENO(order=5))
     m2 = o.NonhydrostaticModel(o.RectilinearGrid(np.float64, **kw), advection=o.WENO(np.float64, 5))
