@@ -29,7 +29,7 @@ typedef struct nh_tridiag nh_tridiag;
 
 enum { NH_F32 = 0, NH_F64 = 1 };
 enum { NH_PERIODIC = 0, NH_BOUNDED = 1, NH_FLAT = 2 };
-enum { NH_CLOSURE_NONE = 0, NH_CLOSURE_SCALAR = 1, NH_CLOSURE_SMAGORINSKY = 2, NH_CLOSURE_SMAGORINSKY_LILLY = 3 };
+enum { NH_CLOSURE_NONE = 0, NH_CLOSURE_SCALAR = 1, NH_CLOSURE_SMAGORINSKY = 2, NH_CLOSURE_SMAGORINSKY_LILLY = 3, NH_CLOSURE_AMD = 4 };
 enum { NH_ADV_NONE = 0, NH_ADV_CENTERED = 1, NH_ADV_UPWIND = 2, NH_ADV_WENO = 3 };
 enum { NH_RK3 = 0, NH_AB2 = 1 };
 enum { NH_BUOYANCY_NONE = 0, NH_BUOYANCY_TRACER = 1, NH_BUOYANCY_SEAWATER_LINEAR = 2 };
@@ -42,7 +42,8 @@ enum {
   NH_FIELD_U = 0, NH_FIELD_V = 1, NH_FIELD_W = 2,
   NH_FIELD_TRACER0 = 3,            /* tracer n = NH_FIELD_TRACER0 + n, n < NH_MAX_TRACERS */
   NH_FIELD_PNHS = 16, NH_FIELD_PHY = 17,
-  NH_FIELD_NUE = 18,               /* eddy viscosity νₑ (model.diffusivity_fields.νₑ) of the Smagorinsky closures */
+  NH_FIELD_NUE = 18,               /* eddy viscosity νₑ (model.diffusivity_fields.νₑ) of the Smagorinsky / AMD closures */
+  NH_FIELD_KAPPAE0 = 19,           /* AMD: eddy diffusivity κₑ of tracer n = NH_FIELD_KAPPAE0 + n (… + NH_MAX_TRACERS - 1 = 26) */
   NH_FIELD_GN0 = 32,               /* Gⁿ of prognostic field f = NH_FIELD_GN0 + f */
   NH_FIELD_GM0 = 48                /* G⁻ of prognostic field f = NH_FIELD_GM0 + f */
 };
@@ -74,12 +75,14 @@ typedef struct {
   int32_t has_coriolis;            /* FPlane */
   double  coriolis_f;
   int32_t has_closure;             /* NH_CLOSURE_*: none, ScalarDiffusivity (explicit, isotropic), Smagorinsky(coefficient =
-                                      number) or SmagorinskyLilly — src/TurbulenceClosures/turbulence_closure_implementations/
-                                      Smagorinskys/smagorinsky.jl:88-137, lilly_coefficient.jl:108-139 */
+                                      number), SmagorinskyLilly — src/TurbulenceClosures/turbulence_closure_implementations/
+                                      Smagorinskys/smagorinsky.jl:88-137, lilly_coefficient.jl:108-139 — or
+                                      AnisotropicMinimumDissipation (Cb = nothing) — …/anisotropic_minimum_dissipation.jl:110-208 */
   double  nu;
   double  kappa[NH_MAX_TRACERS];
   double  smagorinsky_C, smagorinsky_Cb;   /* Cˢ (default 0.16) and the Lilly buoyancy multiplier Cb (default 1) */
   double  smagorinsky_Pr[NH_MAX_TRACERS];  /* turbulent Prandtl number of each tracer: κₑ = ℑ(νₑ) / Pr */
+  double  amd_Cnu, amd_Ckappa[NH_MAX_TRACERS];   /* Poincaré constants Cν and Cκ of each tracer (default 1/12) */
   int32_t hydrostatic_pressure_anomaly;   /* -1 default (on iff buoyancy), 0 off, 1 on */
   int32_t exact_arithmetic;        /* 1: kernels compiled without FMA contraction, reference expression order (parity
                                       mode); 0: fused fast kernels where available */

@@ -186,6 +186,19 @@ class Smagorinsky(SmagorinskyLilly):
         self.C, self.Cb, self.Pr = coefficient, 0.0, Pr
 
 
+class AnisotropicMinimumDissipation:
+    """AnisotropicMinimumDissipation(FT; C = 1/12, Cν = C, Cκ = C (a number or a dict by tracer name)); Cb = nothing —
+    anisotropic_minimum_dissipation.jl:110-121."""
+    kind = L.CLOSURE_AMD
+
+    def __init__(self, C=1 / 12, Cnu=None, Ckappa=None):
+        self.Cnu = C if Cnu is None else Cnu
+        self.Ckappa = C if Ckappa is None else Ckappa
+
+    def Ckappa_for(self, name):
+        return self.Ckappa[name] if isinstance(self.Ckappa, dict) else self.Ckappa
+
+
 class ScalarDiffusivity:
     kind = L.CLOSURE_SCALAR
 

@@ -15,8 +15,8 @@ HOST, DEVICE = 0, 1
 INTERIOR, PARENT = 0, 1
 SOLVER_FFT, SOLVER_FOURIER_TRIDIAGONAL = 0, 1
 FIELD_U, FIELD_V, FIELD_W, FIELD_TRACER0, FIELD_PNHS, FIELD_PHY, FIELD_GN0, FIELD_GM0 = 0, 1, 2, 3, 16, 17, 32, 48
-FIELD_NUE = 18
-CLOSURE_NONE, CLOSURE_SCALAR, CLOSURE_SMAGORINSKY, CLOSURE_SMAGORINSKY_LILLY = range(4)
+FIELD_NUE, FIELD_KAPPAE0 = 18, 19
+CLOSURE_NONE, CLOSURE_SCALAR, CLOSURE_SMAGORINSKY, CLOSURE_SMAGORINSKY_LILLY, CLOSURE_AMD = range(5)
 
 
 class GridDesc(C.Structure):
@@ -31,7 +31,8 @@ class ModelDesc(C.Structure):
                 ("thermal_expansion", C.c_double), ("haline_contraction", C.c_double), ("has_coriolis", C.c_int32),
                 ("coriolis_f", C.c_double), ("has_closure", C.c_int32), ("nu", C.c_double),
                 ("kappa", C.c_double * NH_MAX_TRACERS), ("smagorinsky_C", C.c_double), ("smagorinsky_Cb", C.c_double),
-                ("smagorinsky_Pr", C.c_double * NH_MAX_TRACERS), ("hydrostatic_pressure_anomaly", C.c_int32),
+                ("smagorinsky_Pr", C.c_double * NH_MAX_TRACERS), ("amd_Cnu", C.c_double),
+                ("amd_Ckappa", C.c_double * NH_MAX_TRACERS), ("hydrostatic_pressure_anomaly", C.c_int32),
                 ("exact_arithmetic", C.c_int32)]
 
 

@@ -78,7 +78,8 @@ struct TendParams {
   int has_coriolis; FT fcor;
   int has_closure; FT nu; FT kappa[NH_MAXTR];
   const FT* nue;              // eddy viscosity νₑ at ccc (Smagorinsky closures); nullptr ⇒ the constants above
-  FT Pr[NH_MAXTR];            // κₑ = ℑ(νₑ) / Pr
+  const FT* kape[NH_MAXTR];   // eddy diffusivity field of each tracer at ccc: νₑ itself (Smagorinsky) or κₑ[n] (AMD)
+  FT Pr[NH_MAXTR];            // κ on a face = ℑ(kape[n]) / Pr[n]  (Pr = 1 for AMD)
 };
 
 struct FieldExtent { int n[3]; };   // interior size of a field (N, or N+1 on a Bounded Face dim)

@@ -3,6 +3,7 @@
 // live in step_fast.cu.
 #pragma once
 #include "tendency_generic.cuh"
+#include "closure_amd.cuh"
 
 #define NH_MAXF (3 + NH_MAXTR)
 

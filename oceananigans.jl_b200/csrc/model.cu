@@ -62,8 +62,12 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   pNHS = alloc_field();
   bool want_phy = d.hydrostatic_pressure_anomaly < 0 ? d.buoyancy_kind != NH_BUOYANCY_NONE : d.hydrostatic_pressure_anomaly != 0;
   if (want_phy) pHY = alloc_field();
-  NH_REQUIRE(d.has_closure >= NH_CLOSURE_NONE && d.has_closure <= NH_CLOSURE_SMAGORINSKY_LILLY, "unknown closure kind");
-  if (d.has_closure >= NH_CLOSURE_SMAGORINSKY) {
+  NH_REQUIRE(d.has_closure >= NH_CLOSURE_NONE && d.has_closure <= NH_CLOSURE_AMD, "unknown closure kind");
+  if (d.has_closure == NH_CLOSURE_AMD) {
+    // build_diffusivity_fields (anisotropic_minimum_dissipation.jl:371-385): νₑ and one κₑ per tracer, default conditions
+    nue = alloc_field();
+    for (int n = 0; n < ntr; ++n) kape[n] = alloc_field();
+  } else if (d.has_closure >= NH_CLOSURE_SMAGORINSKY) {
     // build_diffusivity_fields (smagorinsky.jl:123-133); filter width Δᶠ = cbrt(Δx·Δy·Δz), correctly rounded on the host
     nue = alloc_field();
     std::vector<FT> t(gh.g.N[2]);
@@ -176,7 +180,11 @@ FT* Model<FT>::field_ptr(int field) {
   if (field >= 0 && field < nf) return F[field];
   if (field == NH_FIELD_PNHS) return pNHS;
   if (field == NH_FIELD_PHY) { NH_REQUIRE(pHY, "model has no hydrostatic pressure anomaly"); return pHY; }
-  if (field == NH_FIELD_NUE) { NH_REQUIRE(nue, "model has no eddy viscosity (closure is not a Smagorinsky)"); return nue; }
+  if (field == NH_FIELD_NUE) { NH_REQUIRE(nue, "model has no eddy viscosity (closure is not a Smagorinsky or AMD)"); return nue; }
+  if (field >= NH_FIELD_KAPPAE0 && field < NH_FIELD_KAPPAE0 + NH_MAXTR) {
+    NH_REQUIRE(field - NH_FIELD_KAPPAE0 < ntr && kape[field - NH_FIELD_KAPPAE0], "model has no such eddy diffusivity field");
+    return kape[field - NH_FIELD_KAPPAE0];
+  }
   if (field >= NH_FIELD_GN0 && field < NH_FIELD_GN0 + nf) return Gn[field - NH_FIELD_GN0];
   if (field >= NH_FIELD_GM0 && field < NH_FIELD_GM0 + nf) return Gm[field - NH_FIELD_GM0];
   throw NhError("unknown field id");
@@ -331,7 +339,8 @@ TendParams<FT> Model<FT>::tend_params() const {
   P.has_coriolis = desc.has_coriolis; P.fcor = (FT)desc.coriolis_f;
   P.has_closure = desc.has_closure; P.nu = (FT)desc.nu;
   P.nue = nue;
-  for (int t = 0; t < ntr; ++t) P.Pr[t] = (FT)desc.smagorinsky_Pr[t];
+  const bool amd = desc.has_closure == NH_CLOSURE_AMD;
+  for (int t = 0; t < ntr; ++t) { P.Pr[t] = amd ? FT(1) : (FT)desc.smagorinsky_Pr[t]; P.kape[t] = amd ? kape[t] : nue; }
   return P;
 }
 
@@ -339,6 +348,18 @@ TendParams<FT> Model<FT>::tend_params() const {
 template <typename FT>
 void Model<FT>::compute_diffusivities() {
   if (!nue) return;
+  if (desc.has_closure == NH_CLOSURE_AMD) {
+    // compute_diffusivities!(…, ::AnisotropicMinimumDissipation, …): νₑ, then κₑ of each tracer
+    TendParams<FT> P = tend_params();
+    dim3 blk(32, 4, 1);
+    amd_viscosity_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, nue, (FT)desc.amd_Cnu);
+    KLAUNCH(lc);
+    for (int n = 0; n < ntr; ++n) {
+      amd_diffusivity_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, F[3 + n], kape[n], (FT)desc.amd_Ckappa[n]);
+      KLAUNCH(lc);
+    }
+    return;
+  }
   SmagJob<FT> J;
   J.P = tend_params(); J.nue = nue; J.df2 = df2.p;
   J.lilly = desc.has_closure == NH_CLOSURE_SMAGORINSKY_LILLY;
@@ -388,7 +409,11 @@ void Model<FT>::update_state(int compute) {
   fill_halo_regions(mask, 0);
   compute_diffusivities();                       // compute_auxiliaries!: diffusivities, then hydrostatic pressure
   update_hydrostatic_pressure();
-  if (nue) fill_halo_regions(1u << NH_FIELD_NUE, 1);
+  if (nue) {
+    uint32_t dmask = 1u << NH_FIELD_NUE;
+    if (desc.has_closure == NH_CLOSURE_AMD) for (int n = 0; n < ntr; ++n) dmask |= 1u << (NH_FIELD_KAPPAE0 + n);
+    fill_halo_regions(dmask, 1);
+  }
   if (compute) compute_tendencies();
 }
 

@@ -331,7 +331,8 @@ struct Model : nh_model {
   FT* Gm[NH_MAXF];
   FT* pNHS = nullptr;
   FT* pHY = nullptr;
-  FT* nue = nullptr;       // νₑ of the Smagorinsky closures (diffusivity_fields.νₑ)
+  FT* nue = nullptr;       // νₑ of the Smagorinsky / AMD closures (diffusivity_fields.νₑ)
+  FT* kape[NH_MAXTR] = {}; // AMD: κₑ of each tracer (diffusivity_fields.κₑ)
   DevBuf<FT> df2;          // Δᶠ² = cbrt(ΔxΔyΔz)² per k
   void compute_diffusivities();
   SchemeDev adv[3];

@@ -33,12 +33,22 @@
 #ifndef TF_PREFETCH
 #define TF_PREFETCH 0    // L2 prefetch of the tiles the next phase reads: measured slower (1.27 vs 1.16 ms at 256³), kept off
 #endif
+#ifndef TF_XWINDOW
+#define TF_XWINDOW 0     // x-direction fluxes load the six-point stencil window unconditionally and select the upwind five in
+                         // registers (like the marched lines) instead of loading five values from a sign-dependent address:
+                         // one more load (three fewer when a == x), but no load that waits for the advecting velocity
+#endif
 #ifndef TF_PIPELINE
 #define TF_PIPELINE 0    // marching loops load the next face's stencil value and advecting velocities right after the current
                          // face's upwind selection (into the registers that selection just freed) instead of at the top of
                          // the next step: the loads fly during the WENO arithmetic
 #endif
+#ifndef TF_DIVUNROLL
+#define TF_DIVUNROLL 4   // unroll factor of the divergence / substep loop over the tile's planes (loads of U and G⁻ of the next
+                         // planes can then be issued ahead of the current plane's stores)
+#endif
 constexpr int tf_unroll = TF_UNROLL;
+constexpr int tf_divunroll = TF_DIVUNROLL;
 #define TF_SMEM_ELEMS (TF_TZ * TF_TY * (TF_TX + 1) + TF_TZ * (TF_TY + 1) * TF_TX + (TF_TZ + 1) * TF_TY * TF_TX)
 
 template <typename FT>
@@ -257,8 +267,17 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
         const int lj = row % TF_TY, lk = row / TF_TY;
         // partial tiles: clamp to the last valid point (the value is computed but never used)
         const int n = g.idx32(i0 + min(li, nx) - (a == 0 ? 1 : 0), j0 + min(lj, ny - 1), k0 + min(lk, nz - 1));
+#if TF_XWINDOW
+        {
+          const FT* w = ua + n + (a == 0 ? -2 : -3);
+          const FT S0 = w[0], S1 = w[1], S2 = w[2], S3 = w[3], S4 = w[4], S5 = w[5];
+          Fx[lk][lj][li] = a == 0 ? march_one<FT, VARIANT, true>(J.tab, S0, S1, S2, S3, S4, S5, nullptr, sa, Ax)
+                                  : march_one<FT, VARIANT, false>(J.tab, S0, S1, S2, S3, S4, S5, J.U[0] + n - 2 * sa, sa, Ax);
+        }
+#else
         Fx[lk][lj][li] = a == 0 ? fast_flux<FT, true, VARIANT>(J.tab, ua, J.U[0], n, sa, 1, Ax)
                                 : fast_flux<FT, false, VARIANT>(J.tab, ua, J.U[0], n, sa, 1, Ax);
+#endif
         li += DL; row += DR;
         if (li > TF_TX) { li -= TF_TX + 1; ++row; }
       }
@@ -289,6 +308,7 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
         FT* __restrict__ gn = J.Gn[a];
         FT* __restrict__ un = J.Unew[a];
         FT* vp = (a == 1 && j0 + lj == 1) ? J.v_prev : nullptr;
+#pragma unroll tf_divunroll
         for (int lk = 0; lk < nz; ++lk, n += st[2]) {
           FT total = (Fx[lk][lj][li + 1] - Fx[lk][lj][li]) + (Fy[lk][lj + 1][li] - Fy[lk][lj][li]);
           total = total + (Fz[lk + 1][lj][li] - Fz[lk][lj][li]);

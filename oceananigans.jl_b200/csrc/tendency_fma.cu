@@ -3,6 +3,15 @@
 // kernel, so every a·b + c of the reference's expressions becomes one FMA (one rounding instead of two).  Results are not
 // bit-identical to the reference's CPU code any more but stay within the north_star tolerance (tests/test_gpu_parity.py
 // test_contracted_arithmetic_*), with roughly a third fewer FP64 instructions per cell.
+// Measured at 256³ Float64 on B200 (tools/ab_pipeline.sh): 1.148 ms per launch as the exact kernel's source compiles,
+// 1.120 with the unconditional six-point x window, 1.106 with the software-pipelined marching loops on top.  The exact
+// build gains nothing from either (FP64-pipe bound with its checked divisions), so the switches live here.
+#ifndef TF_XWINDOW
+#define TF_XWINDOW 1
+#endif
+#ifndef TF_PIPELINE
+#define TF_PIPELINE 1
+#endif
 #include "fft_generic.cuh"      // cx_of (two-element vector types)
 #include "tendency_fast.cuh"
 

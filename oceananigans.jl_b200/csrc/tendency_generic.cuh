@@ -230,11 +230,11 @@ __device__ __forceinline__ FT div_viscous_flux(const TendParams<FT>& P, int i, i
   return FT(1) / volume_at(P.g, a == 2 ? 0 : 1, k) * total;
 }
 
-// diffusive_flux = -κ·∂c with κ the constant, or ℑ_b(νₑ) / Pr (Smagorinskys/smagorinsky.jl:135-137)
+// diffusive_flux = -κ·∂c with κ the constant, ℑ_b(νₑ) / Pr (Smagorinskys/smagorinsky.jl:135-137) or ℑ_b(κₑ[n]) (AMD)
 template <typename FT, int b>
 __device__ __forceinline__ FT diffusive_Aflux(const TendParams<FT>& P, const FT* c, int n, int i, int j, int k) {
   constexpr int zc = b == 2 ? 0 : 1;
-  const FT kappa = P.nue ? interp_to_face<FT, b>(P.g, P.nue, i, j, k) / P.Pr[n] : P.kappa[n];
+  const FT kappa = P.nue ? interp_to_face<FT, b>(P.g, P.kape[n], i, j, k) / P.Pr[n] : P.kappa[n];
   return area_at(P.g, b, zc, k) * (-kappa * deriv<FT, b>(P.g, c, 0, zc, i, j, k));
 }
 

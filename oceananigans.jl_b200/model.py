@@ -168,6 +168,10 @@ class NonhydrostaticModel:
             d.has_closure, d.nu = L.CLOSURE_SCALAR, closure.nu
             for n, name in enumerate(tracers):
                 d.kappa[n] = closure.kappa_for(name)
+        elif closure is not None and closure.kind == L.CLOSURE_AMD:
+            d.has_closure, d.amd_Cnu = L.CLOSURE_AMD, closure.Cnu
+            for n, name in enumerate(tracers):
+                d.amd_Ckappa[n] = closure.Ckappa_for(name)
         elif closure is not None:
             d.has_closure, d.smagorinsky_C, d.smagorinsky_Cb = closure.kind, closure.C, closure.Cb
             for n, name in enumerate(tracers):
@@ -199,6 +203,9 @@ class NonhydrostaticModel:
         self.diffusivity_fields = _Namespace()
         if closure is not None and closure.kind != L.CLOSURE_SCALAR:
             self.diffusivity_fields["nu_e"] = Field(self, L.FIELD_NUE, "nu_e", ("c", "c", "c"))
+            if closure.kind == L.CLOSURE_AMD:
+                self.diffusivity_fields["kappa_e"] = _Namespace(
+                    (n, Field(self, L.FIELD_KAPPAE0 + i, "kappa_e_" + n, ("c", "c", "c"))) for i, n in enumerate(tracers))
         self.timestepper = _Namespace(
             Gn=_Namespace((n, Field(self, L.FIELD_GN0 + i, "Gn_" + n, locs[i])) for i, n in enumerate(names)),
             Gm=_Namespace((n, Field(self, L.FIELD_GM0 + i, "Gm_" + n, locs[i])) for i, n in enumerate(names)))

@@ -29,4 +29,5 @@ from .advection import WENO, Centered, UpwindBiased  # noqa: F401
 from .solvers import (FFTBasedPoissonSolver, FourierTridiagonalPoissonSolver,  # noqa: F401
                       BatchedTridiagonalSolver)
 from .model import (NonhydrostaticModel, time_step, set_model, FPlane,  # noqa: F401
-                    BuoyancyTracer, SeawaterBuoyancy, ScalarDiffusivity, SmagorinskyLilly, Smagorinsky)
+                    BuoyancyTracer, SeawaterBuoyancy, ScalarDiffusivity, SmagorinskyLilly, Smagorinsky,
+                    AnisotropicMinimumDissipation)

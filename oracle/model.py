@@ -78,6 +78,22 @@ class Smagorinsky(SmagorinskyLilly):
         self.C, self.Cb, self.Pr = coefficient, 0.0, Pr
 
 
+class AnisotropicMinimumDissipation:
+    """AnisotropicMinimumDissipation(FT; C = 1/12, Cν = C, Cκ = C (number or by tracer), Cb = nothing) —
+    anisotropic_minimum_dissipation.jl:110-121."""
+    kind = "amd"
+
+    def __init__(self, C=1 / 12, Cnu=None, Ckappa=None):
+        self.Cnu = C if Cnu is None else Cnu
+        self.Ckappa = C if Ckappa is None else Ckappa
+
+    def Ckappa_for(self, name):
+        return self.Ckappa[name] if isinstance(self.Ckappa, dict) else self.Ckappa
+
+    def Pr_for(self, name):       # κₑ is its own field: the face value is ℑ(κₑ), i.e. "Pr = 1"
+        return 1.0
+
+
 class Clock:
     def __init__(self):
         self.time = 0.0
@@ -124,6 +140,9 @@ class NonhydrostaticModel:
         self.pNHS = Field(grid, CCC, prognostic=False, name="pNHS")
         # build_diffusivity_fields (smagorinsky.jl:123-133): νₑ at ccc with default boundary conditions
         self.nu_e = Field(grid, CCC, prognostic=False, name="nu_e") if (closure is not None and closure.kind != "scalar") else None
+        # AMD: one eddy diffusivity field per tracer (anisotropic_minimum_dissipation.jl:371-385)
+        self.kappa_e = ({n: Field(grid, CCC, prognostic=False, name="kappa_e_" + n) for n in tracers}
+                        if (closure is not None and closure.kind == "amd") else None)
         if hydrostatic_pressure_anomaly == "default":
             self.pHY = Field(grid, CCC, prognostic=False, name="pHY") if buoyancy is not None else None
         else:
@@ -163,12 +182,27 @@ def update_state(model, compute_tendencies=True):
     """update_state!: halo fill (normal velocities not re-imposed) → hydrostatic pressure → tendencies."""
     fill_halo_regions(model.prognostic_fields(), fill_boundary_normal_velocities=False)
     if model.nu_e is not None:                     # compute_auxiliaries!: diffusivities, then hydrostatic pressure
-        compute_smagorinsky_viscosity(model)
+        if model.closure.kind == "amd":
+            compute_amd_diffusivities(model)
+        else:
+            compute_smagorinsky_viscosity(model)
     update_hydrostatic_pressure(model.grid, model.pHY, model.buoyancy, model.tracers)
     if model.nu_e is not None:
-        fill_halo_regions(model.nu_e)
+        fill_halo_regions([model.nu_e] + (list(model.kappa_e.values()) if model.kappa_e else []))
     if compute_tendencies:
         compute_tendencies_(model)
+
+
+def compute_amd_diffusivities(model):
+    """compute_diffusivities!(…, ::AnisotropicMinimumDissipation, …) over :xyz (anisotropic_minimum_dissipation.jl:191-208)."""
+    from .amd import amd_viscosity, amd_diffusivity
+    grid = model.grid
+    R = interior_region(grid)
+    shape = model.nu_e.at(*R).shape
+    model.nu_e.at(*R)[...] = np.broadcast_to(amd_viscosity(grid, model.velocities, model.closure.Cnu, R), shape)
+    for n, c in model.tracers.items():
+        model.kappa_e[n].at(*R)[...] = np.broadcast_to(
+            amd_diffusivity(grid, model.velocities, c, model.closure.Ckappa_for(n), R), shape)
 
 
 def compute_tendencies_(model):

@@ -378,7 +378,8 @@ def tracer_tendency(model, name):
     R = tendency_region(grid, CCC)
     G = -div_Uc(grid, model.advection, model.velocities, c, R)
     if model.closure is not None and model.closure.kind != "scalar":
-        G = G - div_diffusive_flux(grid, model.nu_e, c, R, Pr=model.closure.Pr_for(name))
+        kfield = model.kappa_e[name] if model.closure.kind == "amd" else model.nu_e
+        G = G - div_diffusive_flux(grid, kfield, c, R, Pr=model.closure.Pr_for(name))
     elif model.closure is not None:
         G = G - div_diffusive_flux(grid, model.closure.kappa_for(name), c, R)
     else:

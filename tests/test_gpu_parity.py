@@ -62,6 +62,8 @@ def make_pair(oc, FT, size, topo, z=None, advection=("WENO", 5), timestepper="Ru
     c2 = o.FPlane(coriolis) if coriolis is not None else None
     if closure and closure[0] == "lilly":          # ("lilly", C, Cb, Pr)
         k1, k2 = oc.SmagorinskyLilly(*closure[1:]), o.SmagorinskyLilly(*closure[1:])
+    elif closure and closure[0] == "amd":          # ("amd", C, Cnu, Ckappa)
+        k1, k2 = oc.AnisotropicMinimumDissipation(*closure[1:]), o.AnisotropicMinimumDissipation(*closure[1:])
     elif closure and closure[0] == "smagorinsky":  # ("smagorinsky", coefficient, Pr)
         k1, k2 = oc.Smagorinsky(*closure[1:]), o.Smagorinsky(*closure[1:])
     else:
@@ -125,6 +127,13 @@ CONFIGS = [
     ((9, 8, 10), (B, B, B), None, ("Centered", 2), dict(tracers=("c",), closure=("smagorinsky", 0.16, 0.7))),
     ((12, 10, 9), (P, P, P), None, ("WENO", 5), dict(closure=("lilly", 0.16, 1.0, 1.0))),
     ((16, 12), (P, F, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=("lilly", 0.16, 1.0, 1.0))),
+    # AnisotropicMinimumDissipation: νₑ and one κₑ per tracer
+    ((12, 10, 9), (P, P, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=("amd", 1 / 12, None, None))),
+    ((10, 9, 8), (P, P, B), "stretched", ("WENO", 5), dict(buoyancy="seawater", tracers=("T", "S"), coriolis=1e-2,
+                                                           closure=("amd", 1 / 12, 0.1, {"T": 1 / 12, "S": 1 / 6}), bcs=BCS_LES)),
+    ((9, 8, 10), (B, B, B), None, ("Centered", 2), dict(tracers=("c",), closure=("amd", 1 / 12, None, None))),
+    ((12, 10, 9), (P, P, P), None, ("WENO", 5), dict(closure=("amd", 1 / 12, None, None))),
+    ((16, 12), (P, F, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=("amd", 1 / 12, None, None))),
 ]
 
 
@@ -150,6 +159,9 @@ def test_tendencies_and_halos_bit_exact(oc, FT, cfg):
     o_update_state(m2, compute_tendencies=True)
     if m2.nu_e is not None:
         np.testing.assert_array_equal(m1.diffusivity_fields.nu_e.parent(), m2.nu_e.data, err_msg="nu_e")
+    if m2.kappa_e is not None:
+        for n, f2 in m2.kappa_e.items():
+            np.testing.assert_array_equal(m1.diffusivity_fields.kappa_e[n].parent(), f2.data, err_msg=f"kappa_e[{n}]")
     for n, f1, f2 in names_fields(m1, m2):
         np.testing.assert_array_equal(f1.parent(), f2.data, err_msg=f"parent({n}) after halo fill")
         G1 = m1.timestepper.Gn[n].interior()
@@ -310,6 +322,19 @@ def test_100_steps_smagorinsky_lilly_les(oc, FT, tol, timestepper):
     m1, m2 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
     _, m3 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
     ics = smooth_ics(m2, np.random.default_rng(5), amp=0.5)
+    err, floor = _run_steps(oc, m1, m2, ics, 1e-2, 100, m3)
+    check_parity(err, tol, floor)
+
+
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+def test_100_steps_amd_les(oc, FT, tol):
+    """AnisotropicMinimumDissipation with the ocean-LES wall set (the closure of the reference's
+    ocean_large_eddy_simulation_regression_test.jl:14-16 AMD variant) on 16³ — 100 RK3 steps against the oracle."""
+    kw = dict(extent=(1, 1, 1), buoyancy="seawater", tracers=("T", "S"), coriolis=1e-4, closure=("amd", 1 / 12, None, None),
+              bcs=BCS_LES)
+    m1, m2 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
+    _, m3 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
+    ics = smooth_ics(m2, np.random.default_rng(6), amp=0.5)
     err, floor = _run_steps(oc, m1, m2, ics, 1e-2, 100, m3)
     check_parity(err, tol, floor)
 

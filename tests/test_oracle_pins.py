@@ -372,3 +372,37 @@ def test_smagorinsky_time_stepping_stays_incompressible_and_dissipates():
         assert np.abs(divergence_ccc(g, u, v, w, R)).max() < 1e-10
         ke[name] = sum((f.interior ** 2).sum() for f in m.velocities)
     assert ke["smag"] < ke["none"] and ke["lilly"] < ke["none"]
+
+
+def test_amd_analytic_eddy_viscosity_and_diffusivity():
+    """AnisotropicMinimumDissipation (anisotropic_minimum_dissipation.jl:143-189) on linear flows, where every discrete
+    gradient is exact: a pure shear u = S·z has uᵢₐuⱼₐΣᵢⱼ = 0, so νₑ = 0 (the closure switches off in laminar shear);
+    the strain u = a·x, v = b·y, w = -(a+b)·z has r = a³ + b³ - (a+b)³ and q = a² + b² + (a+b)², so
+    νₑ = max(0, -Cν·δ²·r/q) with δ² = 3/(1/Δᶠx² + 1/Δᶠy² + 1/Δᶠz²), Δᶠ = 2Δ; a tracer c = γ·z in it has
+    κₑ = max(0, Cκ·δ²·(a+b))."""
+    from oracle.model import update_state
+    FT = np.float64
+    N = (8, 8, 8)
+    g = o.RectilinearGrid(FT, size=N, x=(0, 1), y=(0, 2), z=(0, 0.5), topology=(B, B, B))
+    d = [1 / 8, 2 / 8, 0.5 / 8]
+    d2 = 3 / sum(1 / (2 * x) ** 2 for x in d)
+    C = 1 / 12
+    xf, yf, zf = (np.arange(9) * d[0]), (np.arange(9) * d[1]), (np.arange(9) * d[2])
+    zc = (np.arange(8) + 0.5) * d[2]
+    inner = (slice(2, -2),) * 3
+    # pure shear
+    m = o.NonhydrostaticModel(g, closure=o.AnisotropicMinimumDissipation())
+    m.velocities[0].set(np.broadcast_to(3.0 * zc, (9, 8, 8)))
+    update_state(m, compute_tendencies=False)
+    assert np.abs(m.nu_e.interior[inner]).max() == 0
+    # three-dimensional strain, both signs of a·b·(a+b)
+    for a, b in ((1.0, 2.0), (-1.0, -0.5)):
+        m = o.NonhydrostaticModel(g, tracers=("c",), closure=o.AnisotropicMinimumDissipation())
+        m.velocities[0].set(np.broadcast_to((a * xf)[:, None, None], (9, 8, 8)))
+        m.velocities[1].set(np.broadcast_to((b * yf)[None, :, None], (8, 9, 8)))
+        m.velocities[2].set(np.broadcast_to((-(a + b) * zf)[None, None, :], (8, 8, 9)))
+        m.tracers["c"].set(np.broadcast_to(0.7 * zc, N))
+        update_state(m, compute_tendencies=False)
+        r, q = a ** 3 + b ** 3 - (a + b) ** 3, a ** 2 + b ** 2 + (a + b) ** 2
+        np.testing.assert_allclose(m.nu_e.interior[inner], max(0.0, -C * d2 * r / q), rtol=1e-12, atol=1e-18)
+        np.testing.assert_allclose(m.kappa_e["c"].interior[inner], max(0.0, C * d2 * (a + b)), rtol=1e-12, atol=1e-18)

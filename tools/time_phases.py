@@ -1,6 +1,8 @@
 """Quick phase timing of one model configuration (development aid):
-   python tools/time_phases.py [N] [steps] [f32] [ppb | les]
-   ppb: (Periodic, Periodic, Bounded) WENO5, no tracers;  les: ppb + buoyancy tracer b + ScalarDiffusivity + FPlane"""
+   python tools/time_phases.py [N] [steps] [f32] [ppb | les | smag | amd]
+   ppb: (Periodic, Periodic, Bounded) WENO5, no tracers;  les: ppb + buoyancy tracer b + ScalarDiffusivity + FPlane;
+   smag / amd: les with SmagorinskyLilly / AnisotropicMinimumDissipation and the ocean-LES wall conditions (wind-stress flux
+   on u, no-slip bottom, surface buoyancy flux and bottom buoyancy gradient) — the widened rows of DESIGN.md §7b"""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -10,12 +12,19 @@ from bench import smooth_ics
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 FT = np.float32 if "f32" in sys.argv else np.float64
-bounded = "ppb" in sys.argv or "les" in sys.argv
+eddy = "smag" in sys.argv or "amd" in sys.argv
+bounded = "ppb" in sys.argv or "les" in sys.argv or eddy
 topo = (oc.Periodic, oc.Periodic, oc.Bounded if bounded else oc.Periodic)
 g = oc.RectilinearGrid(FT, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=topo)
 kw = {}
 if "les" in sys.argv:
     kw = dict(buoyancy=oc.BuoyancyTracer(), tracers=("b",), closure=oc.ScalarDiffusivity(1e-4, 1e-4), coriolis=oc.FPlane(1e-4))
+if eddy:
+    bcs = {"u": oc.FieldBoundaryConditions(top=oc.FluxBoundaryCondition(-1e-4), bottom=oc.ValueBoundaryCondition(0.0)),
+           "v": oc.FieldBoundaryConditions(bottom=oc.ValueBoundaryCondition(0.0)),
+           "b": oc.FieldBoundaryConditions(top=oc.FluxBoundaryCondition(1e-8), bottom=oc.GradientBoundaryCondition(1e-5))}
+    kw = dict(buoyancy=oc.BuoyancyTracer(), tracers=("b",), coriolis=oc.FPlane(1e-4), boundary_conditions=bcs,
+              closure=oc.SmagorinskyLilly() if "smag" in sys.argv else oc.AnisotropicMinimumDissipation())
 m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), exact_arithmetic="fma" not in sys.argv, **kw)
 ics = smooth_ics(N, 1234)
 if bounded:
