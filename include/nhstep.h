@@ -188,6 +188,10 @@ int32_t nh_dist_pressure_correct(nh_model* model, double stage_dt);
  * every rank.  blob = NULL returns the required size in *nbytes. */
 int32_t nh_dist_ipc_export(nh_model* model, unsigned char* blob, int64_t capacity, int64_t* nbytes);
 int32_t nh_dist_ipc_import(nh_model* model, const unsigned char* all_blobs, int64_t nbytes);
+/* Stream-ordered barrier of the peer-to-peer group (replaces the MPI/NCCL synchronisation between the pieces of a stage,
+ * cf. sync_device! + MPI.Waitall of halo_communication.jl:91-112): one small kernel publishes an epoch into every peer's flag
+ * array over NVLink (release, system scope) and waits for all peers' epochs (acquire).  No reference counterpart. */
+int32_t nh_dist_barrier(nh_model* model);
 
 /* ---- standalone solvers ---------------------------------------------------------------------------------- */
 /* FFTBasedPoissonSolver(grid) — src/Solvers/fft_based_poisson_solver.jl:52-74;

@@ -53,6 +53,7 @@ SYMBOLS = [
     "nh_poisson_time_solves", "nh_tridiag_create", "nh_tridiag_solve", "nh_tridiag_destroy",
     "nh_dist_configure", "nh_dist_buffer", "nh_dist_halo", "nh_dist_tendency_substep", "nh_dist_poisson",
     "nh_dist_pressure_correct", "nh_dist_ipc_export", "nh_dist_ipc_import", "nh_model_set_boundary_condition",
+    "nh_dist_barrier",
 ]
 BC_DEFAULT, BC_FLUX, BC_VALUE, BC_GRADIENT = range(4)
 DIST_SEND_LO, DIST_SEND_HI, DIST_RECV_LO, DIST_RECV_HI, DIST_SPECTRAL_A, DIST_SPECTRAL_B = range(6)
@@ -112,6 +113,7 @@ def lib():
             "nh_dist_pressure_correct": [p, C.c_double],
             "nh_dist_ipc_export": [p, p, C.c_int64, C.POINTER(C.c_int64)],
             "nh_dist_ipc_import": [p, p, C.c_int64],
+            "nh_dist_barrier": [p],
             "nh_poisson_create": [p, C.c_int32, C.POINTER(p)],
             "nh_poisson_destroy": [p],
             "nh_poisson_solve": [p, p, p, C.c_double, C.c_int32],

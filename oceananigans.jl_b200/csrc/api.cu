@@ -192,6 +192,7 @@ int32_t nh_dist_tendency_substep(nh_model* m, double dt, int32_t stage, int32_t 
 int32_t nh_dist_poisson(nh_model* m, int32_t phase, double stage_dt) { MODEL_CALL(m, m->dist_poisson(phase, stage_dt)) }
 int32_t nh_dist_pressure_correct(nh_model* m, double stage_dt) { MODEL_CALL(m, m->dist_pressure_correct(stage_dt)) }
 int32_t nh_dist_ipc_export(nh_model* m, unsigned char* blob, int64_t capacity, int64_t* nbytes) { MODEL_CALL(m, int64_t n = m->dist_ipc_export(blob, capacity); if (nbytes) *nbytes = n) }
+int32_t nh_dist_barrier(nh_model* m) { MODEL_CALL(m, m->dist_barrier()) }
 int32_t nh_dist_ipc_import(nh_model* m, const unsigned char* blobs, int64_t nbytes) { MODEL_CALL(m, NH_REQUIRE(blobs, "null argument"); m->dist_ipc_import(blobs, nbytes)) }
 int32_t nh_launch_count(const nh_model* m, int64_t* count) { NH_TRY NH_REQUIRE(m && count, "null argument"); *count = m->lc.n; NH_CATCH }
 

@@ -109,8 +109,8 @@ void Model<FT>::dist_pressure_correct(double stage_dt) {
 }
 
 // ---- peer-to-peer mode: CUDA IPC handles of the buffers other ranks write into -------------------------------------
-// blob = 9 handles: spectral A, spectral B, u, v, w (current state), u, v, w (ping-pong target), pNHS
-static const int kIpcHandles = 9;
+// blob = 10 handles: spectral A, spectral B, u, v, w (current state), u, v, w (ping-pong target), pNHS, barrier flags
+static const int kIpcHandles = 10;
 
 template <typename FT>
 int64_t Model<FT>::dist_ipc_export(unsigned char* blob, int64_t capacity) {
@@ -118,7 +118,8 @@ int64_t Model<FT>::dist_ipc_export(unsigned char* blob, int64_t capacity) {
   const int64_t need = (int64_t)kIpcHandles * sizeof(cudaIpcMemHandle_t);
   if (!blob) return need;
   NH_REQUIRE(capacity >= need, "nh_dist_ipc_export: buffer too small");
-  void* ptrs[kIpcHandles] = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS};
+  if (!dist.flags.p) dist.flags.alloc(1 << 19);       // zero-filled
+  void* ptrs[kIpcHandles] = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS, dist.flags.p};
   for (int q = 0; q < kIpcHandles; ++q) {
     cudaIpcMemHandle_t h;
     CUDA_CHECK(cudaIpcGetMemHandle(&h, ptrs[q]));
@@ -137,7 +138,8 @@ void Model<FT>::dist_ipc_import(const unsigned char* blobs, int64_t nbytes) {
   NH_REQUIRE(R <= PF_MAXR, "peer-to-peer mode supports at most 16 ranks");
   const int64_t per = (int64_t)kIpcHandles * sizeof(cudaIpcMemHandle_t);
   NH_REQUIRE(nbytes == per * R, "nh_dist_ipc_import: expected one export blob per rank");
-  void* own[kIpcHandles] = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS};
+  NH_REQUIRE(dist.flags.p, "nh_dist_ipc_export must be called before nh_dist_ipc_import");
+  void* own[kIpcHandles] = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS, dist.flags.p};
   std::vector<std::vector<void*>> ptr(R, std::vector<void*>(kIpcHandles, nullptr));
   auto open = [&](int r, int q) -> void* {
     if (r == rank) return own[q];
@@ -157,7 +159,22 @@ void Model<FT>::dist_ipc_import(const unsigned char* blobs, int64_t nbytes) {
     dist.nextF[a] = (FT*)open(next, 2 + a); dist.nextF2[a] = (FT*)open(next, 5 + a);
   }
   dist.next_p = (FT*)open(next, 8);
+  for (int r = 0; r < PF_MAXR; ++r) dist.peer_flags[r] = r < R ? (unsigned int*)open(r, 9) : nullptr;
   dist.p2p = true;
+}
+
+// Stream-ordered barrier over all ranks of the peer-to-peer group: everything the ranks enqueued before it (their stores
+// into peer buffers included) is complete and visible before anything enqueued after it starts.  One small kernel.
+template <typename FT>
+void Model<FT>::dist_barrier() {
+  NH_REQUIRE(dist.on && dist.p2p, "nh_dist_barrier needs the peer-to-peer mode (nh_dist_ipc_import)");
+  if (dist.R == 1) return;
+  PeerBarrierJob J;
+  for (int r = 0; r < PF_MAXR; ++r) J.peer_flags[r] = dist.peer_flags[r];
+  J.rank = dist.rank; J.R = dist.R; J.epoch = ++dist.epoch;
+  peer_barrier_kernel<<<1, 32, 0, stream>>>(J);
+  lc.n++;
+  CUDA_CHECK(cudaGetLastError());
 }
 
 #define NH_DIST_INSTANTIATE(FT)                                                          \
@@ -168,6 +185,7 @@ void Model<FT>::dist_ipc_import(const unsigned char* blobs, int64_t nbytes) {
   template void Model<FT>::dist_poisson(int, double);                                    \
   template void Model<FT>::dist_pressure_correct(double);                                \
   template int64_t Model<FT>::dist_ipc_export(unsigned char*, int64_t);                  \
-  template void Model<FT>::dist_ipc_import(const unsigned char*, int64_t);
+  template void Model<FT>::dist_ipc_import(const unsigned char*, int64_t);               \
+  template void Model<FT>::dist_barrier();
 NH_DIST_INSTANTIATE(float)
 NH_DIST_INSTANTIATE(double)

@@ -141,3 +141,35 @@ __global__ void __launch_bounds__(256) y_halo_pack_kernel(const __grid_constant_
     J.f[f][g.idx(i, g.N[1] + 1 + row, k)] = J.hi[e];
   }
 }
+
+
+// ---- peer-to-peer barrier: one-sided flag writes over NVLink instead of a collective --------------------------------
+// Thread r < R publishes this rank's epoch into slot `rank` of rank r's flag array (release, system scope: every store of
+// the kernels that ran before this one on the stream — including their stores into peer memory — is ordered before it),
+// then waits until slot r of its own array has reached the epoch (acquire).  All ranks issue the same sequence of
+// barriers, so epochs only grow.  A wait that lasts longer than 20 s traps (a peer died) instead of hanging the GPU.
+struct PeerBarrierJob {
+  unsigned int* peer_flags[PF_MAXR];     // flag arrays of all ranks (own array at index rank)
+  int rank, R;
+  unsigned int epoch;
+};
+
+static __global__ void peer_barrier_kernel(const __grid_constant__ PeerBarrierJob J) {
+  const int r = threadIdx.x;
+  if (r >= J.R) return;
+  __threadfence_system();
+  unsigned int* dst = J.peer_flags[r] + J.rank;
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(dst), "r"(J.epoch) : "memory");
+  const unsigned int* src = J.peer_flags[J.rank] + r;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(src) : "memory");
+    if ((int)(v - J.epoch) >= 0) break;
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 20000000000ull) __trap();
+  }
+  __threadfence_system();
+}

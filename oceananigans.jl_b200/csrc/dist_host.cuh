@@ -30,6 +30,10 @@ struct DistState {
   CT* peerA[PF_MAXR];
   CT* peerB[PF_MAXR];
   FT *prevF[3], *prevF2[3], *nextF[3], *nextF2[3], *next_p = nullptr;
+  // flag barrier (peer_barrier_kernel): a 2 MB allocation of its own so that its IPC handle covers nothing else
+  DevBuf<unsigned int> flags;
+  unsigned int* peer_flags[PF_MAXR];
+  unsigned int epoch = 0;
   std::vector<void*> opened;
   ~DistState() { for (void* q : opened) cudaIpcCloseMemHandle(q); }
 

@@ -95,6 +95,7 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
     fast = fast && gh.g.topo[e] == NH_PERIODIC && adv[e].kind == NH_ADV_WENO && adv[e].B == 3 && gh.g.N[e] >= 2 * gh.g.H[e] && gh.g.H[e] >= 3;
   fast = fast && gh.volume() < (1ll << 31);        // the fused kernel uses 32-bit element offsets
   if (getenv("NHSTEP_NO_FAST")) fast = false;
+  tiled = getenv("NHSTEP_NO_TILED") == nullptr;
   if (!getenv("NHSTEP_NO_FAST_POISSON")) {
     // fused FFT / DCT / Thomas passes for (Periodic, Periodic, Periodic | Bounded) power-of-two grids, any model physics
     if (!gh.z_stretched && PoissonFast<FT>::supported(gh, true)) pfast.create(gh);
@@ -382,9 +383,16 @@ template <typename FT>
 void Model<FT>::compute_tendencies() {
   gn_stale = false;
   TendParams<FT> P = tend_params();
+  // tiled kernel (each advective face flux once, staged in shared memory); NHSTEP_NO_TILED selects the per-cell kernel that
+  // evaluates every face from both neighbours like the reference (bit-identical results, kept as the cross-check)
   dim3 blk(32, 4, 1);
   for (int what = 0; what < nf; ++what) {
-    tendency_generic_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, what);
+    if (tiled) {
+      dim3 tb(TG_TX, TG_TY, 1), tg(ceil_div(gh.g.N[0], TG_TX), ceil_div(gh.g.N[1], TG_TY), ceil_div(gh.g.N[2], TG_TZ));
+      tendency_tiled_kernel<FT><<<tg, tb, 0, stream>>>(P, what);
+    } else {
+      tendency_generic_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, what);
+    }
     KLAUNCH(lc);
   }
   // compute_boundary_tendency_contributions! (compute_nonhydrostatic_tendencies.jl:202-207): x, then y, then z walls

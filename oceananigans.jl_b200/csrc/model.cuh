@@ -297,6 +297,7 @@ struct nh_model {
   virtual void dist_pressure_correct(double stage_dt) = 0;
   virtual int64_t dist_ipc_export(unsigned char* blob, int64_t capacity) = 0;
   virtual void dist_ipc_import(const unsigned char* blobs, int64_t nbytes) = 0;
+  virtual void dist_barrier() = 0;
   // phase timing (nh_time_step_profiled): CUDA events on the model's stream between the phases of one step
   bool profiling = false;
   std::vector<std::pair<int, cudaEvent_t>> marks;
@@ -345,6 +346,7 @@ struct Model : nh_model {
   FT rk_g1, rk_g2, rk_g3, rk_z2, rk_z3, chi;
   // fused fast path (triply periodic, regular, WENO5, no tracers): ping-pong state, lazily refreshed Gⁿ and p halos
   bool fast = false, gn_stale = false, p_halo_stale = false;
+  bool tiled = true;       // complete path: tiled tendency kernel (each face flux once) instead of the per-cell one
   FT* F2[3] = {nullptr, nullptr, nullptr};
   void fast_stage(int mode, FT dt, FT c1, FT c2, double stage_dt);
   void fast_pressure(double stage_dt);
@@ -390,6 +392,7 @@ struct Model : nh_model {
   void dist_pressure_correct(double stage_dt) override;
   int64_t dist_ipc_export(unsigned char* blob, int64_t capacity) override;
   void dist_ipc_import(const unsigned char* blobs, int64_t nbytes) override;
+  void dist_barrier() override;
 };
 
 struct nh_poisson {

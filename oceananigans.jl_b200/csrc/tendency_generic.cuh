@@ -315,10 +315,11 @@ __global__ void __launch_bounds__(128) smagorinsky_kernel(const __grid_constant_
 }
 
 // ---- the tendencies ---------------------------------------------------------------------------------------
+// `div` = div_𝐯u_a at the cell (evaluated by the caller: per cell, or from face fluxes staged in shared memory)
 template <typename FT, int a>
-__device__ __forceinline__ FT velocity_tendency(const TendParams<FT>& P, int i, int j, int k) {
+__device__ __forceinline__ FT velocity_tendency(const TendParams<FT>& P, int i, int j, int k, FT div) {
   const GridDev<FT>& g = P.g;
-  FT G = -div_Uu<FT, a>(P, i, j, k);
+  FT G = -div;
   if (a == 2 && P.w_buoyancy) {
     FT bz = g.topo[2] == NH_FLAT ? buoyancy_at(P, i, j, k)
                                  : FT(0.5) * (buoyancy_at(P, i, j, k - 1) + buoyancy_at(P, i, j, k));
@@ -337,8 +338,8 @@ __device__ __forceinline__ FT velocity_tendency(const TendParams<FT>& P, int i, 
 }
 
 template <typename FT>
-__device__ __forceinline__ FT tracer_tendency(const TendParams<FT>& P, int n, int i, int j, int k) {
-  FT G = -div_Uc<FT>(P, P.c[n], i, j, k);
+__device__ __forceinline__ FT tracer_tendency(const TendParams<FT>& P, int n, int i, int j, int k, FT div) {
+  FT G = -div;
   if (P.has_closure) G = G - div_diffusive_flux<FT>(P, P.c[n], n, i, j, k);
   else G = G - FT(0);
   return G;
@@ -355,13 +356,95 @@ __global__ void __launch_bounds__(128) tendency_generic_kernel(const __grid_cons
   if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
   long long n = g.idx(i, j, k);
   if (what == 0) {
-    if (!(g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i == 1)) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k);
+    if (!(g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i == 1)) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k, div_Uu<FT, 0>(P, i, j, k));
   } else if (what == 1) {
-    if (!(g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j == 1)) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k);
+    if (!(g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j == 1)) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k, div_Uu<FT, 1>(P, i, j, k));
   } else if (what == 2) {
-    if (!(g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k == 1)) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k);
+    if (!(g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k == 1)) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k, div_Uu<FT, 2>(P, i, j, k));
   } else {
     int t = what - 3;
-    P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k);
+    P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k, div_Uc<FT>(P, P.c[t], i, j, k));
   }
+}
+
+
+// ---- tiled variant: every advective face flux of a TG_TX×TG_TY×TG_TZ tile is evaluated ONCE into shared memory --------
+// Same flux functions, same differences and the same association of the sums as the per-cell kernel above (which evaluates
+// each face twice, once from either neighbour, like the reference's kernels), so the results are bit-identical; the other
+// tendency terms are evaluated per cell as before.  Block = TG_TX×TG_TY threads, each marching the tile's TG_TZ planes.
+#define TG_TX 32
+#define TG_TY 4
+#define TG_TZ 4
+
+template <typename FT, int a>    // a = 0,1,2: velocity component; a = 3: tracer P.c[t]
+__device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, FT* sm) {
+  const GridDev<FT>& g = P.g;
+  typedef FT (*FxT)[TG_TY][TG_TX + 1];
+  typedef FT (*FyT)[TG_TY + 1][TG_TX];
+  typedef FT (*FzT)[TG_TY][TG_TX];
+  FxT Fx = reinterpret_cast<FxT>(sm);
+  FyT Fy = reinterpret_cast<FyT>(sm + TG_TZ * TG_TY * (TG_TX + 1));
+  FzT Fz = reinterpret_cast<FzT>(sm + TG_TZ * TG_TY * (TG_TX + 1) + TG_TZ * (TG_TY + 1) * TG_TX);
+  const int i0 = blockIdx.x * TG_TX + 1, j0 = blockIdx.y * TG_TY + 1, k0 = blockIdx.z * TG_TZ + 1;
+  const int nx = min(TG_TX, g.N[0] - i0 + 1), ny = min(TG_TY, g.N[1] - j0 + 1), nz = min(TG_TZ, g.N[2] - k0 + 1);
+  const int tid = threadIdx.y * TG_TX + threadIdx.x;
+  constexpr int NT = TG_TX * TG_TY;
+  const FT* c = a == 3 ? P.c[t] : nullptr;
+  // a momentum flux along its own component's direction lives at Centers (difference F[i] - F[i-1]): slots i0-1 … i0+nx-1;
+  // every other flux lives at Faces (F[i+1] - F[i]): slots i0 … i0+nx
+  const int ox = a == 0 ? -1 : 0, oy = a == 1 ? -1 : 0, oz = a == 2 ? -1 : 0;
+  if (g.topo[0] != NH_FLAT)
+    for (int s = tid; s < (TG_TX + 1) * TG_TY * TG_TZ; s += NT) {
+      const int li = s % (TG_TX + 1), r = s / (TG_TX + 1), lj = r % TG_TY, lk = r / TG_TY;
+      if (li > nx || lj >= ny || lk >= nz) continue;
+      const int i = i0 + li + ox, j = j0 + lj, k = k0 + lk;
+      if (a == 0 && g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i < 1) continue;   // only the (skipped) periphery cell would read it
+      Fx[lk][lj][li] = a == 3 ? tracer_flux<FT, 0>(P, c, i, j, k) : momentum_flux<FT, a == 3 ? 0 : a, 0>(P, i, j, k);
+    }
+  if (g.topo[1] != NH_FLAT)
+    for (int s = tid; s < TG_TX * (TG_TY + 1) * TG_TZ; s += NT) {
+      const int li = s % TG_TX, r = s / TG_TX, lj = r % (TG_TY + 1), lk = r / (TG_TY + 1);
+      if (li >= nx || lj > ny || lk >= nz) continue;
+      const int i = i0 + li, j = j0 + lj + oy, k = k0 + lk;
+      if (a == 1 && g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j < 1) continue;
+      Fy[lk][lj][li] = a == 3 ? tracer_flux<FT, 1>(P, c, i, j, k) : momentum_flux<FT, a == 3 ? 0 : a, 1>(P, i, j, k);
+    }
+  if (g.topo[2] != NH_FLAT)
+    for (int s = tid; s < TG_TX * TG_TY * (TG_TZ + 1); s += NT) {
+      const int li = s % TG_TX, r = s / TG_TX, lj = r % TG_TY, lk = r / TG_TY;
+      if (li >= nx || lj >= ny || lk > nz) continue;
+      const int i = i0 + li, j = j0 + lj, k = k0 + lk + oz;
+      if (a == 2 && g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k < 1) continue;
+      Fz[lk][lj][li] = a == 3 ? tracer_flux<FT, 2>(P, c, i, j, k) : momentum_flux<FT, a == 3 ? 0 : a, 2>(P, i, j, k);
+    }
+  __syncthreads();
+  const int li = threadIdx.x, lj = threadIdx.y;
+  if (li >= nx || lj >= ny) return;
+  const int i = i0 + li, j = j0 + lj;
+  for (int lk = 0; lk < nz; ++lk) {
+    const int k = k0 + lk;
+    if (a == 0 && g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i == 1) continue;      // exclude_periphery
+    if (a == 1 && g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j == 1) continue;
+    if (a == 2 && g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k == 1) continue;
+    const FT tx = g.topo[0] == NH_FLAT ? FT(0) : Fx[lk][lj][li + 1] - Fx[lk][lj][li];
+    const FT ty = g.topo[1] == NH_FLAT ? FT(0) : Fy[lk][lj + 1][li] - Fy[lk][lj][li];
+    const FT tz = g.topo[2] == NH_FLAT ? FT(0) : Fz[lk + 1][lj][li] - Fz[lk][lj][li];
+    FT total = tx + ty;
+    total = total + tz;
+    const FT div = FT(1) / volume_at(g, a == 2 ? 0 : 1, k) * total;
+    const long long n = g.idx(i, j, k);
+    if (a == 0) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k, div);
+    else if (a == 1) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k, div);
+    else if (a == 2) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k, div);
+    else P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k, div);
+  }
+}
+
+template <typename FT>
+__global__ void __launch_bounds__(TG_TX * TG_TY) tendency_tiled_kernel(const __grid_constant__ TendParams<FT> P, int what) {
+  __shared__ FT sm[TG_TZ * TG_TY * (TG_TX + 1) + TG_TZ * (TG_TY + 1) * TG_TX + (TG_TZ + 1) * TG_TY * TG_TX];
+  if (what == 0) tiled_tendency<FT, 0>(P, 0, sm);
+  else if (what == 1) tiled_tendency<FT, 1>(P, 0, sm);
+  else if (what == 2) tiled_tendency<FT, 2>(P, 0, sm);
+  else tiled_tendency<FT, 3>(P, what - 3, sm);
 }

@@ -10,6 +10,7 @@ module only places the messages between them.  The index helpers below restate t
 that the host logic can be tested on CPU with the ``gloo`` backend (tests/test_distributed_cpu.py).
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -170,13 +171,22 @@ class DistributedNonhydrostaticModel:
         raw = (C.c_ubyte * allb.numel()).from_buffer_copy(allb.numpy().tobytes())
         check(lib().nh_dist_ipc_import(self._h, raw, allb.numel()))
         self._flag = torch.zeros(1, device=self.device)
+        self._nccl_barrier = bool(os.environ.get("NHSTEP_NCCL_BARRIER"))
+        if self.R > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self.arch.group)          # every rank has opened its peers' flag arrays before the first epoch
         self.p2p = True
 
     def _barrier(self):
-        """All ranks' kernels issued so far have completed before anything issued after it starts (stream-ordered)."""
+        """All ranks' kernels issued so far have completed before anything issued after it starts (stream-ordered):
+        the library's flag barrier over NVLink (nh_dist_barrier), or a one-element NCCL all-reduce with
+        NHSTEP_NCCL_BARRIER=1 (the cross-check)."""
         if self.R > 1:
-            import torch.distributed as dist
-            dist.all_reduce(self._flag, group=self.arch.group)
+            if self._nccl_barrier:
+                import torch.distributed as dist
+                dist.all_reduce(self._flag, group=self.arch.group)
+            else:
+                check(lib().nh_dist_barrier(self._h))
 
     # -- pieces ---------------------------------------------------------------------------------------------------
     def exchange(self, mask, width):

@@ -404,6 +404,36 @@ def test_fused_fast_path_is_bit_identical_to_complete_path(oc, FT, timestepper, 
         np.testing.assert_array_equal(a, b)
 
 
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+@pytest.mark.parametrize("cfg", [((37, 9, 11), (P, P, B), "stretched", ("WENO", 5),
+                                  dict(buoyancy="seawater", tracers=("T", "S"), coriolis=1e-2, closure=("lilly", 0.16, 1.0, 1.0))),
+                                 ((9, 8, 10), (B, B, B), None, ("UpwindBiased", 3), dict(tracers=("c",), closure=(1e-2, 1e-2))),
+                                 ((33, 6, 1), (P, B, B), None, ("Centered", 4), {}),
+                                 ((16, 12), (P, F, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",)))],
+                         ids=["ppb-les", "bbb", "nz1", "flat"])
+def test_tiled_tendency_kernel_is_bit_identical_to_the_per_cell_kernel(oc, FT, cfg, monkeypatch):
+    """Complete path: faces evaluated once into shared memory (default) against the reference-style kernel that evaluates
+    every face from both neighbouring cells (NHSTEP_NO_TILED), partial tiles and walls included."""
+    size, topo, zkind, adv, kw = cfg
+    out = []
+    rng = np.random.default_rng(3)
+    ics = None
+    for no_tiled in (False, True):
+        if no_tiled:
+            monkeypatch.setenv("NHSTEP_NO_TILED", "1")
+        else:
+            monkeypatch.delenv("NHSTEP_NO_TILED", raising=False)
+        m1, m2 = make_pair(oc, FT, size, topo, z=_z(zkind, size), advection=adv, **kw)
+        if ics is None:
+            ics = random_ics(m2, rng)
+        for n, f1, _ in names_fields(m1, m2):
+            f1.set(ics[n])
+        oc.update_state(m1, compute_tendencies=True)
+        out.append([m1.timestepper.Gn[n].interior() for n in m2.prognostic_names()])
+    for a, b in zip(*out):
+        np.testing.assert_array_equal(a, b)
+
+
 @pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
 @pytest.mark.parametrize("size", [(32, 32, 32), (64, 16, 32)])
 def test_fused_poisson_path_100_steps_vs_oracle(oc, FT, tol, size):
