@@ -406,3 +406,104 @@ def test_amd_analytic_eddy_viscosity_and_diffusivity():
         r, q = a ** 3 + b ** 3 - (a + b) ** 3, a ** 2 + b ** 2 + (a + b) ** 2
         np.testing.assert_allclose(m.nu_e.interior[inner], max(0.0, -C * d2 * r / q), rtol=1e-12, atol=1e-18)
         np.testing.assert_allclose(m.kappa_e["c"].interior[inner], max(0.0, C * d2 * (a + b)), rtol=1e-12, atol=1e-18)
+
+
+# ---------------------------------------------------------------------------------------------
+# Dynamics — test/test_dynamics.jl:17-86,176-207,404-460,495-600,620-624 (explicit ScalarDiffusivity cases)
+# ---------------------------------------------------------------------------------------------
+
+def _field(m, name):
+    return dict(zip(m.prognostic_names(), m.prognostic_fields()))[name]
+
+
+@pytest.mark.parametrize("timestepper", ["QuasiAdamsBashforth2", "RungeKutta3"])
+@pytest.mark.parametrize("name", ["u", "v", "c"])
+def test_diffusion_simple(name, timestepper):
+    """test_diffusion_simple: a constant field stays constant under ν = κ = 1 diffusion, 10 steps of Δt = 1 on (1, 1, 16)."""
+    from oracle.model import update_state
+    g = o.RectilinearGrid(np.float64, size=(1, 1, 16), extent=(1, 1, 1), topology=(P, P, B))
+    m = o.NonhydrostaticModel(g, timestepper=timestepper, closure=o.ScalarDiffusivity(1, 1), tracers=("c",))
+    f = _field(m, name)
+    f.interior[...] = np.pi
+    update_state(m)
+    for _ in range(10):
+        o.time_step(m, 1.0)
+    assert np.allclose(f.interior, np.pi, rtol=np.sqrt(np.finfo(np.float64).eps), atol=0)
+
+
+_BUDGET_TOPOS = [(P, P, P), (P, P, B), (P, B, B), (B, B, B)]
+
+
+@pytest.mark.parametrize("timestepper", ["QuasiAdamsBashforth2", "RungeKutta3"])
+@pytest.mark.parametrize("topo", _BUDGET_TOPOS, ids=["".join(t[0] for t in tp) for tp in _BUDGET_TOPOS])
+def test_scalar_diffusivity_budget(topo, timestepper):
+    """test_ScalarDiffusivity_budget: the mean of a random field is conserved by isotropic diffusion (c everywhere, a
+    velocity component along each Periodic direction), 10 steps of Δt = 1e-4·Δ²/κ on 4³."""
+    from oracle.model import update_state
+    rng = np.random.default_rng(0)
+    names = ["c"] + [n for n, t in zip("uvw", topo) if t == P]
+    for name in names:
+        g = o.RectilinearGrid(np.float64, size=(4, 4, 4), extent=(1, 1, 1), topology=topo)
+        m = o.NonhydrostaticModel(g, timestepper=timestepper, closure=o.ScalarDiffusivity(1, 1), tracers=("c",))
+        f = _field(m, name)
+        o.set_model(m, **{name: rng.random(f.size)})
+        init = f.interior.mean()
+        update_state(m)
+        dt = 1e-4 * 0.25 ** 2 / 1
+        for _ in range(10):
+            o.time_step(m, dt)
+        assert np.isclose(init, f.interior.mean(), rtol=np.sqrt(np.finfo(np.float64).eps), atol=0), (name, topo)
+
+
+_COSINE = [((128, 1, 1), (B, P, P), 0, ("v", "w", "c")), ((1, 128, 1), (P, B, P), 1, ("u", "w", "c")),
+           ((1, 1, 128), (P, P, B), 2, ("u", "v", "c")), ((128,), (B, F, F), 0, ("v", "w", "c")),
+           ((128,), (F, F, B), 2, ("u", "v", "c"))]
+
+
+@pytest.mark.parametrize("size,topo,dim,names", _COSINE, ids=["x", "y", "z", "x-flat", "z-flat"])
+def test_diffusion_cosine(size, topo, dim, names):
+    """test_diffusion_cosine: cos(2ξ) on ξ ∈ (0, π/2) between no-flux walls decays like exp(-κ m² t), 5 RK3 steps of
+    Δt = 1e-6·Lz²/κ, to atol = rtol = 1e-6 (ScalarDiffusivity(ν = 1, κ = 1), explicit)."""
+    from oracle.model import update_state
+    L = np.pi / 2
+    kw = {}
+    full = []
+    for d, (axis, t) in enumerate(zip("xyz", topo)):
+        if t != F:
+            kw[axis] = (0, L) if d == dim else (0, 1)
+            full.append(d)
+    for name in names:
+        g = o.RectilinearGrid(np.float64, size=size, topology=topo, **kw)
+        m = o.NonhydrostaticModel(g, closure=o.ScalarDiffusivity(1, 1), tracers=("c",), buoyancy=None)
+        f = _field(m, name)
+        xi = (np.arange(128) + 0.5) * L / 128
+        shape = [1, 1, 1]
+        shape[dim] = 128
+        f.interior[...] = np.cos(2 * xi).reshape(shape)
+        update_state(m)
+        dt = 1e-6 * float(g.Lz) ** 2 / 1
+        for _ in range(5):
+            o.time_step(m, dt)
+        expect = (np.exp(-4 * m.clock.time) * np.cos(2 * xi)).reshape(shape)
+        assert np.allclose(f.interior, np.broadcast_to(expect, f.interior.shape), rtol=1e-6, atol=1e-6), name
+
+
+def test_passive_tracer_advection():
+    """passive_tracer_advection_test(:QuasiAdamsBashforth2): a Gaussian carried by (U, V) = (0.5, 0.8) on 128×128×2 for
+    100 steps of Δt = 0.05·Δx/|U| stays within 1e-4 (mean-square relative error) of the translated Gaussian."""
+    N, L, U, V = 128, 1.0, 0.5, 0.8
+    delta, x0, y0 = L / 15, L / 2, L / 2
+    dt = 0.05 * L / N / np.sqrt(U ** 2 + V ** 2)
+    g = o.RectilinearGrid(np.float64, size=(N, N, 2), extent=(L, L, L), topology=(P, P, B))
+    m = o.NonhydrostaticModel(g, closure=o.ScalarDiffusivity(1e-12, 1e-12), timestepper="QuasiAdamsBashforth2",
+                              buoyancy=o.SeawaterBuoyancy(), tracers=("T", "S"))
+    xc = (np.arange(N) + 0.5) * L / N
+
+    def T(t):
+        return np.exp(-(((xc - U * t - x0) ** 2)[:, None] + ((xc - V * t - y0) ** 2)[None, :]) / (2 * delta ** 2))
+    o.set_model(m, u=np.full((N, N, 2), U), v=np.full((N, N, 2), V), T=np.broadcast_to(T(0)[:, :, None], (N, N, 2)))
+    for _ in range(100):
+        o.time_step(m, dt)
+    ans = np.broadcast_to(T(m.clock.time)[:, :, None], (N, N, 2))
+    num = m.tracers["T"].interior
+    assert ((num - ans) ** 2).mean() / (ans ** 2).mean() < 1e-4
