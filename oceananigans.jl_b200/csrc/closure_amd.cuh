@@ -55,6 +55,22 @@ __device__ __forceinline__ FT amd_c2(const GridDev<FT>& g, const F& f, int i, in
   return amd_c1<FT, hi>(g, inner, i, j, k);
 }
 
+// The viscosity kernel evaluates the off-diagonal normalised gradients and strains ONCE at the four corners of each of the
+// three edge planes around the cell (ffc, fcf, cff) and forms every ℑ_ab of the 30 terms from those twelve corner triples:
+// the same products and the same ℑ_hi(ℑ_lo ·) sums as interpolating each term separately, a quarter of the derivative work.
+template <typename FT, int lo, int hi>
+struct AmdCorners {
+  FT p[4], q[4], s[4];      // ∂_lo u_hi, ∂_hi u_lo (normalised) and Σ_lohi at corners (0,0), (1,0), (0,1), (1,1) in (lo, hi)
+  bool flat_lo, flat_hi;
+  template <typename F>
+  __device__ __forceinline__ FT I(const F& f) const {     // ℑ_hi(ℑ_lo f) onto the Center; identity in Flat directions
+    const FT x0 = flat_lo ? f(0) : FT(0.5) * (f(0) + f(1));
+    if (flat_hi) return x0;
+    const FT x1 = flat_lo ? f(2) : FT(0.5) * (f(2) + f(3));
+    return FT(0.5) * (x0 + x1);
+  }
+};
+
 template <typename FT>
 __global__ void __launch_bounds__(128) amd_viscosity_kernel(const __grid_constant__ TendParams<FT> P, FT* nue, FT Cnu) {
   const GridDev<FT>& g = P.g;
@@ -63,15 +79,28 @@ __global__ void __launch_bounds__(128) amd_viscosity_kernel(const __grid_constan
   int k = blockIdx.z + 1;
   if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
   const AmdOps<FT> o(P);
-#define AMD_F(expr) [&](int a, int b, int c) { return (expr); }
-#define XY(expr) amd_c2<FT, 0, 1>(g, AMD_F(expr), i, j, k)
-#define XZ(expr) amd_c2<FT, 0, 2>(g, AMD_F(expr), i, j, k)
-#define YZ(expr) amd_c2<FT, 1, 2>(g, AMD_F(expr), i, j, k)
-#define SQ(f) [&](int a, int b, int c) { const FT x_ = o.f(a, b, c); return x_ * x_; }
+  AmdCorners<FT, 0, 1> xy; AmdCorners<FT, 0, 2> xz; AmdCorners<FT, 1, 2> yz;
+  xy.flat_lo = xz.flat_lo = g.topo[0] == NH_FLAT;
+  xy.flat_hi = yz.flat_lo = g.topo[1] == NH_FLAT;
+  xz.flat_hi = yz.flat_hi = g.topo[2] == NH_FLAT;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int a = c & 1, b = c >> 1;
+    // in a Flat direction only the corners with offset 0 are used (and exist)
+    if (!((a && xy.flat_lo) || (b && xy.flat_hi))) {
+      xy.p[c] = o.dx_v(i + a, j + b, k); xy.q[c] = o.dy_u(i + a, j + b, k); xy.s[c] = FT(0.5) * (xy.q[c] + xy.p[c]);
+    }
+    if (!((a && xz.flat_lo) || (b && xz.flat_hi))) {
+      xz.p[c] = o.dx_w(i + a, j, k + b); xz.q[c] = o.dz_u(i + a, j, k + b); xz.s[c] = FT(0.5) * (xz.q[c] + xz.p[c]);
+    }
+    if (!((a && yz.flat_lo) || (b && yz.flat_hi))) {
+      yz.p[c] = o.dy_w(i, j + a, k + b); yz.q[c] = o.dz_v(i, j + a, k + b); yz.s[c] = FT(0.5) * (yz.q[c] + yz.p[c]);
+    }
+  }
   const FT ux = o.dx_u(i, j, k), vy = o.dy_v(i, j, k), wz = o.dz_w(i, j, k);
-  const FT xv2 = amd_c2<FT, 0, 1>(g, SQ(dx_v), i, j, k), yu2 = amd_c2<FT, 0, 1>(g, SQ(dy_u), i, j, k);
-  const FT xw2 = amd_c2<FT, 0, 2>(g, SQ(dx_w), i, j, k), zu2 = amd_c2<FT, 0, 2>(g, SQ(dz_u), i, j, k);
-  const FT yw2 = amd_c2<FT, 1, 2>(g, SQ(dy_w), i, j, k), zv2 = amd_c2<FT, 1, 2>(g, SQ(dz_v), i, j, k);
+  const FT xv2 = xy.I([&](int c) { return xy.p[c] * xy.p[c]; }), yu2 = xy.I([&](int c) { return xy.q[c] * xy.q[c]; });
+  const FT xw2 = xz.I([&](int c) { return xz.p[c] * xz.p[c]; }), zu2 = xz.I([&](int c) { return xz.q[c] * xz.q[c]; });
+  const FT yw2 = yz.I([&](int c) { return yz.p[c] * yz.p[c]; }), zv2 = yz.I([&](int c) { return yz.q[c] * yz.q[c]; });
   FT q = ux * ux + vy * vy + wz * wz;
   q = q + xv2; q = q + yu2; q = q + xw2; q = q + zu2; q = q + yw2; q = q + zv2;
   FT nu = FT(0);
@@ -80,21 +109,21 @@ __global__ void __launch_bounds__(128) amd_viscosity_kernel(const __grid_constan
     FT g1 = ux * (ux * ux);
     g1 = g1 + vy * xv2;
     g1 = g1 + wz * xw2;
-    g1 = g1 + two * ux * XY(o.dx_v(a, b, c) * o.S12(a, b, c));
-    g1 = g1 + two * ux * XZ(o.dx_w(a, b, c) * o.S13(a, b, c));
-    g1 = g1 + two * XY(o.dx_v(a, b, c)) * XZ(o.dx_w(a, b, c)) * YZ(o.S23(a, b, c));
+    g1 = g1 + two * ux * xy.I([&](int c) { return xy.p[c] * xy.s[c]; });
+    g1 = g1 + two * ux * xz.I([&](int c) { return xz.p[c] * xz.s[c]; });
+    g1 = g1 + two * xy.I([&](int c) { return xy.p[c]; }) * xz.I([&](int c) { return xz.p[c]; }) * yz.I([&](int c) { return yz.s[c]; });
     FT g2 = ux * yu2;
     g2 = g2 + vy * (vy * vy);
     g2 = g2 + wz * yw2;
-    g2 = g2 + two * vy * XY(o.dy_u(a, b, c) * o.S12(a, b, c));
-    g2 = g2 + two * XY(o.dy_u(a, b, c)) * YZ(o.dy_w(a, b, c)) * XZ(o.S13(a, b, c));
-    g2 = g2 + two * vy * YZ(o.dy_w(a, b, c) * o.S23(a, b, c));
+    g2 = g2 + two * vy * xy.I([&](int c) { return xy.q[c] * xy.s[c]; });
+    g2 = g2 + two * xy.I([&](int c) { return xy.q[c]; }) * yz.I([&](int c) { return yz.p[c]; }) * xz.I([&](int c) { return xz.s[c]; });
+    g2 = g2 + two * vy * yz.I([&](int c) { return yz.p[c] * yz.s[c]; });
     FT g3 = ux * zu2;
     g3 = g3 + vy * zv2;
     g3 = g3 + wz * (wz * wz);
-    g3 = g3 + two * XZ(o.dz_u(a, b, c)) * YZ(o.dz_v(a, b, c)) * XY(o.S12(a, b, c));
-    g3 = g3 + two * wz * XZ(o.dz_u(a, b, c) * o.S13(a, b, c));
-    g3 = g3 + two * wz * YZ(o.dz_v(a, b, c) * o.S23(a, b, c));
+    g3 = g3 + two * xz.I([&](int c) { return xz.q[c]; }) * yz.I([&](int c) { return yz.q[c]; }) * xy.I([&](int c) { return xy.s[c]; });
+    g3 = g3 + two * wz * xz.I([&](int c) { return xz.q[c] * xz.s[c]; });
+    g3 = g3 + two * wz * yz.I([&](int c) { return yz.q[c] * yz.s[c]; });
     const FT r = (g1 + g2) + g3;
     nu = -Cnu * o.delta2(k) * (r - FT(0)) / q;
     nu = (nu > FT(0) || nu != nu) ? nu : FT(0);            // max(zero(FT), νˢᵍˢ), NaN-propagating like Julia's max
@@ -102,6 +131,10 @@ __global__ void __launch_bounds__(128) amd_viscosity_kernel(const __grid_constan
   nue[g.idx(i, j, k)] = nu;
 }
 
+#define AMD_F(expr) [&](int a, int b, int c) { return (expr); }
+#define XY(expr) amd_c2<FT, 0, 1>(g, AMD_F(expr), i, j, k)
+#define XZ(expr) amd_c2<FT, 0, 2>(g, AMD_F(expr), i, j, k)
+#define YZ(expr) amd_c2<FT, 1, 2>(g, AMD_F(expr), i, j, k)
 template <typename FT>
 __global__ void __launch_bounds__(128) amd_diffusivity_kernel(const __grid_constant__ TendParams<FT> P, const FT* tr, FT* kape,
                                                               FT Ckappa) {
@@ -142,4 +175,3 @@ __global__ void __launch_bounds__(128) amd_diffusivity_kernel(const __grid_const
 #undef XY
 #undef XZ
 #undef YZ
-#undef SQ

@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(128) smagorinsky_kernel(const __grid_constant_
 // ---- the tendencies ---------------------------------------------------------------------------------------
 // `div` = div_𝐯u_a at the cell (evaluated by the caller: per cell, or from face fluxes staged in shared memory)
 template <typename FT, int a>
-__device__ __forceinline__ FT velocity_tendency(const TendParams<FT>& P, int i, int j, int k, FT div) {
+__device__ __forceinline__ FT velocity_tendency(const TendParams<FT>& P, int i, int j, int k, FT div, FT closure_div) {
   const GridDev<FT>& g = P.g;
   FT G = -div;
   if (a == 2 && P.w_buoyancy) {
@@ -332,15 +332,15 @@ __device__ __forceinline__ FT velocity_tendency(const TendParams<FT>& P, int i, 
     if (P.pHY) G = G - deriv<FT, a>(g, P.pHY, 0, 1, i, j, k);
     else G = G - FT(0);
   }
-  if (P.has_closure) G = G - div_viscous_flux<FT, a>(P, i, j, k);
+  if (P.has_closure) G = G - closure_div;        // ∂ⱼτ_aⱼ, evaluated by the caller
   else G = G - FT(0);
   return G;
 }
 
 template <typename FT>
-__device__ __forceinline__ FT tracer_tendency(const TendParams<FT>& P, int n, int i, int j, int k, FT div) {
+__device__ __forceinline__ FT tracer_tendency(const TendParams<FT>& P, int n, int i, int j, int k, FT div, FT closure_div) {
   FT G = -div;
-  if (P.has_closure) G = G - div_diffusive_flux<FT>(P, P.c[n], n, i, j, k);
+  if (P.has_closure) G = G - closure_div;        // ∇·q_c, evaluated by the caller
   else G = G - FT(0);
   return G;
 }
@@ -356,22 +356,23 @@ __global__ void __launch_bounds__(128) tendency_generic_kernel(const __grid_cons
   if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
   long long n = g.idx(i, j, k);
   if (what == 0) {
-    if (!(g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i == 1)) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k, div_Uu<FT, 0>(P, i, j, k));
+    if (!(g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i == 1)) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k, div_Uu<FT, 0>(P, i, j, k), P.has_closure ? div_viscous_flux<FT, 0>(P, i, j, k) : FT(0));
   } else if (what == 1) {
-    if (!(g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j == 1)) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k, div_Uu<FT, 1>(P, i, j, k));
+    if (!(g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j == 1)) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k, div_Uu<FT, 1>(P, i, j, k), P.has_closure ? div_viscous_flux<FT, 1>(P, i, j, k) : FT(0));
   } else if (what == 2) {
-    if (!(g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k == 1)) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k, div_Uu<FT, 2>(P, i, j, k));
+    if (!(g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k == 1)) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k, div_Uu<FT, 2>(P, i, j, k), P.has_closure ? div_viscous_flux<FT, 2>(P, i, j, k) : FT(0));
   } else {
     int t = what - 3;
-    P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k, div_Uc<FT>(P, P.c[t], i, j, k));
+    P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k, div_Uc<FT>(P, P.c[t], i, j, k), P.has_closure ? div_diffusive_flux<FT>(P, P.c[t], t, i, j, k) : FT(0));
   }
 }
 
 
 // ---- tiled variant: every advective face flux of a TG_TX×TG_TY×TG_TZ tile is evaluated ONCE into shared memory --------
 // Same flux functions, same differences and the same association of the sums as the per-cell kernel above (which evaluates
-// each face twice, once from either neighbour, like the reference's kernels), so the results are bit-identical; the other
-// tendency terms are evaluated per cell as before.  Block = TG_TX×TG_TY threads, each marching the tile's TG_TZ planes.
+// each face twice, once from either neighbour, like the reference's kernels), so the results are bit-identical.  A second
+// pass through the same shared memory stages the closure's viscous / diffusive face fluxes; the remaining terms (buoyancy,
+// Coriolis, hydrostatic pressure gradient) are evaluated per cell as before.  Block = TG_TX×TG_TY threads, each marching the tile's TG_TZ planes.
 #define TG_TX 32
 #define TG_TY 4
 #define TG_TZ 4
@@ -390,53 +391,73 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
   const int tid = threadIdx.y * TG_TX + threadIdx.x;
   constexpr int NT = TG_TX * TG_TY;
   const FT* c = a == 3 ? P.c[t] : nullptr;
-  // a momentum flux along its own component's direction lives at Centers (difference F[i] - F[i-1]): slots i0-1 … i0+nx-1;
-  // every other flux lives at Faces (F[i+1] - F[i]): slots i0 … i0+nx
+  // a momentum / viscous flux along its own component's direction lives at Centers (difference F[i] - F[i-1]): slots
+  // i0-1 … i0+nx-1; every other flux lives at Faces (F[i+1] - F[i]): slots i0 … i0+nx
   const int ox = a == 0 ? -1 : 0, oy = a == 1 ? -1 : 0, oz = a == 2 ? -1 : 0;
-  if (g.topo[0] != NH_FLAT)
-    for (int s = tid; s < (TG_TX + 1) * TG_TY * TG_TZ; s += NT) {
-      const int li = s % (TG_TX + 1), r = s / (TG_TX + 1), lj = r % TG_TY, lk = r / TG_TY;
-      if (li > nx || lj >= ny || lk >= nz) continue;
-      const int i = i0 + li + ox, j = j0 + lj, k = k0 + lk;
-      if (a == 0 && g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i < 1) continue;   // only the (skipped) periphery cell would read it
-      Fx[lk][lj][li] = a == 3 ? tracer_flux<FT, 0>(P, c, i, j, k) : momentum_flux<FT, a == 3 ? 0 : a, 0>(P, i, j, k);
-    }
-  if (g.topo[1] != NH_FLAT)
-    for (int s = tid; s < TG_TX * (TG_TY + 1) * TG_TZ; s += NT) {
-      const int li = s % TG_TX, r = s / TG_TX, lj = r % (TG_TY + 1), lk = r / (TG_TY + 1);
-      if (li >= nx || lj > ny || lk >= nz) continue;
-      const int i = i0 + li, j = j0 + lj + oy, k = k0 + lk;
-      if (a == 1 && g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j < 1) continue;
-      Fy[lk][lj][li] = a == 3 ? tracer_flux<FT, 1>(P, c, i, j, k) : momentum_flux<FT, a == 3 ? 0 : a, 1>(P, i, j, k);
-    }
-  if (g.topo[2] != NH_FLAT)
-    for (int s = tid; s < TG_TX * TG_TY * (TG_TZ + 1); s += NT) {
-      const int li = s % TG_TX, r = s / TG_TX, lj = r % TG_TY, lk = r / TG_TY;
-      if (li >= nx || lj >= ny || lk > nz) continue;
-      const int i = i0 + li, j = j0 + lj, k = k0 + lk + oz;
-      if (a == 2 && g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k < 1) continue;
-      Fz[lk][lj][li] = a == 3 ? tracer_flux<FT, 2>(P, c, i, j, k) : momentum_flux<FT, a == 3 ? 0 : a, 2>(P, i, j, k);
-    }
-  __syncthreads();
+  constexpr int av = a == 3 ? 0 : a;           // keeps the momentum templates well-formed in the tracer instantiation
   const int li = threadIdx.x, lj = threadIdx.y;
-  if (li >= nx || lj >= ny) return;
+  const bool mine = li < nx && lj < ny;
+  FT divs[2][TG_TZ];                           // [0]: advective divergence, [1]: closure divergence, per plane of the tile
+#pragma unroll
+  for (int pass = 0; pass < 2; ++pass) {
+    if (pass == 1 && !P.has_closure) break;
+    if (pass == 1) __syncthreads();            // everyone has read the advective fluxes
+    if (g.topo[0] != NH_FLAT)
+      for (int s = tid; s < (TG_TX + 1) * TG_TY * TG_TZ; s += NT) {
+        const int fi = s % (TG_TX + 1), r = s / (TG_TX + 1), fj = r % TG_TY, fk = r / TG_TY;
+        if (fi > nx || fj >= ny || fk >= nz) continue;
+        const int i = i0 + fi + ox, j = j0 + fj, k = k0 + fk;
+        if (a == 0 && g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i < 1) continue;   // only the (skipped) periphery cell would read it
+        if (pass == 0) Fx[fk][fj][fi] = a == 3 ? tracer_flux<FT, 0>(P, c, i, j, k) : momentum_flux<FT, av, 0>(P, i, j, k);
+        else Fx[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 0>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 0>(P, i, j, k);
+      }
+    if (g.topo[1] != NH_FLAT)
+      for (int s = tid; s < TG_TX * (TG_TY + 1) * TG_TZ; s += NT) {
+        const int fi = s % TG_TX, r = s / TG_TX, fj = r % (TG_TY + 1), fk = r / (TG_TY + 1);
+        if (fi >= nx || fj > ny || fk >= nz) continue;
+        const int i = i0 + fi, j = j0 + fj + oy, k = k0 + fk;
+        if (a == 1 && g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j < 1) continue;
+        if (pass == 0) Fy[fk][fj][fi] = a == 3 ? tracer_flux<FT, 1>(P, c, i, j, k) : momentum_flux<FT, av, 1>(P, i, j, k);
+        else Fy[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 1>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 1>(P, i, j, k);
+      }
+    if (g.topo[2] != NH_FLAT)
+      for (int s = tid; s < TG_TX * TG_TY * (TG_TZ + 1); s += NT) {
+        const int fi = s % TG_TX, r = s / TG_TX, fj = r % TG_TY, fk = r / TG_TY;
+        if (fi >= nx || fj >= ny || fk > nz) continue;
+        const int i = i0 + fi, j = j0 + fj, k = k0 + fk + oz;
+        if (a == 2 && g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k < 1) continue;
+        if (pass == 0) Fz[fk][fj][fi] = a == 3 ? tracer_flux<FT, 2>(P, c, i, j, k) : momentum_flux<FT, av, 2>(P, i, j, k);
+        else Fz[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 2>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 2>(P, i, j, k);
+      }
+    __syncthreads();
+    if (mine) {
+#pragma unroll
+      for (int lk = 0; lk < TG_TZ; ++lk) {
+        if (lk >= nz) break;
+        const FT tx = g.topo[0] == NH_FLAT ? FT(0) : Fx[lk][lj][li + 1] - Fx[lk][lj][li];
+        const FT ty = g.topo[1] == NH_FLAT ? FT(0) : Fy[lk][lj + 1][li] - Fy[lk][lj][li];
+        const FT tz = g.topo[2] == NH_FLAT ? FT(0) : Fz[lk + 1][lj][li] - Fz[lk][lj][li];
+        FT total = tx + ty;
+        total = total + tz;
+        divs[pass][lk] = FT(1) / volume_at(g, a == 2 ? 0 : 1, k0 + lk) * total;
+      }
+    }
+  }
+  if (!mine) return;
   const int i = i0 + li, j = j0 + lj;
-  for (int lk = 0; lk < nz; ++lk) {
+#pragma unroll
+  for (int lk = 0; lk < TG_TZ; ++lk) {
+    if (lk >= nz) break;
     const int k = k0 + lk;
     if (a == 0 && g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i == 1) continue;      // exclude_periphery
     if (a == 1 && g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j == 1) continue;
     if (a == 2 && g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k == 1) continue;
-    const FT tx = g.topo[0] == NH_FLAT ? FT(0) : Fx[lk][lj][li + 1] - Fx[lk][lj][li];
-    const FT ty = g.topo[1] == NH_FLAT ? FT(0) : Fy[lk][lj + 1][li] - Fy[lk][lj][li];
-    const FT tz = g.topo[2] == NH_FLAT ? FT(0) : Fz[lk + 1][lj][li] - Fz[lk][lj][li];
-    FT total = tx + ty;
-    total = total + tz;
-    const FT div = FT(1) / volume_at(g, a == 2 ? 0 : 1, k) * total;
+    const FT div = divs[0][lk], cdiv = P.has_closure ? divs[1][lk] : FT(0);
     const long long n = g.idx(i, j, k);
-    if (a == 0) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k, div);
-    else if (a == 1) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k, div);
-    else if (a == 2) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k, div);
-    else P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k, div);
+    if (a == 0) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k, div, cdiv);
+    else if (a == 1) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k, div, cdiv);
+    else if (a == 2) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k, div, cdiv);
+    else P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k, div, cdiv);
   }
 }
 
