@@ -80,6 +80,9 @@ typedef struct {
                                       AnisotropicMinimumDissipation (Cb = nothing) — …/anisotropic_minimum_dissipation.jl:110-208 */
   double  nu;
   double  kappa[NH_MAX_TRACERS];
+  int32_t vertically_implicit;     /* ScalarDiffusivity(VerticallyImplicitTimeDiscretization(), ν, κ): z-diffusion by a
+                                      tridiagonal solve after each substep — vertically_implicit_diffusion_solver.jl:57-273,
+                                      abstract_scalar_diffusivity_closure.jl:216-252; needs a Bounded z */
   double  smagorinsky_C, smagorinsky_Cb;   /* Cˢ (default 0.16) and the Lilly buoyancy multiplier Cb (default 1) */
   double  smagorinsky_Pr[NH_MAX_TRACERS];  /* turbulent Prandtl number of each tracer: κₑ = ℑ(νₑ) / Pr */
   double  amd_Cnu, amd_Ckappa[NH_MAX_TRACERS];   /* Poincaré constants Cν and Cκ of each tracer (default 1/12) */

@@ -200,10 +200,12 @@ class AnisotropicMinimumDissipation:
 
 
 class ScalarDiffusivity:
+    """ScalarDiffusivity([time_discretization,] ν, κ) (isotropic); vertically_implicit = True stands for
+    VerticallyImplicitTimeDiscretization()."""
     kind = L.CLOSURE_SCALAR
 
-    def __init__(self, nu=0.0, kappa=0.0):
-        self.nu, self.kappa = nu, kappa
+    def __init__(self, nu=0.0, kappa=0.0, vertically_implicit=False):
+        self.nu, self.kappa, self.vitd = nu, kappa, bool(vertically_implicit)
 
     def kappa_for(self, name):
         return self.kappa[name] if isinstance(self.kappa, dict) else self.kappa

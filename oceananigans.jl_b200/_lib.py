@@ -30,7 +30,7 @@ class ModelDesc(C.Structure):
                 ("buoyancy_tracer", C.c_int32 * 2), ("gravitational_acceleration", C.c_double),
                 ("thermal_expansion", C.c_double), ("haline_contraction", C.c_double), ("has_coriolis", C.c_int32),
                 ("coriolis_f", C.c_double), ("has_closure", C.c_int32), ("nu", C.c_double),
-                ("kappa", C.c_double * NH_MAX_TRACERS), ("smagorinsky_C", C.c_double), ("smagorinsky_Cb", C.c_double),
+                ("kappa", C.c_double * NH_MAX_TRACERS), ("vertically_implicit", C.c_int32), ("smagorinsky_C", C.c_double), ("smagorinsky_Cb", C.c_double),
                 ("smagorinsky_Pr", C.c_double * NH_MAX_TRACERS), ("amd_Cnu", C.c_double),
                 ("amd_Ckappa", C.c_double * NH_MAX_TRACERS), ("hydrostatic_pressure_anomaly", C.c_int32),
                 ("exact_arithmetic", C.c_int32)]

@@ -77,6 +77,7 @@ struct TendParams {
   int w_buoyancy;             // buoyancy acts on w directly (pHY′ is nothing)
   int has_coriolis; FT fcor;
   int has_closure; FT nu; FT kappa[NH_MAXTR];
+  int vitd;                   // VerticallyImplicitTimeDiscretization: z-fluxes explicit on the walls k = 1, Nz+1 only
   const FT* nue;              // eddy viscosity νₑ at ccc (Smagorinsky closures); nullptr ⇒ the constants above
   const FT* kape[NH_MAXTR];   // eddy diffusivity field of each tracer at ccc: νₑ itself (Smagorinsky) or κₑ[n] (AMD)
   FT Pr[NH_MAXTR];            // κ on a face = ℑ(kape[n]) / Pr[n]  (Pr = 1 for AMD)

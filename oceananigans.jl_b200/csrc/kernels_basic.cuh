@@ -106,6 +106,56 @@ __global__ void flux_bc_kernel(const __grid_constant__ FluxBcJob<FT> J) {
   }
 }
 
+// ---- vertically implicit diffusion -----------------------------------------------------------------------------------
+// implicit_step!(field, …, Δt) — vertically_implicit_diffusion_solver.jl:57-121,231-273: (1 - Δt ∂z κ ∂z) ϕⁿ⁺¹ = ϕ★ per
+// column with the Thomas sweep of batched_tridiagonal_solver.jl:209-235 (coefficient functions, |β| < 10·eps guard,
+// scratch t in the field's type).  CT is the type the reference forms the coefficients in: Float64 under RK3 (stage Δt
+// is the caller's Float64 Δt times γ + ζ), the field's type under AB2 (Δt converted).  One thread per column of 1:Nx × 1:Ny.
+template <typename FT, typename CT>
+struct ImplicitJob {
+  GridDev<FT> g;
+  FT* phi;
+  FT* t;                  // scratch, same layout as a field
+  CT dt, kappa;
+  int w_field;            // the field sits at Faces in z (w)
+};
+
+template <typename FT, typename CT>
+__global__ void __launch_bounds__(128) implicit_step_kernel(const __grid_constant__ ImplicitJob<FT, CT> J) {
+  const GridDev<FT>& g = J.g;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x + 1, j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  if (i > g.N[0] || j > g.N[1]) return;
+  const int Nz = g.N[2];
+  const CT dt = J.dt, kap = J.kappa;
+  auto dzc = [&](int k) { return (CT)g.Dzc(k); };
+  auto dzf = [&](int k) { return (CT)g.Dzf(k); };
+  auto upper = [&](int k) -> CT {
+    if (!J.w_field) return k > Nz - 1 ? CT(0) : -dt * kap / (dzc(k) * dzf(k + 1));
+    return k < 1 ? CT(0) : -dt * kap / (dzc(k) * dzf(k));
+  };
+  auto lower = [&](int k) -> CT {      // Tridiagonal convention: row k holds the coupling of level k+1 to level k
+    if (!J.w_field) return k < 1 ? CT(0) : -dt * kap / (dzc(k + 1) * dzf(k + 1));
+    return k < 1 ? CT(0) : -dt * kap / (dzc(k + 2) * dzf(k + 1));
+  };
+  auto diag = [&](int k) -> CT { return CT(1) - dt * CT(0) - upper(k) - lower(k - 1); };
+  const long long n1 = g.idx(i, j, 1), sz = g.sz;
+  CT beta = diag(1);
+  J.phi[n1] = (FT)((CT)J.phi[n1] / beta);
+  for (int k = 2; k <= Nz; ++k) {
+    const long long n = n1 + sz * (k - 1);
+    const CT c = upper(k - 1), b = diag(k), a = lower(k - 1);
+    const FT tk = (FT)(c / beta);
+    J.t[n] = tk;
+    beta = b - a * (CT)tk;
+    const CT eps10 = sizeof(CT) == 8 ? CT(10 * 2.220446049250313e-16) : CT(10 * 1.1920929e-7f);
+    if (!(fabs((double)beta) < (double)eps10)) J.phi[n] = (FT)(((CT)J.phi[n] - a * (CT)J.phi[n - sz]) / beta);
+  }
+  for (int k = Nz - 1; k >= 1; --k) {
+    const long long n = n1 + sz * (k - 1);
+    J.phi[n] = J.phi[n] - J.t[n + sz] * J.phi[n + sz];
+  }
+}
+
 // ---- time-stepper substeps ------------------------------------------------------------------------------------
 template <typename FT>
 struct StepJob {

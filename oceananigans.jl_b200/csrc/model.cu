@@ -63,6 +63,13 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   bool want_phy = d.hydrostatic_pressure_anomaly < 0 ? d.buoyancy_kind != NH_BUOYANCY_NONE : d.hydrostatic_pressure_anomaly != 0;
   if (want_phy) pHY = alloc_field();
   NH_REQUIRE(d.has_closure >= NH_CLOSURE_NONE && d.has_closure <= NH_CLOSURE_AMD, "unknown closure kind");
+  vitd = d.has_closure == NH_CLOSURE_SCALAR && d.vertically_implicit != 0;
+  NH_REQUIRE(!d.vertically_implicit || d.has_closure == NH_CLOSURE_SCALAR,
+             "VerticallyImplicitTimeDiscretization is implemented for ScalarDiffusivity only");
+  // implicit_diffusion_solver (vertically_implicit_diffusion_solver.jl:164-169)
+  NH_REQUIRE(!vitd || gh.g.topo[2] == NH_BOUNDED,
+             "VerticallyImplicitTimeDiscretization can only be specified on grids that are Bounded in the z-direction");
+  if (vitd) vitd_t.alloc((size_t)gh.volume(), true);
   if (d.has_closure == NH_CLOSURE_AMD) {
     // build_diffusivity_fields (anisotropic_minimum_dissipation.jl:371-385): νₑ and one κₑ per tracer, default conditions
     nue = alloc_field();
@@ -339,6 +346,7 @@ TendParams<FT> Model<FT>::tend_params() const {
   P.w_buoyancy = (desc.buoyancy_kind != NH_BUOYANCY_NONE && !pHY) ? 1 : 0;
   P.has_coriolis = desc.has_coriolis; P.fcor = (FT)desc.coriolis_f;
   P.has_closure = desc.has_closure; P.nu = (FT)desc.nu;
+  P.vitd = vitd ? 1 : 0;
   P.nue = nue;
   const bool amd = desc.has_closure == NH_CLOSURE_AMD;
   for (int t = 0; t < ntr; ++t) { P.Pr[t] = amd ? FT(1) : (FT)desc.smagorinsky_Pr[t]; P.kape[t] = amd ? kape[t] : nue; }
@@ -437,15 +445,42 @@ void Model<FT>::substep_launch(int mode, FT dt, FT c1, FT c2) {
   CUDA_CHECK(cudaGetLastError());
 }
 
+// implicit_step! of every prognostic field after its explicit substep (runge_kutta_3.jl:157-165,
+// quasi_adams_bashforth_2.jl:134-142).  ab2 = the Δt was converted to the grid's type before the coefficients were formed.
+template <typename FT>
+template <typename CT2>
+void Model<FT>::implicit_launch(double stage_dt) {
+  dim3 blk(32, 4, 1);
+  dim3 grd((gh.g.N[0] + blk.x - 1) / blk.x, (gh.g.N[1] + blk.y - 1) / blk.y, 1);
+  for (int f = 0; f < nf; ++f) {
+    ImplicitJob<FT, CT2> J;
+    J.g = gh.g; J.phi = F[f]; J.t = vitd_t.p; J.dt = (CT2)stage_dt;
+    J.kappa = (CT2)(f < 3 ? (FT)desc.nu : (FT)desc.kappa[f - 3]);
+    J.w_field = f == 2;
+    implicit_step_kernel<FT, CT2><<<grd, blk, 0, stream>>>(J);
+    KLAUNCH(lc);
+  }
+  CUDA_CHECK(cudaGetLastError());
+}
+
+template <typename FT>
+void Model<FT>::implicit_steps(double stage_dt, bool ab2) {
+  if (!vitd) return;
+  if (ab2) implicit_launch<FT>((double)(FT)stage_dt);
+  else implicit_launch<double>(stage_dt);
+}
+
 template <typename FT>
 void Model<FT>::rk3_substep(double dt, double gamma, double zeta, int has_zeta) {
   substep_launch(has_zeta ? 1 : 0, (FT)dt, (FT)gamma, (FT)zeta);
+  implicit_steps(has_zeta ? (double)(FT)((FT)gamma + (FT)zeta) * dt : (double)(FT)gamma * dt, false);
 }
 
 template <typename FT>
 void Model<FT>::ab2_step(double dt, double chi_) {
   FT c = (FT)chi_;
   substep_launch(c != FT(-0.5) ? 2 : 3, (FT)dt, c, FT(0));
+  implicit_steps(dt, true);
 }
 
 template <typename FT>
@@ -525,19 +560,19 @@ void Model<FT>::time_step(double dt, int euler) {
     double second = (double)(FT)(rk_g2 + rk_z2) * dt;
     double third = (double)(FT)(rk_g3 + rk_z3) * dt;
     double t_next = clock.time + dt;
-    substep_launch(0, (FT)dt, rk_g1, FT(0)); mark(0);
+    substep_launch(0, (FT)dt, rk_g1, FT(0)); implicit_steps(first, false); mark(0);
     clock.time += first; clock.stage += 1; clock.last_stage_dt = first;
     calculate_pressure_correction(first); mark(1);
     pressure_correct_velocities(first); mark(2);
     swapG();
     update_state(1); mark(0);
-    substep_launch(1, (FT)dt, rk_g2, rk_z2); mark(0);
+    substep_launch(1, (FT)dt, rk_g2, rk_z2); implicit_steps(second, false); mark(0);
     clock.time += second; clock.stage += 1; clock.last_stage_dt = second;
     calculate_pressure_correction(second); mark(1);
     pressure_correct_velocities(second); mark(2);
     swapG();
     update_state(1); mark(0);
-    substep_launch(1, (FT)dt, rk_g3, rk_z3); mark(0);
+    substep_launch(1, (FT)dt, rk_g3, rk_z3); implicit_steps(third, false); mark(0);
     double corrected = t_next - clock.time;
     clock.time += third; clock.iteration += 1; clock.stage = 1;
     clock.last_stage_dt = corrected; clock.last_dt = dt;
@@ -547,7 +582,7 @@ void Model<FT>::time_step(double dt, int euler) {
   } else {
     bool eul = euler || (dt != clock.last_dt);
     FT c = eul ? FT(-0.5) : chi;
-    substep_launch(eul ? 3 : 2, (FT)dt, c, FT(0)); mark(0);
+    substep_launch(eul ? 3 : 2, (FT)dt, c, FT(0)); implicit_steps(dt, true); mark(0);
     clock.time += dt; clock.iteration += 1; clock.stage = 1; clock.last_dt = dt; clock.last_stage_dt = dt;
     calculate_pressure_correction(dt); mark(1);
     pressure_correct_velocities(dt); mark(2);

@@ -334,6 +334,8 @@ struct Model : nh_model {
   FT* pHY = nullptr;
   FT* nue = nullptr;       // νₑ of the Smagorinsky / AMD closures (diffusivity_fields.νₑ)
   FT* kape[NH_MAXTR] = {}; // AMD: κₑ of each tracer (diffusivity_fields.κₑ)
+  bool vitd = false;       // ScalarDiffusivity with VerticallyImplicitTimeDiscretization
+  DevBuf<FT> vitd_t;       // scratch of the tridiagonal sweeps, one field
   DevBuf<FT> df2;          // Δᶠ² = cbrt(ΔxΔyΔz)² per k
   void compute_diffusivities();
   SchemeDev adv[3];
@@ -382,6 +384,8 @@ struct Model : nh_model {
   void field_device_ptr(int field, void** ptr, int64_t* off, int64_t strides[3]) override;
   void set_stream(cudaStream_t s) override { stream = s; solver.stream = s; }
   void substep_launch(int mode, FT dt, FT c1, FT c2);
+  template <typename CT2> void implicit_launch(double stage_dt);
+  void implicit_steps(double stage_dt, bool ab2);
   void update_hydrostatic_pressure();
   DistState<FT> dist;
   void dist_configure(int rank, int nranks, double y0, double y1, int Ny) override;

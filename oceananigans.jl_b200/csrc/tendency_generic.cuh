@@ -212,7 +212,14 @@ __device__ __forceinline__ FT nu_at(const TendParams<FT>& P, int i, int j, int k
 template <typename FT, int a, int b>
 __device__ __forceinline__ FT viscous_Aflux(const TendParams<FT>& P, int i, int j, int k) {
   constexpr int zc = (a != b && (a == 2 || b == 2)) ? 0 : 1;
-  return area_at(P.g, b, zc, k) * (FT(-2) * (nu_at<FT, a, b>(P, i, j, k) * strain<FT, a, b>(P, i, j, k)));
+  FT flux = FT(-2) * (nu_at<FT, a, b>(P, i, j, k) * strain<FT, a, b>(P, i, j, k));
+  if (b == 2 && P.vitd && !(k == 1 || k == P.g.N[2] + 1)) {
+    // VerticallyImplicitTimeDiscretization (abstract_scalar_diffusivity_closure.jl:219-246): off the walls only the part that
+    // the tridiagonal solve does not carry stays explicit: -(ν·∂x w) for u, -(ν·∂y w) for v, nothing for w
+    if (a == 2) flux = FT(0);
+    else flux = -(nu_at<FT, a, b>(P, i, j, k) * deriv<FT, a == 2 ? 0 : a>(P.g, P.U[2], 0, 0, i, j, k));
+  }
+  return area_at(P.g, b, zc, k) * flux;
 }
 
 template <typename FT, int a, int b>
@@ -235,7 +242,9 @@ template <typename FT, int b>
 __device__ __forceinline__ FT diffusive_Aflux(const TendParams<FT>& P, const FT* c, int n, int i, int j, int k) {
   constexpr int zc = b == 2 ? 0 : 1;
   const FT kappa = P.nue ? interp_to_face<FT, b>(P.g, P.kape[n], i, j, k) / P.Pr[n] : P.kappa[n];
-  return area_at(P.g, b, zc, k) * (-kappa * deriv<FT, b>(P.g, c, 0, zc, i, j, k));
+  FT flux = -kappa * deriv<FT, b>(P.g, c, 0, zc, i, j, k);
+  if (b == 2 && P.vitd && !(k == 1 || k == P.g.N[2] + 1)) flux = FT(0);     // diffusive_flux_z is implicit off the walls (:248-252)
+  return area_at(P.g, b, zc, k) * flux;
 }
 
 template <typename FT>

@@ -166,6 +166,7 @@ class NonhydrostaticModel:
             d.has_coriolis, d.coriolis_f = 1, coriolis.f
         if closure is not None and closure.kind == L.CLOSURE_SCALAR:
             d.has_closure, d.nu = L.CLOSURE_SCALAR, closure.nu
+            d.vertically_implicit = int(getattr(closure, "vitd", False))
             for n, name in enumerate(tracers):
                 d.kappa[n] = closure.kappa_for(name)
         elif closure is not None and closure.kind == L.CLOSURE_AMD:

@@ -50,10 +50,11 @@ class SeawaterBuoyancy:
 
 
 class ScalarDiffusivity:
+    """ScalarDiffusivity([time_discretization,] ν, κ): isotropic; vertically_implicit = VerticallyImplicitTimeDiscretization()."""
     kind = "scalar"
 
-    def __init__(self, nu=0.0, kappa=0.0):
-        self.nu, self.kappa = nu, kappa
+    def __init__(self, nu=0.0, kappa=0.0, vertically_implicit=False):
+        self.nu, self.kappa, self.vitd = nu, kappa, bool(vertically_implicit)
 
     def kappa_for(self, name):
         return self.kappa[name] if isinstance(self.kappa, dict) else self.kappa
@@ -128,6 +129,8 @@ class NonhydrostaticModel:
         self.grid = grid
         self.advection = adv
         self.buoyancy, self.coriolis, self.closure = buoyancy, coriolis, closure
+        if getattr(closure, "vitd", False) and grid.topology[2] != Bounded:
+            raise ValueError("VerticallyImplicitTimeDiscretization can only be specified on grids that are Bounded in the z-direction.")
         self.velocities = tuple(Field(grid, VEL_LOC[a], name="uvw"[a]) for a in range(3))
         self.tracers = {n: Field(grid, CCC, name=n) for n in tracers}
         # boundary_conditions = {field name: {"west"|"east"|"south"|"north"|"bottom"|"top": (kind, number)}} —
@@ -289,8 +292,66 @@ def cache_previous_tendencies(model):
         model.Gm[n].at(*R)[...] = model.Gn[n].at(*R)
 
 
+def implicit_step(model, name, f, dt):
+    """implicit_step!(field, solver, closure, …, Δt) — vertically_implicit_diffusion_solver.jl:57-121,231-273 with the Thomas
+    sweep of batched_tridiagonal_solver.jl:209-235 on coefficient functions: (1 - Δt ∂z κ ∂z) ϕⁿ⁺¹ = ϕ★ per column, for the
+    grid's Nz rows over the grid's Nx × Ny columns.  The coefficients are formed in the type of Δt·κ/Δz² — Float64 under RK3
+    (stage_Δt = Δt·(γ + ζ) with the caller's Float64 Δt, runge_kutta_3.jl:157-158), eltype(grid) under AB2 (Δt is converted,
+    quasi_adams_bashforth_2.jl:134) — and the scratch t has eltype(grid) (batched_tridiagonal_solver.jl:69-79)."""
+    cl = model.closure
+    if cl is None or not getattr(cl, "vitd", False):
+        return
+    grid = model.grid
+    FT = grid.FT
+    Nz = grid.N[2]
+    cz = grid.coords[2]
+    CT = np.float64 if isinstance(dt, np.float64) else FT        # coefficient type
+    dt = CT(dt)
+
+    def dzc(k):
+        return CT(cz.dc if cz.regular else cz.dc[k])
+
+    def dzf(k):
+        return CT(cz.df if cz.regular else cz.df[k])
+    w_field = f.loc[2] == "f"
+    kap = CT(FT(cl.nu if name in "uvw" else cl.kappa_for(name)))
+    if not w_field:
+        def upper(k):
+            return CT(0) if k > Nz - 1 else -dt * kap / (dzc(k) * dzf(k + 1))
+
+        def lower(kp):
+            k = kp + 1
+            return CT(0) if kp < 1 else -dt * kap / (dzc(k) * dzf(k))
+    else:
+        def upper(k):
+            return CT(0) if k < 1 else -dt * kap / (dzc(k) * dzf(k))
+
+        def lower(k):
+            kp = k + 2
+            return CT(0) if k < 1 else -dt * kap / (dzc(kp) * dzf(kp - 1))
+
+    def diag(k):
+        return CT(1) - dt * CT(0) - upper(k) - lower(k - 1)
+    phi = f.at((1, grid.N[0]), (1, grid.N[1]), (1, Nz))          # in place: ϕ and the right-hand side are the same array
+    t = np.zeros(phi.shape[:2] + (Nz + 1,), dtype=FT)
+    beta = diag(1)
+    phi[:, :, 0] = (phi[:, :, 0] / beta).astype(FT)
+    for k in range(2, Nz + 1):
+        c_km1, b_k, a_km1 = upper(k - 1), diag(k), lower(k - 1)
+        t[:, :, k] = (c_km1 / beta).astype(FT) if np.ndim(beta) else FT(c_km1 / beta)
+        beta = b_k - a_km1 * t[:, :, k]
+        fk = phi[:, :, k - 1]
+        new = (fk - a_km1 * phi[:, :, k - 2]) / beta
+        ok = ~(np.abs(beta) < 10 * np.finfo(beta.dtype).eps)
+        phi[:, :, k - 1] = np.where(ok, new, fk).astype(FT)
+    for k in range(Nz - 1, 0, -1):
+        phi[:, :, k - 1] = (phi[:, :, k - 1] - t[:, :, k + 1] * phi[:, :, k]).astype(FT)
+
+
 def rk3_substep(model, dt, gamma, zeta):
     FT = model.grid.FT
+    dtj = _as_dt(model.grid, dt)
+    stage_dt = dtj * gamma if zeta is None else dtj * (gamma + zeta)       # stage_Δt(Δt, γⁿ, ζⁿ), runge_kutta_3.jl:153-154
     dt = FT(dt)
     for n, f in zip(model.prognostic_names(), model.prognostic_fields()):
         R = tendency_region(model.grid, f.loc)
@@ -300,6 +361,7 @@ def rk3_substep(model, dt, gamma, zeta):
             f.at(*R)[...] += dt * gamma * model.Gn[n].at(*R)
         else:
             f.at(*R)[...] += dt * (gamma * model.Gn[n].at(*R) + zeta * model.Gm[n].at(*R))
+        implicit_step(model, n, f, np.float64(stage_dt))
 
 
 def ab2_step(model, dt, chi):
@@ -315,6 +377,7 @@ def ab2_step(model, dt, chi):
         else:   # `x * false` is a strong zero in Julia: stale NaNs in G⁻ do not propagate
             G = (FT(1.5) + chi) * model.Gn[n].at(*R) - FT(0)
         f.at(*R)[...] += dt * G
+        implicit_step(model, n, f, dt)
 
 
 def time_step(model, dt, euler=False):

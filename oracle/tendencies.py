@@ -298,8 +298,17 @@ def _nu_getter(grid, nu, a, b):
     return lambda RR: interp(grid, inner, hi, "f", RR)
 
 
-def div_viscous_flux(grid, nu, U, a, R):
-    """∂ⱼ_τ_aⱼ (closure_kernel_operators.jl:22-41) with viscous_flux = -2·(ν·Σ); ν a number or the eddy-viscosity field."""
+def _wall_mask_z(grid, RR):
+    """(k == 1) | (k == Nz+1) over the flux region RR, broadcastable."""
+    k = np.arange(RR[2][0], RR[2][1] + 1)
+    return ((k == 1) | (k == grid.N[2] + 1)).reshape(1, 1, -1)
+
+
+def div_viscous_flux(grid, nu, U, a, R, vitd=False):
+    """∂ⱼ_τ_aⱼ (closure_kernel_operators.jl:22-41) with viscous_flux = -2·(ν·Σ); ν a number or the eddy-viscosity field.
+    vitd: VerticallyImplicitTimeDiscretization on a vertically Bounded grid (abstract_scalar_diffusivity_closure.jl:219-252):
+    the z-fluxes keep only what is not solved implicitly — -(ν·∂x w), -(ν·∂y w), 0 for u, v, w — except on the two walls
+    k = 1, Nz+1, where they stay explicit."""
     FT = grid.FT
     total = None
     for b in range(3):
@@ -308,7 +317,14 @@ def div_viscous_flux(grid, nu, U, a, R):
         nu_at = _nu_getter(grid, nu, a, b)
 
         def Aq(RR, b=b, floc=floc, nu_at=nu_at):
-            return area(grid, b, floc, RR) * (FT(-2) * (nu_at(RR) * _strain(grid, U, a, b, RR)))
+            explicit = FT(-2) * (nu_at(RR) * _strain(grid, U, a, b, RR))
+            if vitd and b == 2:
+                if a == 2:
+                    rest = FT(0)
+                else:
+                    rest = -(nu_at(RR) * deriv(grid, U[2].at, a, floc, RR))
+                explicit = np.where(_wall_mask_z(grid, RR), explicit, rest)
+            return area(grid, b, floc, RR) * explicit
         if grid.topology[b] == Flat:
             t = FT(0)
         else:
@@ -317,7 +333,7 @@ def div_viscous_flux(grid, nu, U, a, R):
     return FT(1) / volume(grid, VEL_LOC[a], R) * total
 
 
-def div_diffusive_flux(grid, kappa, c, R, Pr=None):
+def div_diffusive_flux(grid, kappa, c, R, Pr=None, vitd=False):
     """∇_dot_qᶜ (closure_kernel_operators.jl:43-48) with diffusive_flux = -κ·∂c; κ a number, or (Pr given) the field νₑ:
     κ at the face = ℑ_b(νₑ) / Pr (Smagorinskys/smagorinsky.jl:135-137)."""
     FT = grid.FT
@@ -331,7 +347,10 @@ def div_diffusive_flux(grid, kappa, c, R, Pr=None):
             k_at = lambda RR, b=b: interp(grid, kappa.at, b, "f", RR) / FT(Pr)
 
         def Aq(RR, b=b, floc=floc, k_at=k_at):
-            return area(grid, b, floc, RR) * (-k_at(RR) * deriv(grid, c.at, b, floc, RR))
+            flux = -k_at(RR) * deriv(grid, c.at, b, floc, RR)
+            if vitd and b == 2:          # diffusive_flux_z: explicit on the walls only
+                flux = np.where(_wall_mask_z(grid, RR), flux, FT(0))
+            return area(grid, b, floc, RR) * flux
         if grid.topology[b] == Flat:
             t = FT(0)
         else:
@@ -366,7 +385,7 @@ def momentum_tendency(model, a):
             G = G - FT(0)
     if model.closure is not None:
         nu = model.nu_e if model.closure.kind != "scalar" else model.closure.nu
-        G = G - div_viscous_flux(grid, nu, U, a, R)
+        G = G - div_viscous_flux(grid, nu, U, a, R, vitd=getattr(model.closure, "vitd", False))
     else:
         G = G - FT(0)
     return R, G
@@ -381,7 +400,7 @@ def tracer_tendency(model, name):
         kfield = model.kappa_e[name] if model.closure.kind == "amd" else model.nu_e
         G = G - div_diffusive_flux(grid, kfield, c, R, Pr=model.closure.Pr_for(name))
     elif model.closure is not None:
-        G = G - div_diffusive_flux(grid, model.closure.kappa_for(name), c, R)
+        G = G - div_diffusive_flux(grid, model.closure.kappa_for(name), c, R, vitd=getattr(model.closure, "vitd", False))
     else:
         G = G - FT(0)
     return R, G

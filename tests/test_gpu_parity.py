@@ -102,6 +102,8 @@ BCS_BOX = {"b": {"west": ("value", 1.0), "east": ("gradient", -0.5), "south": ("
 BCS_STRETCHED = {"c": {"bottom": ("value", 2.0), "top": ("gradient", -1.0)}, "u": {"bottom": ("value", 0.0), "top": ("flux", 1e-3)},
                  "v": {"top": ("value", 0.2), "bottom": ("flux", -1e-3)}}
 
+BCS_STRETCHED_B = {("b" if k == "c" else k): v for k, v in BCS_STRETCHED.items()}
+
 CONFIGS = [
     # size, topo, z, advection, kwargs
     ((12, 10, 9), (P, P, P), None, ("WENO", 5), {}),
@@ -134,6 +136,11 @@ CONFIGS = [
     ((9, 8, 10), (B, B, B), None, ("Centered", 2), dict(tracers=("c",), closure=("amd", 1 / 12, None, None))),
     ((12, 10, 9), (P, P, P), None, ("WENO", 5), dict(closure=("amd", 1 / 12, None, None))),
     ((16, 12), (P, F, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=("amd", 1 / 12, None, None))),
+    # ScalarDiffusivity(VerticallyImplicitTimeDiscretization(), ν, κ): explicit tendencies keep the wall fluxes and -(ν ∂x,y w)
+    ((12, 10, 9), (P, P, B), None, ("WENO", 5), dict(buoyancy="seawater", tracers=("T", "S"), coriolis=1e-2, closure=(1e-2, 2e-2, True), bcs=BCS_LES)),
+    ((9, 8, 10), (B, B, B), None, ("Centered", 2), dict(tracers=("b",), closure=(1e-2, 1e-2, True), bcs=BCS_BOX)),
+    ((10, 9, 8), (P, P, B), "stretched", ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=(1e-3, 2e-3, True), bcs=BCS_STRETCHED_B)),
+    ((16, 12), (P, F, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=(1e-2, 1e-2, True))),
 ]
 
 
@@ -324,6 +331,63 @@ def test_100_steps_smagorinsky_lilly_les(oc, FT, tol, timestepper):
     ics = smooth_ics(m2, np.random.default_rng(5), amp=0.5)
     err, floor = _run_steps(oc, m1, m2, ics, 1e-2, 100, m3)
     check_parity(err, tol, floor)
+
+
+@pytest.mark.parametrize("zkind", [None, "stretched"])
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+def test_100_steps_vertically_implicit_diffusion(oc, FT, tol, timestepper, zkind):
+    """ScalarDiffusivity(VerticallyImplicitTimeDiscretization(), ν, κ) with the ocean-LES wall set on (P,P,B) at a vertical
+    diffusion number ν·Δt/Δz² = 2.56 (unstable if explicit; horizontal 0.04) — 100 steps against the oracle (implicit_step!
+    after every substep, vertically_implicit_diffusion_solver.jl:231-273).  The walls carry Flux and Gradient conditions only:
+    the reference keeps the wall fluxes explicit, so a Value wall is bound by the explicit limit."""
+    bcs = {"u": {"top": ("flux", -1e-4)}, "v": {"bottom": ("gradient", 0.1)},
+           "T": {"top": ("flux", 1e-3), "bottom": ("gradient", 0.01)}, "S": {"top": ("flux", -2e-4)}}
+    kw = dict(buoyancy="seawater", tracers=("T", "S"), coriolis=1e-4, closure=(1.0, {"T": 1.0, "S": 0.5}, True),
+              timestepper=timestepper, bcs=bcs)
+    size = (16, 16, 16)
+    if zkind:
+        kw.update(z=_z(zkind, size), x=(0, 4), y=(0, 4))
+    else:
+        kw.update(extent=(4, 4, 0.5))
+    m1, m2 = make_pair(oc, FT, size, (P, P, B), **kw)
+    _, m3 = make_pair(oc, FT, size, (P, P, B), **kw)
+    ics = smooth_ics(m2, np.random.default_rng(17), amp=0.5)
+    err, floor = _run_steps(oc, m1, m2, ics, 2.5e-3, 100, m3)
+    check_parity(err, tol, floor)
+
+
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+def test_vertically_implicit_substep_bit_exact(oc, FT, timestepper):
+    """One substep + implicit_step! of every field (no FFT in between): bit-exact against the oracle, F64 and F32 (the F32 RK3
+    coefficients are formed in Float64 from the caller's Float64 Δt, the AB2 ones in Float32)."""
+    from oracle.model import rk3_substep, ab2_step
+    kw = dict(extent=(1, 1, 1), tracers=("b",), closure=(1.0, 0.5, True), timestepper=timestepper, bcs=BCS_BOX)
+    m1, m2 = make_pair(oc, FT, (9, 8, 10), (B, B, B), **kw)
+    ics = random_ics(m2, np.random.default_rng(3))
+    for n, f1, f2 in names_fields(m1, m2):
+        f1.set(ics[n])
+        f2.set(ics[n])
+    oc.update_state(m1, compute_tendencies=True)
+    o_update_state(m2, compute_tendencies=True)
+    if timestepper == "RungeKutta3":
+        c = m2.rk3
+        oc.rk3_substep(m1, 0.013, c["g1"], None)
+        rk3_substep(m2, 0.013, c["g1"], None)
+        oc.rk3_substep(m1, 0.013, c["g2"], c["z2"])
+        rk3_substep(m2, 0.013, c["g2"], c["z2"])
+    else:
+        oc.ab2_step(m1, 0.013, 0.1)
+        ab2_step(m2, 0.013, 0.1)
+    for n, f1, f2 in names_fields(m1, m2):
+        np.testing.assert_array_equal(f1.interior(), f2.interior, err_msg=n)
+
+
+def test_vertically_implicit_needs_bounded_z(oc):
+    g = oc.RectilinearGrid(np.float64, size=(8, 8, 8), extent=(1, 1, 1), topology=(P, P, P))
+    with pytest.raises(Exception, match="Bounded in the z-direction"):
+        oc.NonhydrostaticModel(g, closure=oc.ScalarDiffusivity(1e-2, 1e-2, vertically_implicit=True))
 
 
 @pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])

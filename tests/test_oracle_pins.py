@@ -416,13 +416,16 @@ def _field(m, name):
     return dict(zip(m.prognostic_names(), m.prognostic_fields()))[name]
 
 
+@pytest.mark.parametrize("vitd", [False, True], ids=["explicit", "vertically-implicit"])
 @pytest.mark.parametrize("timestepper", ["QuasiAdamsBashforth2", "RungeKutta3"])
 @pytest.mark.parametrize("name", ["u", "v", "c"])
-def test_diffusion_simple(name, timestepper):
-    """test_diffusion_simple: a constant field stays constant under ν = κ = 1 diffusion, 10 steps of Δt = 1 on (1, 1, 16)."""
+def test_diffusion_simple(name, timestepper, vitd):
+    """test_diffusion_simple: a constant field stays constant under ν = κ = 1 diffusion, 10 steps of Δt = 1 on (1, 1, 16),
+    for ExplicitTimeDiscretization and VerticallyImplicitTimeDiscretization (test_dynamics.jl:404-414)."""
     from oracle.model import update_state
     g = o.RectilinearGrid(np.float64, size=(1, 1, 16), extent=(1, 1, 1), topology=(P, P, B))
-    m = o.NonhydrostaticModel(g, timestepper=timestepper, closure=o.ScalarDiffusivity(1, 1), tracers=("c",))
+    m = o.NonhydrostaticModel(g, timestepper=timestepper, closure=o.ScalarDiffusivity(1, 1, vertically_implicit=vitd),
+                              tracers=("c",))
     f = _field(m, name)
     f.interior[...] = np.pi
     update_state(m)
@@ -434,17 +437,25 @@ def test_diffusion_simple(name, timestepper):
 _BUDGET_TOPOS = [(P, P, P), (P, P, B), (P, B, B), (B, B, B)]
 
 
+@pytest.mark.parametrize("vitd", [False, True], ids=["explicit", "vertically-implicit"])
 @pytest.mark.parametrize("timestepper", ["QuasiAdamsBashforth2", "RungeKutta3"])
 @pytest.mark.parametrize("topo", _BUDGET_TOPOS, ids=["".join(t[0] for t in tp) for tp in _BUDGET_TOPOS])
-def test_scalar_diffusivity_budget(topo, timestepper):
+def test_scalar_diffusivity_budget(topo, timestepper, vitd):
     """test_ScalarDiffusivity_budget: the mean of a random field is conserved by isotropic diffusion (c everywhere, a
-    velocity component along each Periodic direction), 10 steps of Δt = 1e-4·Δ²/κ on 4³."""
+    velocity component along each Periodic direction), 10 steps of Δt = 1e-4·Δ²/κ on 4³; the vertically implicit
+    discretization on the vertically Bounded topologies."""
     from oracle.model import update_state
+    if vitd and topo[2] != B:
+        with pytest.raises(ValueError):
+            o.NonhydrostaticModel(o.RectilinearGrid(np.float64, size=(4, 4, 4), extent=(1, 1, 1), topology=topo),
+                                  closure=o.ScalarDiffusivity(1, 1, vertically_implicit=True))
+        return
     rng = np.random.default_rng(0)
     names = ["c"] + [n for n, t in zip("uvw", topo) if t == P]
     for name in names:
         g = o.RectilinearGrid(np.float64, size=(4, 4, 4), extent=(1, 1, 1), topology=topo)
-        m = o.NonhydrostaticModel(g, timestepper=timestepper, closure=o.ScalarDiffusivity(1, 1), tracers=("c",))
+        m = o.NonhydrostaticModel(g, timestepper=timestepper, closure=o.ScalarDiffusivity(1, 1, vertically_implicit=vitd),
+                                  tracers=("c",))
         f = _field(m, name)
         o.set_model(m, **{name: rng.random(f.size)})
         init = f.interior.mean()
@@ -457,13 +468,17 @@ def test_scalar_diffusivity_budget(topo, timestepper):
 
 _COSINE = [((128, 1, 1), (B, P, P), 0, ("v", "w", "c")), ((1, 128, 1), (P, B, P), 1, ("u", "w", "c")),
            ((1, 1, 128), (P, P, B), 2, ("u", "v", "c")), ((128,), (B, F, F), 0, ("v", "w", "c")),
-           ((128,), (F, F, B), 2, ("u", "v", "c"))]
+           ((128,), (F, F, B), 2, ("u", "v", "c")),
+           ((1, 1, 128), (P, P, B), 2, ("u", "v", "c"), True), ((128,), (F, F, B), 2, ("u", "v", "c"), True)]
 
 
-@pytest.mark.parametrize("size,topo,dim,names", _COSINE, ids=["x", "y", "z", "x-flat", "z-flat"])
-def test_diffusion_cosine(size, topo, dim, names):
+@pytest.mark.parametrize("case", _COSINE, ids=["x", "y", "z", "x-flat", "z-flat", "z-implicit", "z-flat-implicit"])
+def test_diffusion_cosine(case):
     """test_diffusion_cosine: cos(2ξ) on ξ ∈ (0, π/2) between no-flux walls decays like exp(-κ m² t), 5 RK3 steps of
-    Δt = 1e-6·Lz²/κ, to atol = rtol = 1e-6 (ScalarDiffusivity(ν = 1, κ = 1), explicit)."""
+    Δt = 1e-6·Lz²/κ, to atol = rtol = 1e-6 (ScalarDiffusivity(ν = 1, κ = 1), explicit or vertically implicit;
+    test_dynamics.jl:495-520)."""
+    size, topo, dim, names = case[:4]
+    vitd = len(case) > 4
     from oracle.model import update_state
     L = np.pi / 2
     kw = {}
@@ -474,7 +489,8 @@ def test_diffusion_cosine(size, topo, dim, names):
             full.append(d)
     for name in names:
         g = o.RectilinearGrid(np.float64, size=size, topology=topo, **kw)
-        m = o.NonhydrostaticModel(g, closure=o.ScalarDiffusivity(1, 1), tracers=("c",), buoyancy=None)
+        m = o.NonhydrostaticModel(g, closure=o.ScalarDiffusivity(1, 1, vertically_implicit=vitd), tracers=("c",),
+                                  buoyancy=None)
         f = _field(m, name)
         xi = (np.arange(128) + 0.5) * L / 128
         shape = [1, 1, 1]

@@ -1,5 +1,5 @@
 """Quick phase timing of one model configuration (development aid):
-   python tools/time_phases.py [N] [steps] [f32] [ppb | les | smag | amd]
+   python tools/time_phases.py [N] [steps] [f32] [ppb | les | smag | amd | c4]
    ppb: (Periodic, Periodic, Bounded) WENO5, no tracers;  les: ppb + buoyancy tracer b + ScalarDiffusivity + FPlane;
    smag / amd: les with SmagorinskyLilly / AnisotropicMinimumDissipation and the ocean-LES wall conditions (wind-stress flux
    on u, no-slip bottom, surface buoyancy flux and bottom buoyancy gradient) — the widened rows of DESIGN.md §7b"""
@@ -15,7 +15,17 @@ FT = np.float32 if "f32" in sys.argv else np.float64
 eddy = "smag" in sys.argv or "amd" in sys.argv
 bounded = "ppb" in sys.argv or "les" in sys.argv or eddy
 topo = (oc.Periodic, oc.Periodic, oc.Bounded if bounded else oc.Periodic)
-g = oc.RectilinearGrid(FT, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=topo)
+if "c4" in sys.argv:
+    # BASELINE.json configs[3]: N × N × N/2, tanh-stretched Bounded z (test_time_stepping.jl:439-445), Fourier-tridiagonal solve
+    Nz = N // 2
+    kk = np.arange(1, Nz + 2)
+    zf = np.tanh(1.3 * (2 * (kk - 1) / Nz - 1)) / np.tanh(1.3)
+    topo = (oc.Periodic, oc.Periodic, oc.Bounded)
+    g = oc.RectilinearGrid(FT, size=(N, N, Nz), x=(0, 2 * np.pi), y=(0, 2 * np.pi), z=zf, topology=topo)
+    bounded = True
+else:
+    Nz = N
+    g = oc.RectilinearGrid(FT, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=topo)
 kw = {}
 if "les" in sys.argv:
     kw = dict(buoyancy=oc.BuoyancyTracer(), tracers=("b",), closure=oc.ScalarDiffusivity(1e-4, 1e-4), coriolis=oc.FPlane(1e-4))
@@ -26,7 +36,7 @@ if eddy:
     kw = dict(buoyancy=oc.BuoyancyTracer(), tracers=("b",), coriolis=oc.FPlane(1e-4), boundary_conditions=bcs,
               closure=oc.SmagorinskyLilly() if "smag" in sys.argv else oc.AnisotropicMinimumDissipation())
 m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), exact_arithmetic="fma" not in sys.argv, **kw)
-ics = smooth_ics(N, 1234)
+ics = smooth_ics(N, 1234, size=(N, N, Nz))
 if bounded:
     ics["w"] = np.concatenate([ics["w"], ics["w"][:, :, :1]], axis=2)
     ics["w"][:, :, 0] = 0
