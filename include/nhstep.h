@@ -127,6 +127,14 @@ int32_t nh_set_state_finalize(nh_model* model, int32_t enforce_incompressibility
 enum { NH_BC_DEFAULT = 0, NH_BC_FLUX = 1, NH_BC_VALUE = 2, NH_BC_GRADIENT = 3 };
 int32_t nh_model_set_boundary_condition(nh_model* model, int32_t field, int32_t dim, int32_t side, int32_t kind, double value);
 
+/* The same with an array condition — Value/Gradient/FluxBoundaryCondition(array), boundary_condition.jl:118
+ * (getbc = condition[i, j] with the wall's two transverse grid indices).  `data` holds N_e1 × N_e2 values of the model's float
+ * type in the reference's (column-major) order: the lower transverse direction runs fastest, N_e the GRID size of that
+ * direction (the fill and flux kernels run over `:yz` / `:xz` / `:xy`, fill_halo_regions.jl:354-363).  The values are copied
+ * (a later change of the caller's array needs another call).  `where` = NH_HOST or NH_DEVICE. */
+int32_t nh_model_set_boundary_condition_array(nh_model* model, int32_t field, int32_t dim, int32_t side, int32_t kind,
+                                              const void* data, int64_t count, int32_t where);
+
 /* fill_halo_regions!(fields…; fill_boundary_normal_velocities) — src/Fields/field_tuples.jl:56-119,
  * src/BoundaryConditions/fill_halo_regions.jl:50-82.  field_mask bit f = field id f (ids < 32). */
 int32_t nh_fill_halo_regions(nh_model* model, uint32_t field_mask, int32_t fill_boundary_normal_velocities);

@@ -18,6 +18,7 @@ struct HaloJob {
   int mode[NH_MAXF];      // 0 skip, 1 periodic, 2 wall (per-side kind below), 3 open (wall-normal velocity := 0)
   int side_kind[NH_MAXF][2];   // mode 2: NH_BC_DEFAULT / NH_BC_FLUX (mirror), NH_BC_VALUE, NH_BC_GRADIENT at the left / right wall
   FT side_val[NH_MAXF][2];
+  const FT* side_arr[NH_MAXF][2];   // array condition (N_e1 × N_e2 over the transverse grid range, e1 fastest) or nullptr
   int nf;
   int d;                  // direction being filled
   int lo[3], hi[3];       // transverse logical index range (inclusive); entry d unused
@@ -53,7 +54,8 @@ __global__ void halo_fill_kernel(const __grid_constant__ HaloJob<FT> J) {
       const FT cI = at(iI);
       if (kind != NH_BC_VALUE && kind != NH_BC_GRADIENT) { at(iH) = cI; continue; }
       const FT D = d == 0 ? g.dx : d == 1 ? g.dy : g.Dzf(iB);
-      const FT v = J.side_val[f][side];
+      const FT* arr = J.side_arr[f][side];
+      const FT v = arr ? arr[(a1 - 1) + (long long)(a2 - 1) * g.N[e1]] : J.side_val[f][side];
       FT grad;
       if (kind == NH_BC_GRADIENT) grad = v;
       else grad = side ? (v - cI) / (D / FT(2)) : (cI - v) / (D / FT(2));
@@ -76,6 +78,7 @@ struct FluxBcJob {
   int zloc_face;          // the field sits at Faces in z (w): Δz of its volume / transverse areas is Δzᶠ
   int has[2];
   FT q[2];
+  const FT* qarr[2];      // array condition or nullptr
 };
 
 template <typename FT>
@@ -101,7 +104,8 @@ __global__ void flux_bc_kernel(const __grid_constant__ FluxBcJob<FT> J) {
     else A = g.dx * g.dy;                   // Az = Δx·Δy
     const FT V = (g.dx * g.dy) * dzl;       // V = Az·Δz
     FT& G = J.G[g.idx(c[0], c[1], c[2])];
-    const FT inc = J.q[side] * A / V;
+    const FT q = J.qarr[side] ? J.qarr[side][t] : J.q[side];
+    const FT inc = q * A / V;
     if (side == 0) G += inc; else G -= inc;
   }
 }

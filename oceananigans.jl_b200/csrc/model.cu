@@ -265,9 +265,24 @@ void Model<FT>::set_boundary_condition(int field, int dim, int side, int kind, d
   NH_REQUIRE(field_face_dim(field) != dim, "a wall-normal velocity component keeps the impenetrable (Open) condition");
   bc_kind[field][dim][side] = kind;
   bc_val[field][dim][side] = kind == NH_BC_DEFAULT ? FT(0) : (FT)value;
+  bc_arr[field][dim][side].alloc(0);
   has_flux_bcs = false;
   for (int f = 0; f < nf; ++f) for (int d = 0; d < 3; ++d) for (int s2 = 0; s2 < 2; ++s2)
     if (bc_kind[f][d][s2] == NH_BC_FLUX) has_flux_bcs = true;
+}
+
+template <typename FT>
+void Model<FT>::set_boundary_condition_array(int field, int dim, int side, int kind, const void* data, long long count, int where) {
+  NH_REQUIRE(kind >= NH_BC_FLUX && kind <= NH_BC_GRADIENT, "an array condition is a Flux, Value or Gradient condition");
+  NH_REQUIRE(data != nullptr, "null boundary condition array");
+  NH_REQUIRE(where == NH_HOST || where == NH_DEVICE, "bad `where`");
+  set_boundary_condition(field, dim, side, kind, 0.0);
+  const int e1 = dim == 0 ? 1 : 0, e2 = dim == 2 ? 1 : 2;
+  NH_REQUIRE(count == (long long)gh.g.N[e1] * gh.g.N[e2], "boundary condition array: count must be the wall's transverse grid size");
+  DevBuf<FT>& b = bc_arr[field][dim][side];
+  b.alloc((size_t)count, false);
+  CUDA_CHECK(cudaMemcpyAsync(b.p, data, count * sizeof(FT), where == NH_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, stream));
+  CUDA_CHECK(cudaStreamSynchronize(stream));
 }
 
 // fill_halo_regions! — open fill, then the three directions sorted so that Periodic runs after the others
@@ -320,6 +335,7 @@ void Model<FT>::fill_halo_regions(uint32_t mask, int fill_normal) {
           const bool prog = id >= 0 && id < nf;
           J.side_kind[J.nf][side] = prog ? bc_kind[id][d][side] : NH_BC_DEFAULT;
           J.side_val[J.nf][side] = prog ? bc_val[id][d][side] : FT(0);
+          J.side_arr[J.nf][side] = prog ? bc_arr[id][d][side].p : nullptr;
         }
         J.nf++;
       }
@@ -408,7 +424,7 @@ void Model<FT>::compute_tendencies() {
     for (int d = 0; d < 3; ++d) for (int f = 0; f < nf; ++f) {
       if (bc_kind[f][d][0] != NH_BC_FLUX && bc_kind[f][d][1] != NH_BC_FLUX) continue;
       FluxBcJob<FT> J; J.g = gh.g; J.G = Gn[f]; J.d = d; J.zloc_face = f == 2;
-      for (int side = 0; side < 2; ++side) { J.has[side] = bc_kind[f][d][side] == NH_BC_FLUX; J.q[side] = bc_val[f][d][side]; }
+      for (int side = 0; side < 2; ++side) { J.has[side] = bc_kind[f][d][side] == NH_BC_FLUX; J.q[side] = bc_val[f][d][side]; J.qarr[side] = bc_arr[f][d][side].p; }
       const int e1 = d == 0 ? 1 : 0, e2 = d == 2 ? 1 : 2;
       long long n = (long long)gh.g.N[e1] * gh.g.N[e2];
       flux_bc_kernel<FT><<<ceil_div(n, 128), 128, 0, stream>>>(J);

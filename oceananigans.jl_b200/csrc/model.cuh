@@ -276,6 +276,7 @@ struct nh_model {
   virtual void get_field(int field, int region, void* data, int64_t count, int where) = 0;
   virtual void fill_halo_regions(uint32_t mask, int fill_normal) = 0;
   virtual void set_boundary_condition(int field, int dim, int side, int kind, double value) = 0;
+  virtual void set_boundary_condition_array(int field, int dim, int side, int kind, const void* data, long long count, int where) = 0;
   virtual void update_state(int compute_tendencies) = 0;
   virtual void compute_tendencies() = 0;
   virtual void rk3_substep(double dt, double gamma, double zeta, int has_zeta) = 0;
@@ -368,8 +369,10 @@ struct Model : nh_model {
   void get_field(int field, int region, void* data, int64_t count, int where) override;
   void fill_halo_regions(uint32_t mask, int fill_normal) override;
   void set_boundary_condition(int field, int dim, int side, int kind, double value) override;
+  void set_boundary_condition_array(int field, int dim, int side, int kind, const void* data, long long count, int where) override;
   int bc_kind[NH_MAXF][3][2] = {};   // NH_BC_* of each prognostic field's walls (constant conditions)
   FT bc_val[NH_MAXF][3][2] = {};
+  DevBuf<FT> bc_arr[NH_MAXF][3][2];  // array conditions (empty: the number above)
   bool has_flux_bcs = false;
   void update_state(int compute_tendencies) override;
   void compute_tendencies() override;

@@ -82,11 +82,13 @@ class _Namespace(dict):
 
 
 class BoundaryCondition:
-    """BoundaryCondition(classification, number) — src/BoundaryConditions/boundary_condition.jl:17-60 with a number
-    condition (converted to eltype(grid), field_boundary_conditions.jl:199-201)."""
+    """BoundaryCondition(classification, condition) — src/BoundaryConditions/boundary_condition.jl:17-60,117-118 with a
+    number (converted to eltype(grid), field_boundary_conditions.jl:199-201) or a 2-D array indexed by the wall's two
+    transverse grid indices, shape (N_e1, N_e2)."""
 
     def __init__(self, kind, condition):
-        self.kind, self.condition = kind, float(condition)
+        self.kind = kind
+        self.condition = float(condition) if np.ndim(condition) == 0 else np.array(condition)
 
 
 def ValueBoundaryCondition(val):
@@ -190,7 +192,19 @@ class NonhydrostaticModel:
                 raise ValueError(f"boundary_conditions: {name} is not a prognostic field of this model")
             for side, bc in fbcs.sides.items():
                 dim, s_ = _SIDES[side]
-                check(lib().nh_model_set_boundary_condition(self._h, names_.index(name), dim, s_, bc.kind, bc.condition))
+                if np.ndim(bc.condition) == 0:
+                    check(lib().nh_model_set_boundary_condition(self._h, names_.index(name), dim, s_, bc.kind,
+                                                                float(bc.condition)))
+                    continue
+                # array condition: condition[i, j] over the wall's transverse grid range, handed over column-major
+                e1, e2 = [e for e in range(3) if e != dim]
+                want = (grid.N[e1], grid.N[e2])
+                a = np.asarray(bc.condition, dtype=grid.FT)
+                if a.shape != want:
+                    raise ValueError(f"boundary_conditions: the {side} condition of {name} must have shape {want}, got {a.shape}")
+                a = np.asfortranarray(a)
+                check(lib().nh_model_set_boundary_condition_array(self._h, names_.index(name), dim, s_, bc.kind,
+                                                                  a.ctypes.data_as(C.c_void_p), a.size, L.HOST))
         gi = L.GridDesc()
         check(lib().nh_model_grid_info(self._h, C.byref(gi)))
         self.halo = tuple(gi.H)

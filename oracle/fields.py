@@ -41,7 +41,7 @@ class Field:
         self.H = grid.H
         self.data = np.zeros(tuple(self.size[d] + 2 * self.H[d] for d in range(3)), dtype=grid.FT)
         self.bcs = default_bcs(grid, self.loc, prognostic)
-        # non-default conditions with a constant: side_bcs[d][side] = None | ("value" | "gradient" | "flux", number)
+        # non-default conditions: side_bcs[d][side] = None | ("value" | "gradient" | "flux", number or wall array)
         self.side_bcs = [[None, None], [None, None], [None, None]]
 
     # 1-based inclusive ranges → parent view
@@ -75,7 +75,15 @@ class Field:
             raise ValueError(f"{kind} boundary condition needs a Bounded direction in which '{self.name}' sits at Centers")
         if kind not in ("value", "gradient", "flux"):
             raise ValueError(kind)
-        self.side_bcs[d][side] = (kind, self.grid.FT(value))
+        if np.ndim(value) == 0:
+            self.side_bcs[d][side] = (kind, self.grid.FT(value))
+            return
+        # array condition (boundary_condition.jl:118): condition[i, j] over the wall's transverse grid range
+        want = tuple(self.grid.N[e] for e in range(3) if e != d)
+        a = np.asarray(value, dtype=self.grid.FT)
+        if a.shape != want:
+            raise ValueError(f"the array condition must have shape {want}, got {a.shape}")
+        self.side_bcs[d][side] = (kind, np.expand_dims(a, d).copy())
 
 
 # ---------------------------------------------------------------------------------------------

@@ -102,6 +102,28 @@ BCS_BOX = {"b": {"west": ("value", 1.0), "east": ("gradient", -0.5), "south": ("
 BCS_STRETCHED = {"c": {"bottom": ("value", 2.0), "top": ("gradient", -1.0)}, "u": {"bottom": ("value", 0.0), "top": ("flux", 1e-3)},
                  "v": {"top": ("value", 0.2), "bottom": ("flux", -1e-3)}}
 
+def _array_bcs(size, which):
+    """Wall arrays of shape (N_e1, N_e2), seeded per wall."""
+    rng = np.random.default_rng(2024)
+    Nx, Ny, Nz = size
+
+    def A(shape, lo=-0.5, hi=0.5):
+        return rng.uniform(lo, hi, shape)
+    if which == "z":
+        return {"c": {"bottom": ("value", A((Nx, Ny))), "top": ("gradient", A((Nx, Ny)))},
+                "u": {"bottom": ("value", A((Nx, Ny))), "top": ("flux", A((Nx, Ny), -1e-3, 1e-3))},
+                "v": {"top": ("value", A((Nx, Ny))), "bottom": ("flux", A((Nx, Ny), -1e-3, 1e-3))}}
+    if which == "les":
+        return {"u": {"top": ("flux", A((Nx, Ny), -1e-4, 1e-4)), "bottom": ("value", 0.0)}, "v": {"bottom": ("value", A((Nx, Ny)))},
+                "T": {"top": ("flux", A((Nx, Ny), 0, 1e-3)), "bottom": ("gradient", A((Nx, Ny), 0, 0.02))},
+                "S": {"top": ("flux", -2e-4)}}
+    return {"b": {"west": ("value", A((Ny, Nz))), "east": ("gradient", A((Ny, Nz))), "south": ("flux", A((Nx, Nz))),
+                  "north": ("value", A((Nx, Nz))), "bottom": ("gradient", A((Nx, Ny))), "top": ("flux", A((Nx, Ny)))},
+            "u": {"south": ("value", A((Nx, Nz))), "north": ("flux", A((Nx, Nz))), "top": ("gradient", A((Nx, Ny)))},
+            "v": {"west": ("value", A((Ny, Nz))), "bottom": ("flux", A((Nx, Ny)))},
+            "w": {"west": ("flux", A((Ny, Nz))), "east": ("value", A((Ny, Nz))), "north": ("gradient", A((Nx, Nz)))}}
+
+
 BCS_STRETCHED_B = {("b" if k == "c" else k): v for k, v in BCS_STRETCHED.items()}
 
 CONFIGS = [
@@ -141,6 +163,10 @@ CONFIGS = [
     ((9, 8, 10), (B, B, B), None, ("Centered", 2), dict(tracers=("b",), closure=(1e-2, 1e-2, True), bcs=BCS_BOX)),
     ((10, 9, 8), (P, P, B), "stretched", ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=(1e-3, 2e-3, True), bcs=BCS_STRETCHED_B)),
     ((16, 12), (P, F, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=(1e-2, 1e-2, True))),
+    # array-valued conditions (condition[i, j] over the wall's transverse grid range) on every wall pair
+    ((9, 8, 10), (B, B, B), None, ("WENO", 5), dict(buoyancy="tracer", tracers=("b",), closure=(1e-2, 1e-2), bcs=_array_bcs((9, 8, 10), "box"))),
+    ((10, 9, 8), (P, P, B), "stretched", ("Centered", 2), dict(tracers=("c",), closure=(1e-3, 1e-3), bcs=_array_bcs((10, 9, 8), "z"))),
+    ((12, 10, 9), (P, P, B), None, ("WENO", 5), dict(buoyancy="seawater", tracers=("T", "S"), closure=("lilly", 0.16, 1.0, 1.0), bcs=_array_bcs((12, 10, 9), "les"))),
 ]
 
 
@@ -382,6 +408,27 @@ def test_vertically_implicit_substep_bit_exact(oc, FT, timestepper):
         ab2_step(m2, 0.013, 0.1)
     for n, f1, f2 in names_fields(m1, m2):
         np.testing.assert_array_equal(f1.interior(), f2.interior, err_msg=n)
+
+
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+def test_100_steps_with_array_boundary_conditions(oc, FT, tol, timestepper):
+    """The ocean-LES wall set with array conditions (a wind-stress pattern, a cooling pattern, a bottom-gradient map;
+    boundary_condition.jl:118) on (P,P,B) — 100 steps against the oracle."""
+    kw = dict(extent=(1, 1, 1), buoyancy="seawater", tracers=("T", "S"), coriolis=1e-4, closure=(1e-3, 1e-3),
+              timestepper=timestepper, bcs=_array_bcs((16, 16, 16), "les"))
+    m1, m2 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
+    _, m3 = make_pair(oc, FT, (16, 16, 16), (P, P, B), **kw)
+    ics = smooth_ics(m2, np.random.default_rng(77), amp=0.5)
+    err, floor = _run_steps(oc, m1, m2, ics, 1e-2, 100, m3)
+    check_parity(err, tol, floor)
+
+
+def test_array_boundary_condition_errors(oc):
+    g = oc.RectilinearGrid(np.float64, size=(8, 6, 4), extent=(1, 1, 1), topology=(P, P, B))
+    with pytest.raises(ValueError, match="shape"):
+        oc.NonhydrostaticModel(g, tracers=("c",), boundary_conditions={
+            "c": oc.FieldBoundaryConditions(top=oc.FluxBoundaryCondition(np.zeros((6, 8))))})
 
 
 def test_vertically_implicit_needs_bounded_z(oc):

@@ -279,6 +279,61 @@ def test_nonhydrostatic_flux_budget(topo, name, side):
 
 
 @pytest.mark.parametrize("kind", ["value", "gradient", "flux"])
+@pytest.mark.parametrize("side", ["east", "south", "top"])
+def test_array_boundary_condition_time_steps(kind, side):
+    """test_boundary_condition(..., array_bc) of test_boundary_conditions_integration.jl:10-28,355-358: a 1×1 array condition
+    on T of a (1, 1, 1) Bounded box steps (Δt = 1e-16) without error; utils_for_runtests.jl:218."""
+    g = o.RectilinearGrid(np.float64, size=(1, 1, 1), extent=(1, np.pi, 42), topology=(B, B, B))
+    arr = np.random.default_rng(0).random((1, 1))
+    m = o.NonhydrostaticModel(g, tracers=("T", "S"), buoyancy=o.SeawaterBuoyancy(), boundary_conditions={"T": {side: (kind, arr)}})
+    o.time_step(m, 1e-16)
+    assert np.all(np.isfinite(m.tracers["T"].interior))
+
+
+def _wall_G(kind, cb, ct):
+    from oracle.model import update_state
+    g = o.RectilinearGrid(np.float64, size=(4, 3, 5), extent=(1, 1, 2), topology=(P, P, B))
+    m = o.NonhydrostaticModel(g, tracers=("c",), closure=o.ScalarDiffusivity(1e-2, 1e-2),
+                              boundary_conditions={"c": {"bottom": (kind, cb), "top": (kind, ct)}})
+    m.tracers["c"].set(np.broadcast_to(np.linspace(0.1, 0.9, 5), (4, 3, 5)).copy())
+    update_state(m)
+    return m.Gn["c"].interior.copy()
+
+
+@pytest.mark.parametrize("kind", ["value", "gradient", "flux"])
+def test_array_boundary_condition_is_the_number_condition_pointwise(kind):
+    """getbc(bc::BC{<:AbstractArray}, i, j) = condition[i, j] (boundary_condition.jl:118): a wall array acts at each wall
+    point like the number it holds there — a constant array reproduces the number condition bit for bit and a two-valued
+    array reproduces, column by column, the tendencies of the two number-condition models (horizontally uniform state)."""
+    lo = np.full((4, 3), 0.7); lo[2:, :] = -0.2
+    hi = np.full((4, 3), -0.3); hi[2:, :] = 0.5
+    G1, G2 = _wall_G(kind, 0.7, -0.3), _wall_G(kind, -0.2, 0.5)
+    np.testing.assert_array_equal(_wall_G(kind, np.full((4, 3), 0.7), np.full((4, 3), -0.3)), G1)
+    Gm = _wall_G(kind, lo, hi)
+    np.testing.assert_array_equal(Gm[:2], G1[:2])
+    np.testing.assert_array_equal(Gm[2:], G2[2:])
+    assert not np.array_equal(G1, G2)
+
+
+def test_array_flux_budget():
+    """The budget of test_nonhydrostatic_flux_budget with a non-uniform wall array: the mean rises by mean(flux)·t/L and
+    each bottom cell by its own flux·t/Δz."""
+    FT = np.float64
+    q = np.random.default_rng(1).uniform(0.5, 1.5, (4, 3))
+    g = o.RectilinearGrid(FT, size=(4, 3, 2), x=(0, 0.3), y=(0, 0.4), z=(0, 0.5), topology=(P, P, B))
+    m = o.NonhydrostaticModel(g, tracers=("c",), boundary_conditions={"c": {"bottom": ("flux", q)}})
+    o.time_step(m, 1.0)
+    assert np.isclose(m.tracers["c"].interior.mean(), q.mean() * m.clock.time / 0.5, rtol=1e-7, atol=0)
+    np.testing.assert_allclose(m.tracers["c"].interior[:, :, 0], q * m.clock.time / 0.25, rtol=1e-12)
+
+
+def test_array_boundary_condition_shape_is_checked():
+    g = o.RectilinearGrid(np.float64, size=(4, 3, 2), extent=(1, 1, 1), topology=(P, P, B))
+    with pytest.raises(ValueError, match="shape"):
+        o.NonhydrostaticModel(g, tracers=("c",), boundary_conditions={"c": {"top": ("flux", np.zeros((3, 4)))}})
+
+
+@pytest.mark.parametrize("kind", ["value", "gradient", "flux"])
 def test_value_gradient_halo_definitions(kind):
     """fill_halo_regions_value_gradient.jl:10-15: the wall value is the mean of halo and first interior cell; the wall
     gradient is their difference over Δ; Flux leaves the no-flux mirror (the flux enters the tendency instead)."""
