@@ -114,22 +114,24 @@ __global__ void flux_bc_kernel(const __grid_constant__ FluxBcJob<FT> J) {
 // implicit_step!(field, …, Δt) — vertically_implicit_diffusion_solver.jl:57-121,231-273: (1 - Δt ∂z κ ∂z) ϕⁿ⁺¹ = ϕ★ per
 // column with the Thomas sweep of batched_tridiagonal_solver.jl:209-235 (coefficient functions, |β| < 10·eps guard,
 // scratch t in the field's type).  CT is the type the reference forms the coefficients in: Float64 under RK3 (stage Δt
-// is the caller's Float64 Δt times γ + ζ), the field's type under AB2 (Δt converted).  One thread per column of 1:Nx × 1:Ny.
+// is the caller's Float64 Δt times γ + ζ), the field's type under AB2 (Δt converted).
+// With a constant κ on a horizontally regular grid the coefficient recurrence (a, β, t per level) is the same in every
+// column, so it is evaluated once per (Δt, κ, location) by implicit_coeff_kernel — the same expressions in the same order
+// as the reference evaluates per column — into a table of 4 × (Nz + 2) doubles (a Float32 value is held exactly), and
+// implicit_step_kernel streams the columns: one thread per column, 8 levels of loads in flight, ϕ read and written twice.
 template <typename FT, typename CT>
-struct ImplicitJob {
+struct ImplicitCoeffJob {
   GridDev<FT> g;
-  FT* phi;
-  FT* t;                  // scratch, same layout as a field
+  double* tab;            // [0] a_k = lower(k-1), [1] β_k, [2] t_k, [3] 1 if |β_k| ≥ 10 eps — each Nz + 2 long, indexed by k
   CT dt, kappa;
   int w_field;            // the field sits at Faces in z (w)
 };
 
 template <typename FT, typename CT>
-__global__ void __launch_bounds__(128) implicit_step_kernel(const __grid_constant__ ImplicitJob<FT, CT> J) {
+__global__ void implicit_coeff_kernel(const __grid_constant__ ImplicitCoeffJob<FT, CT> J) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
   const GridDev<FT>& g = J.g;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x + 1, j = blockIdx.y * blockDim.y + threadIdx.y + 1;
-  if (i > g.N[0] || j > g.N[1]) return;
-  const int Nz = g.N[2];
+  const int Nz = g.N[2], L = Nz + 2;
   const CT dt = J.dt, kap = J.kappa;
   auto dzc = [&](int k) { return (CT)g.Dzc(k); };
   auto dzf = [&](int k) { return (CT)g.Dzf(k); };
@@ -142,21 +144,67 @@ __global__ void __launch_bounds__(128) implicit_step_kernel(const __grid_constan
     return k < 1 ? CT(0) : -dt * kap / (dzc(k + 2) * dzf(k + 1));
   };
   auto diag = [&](int k) -> CT { return CT(1) - dt * CT(0) - upper(k) - lower(k - 1); };
-  const long long n1 = g.idx(i, j, 1), sz = g.sz;
+  const CT eps10 = sizeof(CT) == 8 ? CT(10 * 2.220446049250313e-16) : CT(10 * 1.1920929e-7f);
   CT beta = diag(1);
-  J.phi[n1] = (FT)((CT)J.phi[n1] / beta);
+  J.tab[1] = 0.0; J.tab[L + 1] = (double)beta; J.tab[2 * L + 1] = 0.0; J.tab[3 * L + 1] = 1.0;
   for (int k = 2; k <= Nz; ++k) {
-    const long long n = n1 + sz * (k - 1);
     const CT c = upper(k - 1), b = diag(k), a = lower(k - 1);
     const FT tk = (FT)(c / beta);
-    J.t[n] = tk;
     beta = b - a * (CT)tk;
-    const CT eps10 = sizeof(CT) == 8 ? CT(10 * 2.220446049250313e-16) : CT(10 * 1.1920929e-7f);
-    if (!(fabs((double)beta) < (double)eps10)) J.phi[n] = (FT)(((CT)J.phi[n] - a * (CT)J.phi[n - sz]) / beta);
+    J.tab[k] = (double)a; J.tab[L + k] = (double)beta; J.tab[2 * L + k] = (double)tk;
+    J.tab[3 * L + k] = fabs((double)beta) < (double)eps10 ? 0.0 : 1.0;
   }
-  for (int k = Nz - 1; k >= 1; --k) {
-    const long long n = n1 + sz * (k - 1);
-    J.phi[n] = J.phi[n] - J.t[n + sz] * J.phi[n + sz];
+}
+
+template <typename FT, typename CT>
+struct ImplicitJob {
+  GridDev<FT> g;
+  FT* phi;
+  const double* tab;
+};
+
+template <typename FT, typename CT>
+__global__ void __launch_bounds__(64) implicit_step_kernel(const __grid_constant__ ImplicitJob<FT, CT> J) {
+  const GridDev<FT>& g = J.g;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x + 1, j = blockIdx.y + 1;
+  if (i > g.N[0]) return;
+  constexpr int U = 8;
+  const int Nz = g.N[2], L = Nz + 2;
+  const double* __restrict__ ta = J.tab;
+  const double* __restrict__ tb = J.tab + L;
+  const double* __restrict__ tt = J.tab + 2 * L;
+  const double* __restrict__ tok = J.tab + 3 * L;
+  const long long sz = g.sz;
+  FT* col = J.phi + g.idx(i, j, 1) - sz;                 // col[k·sz] = ϕ[i, j, k]
+  FT prev = (FT)((CT)col[sz] / (CT)__ldg(tb + 1));
+  col[sz] = prev;
+  for (int k0 = 2; k0 <= Nz; k0 += U) {
+    FT v[U];
+#pragma unroll
+    for (int q = 0; q < U; ++q) if (k0 + q <= Nz) v[q] = col[(long long)(k0 + q) * sz];
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int k = k0 + q;
+      if (k <= Nz) {
+        if (__ldg(tok + k) != 0.0) v[q] = (FT)(((CT)v[q] - (CT)__ldg(ta + k) * (CT)prev) / (CT)__ldg(tb + k));
+        prev = v[q];
+        col[(long long)k * sz] = prev;
+      }
+    }
+  }
+  // back-substitution ϕ_k -= t_{k+1} ϕ_{k+1}, k = Nz-1 … 1 (prev = ϕ_Nz)
+  for (int k0 = Nz - 1; k0 >= 1; k0 -= U) {
+    FT v[U];
+#pragma unroll
+    for (int q = 0; q < U; ++q) if (k0 - q >= 1) v[q] = col[(long long)(k0 - q) * sz];
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int k = k0 - q;
+      if (k >= 1) {
+        prev = v[q] - (FT)__ldg(tt + k + 1) * prev;
+        col[(long long)k * sz] = prev;
+      }
+    }
   }
 }
 

@@ -69,7 +69,6 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   // implicit_diffusion_solver (vertically_implicit_diffusion_solver.jl:164-169)
   NH_REQUIRE(!vitd || gh.g.topo[2] == NH_BOUNDED,
              "VerticallyImplicitTimeDiscretization can only be specified on grids that are Bounded in the z-direction");
-  if (vitd) vitd_t.alloc((size_t)gh.volume(), true);
   if (d.has_closure == NH_CLOSURE_AMD) {
     // build_diffusivity_fields (anisotropic_minimum_dissipation.jl:371-385): νₑ and one κₑ per tracer, default conditions
     nue = alloc_field();
@@ -466,13 +465,26 @@ void Model<FT>::substep_launch(int mode, FT dt, FT c1, FT c2) {
 template <typename FT>
 template <typename CT2>
 void Model<FT>::implicit_launch(double stage_dt) {
-  dim3 blk(32, 4, 1);
-  dim3 grd((gh.g.N[0] + blk.x - 1) / blk.x, (gh.g.N[1] + blk.y - 1) / blk.y, 1);
+  const int L = gh.g.N[2] + 2;
+  dim3 blk(64, 1, 1);
+  dim3 grd((gh.g.N[0] + blk.x - 1) / blk.x, gh.g.N[1], 1);
   for (int f = 0; f < nf; ++f) {
+    const CT2 dt = (CT2)stage_dt, kap = (CT2)(f < 3 ? (FT)desc.nu : (FT)desc.kappa[f - 3]);
+    const int w_field = f == 2, ct = (int)sizeof(CT2);
+    // coefficient tables are cached per (Δt, κ, location, coefficient type): with a constant Δt every stage finds its own
+    ImplicitTable* T = nullptr;
+    for (auto& e : vitd_tabs) if (e.dt == (double)dt && e.kappa == (double)kap && e.w_field == w_field && e.ct == ct) T = &e;
+    if (!T) {
+      if (vitd_tabs.size() < 24) { vitd_tabs.emplace_back(); T = &vitd_tabs.back(); T->tab.alloc(4 * (size_t)L); }
+      else { T = &vitd_tabs[vitd_next]; vitd_next = (vitd_next + 1) % vitd_tabs.size(); }
+      T->dt = (double)dt; T->kappa = (double)kap; T->w_field = w_field; T->ct = ct;
+      ImplicitCoeffJob<FT, CT2> C;
+      C.g = gh.g; C.tab = T->tab.p; C.dt = dt; C.kappa = kap; C.w_field = w_field;
+      implicit_coeff_kernel<FT, CT2><<<1, 32, 0, stream>>>(C);
+      KLAUNCH(lc);
+    }
     ImplicitJob<FT, CT2> J;
-    J.g = gh.g; J.phi = F[f]; J.t = vitd_t.p; J.dt = (CT2)stage_dt;
-    J.kappa = (CT2)(f < 3 ? (FT)desc.nu : (FT)desc.kappa[f - 3]);
-    J.w_field = f == 2;
+    J.g = gh.g; J.phi = F[f]; J.tab = T->tab.p;
     implicit_step_kernel<FT, CT2><<<grd, blk, 0, stream>>>(J);
     KLAUNCH(lc);
   }

@@ -6,6 +6,7 @@
 #include "poisson_fast.cuh"
 #include "grid_host.h"
 #include <memory>
+#include <deque>
 #include <cstring>
 #include <cmath>
 
@@ -336,7 +337,9 @@ struct Model : nh_model {
   FT* nue = nullptr;       // νₑ of the Smagorinsky / AMD closures (diffusivity_fields.νₑ)
   FT* kape[NH_MAXTR] = {}; // AMD: κₑ of each tracer (diffusivity_fields.κₑ)
   bool vitd = false;       // ScalarDiffusivity with VerticallyImplicitTimeDiscretization
-  DevBuf<FT> vitd_t;       // scratch of the tridiagonal sweeps, one field
+  struct ImplicitTable { double dt = 0, kappa = 0; int w_field = 0, ct = 0; DevBuf<double> tab; };
+  std::deque<ImplicitTable> vitd_tabs;   // per-level Thomas coefficients, cached per (Δt, κ, location, coefficient type)
+  size_t vitd_next = 0;
   DevBuf<FT> df2;          // Δᶠ² = cbrt(ΔxΔyΔz)² per k
   void compute_diffusivities();
   SchemeDev adv[3];

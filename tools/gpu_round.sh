@@ -15,6 +15,7 @@ timeout 600 ncu --set full --import-source on --clock-control none -k regex:tend
     -f -o gpurun_out/tendency python tools/profile_tendency.py > gpurun_out/ncu_full.log 2>&1
 timeout 600 ncu --set full --import-source on --clock-control none -k 'regex:tendency_fast|pf_|pressure_correct_halo' \
     --launch-skip 28 -c 7 -f -o gpurun_out/step256 python tools/profile_step.py > gpurun_out/ncu_step.log 2>&1
-for cfg in ppb les smag amd; do echo "$cfg: $(python tools/time_phases.py 256 5 $cfg 2>&1 | tail -1)"; done > gpurun_out/les_times.txt
+for cfg in ppb les "les vitd" smag amd; do echo "$cfg: $(python tools/time_phases.py 256 5 $cfg 2>&1 | tail -1)"; done > gpurun_out/les_times.txt
+echo "c4 512x512x256 stretched: $(python tools/time_phases.py 512 3 c4 2>&1 | tail -1)" >> gpurun_out/les_times.txt
 python tools/time_solvers.py > gpurun_out/solver_times.txt 2>&1
 nproc > gpurun_out/nproc.txt; lscpu | head -20 >> gpurun_out/nproc.txt

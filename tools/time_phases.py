@@ -1,5 +1,5 @@
 """Quick phase timing of one model configuration (development aid):
-   python tools/time_phases.py [N] [steps] [f32] [ppb | les | smag | amd | c4]
+   python tools/time_phases.py [N] [steps] [f32] [ppb | les [vitd] | smag | amd | c4]
    ppb: (Periodic, Periodic, Bounded) WENO5, no tracers;  les: ppb + buoyancy tracer b + ScalarDiffusivity + FPlane;
    smag / amd: les with SmagorinskyLilly / AnisotropicMinimumDissipation and the ocean-LES wall conditions (wind-stress flux
    on u, no-slip bottom, surface buoyancy flux and bottom buoyancy gradient) — the widened rows of DESIGN.md §7b"""
@@ -28,7 +28,7 @@ else:
     g = oc.RectilinearGrid(FT, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=topo)
 kw = {}
 if "les" in sys.argv:
-    kw = dict(buoyancy=oc.BuoyancyTracer(), tracers=("b",), closure=oc.ScalarDiffusivity(1e-4, 1e-4), coriolis=oc.FPlane(1e-4))
+    kw = dict(buoyancy=oc.BuoyancyTracer(), tracers=("b",), closure=oc.ScalarDiffusivity(1e-4, 1e-4, vertically_implicit="vitd" in sys.argv), coriolis=oc.FPlane(1e-4))
 if eddy:
     bcs = {"u": oc.FieldBoundaryConditions(top=oc.FluxBoundaryCondition(-1e-4), bottom=oc.ValueBoundaryCondition(0.0)),
            "v": oc.FieldBoundaryConditions(bottom=oc.ValueBoundaryCondition(0.0)),
