@@ -181,6 +181,14 @@ int32_t nh_launch_count(const nh_model* model, int64_t* count);
 enum { NH_DIST_SEND_LO = 0, NH_DIST_SEND_HI = 1, NH_DIST_RECV_LO = 2, NH_DIST_RECV_HI = 3, NH_DIST_SPECTRAL_A = 4, NH_DIST_SPECTRAL_B = 5 };
 /* the model was created on this rank's LOCAL grid (Nx, Ny/R, Nz; y Periodic); y0, y1, Ny describe the global y extent */
 int32_t nh_dist_configure(nh_model* model, int32_t rank, int32_t nranks, double y0, double y1, int32_t Ny_global);
+/* mode: 0 = not distributed, 1 = fused path (stepped through the nh_dist_* pieces below), 2 = complete path: any model that
+ * is not the fused configuration (tracers, buoyancy, Coriolis, closures, boundary conditions, a Bounded — regular or
+ * stretched — z with the distributed Fourier-tridiagonal solve of distributed_fft_tridiagonal_solver.jl:260-291).  Such a
+ * model needs nh_dist_ipc_export / nh_dist_ipc_import right after nh_dist_configure and is then driven by the ordinary
+ * entry points (nh_set_field, nh_set_state_finalize, nh_time_step, …) called in the same order on every rank: its y halo
+ * fills read the neighbours' rows over NVLink and its pressure solve transposes through peer stores, each bracketed by the
+ * flag barrier of nh_dist_barrier inside the library. */
+int32_t nh_dist_mode(nh_model* model, int32_t* mode);
 int32_t nh_dist_buffer(nh_model* model, int32_t which, void** device_ptr, int64_t* bytes);
 /* field_mask as in nh_fill_halo_regions (u, v, w, pNHS; at most three); `elements` = values per side just packed/unpacked */
 int32_t nh_dist_halo(nh_model* model, uint32_t field_mask, int32_t width, int32_t unpack, int64_t* elements);

@@ -53,7 +53,7 @@ SYMBOLS = [
     "nh_poisson_time_solves", "nh_tridiag_create", "nh_tridiag_solve", "nh_tridiag_destroy",
     "nh_dist_configure", "nh_dist_buffer", "nh_dist_halo", "nh_dist_tendency_substep", "nh_dist_poisson",
     "nh_dist_pressure_correct", "nh_dist_ipc_export", "nh_dist_ipc_import", "nh_model_set_boundary_condition",
-    "nh_model_set_boundary_condition_array",
+    "nh_model_set_boundary_condition_array", "nh_dist_mode",
     "nh_dist_barrier",
 ]
 BC_DEFAULT, BC_FLUX, BC_VALUE, BC_GRADIENT = range(4)
@@ -90,6 +90,7 @@ def lib():
             "nh_set_state_finalize": [p, C.c_int32],
             "nh_fill_halo_regions": [p, C.c_uint32, C.c_int32],
             "nh_model_set_boundary_condition": [p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_double],
+            "nh_dist_mode": [p, C.POINTER(C.c_int32)],
             "nh_model_set_boundary_condition_array": [p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64,
                                                       C.c_int32],
             "nh_update_state": [p, C.c_int32],

@@ -186,6 +186,7 @@ int32_t nh_max_abs_divergence(nh_model* m, double* out) { MODEL_CALL(m, *out = m
 int32_t nh_synchronize(nh_model* m) { MODEL_CALL(m, CUDA_CHECK(cudaStreamSynchronize(m->stream))) }
 int32_t nh_field_device_ptr(nh_model* m, int32_t field, void** ptr, int64_t off[1], int64_t strides[3]) { MODEL_CALL(m, m->field_device_ptr(field, ptr, off, strides)) }
 int32_t nh_model_set_stream(nh_model* m, void* s) { NH_TRY NH_REQUIRE(m, "null model"); m->set_stream((cudaStream_t)s); NH_CATCH }
+int32_t nh_dist_mode(nh_model* m, int32_t* mode) { MODEL_CALL(m, *mode = m->dist_mode()) }
 int32_t nh_dist_configure(nh_model* m, int32_t rank, int32_t nranks, double y0, double y1, int32_t Ny) { MODEL_CALL(m, m->dist_configure(rank, nranks, y0, y1, Ny)) }
 int32_t nh_dist_buffer(nh_model* m, int32_t which, void** ptr, int64_t* bytes) { MODEL_CALL(m, NH_REQUIRE(ptr && bytes, "null argument"); m->dist_buffer(which, ptr, bytes)) }
 int32_t nh_dist_halo(nh_model* m, uint32_t mask, int32_t w, int32_t unpack, int64_t* elements) { MODEL_CALL(m, int64_t n = m->dist_halo(mask, w, unpack); if (elements) *elements = n) }

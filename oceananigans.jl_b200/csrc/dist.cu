@@ -8,10 +8,17 @@
 
 template <typename FT>
 void Model<FT>::dist_configure(int rank, int nranks, double y0, double y1, int Ny) {
-  NH_REQUIRE(fast, "the distributed path needs the fused configuration (triply periodic, regular, WENO5, no tracers/forcing terms)");
   NH_REQUIRE(!dist.on, "model is already configured for a distributed run");
+  // anything that is not the fused configuration (triply periodic, regular, WENO5, no tracers / forcing terms) runs the
+  // complete path on its slab: x and y Periodic, z Periodic or Bounded (regular or stretched)
+  const bool generic = !fast || getenv("NHSTEP_DIST_GENERIC") != nullptr;
+  if (generic) {
+    NH_REQUIRE(gh.g.topo[0] == NH_PERIODIC && gh.g.topo[1] == NH_PERIODIC && gh.g.topo[2] != NH_FLAT,
+               "a distributed model needs Periodic x and y and a Periodic or Bounded z");
+    fast = false;
+  }
   FT dy;
-  dist.create(gh, rank, nranks, y0, y1, Ny, dy);
+  dist.create(gh, rank, nranks, y0, y1, Ny, dy, generic);
   gh.g.dy = dy;                       // the global spacing, so every rank computes with the same metric bits
   pfast.ok = false;                   // the single-GPU solve would wrap y locally
 }
@@ -108,19 +115,25 @@ void Model<FT>::dist_pressure_correct(double stage_dt) {
   CUDA_CHECK(cudaGetLastError());
 }
 
-// ---- peer-to-peer mode: CUDA IPC handles of the buffers other ranks write into -------------------------------------
-// blob = 10 handles: spectral A, spectral B, u, v, w (current state), u, v, w (ping-pong target), pNHS, barrier flags
+// ---- peer-to-peer mode: CUDA IPC handles of the buffers other ranks write into (or, on the complete path, read) --------
+// blob = 10 handles: spectral A, spectral B, u, v, w (current state), u, v, w (ping-pong target), pNHS, barrier flags;
+// complete-path models append one handle per halo-filled field id 0 … 31 (zero where the model has no such field)
 static const int kIpcHandles = 10;
+static const int kIpcHandlesGeneric = kIpcHandles + 32;
 
 template <typename FT>
 int64_t Model<FT>::dist_ipc_export(unsigned char* blob, int64_t capacity) {
   NH_REQUIRE(dist.on, "model is not configured for a distributed run");
-  const int64_t need = (int64_t)kIpcHandles * sizeof(cudaIpcMemHandle_t);
+  const int nh = dist.generic ? kIpcHandlesGeneric : kIpcHandles;
+  const int64_t need = (int64_t)nh * sizeof(cudaIpcMemHandle_t);
   if (!blob) return need;
   NH_REQUIRE(capacity >= need, "nh_dist_ipc_export: buffer too small");
   if (!dist.flags.p) dist.flags.alloc(1 << 19);       // zero-filled
-  void* ptrs[kIpcHandles] = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS, dist.flags.p};
-  for (int q = 0; q < kIpcHandles; ++q) {
+  std::vector<void*> ptrs = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS, dist.flags.p};
+  if (dist.generic) for (int id = 0; id < 32; ++id) ptrs.push_back(halo_field_or_null(id));
+  std::memset(blob, 0, need);
+  for (int q = 0; q < nh; ++q) {
+    if (!ptrs[q]) continue;
     cudaIpcMemHandle_t h;
     CUDA_CHECK(cudaIpcGetMemHandle(&h, ptrs[q]));
     std::memcpy(blob + q * sizeof(h), &h, sizeof(h));
@@ -136,13 +149,15 @@ void Model<FT>::dist_ipc_import(const unsigned char* blobs, int64_t nbytes) {
   NH_REQUIRE(!dist.p2p, "peer buffers are already open");
   const int R = dist.R, rank = dist.rank;
   NH_REQUIRE(R <= PF_MAXR, "peer-to-peer mode supports at most 16 ranks");
-  const int64_t per = (int64_t)kIpcHandles * sizeof(cudaIpcMemHandle_t);
+  const int nh = dist.generic ? kIpcHandlesGeneric : kIpcHandles;
+  const int64_t per = (int64_t)nh * sizeof(cudaIpcMemHandle_t);
   NH_REQUIRE(nbytes == per * R, "nh_dist_ipc_import: expected one export blob per rank");
   NH_REQUIRE(dist.flags.p, "nh_dist_ipc_export must be called before nh_dist_ipc_import");
-  void* own[kIpcHandles] = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS, dist.flags.p};
-  std::vector<std::vector<void*>> ptr(R, std::vector<void*>(kIpcHandles, nullptr));
+  std::vector<void*> own = {dist.A.p, dist.B.p, F[0], F[1], F[2], F2[0], F2[1], F2[2], pNHS, dist.flags.p};
+  if (dist.generic) for (int id = 0; id < 32; ++id) own.push_back(halo_field_or_null(id));
+  std::vector<std::vector<void*>> ptr(R, std::vector<void*>(nh, nullptr));
   auto open = [&](int r, int q) -> void* {
-    if (r == rank) return own[q];
+    if (r == rank || !own[q]) return own[q];
     if (ptr[r][q]) return ptr[r][q];
     cudaIpcMemHandle_t h;
     std::memcpy(&h, blobs + r * per + q * sizeof(h), sizeof(h));
@@ -154,11 +169,18 @@ void Model<FT>::dist_ipc_import(const unsigned char* blobs, int64_t nbytes) {
   };
   for (int r = 0; r < R; ++r) { dist.peerA[r] = (CT*)open(r, 0); dist.peerB[r] = (CT*)open(r, 1); }
   const int prev = (rank + R - 1) % R, next = (rank + 1) % R;
-  for (int a = 0; a < 3; ++a) {
-    dist.prevF[a] = (FT*)open(prev, 2 + a); dist.prevF2[a] = (FT*)open(prev, 5 + a);
-    dist.nextF[a] = (FT*)open(next, 2 + a); dist.nextF2[a] = (FT*)open(next, 5 + a);
+  if (!dist.generic) {
+    for (int a = 0; a < 3; ++a) {
+      dist.prevF[a] = (FT*)open(prev, 2 + a); dist.prevF2[a] = (FT*)open(prev, 5 + a);
+      dist.nextF[a] = (FT*)open(next, 2 + a); dist.nextF2[a] = (FT*)open(next, 5 + a);
+    }
+    dist.next_p = (FT*)open(next, 8);
+  } else {
+    for (int id = 0; id < 32; ++id) {
+      dist.peer_prev[id] = (FT*)open(prev, kIpcHandles + id);
+      dist.peer_next[id] = (FT*)open(next, kIpcHandles + id);
+    }
   }
-  dist.next_p = (FT*)open(next, 8);
   for (int r = 0; r < PF_MAXR; ++r) dist.peer_flags[r] = r < R ? (unsigned int*)open(r, 9) : nullptr;
   dist.p2p = true;
 }

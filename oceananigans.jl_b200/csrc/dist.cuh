@@ -65,9 +65,23 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pd_z_scatter_kernel(const _
   }
 }
 
+// The transpose alone (vertically Bounded models: z is not transformed before the y pass): block d of the z-local buffer is
+// copied into block `rank` of rank d's y-local buffer.  One thread per element.
+template <typename CT>
+struct ScatterJob { const CT* src; CT* peer[PF_MAXR]; long long chunk; int R, rank; };
+template <typename CT>
+__global__ void __launch_bounds__(256) pd_scatter_kernel(const __grid_constant__ ScatterJob<CT> J) {
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e >= J.chunk * J.R) return;
+  const int d = (int)(e / J.chunk);
+  J.peer[d][J.chunk * J.rank + (e - d * J.chunk)] = J.src[e];
+}
+
 // forward c2c along the GLOBAL y, spectral division, inverse c2c along y, on the transposed buffer T (this rank's Cx
 // columns, all Ny rows).  grid (Cx/8, Nz), block N = Ny (global)
-template <typename FT, typename CT, int N>
+// MODE 0: all three; 1: forward transform only, in place (a Thomas sweep along z follows, pf_thomas_kernel<…, true>);
+// 2: inverse transform only, with the 1/N scale and the scatter back.
+template <typename FT, typename CT, int N, int MODE = 0>
 __global__ void __launch_bounds__(N, pf_min_ctas(N)) pd_y_solve_kernel(const __grid_constant__ PFJob<FT, CT> J, CT* __restrict__ T, int rank) {
   extern __shared__ __align__(16) unsigned char pf_smem[];
   CT* X = reinterpret_cast<CT*>(pf_smem);
@@ -86,20 +100,29 @@ __global__ void __launch_bounds__(N, pf_min_ctas(N)) pd_y_solve_kernel(const __g
     off[m] = (long long)J.Cx * (j % NyL) + plane * J.Nz * (j / NyL);
     if (active) v[m] = base[off[m]]; else { v[m].x = 0; v[m].y = 0; }
   }
-  ff_line_fft_regs<CT, N, false>(v, X + c * pitch, t, J.twy);
-  const double lamx = active ? J.lx[kx] : 1.0, lamz = J.lz[kz];
+  if (MODE != 2) ff_line_fft_regs<CT, N, false>(v, X + c * pitch, t, J.twy);
+  if (MODE == 1) {
+    if (active) {
 #pragma unroll
-  for (int m = 0; m < 8; ++m) {
-    const int j = t + m * (N / 8);
-    // same association as the single-GPU kernel and the reference: ((λx + λy) + λz) - m
-    double den = ((lamx + J.ly[j]) + lamz) - J.m;
-    const bool den_ok = nh_den_ok(den);
-    const double yr = nh_rcp_refined(den);
-    CT r;
-    r.x = (FT)nh_div_checked((double)(-v[m].x), den, yr, den_ok);
-    r.y = (FT)nh_div_checked((double)(-v[m].y), den, yr, den_ok);
-    if (J.m == 0.0 && kx == 0 && j == 0 && kz == 0) { r.x = 0; r.y = 0; }
-    v[m] = r;
+      for (int m = 0; m < 8; ++m) base[off[m]] = v[m];
+    }
+    return;
+  }
+  if (MODE == 0) {
+    const double lamx = active ? J.lx[kx] : 1.0, lamz = J.lz[kz];
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      const int j = t + m * (N / 8);
+      // same association as the single-GPU kernel and the reference: ((λx + λy) + λz) - m
+      double den = ((lamx + J.ly[j]) + lamz) - J.m;
+      const bool den_ok = nh_den_ok(den);
+      const double yr = nh_rcp_refined(den);
+      CT r;
+      r.x = (FT)nh_div_checked((double)(-v[m].x), den, yr, den_ok);
+      r.y = (FT)nh_div_checked((double)(-v[m].y), den, yr, den_ok);
+      if (J.m == 0.0 && kx == 0 && j == 0 && kz == 0) { r.x = 0; r.y = 0; }
+      v[m] = r;
+    }
   }
   ff_line_fft_regs<CT, N, true>(v, X + c * pitch, t, J.twy);
   if (active) {

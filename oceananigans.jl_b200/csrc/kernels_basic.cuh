@@ -19,6 +19,10 @@ struct HaloJob {
   int side_kind[NH_MAXF][2];   // mode 2: NH_BC_DEFAULT / NH_BC_FLUX (mirror), NH_BC_VALUE, NH_BC_GRADIENT at the left / right wall
   FT side_val[NH_MAXF][2];
   const FT* side_arr[NH_MAXF][2];   // array condition (N_e1 × N_e2 over the transverse grid range, e1 fastest) or nullptr
+  // slab runs (csrc/dist.cuh): the periodic fill along y reads the previous / next rank's field over NVLink instead of this
+  // rank's own far end (same index arithmetic, different base pointer); nullptr = this rank's own field
+  const FT* pull_prev[NH_MAXF];
+  const FT* pull_next[NH_MAXF];
   int nf;
   int d;                  // direction being filled
   int lo[3], hi[3];       // transverse logical index range (inclusive); entry d unused
@@ -42,9 +46,13 @@ __global__ void halo_fill_kernel(const __grid_constant__ HaloJob<FT> J) {
   c[e1] = a1; c[e2] = a2;
   auto at = [&](int q) -> FT& { c[d] = q; return p[g.idx(c[0], c[1], c[2])]; };
   if (mode == 1) {
+    const FT* pp = J.pull_prev[f] ? J.pull_prev[f] : p;
+    const FT* pn = J.pull_next[f] ? J.pull_next[f] : p;
     for (int h = 1; h <= H; ++h) {
-      at(h - H) = at(N - H + h);       // west halo  ← east end of the interior
-      at(N + h) = at(h);               // east halo  ← west end of the interior
+      c[d] = N - H + h; const FT lo = pp[g.idx(c[0], c[1], c[2])];
+      c[d] = h;         const FT hi = pn[g.idx(c[0], c[1], c[2])];
+      at(h - H) = lo;                  // west halo  ← east end of the interior (of the previous rank on a slab)
+      at(N + h) = hi;                  // east halo  ← west end of the interior (of the next rank)
     }
   } else if (mode == 2) {
     // Δ between the first interior and the first halo point: the Face spacing at index 1 / N+1

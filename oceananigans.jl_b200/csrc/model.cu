@@ -324,7 +324,23 @@ void Model<FT>::fill_halo_regions(uint32_t mask, int fill_normal) {
       int minext[3] = {1 << 30, 1 << 30, 1 << 30};
       for (int id : ids) { int n[3]; field_extent(id, n); for (int e = 0; e < 3; ++e) minext[e] = std::min(minext[e], n[e] + 2 * g.H[e]); }
       for (int e = 0; e < 3; ++e) { J.lo[e] = 1 - g.H[e]; J.hi[e] = minext[e] - g.H[e]; }
-      for (int id : ids) { J.p[J.nf] = field_ptr(id); J.mode[J.nf] = 1; J.nf++; }
+      const bool pull = dist.on && dist.generic && d == 1;
+      if (pull) NH_REQUIRE(dist.p2p, "a distributed complete-path model needs nh_dist_ipc_import before its first halo fill");
+      for (int id : ids) {
+        J.p[J.nf] = field_ptr(id); J.mode[J.nf] = 1;
+        J.pull_prev[J.nf] = pull ? dist.peer_prev[id] : nullptr;
+        J.pull_next[J.nf] = pull ? dist.peer_next[id] : nullptr;
+        if (pull) NH_REQUIRE(dist.peer_prev[id] && dist.peer_next[id], "field has no peer pointers");
+        J.nf++;
+      }
+      if (pull) {
+        // the neighbours' rows (and their x / z images, filled before y in the reference's order) must be complete before
+        // they are read, and read before the neighbours write them again
+        dist_barrier();
+        launch(J);
+        dist_barrier();
+        continue;
+      }
     } else {
       for (int e = 0; e < 3; ++e) { J.lo[e] = 1; J.hi[e] = g.N[e]; }
       for (int id : ids) {
@@ -519,6 +535,24 @@ template <typename FT>
 void Model<FT>::calculate_pressure_correction(double dt) {
   fill_halo_regions(0x7u, 1);
   dim3 blk(64, 4, 1);
+  if (dist.on && dist.generic) {
+    // slab run: the same real source term, then the distributed solve (x-FFT → transpose → y-FFT, division or Thomas sweep,
+    // y-IFFT → transpose back → x-IFFT); the transposes are peer stores, separated by stream-ordered barriers
+    NH_REQUIRE(dist.p2p, "a distributed complete-path model needs nh_dist_ipc_import first");
+    const long long n = (long long)gh.g.N[0] * gh.g.N[1] * gh.g.N[2];
+    if (prhs.n < (size_t)n) prhs.alloc(n, false);
+    source_term_real_kernel<FT><<<grid3(blk), blk, 0, stream>>>(gh.g, F[0], F[1], F[2], dt, dist.tri ? 1 : 0, prhs.p);
+    KLAUNCH(lc);
+    dist.generic_forward(prhs.p, stream, lc);
+    dist_barrier();
+    dist.generic_solve_y(stream, lc);
+    dist_barrier();
+    dist.generic_backward(pNHS, stream, lc);
+    fill_halo_regions(1u << NH_FIELD_PNHS, 1);
+    p_halo_stale = false;
+    CUDA_CHECK(cudaGetLastError());
+    return;
+  }
   if (pfast.ok) {
     // fused passes: real source term (same expression as below) → x/y FFT + z FFT | DCT | Thomas → interior of pNHS
     const long long n = (long long)gh.g.N[0] * gh.g.N[1] * gh.g.N[2];
@@ -555,7 +589,8 @@ void Model<FT>::pressure_correct_velocities(double dt) {
 // store_tendencies.jl is replaced by a pointer swap (Gⁿ is fully rewritten by the next compute_tendencies!).
 template <typename FT>
 void Model<FT>::time_step(double dt, int euler) {
-  if (dist.on) throw NhError("a distributed model is stepped through nh_dist_* (see include/nhstep.h), not nh_time_step");
+  if (dist.on && !dist.generic)
+    throw NhError("a distributed model on the fused path is stepped through nh_dist_* (see include/nhstep.h), not nh_time_step");
   if (fast) {
     // same sequence as below with compute_tendencies! + the next substep fused and the halo fills folded into the
     // pressure-correction kernel; Gⁿ of the final state is refreshed lazily (ensure_tendencies).

@@ -107,6 +107,19 @@ struct PoissonFast {
     }
     return gh.g.topo[2] == NH_BOUNDED && gh.g.N[2] >= 2;
   }
+  static void tri_tables(const GridHost<FT>& gh, std::vector<double>& a, std::vector<double>& c, std::vector<FT>& low,
+                         std::vector<FT>& dz1) {
+    const GridDev<FT>& g = gh.g;
+    const int Nz = g.N[2];
+    auto Dzf = [&](int k) { return gh.dzf_h[k + g.zoff]; };
+    auto Dzc = [&](int k) { return gh.dzc_h[k + g.zoff]; };
+    a.assign(Nz, 0.0); c.assign(Nz, 0.0); dz1.assign(Nz, FT(0)); low.clear();
+    a[0] = (double)(FT(-1) / Dzf(2));
+    for (int k = 2; k <= Nz - 1; ++k) a[k - 1] = (double)(-(FT(1) / Dzf(k + 1) + FT(1) / Dzf(k)));
+    a[Nz - 1] = (double)(FT(-1) / Dzf(Nz));
+    for (int k = 1; k <= Nz; ++k) { c[k - 1] = (double)Dzc(k); dz1[k - 1] = Dzc(k); }
+    for (int q = 2; q <= Nz; ++q) low.push_back(FT(1) / Dzf(q));
+  }
   void create(const GridHost<FT>& gh, bool tridiagonal = false) {
     const GridDev<FT>& g = gh.g;
     tri = tridiagonal;
@@ -125,16 +138,9 @@ struct PoissonFast {
     if (tri) {
       // grid-only parts of the main diagonal and the off-diagonals, in the reference's expression and precision
       // (compute_main_diagonal!, fourier_tridiagonal_poisson_solver.jl:41-51,88-96)
-      const int Nz = J.Nz;
-      auto Dzf = [&](int k) { return gh.dzf_h[k + g.zoff]; };
-      auto Dzc = [&](int k) { return gh.dzc_h[k + g.zoff]; };
-      std::vector<double> a(Nz), c(Nz);
-      std::vector<FT> low, dz1(Nz);
-      a[0] = (double)(FT(-1) / Dzf(2));
-      for (int k = 2; k <= Nz - 1; ++k) a[k - 1] = (double)(-(FT(1) / Dzf(k + 1) + FT(1) / Dzf(k)));
-      a[Nz - 1] = (double)(FT(-1) / Dzf(Nz));
-      for (int k = 1; k <= Nz; ++k) { c[k - 1] = (double)Dzc(k); dz1[k - 1] = Dzc(k); }
-      for (int q = 2; q <= Nz; ++q) low.push_back(FT(1) / Dzf(q));
+      std::vector<double> a, c;
+      std::vector<FT> low, dz1;
+      tri_tables(gh, a, c, low, dz1);
       dA.upload(a); dC.upload(c); lower.upload(low); dzc1.upload(dz1);
       tt.alloc((size_t)J.Mx * J.Ny * J.Nz);
       stale.alloc(1);
@@ -278,6 +284,7 @@ struct nh_model {
   virtual void fill_halo_regions(uint32_t mask, int fill_normal) = 0;
   virtual void set_boundary_condition(int field, int dim, int side, int kind, double value) = 0;
   virtual void set_boundary_condition_array(int field, int dim, int side, int kind, const void* data, long long count, int where) = 0;
+  virtual int dist_mode() = 0;
   virtual void update_state(int compute_tendencies) = 0;
   virtual void compute_tendencies() = 0;
   virtual void rk3_substep(double dt, double gamma, double zeta, int has_zeta) = 0;
@@ -373,6 +380,15 @@ struct Model : nh_model {
   void fill_halo_regions(uint32_t mask, int fill_normal) override;
   void set_boundary_condition(int field, int dim, int side, int kind, double value) override;
   void set_boundary_condition_array(int field, int dim, int side, int kind, const void* data, long long count, int where) override;
+  int dist_mode() override { return !dist.on ? 0 : (dist.generic ? 2 : 1); }
+  FT* halo_field_or_null(int id) {       // the field of a halo-fill mask bit, nullptr when the model has none
+    if (id >= 0 && id < nf) return F[id];
+    if (id == NH_FIELD_PNHS) return pNHS;
+    if (id == NH_FIELD_PHY) return pHY;
+    if (id == NH_FIELD_NUE) return nue;
+    if (id >= NH_FIELD_KAPPAE0 && id < NH_FIELD_KAPPAE0 + NH_MAXTR && id - NH_FIELD_KAPPAE0 < ntr) return kape[id - NH_FIELD_KAPPAE0];
+    return nullptr;
+  }
   int bc_kind[NH_MAXF][3][2] = {};   // NH_BC_* of each prognostic field's walls (constant conditions)
   FT bc_val[NH_MAXF][3][2] = {};
   DevBuf<FT> bc_arr[NH_MAXF][3][2];  // array conditions (empty: the number above)

@@ -294,17 +294,22 @@ struct PFStale { int n; int pos[PF_STALE_MAX][3]; FT val[PF_STALE_MAX]; };
 template <typename FT>
 __global__ void pf_stale_gather_kernel(PFStale<FT>* st, const FT* __restrict__ phi, GridDev<FT> g) {
   const int q = threadIdx.x;
-  if (q < min(st->n, PF_STALE_MAX)) st->val[q] = phi[g.idx(st->pos[q][0] + 1, st->pos[q][1] + 1, st->pos[q][2] + 1)];
+  if (q < min(st->n, PF_STALE_MAX) && st->pos[q][1] < g.N[1]) st->val[q] = phi[g.idx(st->pos[q][0] + 1, st->pos[q][1] + 1, st->pos[q][2] + 1)];
 }
 
-template <typename FT, typename CT>
+// DIST: the y-local buffer of a slab run (csrc/dist.cuh): this rank's Cx columns kx = rank·Cx + kxl, all GLOBAL rows ky,
+// element (kxl, ky, k) at kxl + Cx·(ky % NyL) + Cx·NyL·(k + Nz·(ky / NyL)); J.S is that buffer, J.Ny = NyL.
+template <typename FT, typename CT, bool DIST = false>
 __global__ void __launch_bounds__(128) pf_thomas_kernel(const __grid_constant__ PFJob<FT, CT> J, const FT* __restrict__ lower,
                                                         const double* __restrict__ dA, const double* __restrict__ dC,
-                                                        CT* __restrict__ Phi, FT* __restrict__ tt, PFStale<FT>* st) {
-  const int kx = blockIdx.x * blockDim.x + threadIdx.x, ky = blockIdx.y;
-  if (kx > J.Nx / 2) return;
+                                                        CT* __restrict__ Phi, FT* __restrict__ tt, PFStale<FT>* st, int rank = 0) {
+  const int kxl = blockIdx.x * blockDim.x + threadIdx.x, ky = blockIdx.y;
+  const int kx = DIST ? rank * J.Cx + kxl : kxl;
+  if (kx > J.Nx / 2 || (DIST && kxl >= J.Cx)) return;
   const int Nz = J.Nz;
-  const long long sz = (long long)J.Mx * J.Ny, col = kx + (long long)J.Mx * ky;
+  const long long plane = (long long)J.Cx * J.Ny;
+  const long long sz = DIST ? plane : (long long)J.Mx * J.Ny;
+  const long long col = DIST ? kxl + (long long)J.Cx * (ky % J.Ny) + plane * Nz * (ky / J.Ny) : kx + (long long)J.Mx * ky;
   const double lam = J.lx[kx] + J.ly[ky];
   const double guard = 10.0 * (sizeof(FT) == 4 ? 1.1920928955078125e-07 : 2.220446049250313e-16);
   double beta = dA[0] - dC[0] * lam;

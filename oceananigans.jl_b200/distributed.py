@@ -117,7 +117,7 @@ class DistributedNonhydrostaticModel:
     """
 
     def __init__(self, arch, FT=np.float64, size=None, x=None, y=None, z=None, halo=(3, 3, 3), advection=None,
-                 timestepper="RungeKutta3", device=0, p2p=False, **kw):
+                 timestepper="RungeKutta3", device=0, p2p=False, topology=None, **kw):
         import torch
         from . import RectilinearGrid, Periodic, WENO
         from .model import NonhydrostaticModel
@@ -130,7 +130,7 @@ class DistributedNonhydrostaticModel:
         yhi = y0 + (y1 - y0) * (self.rank + 1) / self.R
         self.global_grid_spec = dict(FT=FT, size=self.global_size, x=x, y=y, z=z, halo=halo)
         self.grid = RectilinearGrid(FT, size=(Nx, self.NyL, Nz), x=x, y=(ylo, yhi), z=z, halo=halo,
-                                    topology=(Periodic, Periodic, Periodic), device=device)
+                                    topology=topology or (Periodic, Periodic, Periodic), device=device)
         self.model = NonhydrostaticModel(self.grid, advection=advection or WENO(FT, 5), timestepper=timestepper, **kw)
         self._h = self.model._h
         check(lib().nh_dist_configure(self._h, self.rank, self.R, y0, y1, Ny))
@@ -149,7 +149,13 @@ class DistributedNonhydrostaticModel:
         self.halo = self.model.halo
         self._uvw = (1 << L.FIELD_U) | (1 << L.FIELD_V) | (1 << L.FIELD_W)
         self.p2p = False
-        if p2p:
+        mode = C.c_int32()
+        check(lib().nh_dist_mode(self._h, C.byref(mode)))
+        # complete path (anything but the fused triply periodic configuration): the library drives the whole step itself
+        # over peer memory, so the peer-to-peer mode is not optional and the host loop is the single-GPU one
+        self.generic = mode.value == 2
+        self.tracers = self.model.tracers
+        if p2p or self.generic:
             self._enable_peer_to_peer()
 
     def _enable_peer_to_peer(self):
@@ -225,6 +231,9 @@ class DistributedNonhydrostaticModel:
 
     def time_step(self, dt, euler=False, n_steps=1):
         """time_step!(model, Δt) — runge_kutta_3.jl:77-151 / quasi_adams_bashforth_2.jl:74-115 on the slab partition."""
+        if self.generic:
+            check(lib().nh_time_step(self._h, float(dt), int(euler), int(n_steps)))
+            return
         stages = 3 if self.model.timestepper_name in ("RungeKutta3", "RK3") else 1
         sdt = C.c_double()
         for _ in range(n_steps):
@@ -293,13 +302,24 @@ class DistributedNonhydrostaticModel:
         rows = {}
         for name, a in global_arrays.items():
             a = np.asarray(a)
-            if a.shape != self.global_size:
+            if a.shape[:2] != self.global_size[:2]:
                 raise ValueError(f"{name} must have the global size {self.global_size}")
             rows[name] = a[:, self.j0:self.j0 + self.NyL, :]
         self.set_local(enforce_incompressibility, **rows)
 
+    def _field(self, name):
+        for ns in (self.velocities, self.tracers, self.pressures):
+            if name in ns:
+                return ns[name]
+        raise KeyError(name)
+
     def set_local(self, enforce_incompressibility=True, **local_arrays):
         """As ``set`` with this rank's own (Nx, Ny/R, Nz) rows."""
+        if self.generic:
+            # every rank sets the same fields in the same order (each set fills halos, i.e. meets the others at a barrier)
+            from .model import set_model
+            set_model(self.model, enforce_incompressibility, **{n: local_arrays[n] for n in sorted(local_arrays)})
+            return
         for name, a in local_arrays.items():
             self.velocities[name].set(a)
         check(lib().nh_fill_halo_regions(self._h, self._uvw, 1))
@@ -308,8 +328,7 @@ class DistributedNonhydrostaticModel:
             self.pressure_phase(1.0)
 
     def local_interior(self, name):
-        f = self.pressures[name] if name in self.pressures else self.velocities[name]
-        return f.interior()
+        return self._field(name).interior()
 
     def gather(self, name):
         """Global (Nx, Ny, Nz) array of a field on every rank (diagnostics / tests only)."""

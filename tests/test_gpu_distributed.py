@@ -135,3 +135,134 @@ def test_multi_gpu_matches_single_gpu(world, FT, timestepper, size, p2p, tmp_pat
     mp.spawn(_worker, args=(world, port, size, FT, timestepper, steps, dt, path, p2p), nprocs=world, join=True)
     res = dict(np.load(path))
     _check(res, ref, FT, steps, dt)
+
+
+# ---- complete-path models on a slab (tracers, buoyancy, closures, boundary conditions, Bounded / stretched z) -----------------
+# DistributedFFTBasedPoissonSolver / DistributedFourierTridiagonalPoissonSolver rows of SURVEY.md §8 a32: the y halo fill pulls
+# the neighbours' rows over NVLink, the solve transposes through peer stores, the host loop is the single-GPU one.
+
+def _zfaces(Nz, stretched):
+    if not stretched:
+        return (0, 1)
+    k = np.arange(Nz + 1)
+    return 0.5 * (1 + np.tanh(1.3 * (2 * k / Nz - 1)) / np.tanh(1.3))
+
+
+GENERIC = {
+    # name: (size, z topology Bounded?, stretched, model kwargs builder)
+    "ppp-tracer": ((32, 32, 16), False, False),
+    "ppb-les": ((32, 32, 16), True, False),
+    "ppb-stretched-smag": ((16, 32, 12), True, True),
+}
+
+
+def _generic_kwargs(oc, name, FT):
+    if name == "ppp-tracer":
+        return dict(tracers=("c",), closure=oc.ScalarDiffusivity(1e-3, 2e-3), coriolis=oc.FPlane(0.5))
+    bcs = {"u": oc.FieldBoundaryConditions(top=oc.FluxBoundaryCondition(-1e-2), bottom=oc.ValueBoundaryCondition(0.0)),
+           "b": oc.FieldBoundaryConditions(top=oc.FluxBoundaryCondition(1e-3), bottom=oc.GradientBoundaryCondition(0.1))}
+    if name == "ppb-les":
+        return dict(tracers=("b",), buoyancy=oc.BuoyancyTracer(), coriolis=oc.FPlane(0.3), boundary_conditions=bcs,
+                    closure=oc.ScalarDiffusivity(1e-3, 1e-3, vertically_implicit=True))
+    return dict(tracers=("b",), buoyancy=oc.BuoyancyTracer(), boundary_conditions=bcs, closure=oc.SmagorinskyLilly())
+
+
+def _generic_ics(size, FT, bounded, names):
+    ics = _ics(size, FT)
+    if bounded:
+        w = np.concatenate([ics["w"], ics["w"][:, :, :1]], axis=2)
+        w[:, :, 0] = 0
+        w[:, :, -1] = 0
+        ics["w"] = w
+    rng = np.random.default_rng(11)
+    for n in names:
+        ics[n] = (0.2 * rng.standard_normal(size)).astype(FT)
+    return ics
+
+
+def _generic_single(name, FT, timestepper, steps, dt):
+    import oceananigans_jl_b200 as oc
+    size, bounded, stretched = GENERIC[name]
+    topo = (oc.Periodic, oc.Periodic, oc.Bounded if bounded else oc.Periodic)
+    g = oc.RectilinearGrid(FT, size=size, x=(0, 1), y=(0, 2), z=_zfaces(size[2], stretched), halo=(3, 3, 3), topology=topo)
+    kw = _generic_kwargs(oc, name, FT)
+    m = oc.NonhydrostaticModel(g, advection=oc.WENO(FT, 5), timestepper=timestepper, **kw)
+    oc.set_model(m, **_generic_ics(size, FT, bounded, kw["tracers"]))
+    oc.time_step(m, dt, n_steps=steps)
+    fields = {n: m.velocities[n].interior() for n in "uvw"} | {n: m.tracers[n].interior() for n in kw["tracers"]}
+    fields["pNHS"] = m.pressures.pNHS.interior()
+    return fields | {"time": m.clock.time, "iteration": m.clock.iteration}
+
+
+def _generic_distributed(rank, world, name, FT, timestepper, steps, dt, out):
+    import oceananigans_jl_b200 as oc
+    from oceananigans_jl_b200 import distributed as D
+    size, bounded, stretched = GENERIC[name]
+    topo = (oc.Periodic, oc.Periodic, oc.Bounded if bounded else oc.Periodic)
+    kw = _generic_kwargs(oc, name, FT)
+    arch = D.Distributed(D.Partition(y=world))
+    m = D.DistributedNonhydrostaticModel(arch, FT, size=size, x=(0, 1), y=(0, 2), z=_zfaces(size[2], stretched), halo=(3, 3, 3),
+                                         advection=oc.WENO(FT, 5), timestepper=timestepper, device=rank, topology=topo, **kw)
+    assert m.generic
+    m.set(**_generic_ics(size, FT, bounded, kw["tracers"]))
+    m.time_step(dt, n_steps=steps)
+    res = {n: m.gather(n) for n in ("u", "v", "w", "pNHS") + tuple(kw["tracers"])}
+    res["time"], res["iteration"], res["div"] = m.clock.time, m.clock.iteration, m.max_abs_divergence()
+    if rank == 0:
+        out.update(res)
+
+
+def _generic_check(res, ref, FT, name):
+    # stretched z: the same Fourier-tridiagonal algorithm on both sides; regular Bounded z: the slab run solves with the
+    # tridiagonal sweep where one GPU uses the cosine transform, triply periodic: FFT passes in a different order
+    tol = 1e-12 if FT == np.float64 else 1e-5
+    for n in ref:
+        if n in ("time", "iteration"):
+            continue
+        assert _rel(res[n], ref[n]) <= tol, (name, n, _rel(res[n], ref[n]))
+    assert res["iteration"] == ref["iteration"] and res["time"] == ref["time"]
+    assert res["div"] < (1e-11 if FT == np.float64 else 1e-3)
+
+
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+@pytest.mark.parametrize("name", list(GENERIC))
+def test_one_rank_complete_path_slab_matches_single_gpu(name, timestepper, FT):
+    steps, dt = 10, 2e-3
+    ref = _generic_single(name, FT, timestepper, steps, dt)
+    out = {}
+    _generic_distributed(0, 1, name, FT, timestepper, steps, dt, out)
+    _generic_check(out, ref, FT, name)
+
+
+def _generic_worker(rank, world, port, name, FT, timestepper, steps, dt, path):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        out = {}
+        _generic_distributed(rank, world, name, FT, timestepper, steps, dt, out)
+        if rank == 0:
+            np.savez(path, **out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("FT,timestepper", [(np.float64, "RungeKutta3"), (np.float32, "QuasiAdamsBashforth2")])
+@pytest.mark.parametrize("name", list(GENERIC))
+def test_multi_gpu_complete_path_slab_matches_single_gpu(name, FT, timestepper, world, tmp_path):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    steps, dt = 10, 2e-3
+    ref = _generic_single(name, FT, timestepper, steps, dt)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    path = str(tmp_path / "dist.npz")
+    mp.spawn(_generic_worker, args=(world, port, name, FT, timestepper, steps, dt, path), nprocs=world, join=True)
+    res = dict(np.load(path))
+    _generic_check(res, ref, FT, name)
