@@ -11,10 +11,12 @@ timeout 600 python bench.py --size 512 --steps 20 --warmup 3 --no-cpu-baseline >
 timeout 600 python bench.py --impl reference --steps 10 --warmup 2 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launch.log 2>&1
+if [ -z "$NO_NCU_FULL" ]; then
 timeout 600 ncu --set full --import-source on --clock-control none -k regex:tendency_fast --launch-skip 5 -c 2 \
     -f -o gpurun_out/tendency python tools/profile_tendency.py > gpurun_out/ncu_full.log 2>&1
 timeout 600 ncu --set full --import-source on --clock-control none -k 'regex:tendency_fast|pf_|pressure_correct_halo' \
     --launch-skip 28 -c 7 -f -o gpurun_out/step256 python tools/profile_step.py > gpurun_out/ncu_step.log 2>&1
+fi
 for cfg in ppb les "les vitd" smag amd; do echo "$cfg: $(python tools/time_phases.py 256 5 $cfg 2>&1 | tail -1)"; done > gpurun_out/les_times.txt
 echo "c4 512x512x256 stretched: $(python tools/time_phases.py 512 3 c4 2>&1 | tail -1)" >> gpurun_out/les_times.txt
 python tools/time_solvers.py > gpurun_out/solver_times.txt 2>&1
