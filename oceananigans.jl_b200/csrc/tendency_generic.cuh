@@ -473,7 +473,11 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
         if (fi > nx || fj >= ny || fk >= nz) continue;
         const int i = i0 + fi + ox, j = j0 + fj, k = k0 + fk;
         if (a == 0 && g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i < 1) continue;   // only the (skipped) periphery cell would read it
+        #if TG_FASTFLUX
         if (pass == 0) Fx[fk][fj][fi] = tiled_adv_flux<FT, a, 0>(P, c, i, j, k);
+#else
+        if (pass == 0) Fx[fk][fj][fi] = a == 3 ? tracer_flux<FT, 0>(P, c, i, j, k) : momentum_flux<FT, av, 0>(P, i, j, k);
+#endif
         else Fx[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 0>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 0>(P, i, j, k);
       }
     if (g.topo[1] != NH_FLAT)
@@ -482,7 +486,11 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
         if (fi >= nx || fj > ny || fk >= nz) continue;
         const int i = i0 + fi, j = j0 + fj + oy, k = k0 + fk;
         if (a == 1 && g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j < 1) continue;
+        #if TG_FASTFLUX
         if (pass == 0) Fy[fk][fj][fi] = tiled_adv_flux<FT, a, 1>(P, c, i, j, k);
+#else
+        if (pass == 0) Fy[fk][fj][fi] = a == 3 ? tracer_flux<FT, 1>(P, c, i, j, k) : momentum_flux<FT, av, 1>(P, i, j, k);
+#endif
         else Fy[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 1>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 1>(P, i, j, k);
       }
     if (g.topo[2] != NH_FLAT)
@@ -491,7 +499,11 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
         if (fi >= nx || fj >= ny || fk > nz) continue;
         const int i = i0 + fi, j = j0 + fj, k = k0 + fk + oz;
         if (a == 2 && g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k < 1) continue;
+        #if TG_FASTFLUX
         if (pass == 0) Fz[fk][fj][fi] = tiled_adv_flux<FT, a, 2>(P, c, i, j, k);
+#else
+        if (pass == 0) Fz[fk][fj][fi] = a == 3 ? tracer_flux<FT, 2>(P, c, i, j, k) : momentum_flux<FT, av, 2>(P, i, j, k);
+#endif
         else Fz[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 2>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 2>(P, i, j, k);
       }
     __syncthreads();
@@ -527,7 +539,12 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
 }
 
 template <typename FT>
-__global__ void __launch_bounds__(TG_TX * TG_TY, TG_MINBLOCKS) tendency_tiled_kernel(const __grid_constant__ TendParams<FT> P, int what) {
+#if TG_MINBLOCKS > 1
+#define TG_BOUNDS __launch_bounds__(TG_TX * TG_TY, TG_MINBLOCKS)
+#else
+#define TG_BOUNDS __launch_bounds__(TG_TX * TG_TY)
+#endif
+__global__ void TG_BOUNDS tendency_tiled_kernel(const __grid_constant__ TendParams<FT> P, int what) {
   __shared__ FT sm[TG_TZ * TG_TY * (TG_TX + 1) + TG_TZ * (TG_TY + 1) * TG_TX + (TG_TZ + 1) * TG_TY * TG_TX];
   if (what == 0) tiled_tendency<FT, 0>(P, 0, sm);
   else if (what == 1) tiled_tendency<FT, 1>(P, 0, sm);
