@@ -419,9 +419,10 @@ __device__ __forceinline__ FT tiled_adv_flux(const TendParams<FT>& P, const FT* 
       const FT A = area_at(g, b, b == 2 ? 0 : 1, k);
       const FT ub = P.U[b][n];
       const bool left = ub > FT(0);
-      const FT* q = c + n;
-      const FT q0 = q[(left ? -3 : 2) * sb], q1 = q[(left ? -2 : 1) * sb], q2 = q[(left ? -1 : 0) * sb];
-      const FT q3 = q[(left ? 0 : -1) * sb], q4 = q[(left ? 1 : -2) * sb];
+      // q_m at offset -3 + m (left-biased) or 2 - m (right-biased): start at the far upwind point and step towards downwind
+      const long long step = left ? sb : -sb;
+      const FT* q = c + n + (left ? -3 * sb : 2 * sb);
+      const FT q0 = q[0], q1 = q[step], q2 = q[2 * step], q3 = q[3 * step], q4 = q[4 * step];
       return A * ub * weno5_from_q<FT>(P.tab, q0, q1, q2, q3, q4);
     }
     const long long ss = sym_dim == 0 ? 1 : (sym_dim == 1 ? g.sy : g.sz);
@@ -433,9 +434,9 @@ __device__ __forceinline__ FT tiled_adv_flux(const TendParams<FT>& P, const FT* 
     ut = ut + P.tab.sym[2][1] * (area_at(g, b, zcb, k + kz * stag_c) * ub[stag_c * ss]);
     ut = ut + P.tab.sym[2][0] * (area_at(g, b, zcb, k + kz * (1 + stag_c)) * ub[(1 + stag_c) * ss]);
     const bool left = ut > FT(0);
-    const FT* q = P.U[av] + n + stag_c * sb;
-    const FT q0 = q[(left ? -3 : 2) * sb], q1 = q[(left ? -2 : 1) * sb], q2 = q[(left ? -1 : 0) * sb];
-    const FT q3 = q[(left ? 0 : -1) * sb], q4 = q[(left ? 1 : -2) * sb];
+    const long long step = left ? sb : -sb;
+    const FT* q = P.U[av] + n + stag_c * sb + (left ? -3 * sb : 2 * sb);
+    const FT q0 = q[0], q1 = q[step], q2 = q[2 * step], q3 = q[3 * step], q4 = q[4 * step];
     return ut * weno5_from_q<FT>(P.tab, q0, q1, q2, q3, q4);
   }
   if (a == 3) return tracer_flux<FT, b>(P, c, i, j, k);
