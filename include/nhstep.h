@@ -233,6 +233,21 @@ int32_t nh_tridiag_create(nh_grid* grid, const double* a, const double* b, const
 int32_t nh_tridiag_solve(nh_tridiag* solver, const void* rhs, void* phi);
 int32_t nh_tridiag_destroy(nh_tridiag* solver);
 
+/* nh_tridiag_solve_static — the same batched tridiagonal sweep as nh_tridiag_solve for callers that may not allocate device
+ * memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in the
+ * reference.  Every array is the caller's DEVICE memory of the given
+ * float type: a, c = N[direction]-1 values, b = N[direction] values (or Nx*Ny*Nz, x fastest, when b_is_3d), rhs and phi =
+ * Nx*Ny*Nz values (x fastest).  Where the reference's |beta| guard fails phi keeps what the caller's array held.  The scratch
+ * of the forward sweep is a file-scope __device__ array of NH_TRIDIAG_STATIC_MAX_ELEMENTS * 8 bytes (8 MiB, held by every GPU
+ * that loads the library until exit): Nx*Ny*Nz beyond that limit is rejected with an error.  The call allocates nothing and
+ * is asynchronous on `cuda_stream` (NULL = the default stream).  All calls on a device share the scratch array, so calls that
+ * overlap on the GPU race: serialise them.  The first call on a device resolves the array's device address
+ * (cudaGetSymbolAddress); make that one outside a graph capture. */
+#define NH_TRIDIAG_STATIC_MAX_ELEMENTS (1 << 20)
+int32_t nh_tridiag_solve_static(int32_t device, int32_t float_type, const int32_t N[3], int32_t direction,
+                                const void* a_dev, const void* b_dev, int32_t b_is_3d, const void* c_dev,
+                                const void* rhs_dev, void* phi_dev, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,6 +6,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("NHSTEP_LIB", os.path.join(_HERE, "libnhstep.so"))   # override: development A/B builds only
 
 NH_MAX_TRACERS = 8
+TRIDIAG_STATIC_MAX_ELEMENTS = 1 << 20
 F32, F64 = 0, 1
 PERIODIC, BOUNDED, FLAT = 0, 1, 2
 ADV_NONE, ADV_CENTERED, ADV_UPWIND, ADV_WENO = 0, 1, 2, 3
@@ -54,7 +55,7 @@ SYMBOLS = [
     "nh_dist_configure", "nh_dist_buffer", "nh_dist_halo", "nh_dist_tendency_substep", "nh_dist_poisson",
     "nh_dist_pressure_correct", "nh_dist_ipc_export", "nh_dist_ipc_import", "nh_model_set_boundary_condition",
     "nh_model_set_boundary_condition_array", "nh_dist_mode",
-    "nh_dist_barrier",
+    "nh_dist_barrier", "nh_tridiag_solve_static",
 ]
 BC_DEFAULT, BC_FLUX, BC_VALUE, BC_GRADIENT = range(4)
 DIST_SEND_LO, DIST_SEND_HI, DIST_RECV_LO, DIST_RECV_HI, DIST_SPECTRAL_A, DIST_SPECTRAL_B = range(6)
@@ -128,6 +129,7 @@ def lib():
                                   C.c_int32, C.POINTER(p)],
             "nh_tridiag_solve": [p, p, p],
             "nh_tridiag_destroy": [p],
+            "nh_tridiag_solve_static": [C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.c_int32, p, p, C.c_int32, p, p, p, p],
             "nh_device_count": [C.POINTER(C.c_int32)],
         }
         for name, args in sig.items():
