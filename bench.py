@@ -9,6 +9,11 @@ device-resident throughput (CUDA events), `e2e` the same step driven through the
 host→device before and u, v, w, p device→host after every step), `roofline` the dominant phase against measured HBM
 bandwidth, `cpu_baseline` the compiled C / OpenMP restatement of the reference's CPU path (oracle/cpu_step.c) on a bounded sample,
 all host threads.
+
+Beside the contract's keys the N = 1 line carries `targets` (the other BASELINE.json configurations timed in the same process:
+the north_star 512³ step, the standalone solvers of configs[2] / configs[3], a 256³ LES-type model) and the N > 1 lines carry
+`parity` (10 steps of a small slab problem on the N ranks against the same problem on rank 0 alone) and `targets` (512³ per
+GPU, the size SURVEY.md §8e defines the scaling target on, and configs[4]: 1024³ global).
 """
 import argparse
 import json
@@ -67,10 +72,11 @@ def smooth_ics(N, seed, size=None, rows=None):
     return out
 
 
-def cpu_oracle_rate(N, steps, warmup=1):
+def cpu_oracle_rate(N, steps, warmup=1, budget_s=None):
     """The compiled C / OpenMP restatement of the reference's CPU() path (oracle/cpu_step.c: one pass per reference
-    kernel, every face flux evaluated twice, full complex FFT — pinned against the NumPy oracle in tests/test_cpu_step.py)
-    on an N³ sample of the same workload, on all host threads OpenMP gives it.  Returns (rate, s/step, threads)."""
+    kernel, every face flux evaluated twice, full complex radix-2 FFT of its own — not FFTW — pinned against the NumPy oracle
+    in tests/test_cpu_step.py) on an N³ sample of the same workload, on all host threads OpenMP gives it.  With ``budget_s`` the
+    timed loop stops early (after at least 2 steps) once that much time has gone.  Returns (rate, s/step, threads, steps)."""
     from oracle.cpu_step import CpuStepModel
     CpuStepModel.use_all_cores()
     m = CpuStepModel((N, N, N), (2 * np.pi,) * 3)
@@ -79,13 +85,18 @@ def cpu_oracle_rate(N, steps, warmup=1):
     dt = 0.2 * (2 * np.pi / N) / 2.0
     m.time_step(dt, max(1, warmup))
     t0 = time.perf_counter()
-    m.time_step(dt, steps)
+    done = 0
+    while done < steps:
+        m.time_step(dt, 1)
+        done += 1
+        if budget_s is not None and done >= 2 and time.perf_counter() - t0 > budget_s:
+            break
     t = time.perf_counter() - t0
-    return N ** 3 * steps / t, t / steps, m.threads()
+    return N ** 3 * done / t, t / done, m.threads(), done
 
 
-CPU_SAMPLE = ("oracle/cpu_step.c (C / OpenMP restatement of the reference CPU() path; Julia is absent on this box), "
-              "{n}^3 cells x {k} steps on {c} threads, {s:.3f} s/step")
+CPU_SAMPLE = ("oracle/cpu_step.c (C / OpenMP restatement of the reference CPU() path with its own radix-2 FFT, not the reference's "
+              "FFTW; Julia is absent on this box), {n}^3 cells x {k} steps on {c} threads, {s:.3f} s/step")
 
 
 class NvmlSampler:
@@ -212,20 +223,263 @@ class ClockSampler:
         return out
 
 
-def run_reference(args, rank):
+def workload_config(args, world):
+    """The `config` object of the JSON line: a static description of the workload, identical on both arms."""
+    N = args.size
+    fx, fy = WORLD_FACTORS.get(world, (1, world))
+    gsize = (N * fx, N * fy, N)
+    exact = args.arithmetic == "exact"
+    return {"workload": f"3D triply-periodic NonhydrostaticModel {N}^3 Float64 WENO5 RK3 FFTBasedPoissonSolver"
+                        + (f" per GPU (global {gsize[0]}x{gsize[1]}x{gsize[2]})" if world > 1 else ""),
+            "arithmetic": ("exact: bit-identical to the reference's CPU arithmetic (no FMA contraction)" if exact else
+                           "contracted: FMA contraction + regrouped WENO5 weights in the tendency sweep; rel. L2 vs the compiled "
+                           "CPU oracle after 100 steps at this size: profiles/r2_parity_errors.jsonl"),
+            "l2_policy": "working set (>= 10 fields x %.0f MB) exceeds the 126 MB L2" % (N ** 3 * 8 / 1e6),
+            "parallelism": "single GPU" if world == 1 else
+            (f"y-slabs over {world} GPUs: kernels store halo rows and FFT transpose blocks into the peers' buffers over NVLink "
+             "(CUDA IPC peer pointers), 5 stream-ordered flag barriers per stage (nh_dist_barrier; no NCCL on the data path)"
+             if not os.environ.get("NHSTEP_NO_P2P") else
+             f"y-slabs over {world} GPUs: NCCL halo exchange + 2 all-to-all transposes per pressure solve")}
+
+
+WORLD_FACTORS = {1: (1, 1), 2: (1, 2), 4: (2, 2), 8: (2, 4), 16: (4, 4)}
+
+
+def run_reference(args, rank, world):
+    """The reference arm: the CPU implementation of the same step on the box's host cores (oracle/cpu_step.c — Julia is
+    absent, so `kind` is "port"), rank 0 only, each step one N³ sample of the workload (N = --ref-size, default --size)."""
     if rank != 0:
         return
-    N = args.ref_size
-    rate, sps, cores = cpu_oracle_rate(N, max(1, args.steps), max(1, args.warmup))
+    N = args.ref_size or args.size
+    rate, sps, cores, done = cpu_oracle_rate(N, max(1, args.steps), max(1, args.warmup))
     line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"3D triply-periodic NonhydrostaticModel {args.size}^3 Float64 WENO5 RK3 FFTBasedPoissonSolver",
-                       "sample": f"{N}^3 cells per step"},
+            "dtype": "f64", "data": "synthetic", "config": workload_config(args, world),
             "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": CPU_SAMPLE.format(n=N, k=args.steps, c=cores, s=sps)},
+                             "sample": CPU_SAMPLE.format(n=N, k=done, c=cores, s=sps)},
             "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
+
+
+FT_B = 8
+# algorithmic bytes per cell and step (SURVEY.md §8d, w = 8 B, F = 3): tendencies + substep 9w + 2·12w, three pressure solves
+# 3·12w, three corrections 3·7w = 90w = 720 B
+STEP_WORDS = 90
+
+
+def event_time(fn, stream_sync):
+    """ms of fn() between two CUDA events on torch's current stream (the library's default stream is the same stream 0)."""
+    import torch
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stream_sync()
+    e0.record()
+    fn()
+    e1.record()
+    stream_sync()
+    return e0.elapsed_time(e1)
+
+
+def solver_target(oc, FT, size, z, reps=10):
+    """Standalone solve on device-resident data (BASELINE.json configs[2] / configs[3]): ms per solve from CUDA events on the
+    solver's stream (nh_poisson_time_solves) and the HBM fraction for SURVEY.md §8d's 10 words per cell."""
+    import ctypes as C
+    import torch
+    from oceananigans_jl_b200._lib import lib, check
+    topo = (oc.Periodic, oc.Periodic, oc.Bounded)
+    kw = dict(x=(0, 1), y=(0, 1), z=z)
+    g = oc.RectilinearGrid(FT, size=size, topology=topo, **kw)
+    solver = (oc.FourierTridiagonalPoissonSolver if g.z_stretched else oc.FFTBasedPoissonSolver)(g)
+    tdt = torch.float64 if FT == np.float64 else torch.float32
+    rhs = torch.randn(size[::-1], dtype=tdt, device="cuda")
+    rhs -= rhs.mean()
+    phi = torch.empty_like(rhs)
+    ms = C.c_float()
+    for n in (3, reps):
+        check(lib().nh_poisson_time_solves(solver._h, C.c_void_p(rhs.data_ptr()), C.c_void_p(phi.data_ptr()), n, C.byref(ms)))
+    per = ms.value / reps
+    cells = size[0] * size[1] * size[2]
+    peak, _ = peaks()
+    gbs = 10 * np.dtype(FT).itemsize * cells / (per * 1e-3) / 1e9
+    return {"ms_per_solve": per, "algorithmic_words_per_cell": 10, "achieved_gbs": gbs, "frac": gbs / peak, "solves": reps}
+
+
+def tanh_faces(Nz):
+    k = np.arange(1, Nz + 2)
+    return np.tanh(1.3 * (2 * (k - 1) / Nz - 1)) / np.tanh(1.3)        # test_time_stepping.jl:439-445
+
+
+def single_gpu_targets(oc, args, exact):
+    """The other BASELINE.json configurations, timed in this process on device-resident data (a few seconds each)."""
+    import torch
+    peak, _ = peaks()
+    out = {}
+
+    def guarded(name, fn):
+        try:
+            out[name] = fn()
+        except Exception as e:                                    # a target that cannot run must not cost the headline line
+            out[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+
+    def step_512():
+        N = 512
+        g = oc.RectilinearGrid(np.float64, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=(oc.Periodic,) * 3)
+        dt = 0.2 * (2 * np.pi / N) / 2.0
+        res = {}
+        for name, ex in (("contracted", False), ("exact", True)):
+            m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), timestepper="RungeKutta3", exact_arithmetic=ex)
+            oc.set_model(m, **smooth_ics(N, 1234))
+            oc.time_step(m, dt, n_steps=3)
+            n = 10
+            ms = event_time(lambda: oc.time_step(m, dt, n_steps=n), torch.cuda.synchronize) / n
+            ph = {}
+            for _ in range(3):
+                for k, v in oc.time_step_profiled(m, dt).items():
+                    ph[k] = ph.get(k, 0.0) + v / 3
+            gbs = STEP_WORDS * FT_B * N ** 3 / (ms * 1e-3) / 1e9
+            res[name] = {"ms_per_step": ms, "value": N ** 3 / (ms * 1e-3), "unit": UNIT, "steps": n, "whole_step_gbs": gbs,
+                         "whole_step_frac": gbs / peak, "phase_ms_per_step": ph,
+                         "pressure_solve_frac": 3 * 12 * FT_B * N ** 3 / (ph["pressure_solve"] * 1e-3) / 1e9 / peak}
+            del m
+            torch.cuda.synchronize()
+        return {"workload": "512^3 (P,P,P) Float64 WENO5 RK3 — the north_star target size", **res}
+
+    def model_les():
+        N = 256
+        g = oc.RectilinearGrid(np.float64, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=(oc.Periodic, oc.Periodic, oc.Bounded))
+        m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), buoyancy=oc.SeawaterBuoyancy(), tracers=("T", "S"),
+                                   coriolis=oc.FPlane(1e-4), closure=oc.ScalarDiffusivity(1e-4, 1e-4), exact_arithmetic=True)
+        ics = smooth_ics(N, 1234)
+        ics["w"] = np.concatenate([ics["w"], ics["w"][:, :, :1]], axis=2)
+        ics["w"][:, :, 0] = 0
+        ics["w"][:, :, -1] = 0
+        z = (np.arange(N) + 0.5) / N
+        ics["T"] = 20 + 0.01 * z[None, None, :] + 1e-3 * ics["u"]
+        ics["S"] = np.full((N, N, N), 35.0)
+        oc.set_model(m, **ics)
+        dt = 0.2 * (2 * np.pi / N) / 2.0
+        oc.time_step(m, dt, n_steps=3)
+        n = 5
+        ms = event_time(lambda: oc.time_step(m, dt, n_steps=n), torch.cuda.synchronize) / n
+        words = 124                                                # SURVEY.md §8d for F = 5 prognostic fields + pHY′
+        gbs = words * FT_B * N ** 3 / (ms * 1e-3) / 1e9
+        return {"workload": "256^3 (P,P,B) Float64 WENO5 RK3, T + S, SeawaterBuoyancy, FPlane, ScalarDiffusivity (exact arithmetic)",
+                "ms_per_step": ms, "value": N ** 3 / (ms * 1e-3), "unit": UNIT, "steps": n, "algorithmic_words_per_cell": words,
+                "whole_step_frac": gbs / peak, "max_abs_divergence": m.max_abs_divergence()}
+
+    def model_c3():
+        Nx, Nz = 512, 256
+        g = oc.RectilinearGrid(np.float64, size=(Nx, Nx, Nz), x=(0, 2 * np.pi), y=(0, 2 * np.pi), z=tanh_faces(Nz),
+                               topology=(oc.Periodic, oc.Periodic, oc.Bounded))
+        m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), exact_arithmetic=True)
+        ics = smooth_ics(Nx, 1234, size=(Nx, Nx, Nz))
+        ics["w"] = np.concatenate([ics["w"], ics["w"][:, :, :1]], axis=2)
+        ics["w"][:, :, 0] = 0
+        ics["w"][:, :, -1] = 0
+        oc.set_model(m, **ics)
+        dt = 0.2 * (2 * np.pi / Nx) / 2.0
+        oc.time_step(m, dt, n_steps=2)
+        n = 3
+        ms = event_time(lambda: oc.time_step(m, dt, n_steps=n), torch.cuda.synchronize) / n
+        cells = Nx * Nx * Nz
+        gbs = STEP_WORDS * FT_B * cells / (ms * 1e-3) / 1e9
+        return {"workload": "configs[3]: 512x512x256 tanh-stretched Bounded z, WENO5 RK3, FourierTridiagonalPoissonSolver (exact arithmetic)",
+                "ms_per_step": ms, "value": cells / (ms * 1e-3), "unit": UNIT, "steps": n, "whole_step_frac": gbs / peak}
+
+    guarded("step_512", step_512)
+    guarded("solver_c2_f64", lambda: solver_target(oc, np.float64, (512, 512, 512), (0, 1)))
+    guarded("solver_c2_f32", lambda: solver_target(oc, np.float32, (512, 512, 512), (0, 1)))
+    guarded("solver_c3_f64", lambda: solver_target(oc, np.float64, (512, 512, 256), tanh_faces(256)))
+    guarded("solver_c3_f32", lambda: solver_target(oc, np.float32, (512, 512, 256), tanh_faces(256)))
+    guarded("model_c3_stretched", model_c3)
+    guarded("model_les_256", model_les)
+    return out
+
+
+def slab_model(oc, D, world, local_rank, gsize, exact, extent_xy):
+    arch = D.Distributed(D.Partition(y=world))
+    return D.DistributedNonhydrostaticModel(arch, np.float64, size=gsize, x=(0, extent_xy[0]), y=(0, extent_xy[1]),
+                                            z=(-2 * np.pi, 0), advection=oc.WENO(order=5), timestepper="RungeKutta3",
+                                            device=local_rank, p2p=not os.environ.get("NHSTEP_NO_P2P"), exact_arithmetic=exact)
+
+
+def multi_gpu_parity(oc, D, world, rank, local_rank, exact):
+    """10 steps of a 64 x (32·N) x 32 problem on the N ranks AND on rank 0 alone (single-GPU model): the gathered u, v, w, p must
+    agree to rel. L2 <= 1e-12 (the distributed FFT runs x, z, y instead of x, y, z, so agreement is to rounding) and the
+    divergence must stay at rounding level.  The driver's test box has one GPU; this is where it sees the slab path checked."""
+    import torch
+    import torch.distributed as dist
+    gsize = (64, 32 * world, 32)
+    ics = smooth_ics(64, 4321, gsize)
+    dt = 0.2 * (2 * np.pi / 64) / 2.0
+    m = slab_model(oc, D, world, local_rank, gsize, exact, (2 * np.pi, 2 * np.pi * world / 2))
+    m.set(**ics)
+    m.time_step(dt, n_steps=10)
+    got = {n: m.gather(n) for n in ("u", "v", "w", "pNHS")}
+    div = m.max_abs_divergence()
+    err = {}
+    if rank == 0:
+        g = oc.RectilinearGrid(np.float64, size=gsize, x=(0, 2 * np.pi), y=(0, 2 * np.pi * world / 2), z=(-2 * np.pi, 0),
+                               topology=(oc.Periodic,) * 3, device=local_rank)
+        s = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), timestepper="RungeKutta3", exact_arithmetic=exact)
+        oc.set_model(s, **ics)
+        oc.time_step(s, dt, n_steps=10)
+        ref = {"u": s.velocities["u"].interior(), "v": s.velocities["v"].interior(), "w": s.velocities["w"].interior(),
+               "pNHS": s.pressures.pNHS.interior()}
+        for n in got:
+            err[n] = float(np.linalg.norm((got[n] - ref[n]).ravel()) / np.linalg.norm(ref[n].ravel()))
+        del s
+    worst = torch.tensor([max(err.values()) if err else 0.0, div], device="cuda", dtype=torch.float64)
+    dist.broadcast(worst, 0)
+    del m
+    torch.cuda.synchronize()
+    ok = bool(worst[0].item() <= 1e-12 and worst[1].item() < 1e-10)
+    return {"workload": f"{gsize[0]}x{gsize[1]}x{gsize[2]} (P,P,P) WENO5 RK3, 10 steps, {world} slabs vs one GPU", "vs_single_gpu": err,
+            "max_div": div, "tolerance": 1e-12, "ok": ok}
+
+
+def timed_slab_run(oc, D, world, rank, local_rank, gsize, extent_xy, exact, warmup, steps):
+    import torch
+    import torch.distributed as dist
+    m = slab_model(oc, D, world, local_rank, gsize, exact, extent_xy)
+    m.set_local(**smooth_ics(gsize[0], 1234, gsize, (m.j0, m.NyL)))
+    N = gsize[2]
+    dt = 0.2 * (2 * np.pi / N) / 2.0
+    m.time_step(dt, n_steps=warmup)
+    dist.barrier()
+    ms = event_time(lambda: m.time_step(dt, n_steps=steps), torch.cuda.synchronize)
+    t = torch.tensor([ms], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    div = m.max_abs_divergence()
+    del m
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    cells = gsize[0] * gsize[1] * gsize[2]
+    peak, _ = peaks()
+    gbs = STEP_WORDS * FT_B * cells / world / (ms * 1e-3) / 1e9
+    return {"global_size": list(gsize), "ms_per_step": ms, "value": cells / (ms * 1e-3), "unit": UNIT, "steps": steps, "warmup": warmup,
+            "whole_step_frac_per_gpu": gbs / peak, "max_abs_divergence": div}
+
+
+def multi_gpu_targets(oc, D, world, rank, local_rank, exact):
+    """512³ cells per GPU (the per-GPU size SURVEY.md §8e defines the ≥ 80 % weak-scaling target on; compare `value` / N with
+    targets.step_512 of the N = 1 line) and BASELINE.json configs[4]: 1024³ global, strong scaling from 2 GPUs."""
+    out = {}
+    fx, fy = WORLD_FACTORS[world]
+
+    def guarded(name, fn):
+        try:
+            out[name] = fn()
+        except Exception as e:
+            out[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+
+    guarded("weak_512_per_gpu", lambda: {"scaling": "weak", **timed_slab_run(
+        oc, D, world, rank, local_rank, (512 * fx, 512 * fy, 512), (2 * np.pi * fx, 2 * np.pi * fy), exact, 2, 5)})
+    guarded("c4_1024_cubed", lambda: {"scaling": "strong", **timed_slab_run(
+        oc, D, world, rank, local_rank, (1024, 1024, 1024), (2 * np.pi, 2 * np.pi), exact, 2, 3)})
+    return out
 
 
 def main():
@@ -235,8 +489,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--size", type=int, default=256)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--ref-size", type=int, default=128)
+    ap.add_argument("--ref-size", type=int, default=None, help="cells per side of the CPU sample (default: --size)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-targets", action="store_true", help="skip the `targets` / `parity` records (development)")
     # contracted: FMA contraction in the tendency sweep (what a GPU build of the reference computes; within the north_star
     # tolerance of the CPU reference); exact: bit-identical to the reference's CPU arithmetic.  Both are reported at N = 1.
     ap.add_argument("--arithmetic", choices=["contracted", "exact"], default="contracted")
@@ -246,7 +501,7 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
-        run_reference(args, rank)
+        run_reference(args, rank, world)
         return
 
     import torch
@@ -257,9 +512,12 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        if world not in WORLD_FACTORS:
+            raise SystemExit("--gpus must be 1, 2, 4, 8 or 16")
 
     N = args.size
     dt = 0.2 * (2 * np.pi / N) / 2.0
+    parity = None
     if world == 1:
         gsize = (N, N, N)
         grid = oc.RectilinearGrid(np.float64, size=gsize, extent=(2 * np.pi,) * 3, topology=(oc.Periodic,) * 3, device=local_rank)
@@ -270,16 +528,11 @@ def main():
     else:
         # weak scaling: N³ cells per GPU, the global grid grows in x and y at constant spacing; y-slabs over the ranks
         from oceananigans_jl_b200 import distributed as D
-        factors = {2: (1, 2), 4: (2, 2), 8: (2, 4), 16: (4, 4)}
-        if world not in factors:
-            raise SystemExit("--gpus must be 1, 2, 4, 8 or 16")
-        fx, fy = factors[world]
+        if not args.no_targets:
+            parity = multi_gpu_parity(oc, D, world, rank, local_rank, exact)
+        fx, fy = WORLD_FACTORS[world]
         gsize = (N * fx, N * fy, N)
-        arch = D.Distributed(D.Partition(y=world))
-        model = D.DistributedNonhydrostaticModel(arch, np.float64, size=gsize, x=(0, 2 * np.pi * fx), y=(0, 2 * np.pi * fy),
-                                                 z=(-2 * np.pi, 0), advection=oc.WENO(order=5), timestepper="RungeKutta3",
-                                                 device=local_rank, p2p=not os.environ.get("NHSTEP_NO_P2P"),
-                                                 exact_arithmetic=exact)
+        model = slab_model(oc, D, world, local_rank, gsize, exact, (2 * np.pi * fx, 2 * np.pi * fy))
         model.set_local(**smooth_ics(N, 1234, gsize, (model.j0, model.NyL)))
         step = lambda n=1: model.time_step(dt, n_steps=n)                                  # noqa: E731
         profiled = lambda: model.time_step_profiled(dt)                                    # noqa: E731
@@ -313,11 +566,10 @@ def main():
         ms = float(t.item())
     ms_per_step = ms / args.steps
     value = cells * world * args.steps / (ms * 1e-3)
-    assert np.isfinite(model.max_abs_divergence()), "model blew up"
+    max_div = model.max_abs_divergence()
+    assert max_div < 1e-9, f"the timed model lost incompressibility: max |div U| = {max_div}"
 
-    # ---- phases (per-kernel-group CUDA-event times; same step composed from the individual ABI calls) ----
-    FT_B = 8
-    # CUDA events on the model's stream between the phases of the very same time_step! (nh_time_step_profiled)
+    # ---- phases: CUDA events on the model's stream between the phases of the very same time_step! (nh_time_step_profiled)
     phases = {"tendencies_substep": 0.0, "pressure_solve": 0.0, "pressure_correct": 0.0, "other": 0.0}
     nprof = max(1, min(args.steps, 5))
     for _ in range(nprof):
@@ -335,17 +587,18 @@ def main():
     dom = max(alg, key=lambda k: phases[k])
     peak, peak_kind = peaks()
     achieved = alg[dom] / (phases[dom] * 1e-3) / 1e9
-    step_bytes = 90 * FT_B * cells
+    step_bytes = STEP_WORDS * FT_B * cells
     roofline = {"bound": "hbm", "kernel": kernel_names[dom], "launches_per_step": 3,
                 "algorithmic_bytes_per_launch": alg[dom] / 3, "ms_per_launch": phases[dom] / 3,
                 "achieved": achieved, "peak": peak, "peak_source": peak_kind, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": measured_traffic(dom, N),
                 "whole_step": {"algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms_per_step * 1e-3) / 1e9,
                                "frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak},
-                "phase_ms_per_step": phases}
+                "phase_ms_per_step": phases,
+                "phase_frac": {k: alg[k] / (phases[k] * 1e-3) / 1e9 / peak for k in alg if phases[k] > 0}}
     if dom == "tendencies_substep":
         # the sweep is FP64-issue bound, not HBM bound: FP64 instructions per cell (ncu opcode mix,
-        # profiles/r1_tendency_sass_mix.md) against 64 FP64 instr/clk/SM × 148 SMs at the sampled SM clock
+        # profiles/) against 64 FP64 instr/clk/SM × 148 SMs at the sampled SM clock
         mhz = (clocks or {}).get("sm_mhz") or 1965.0
         fp64_peak = 64 * 148 * mhz * 1e6
         per_cell = FP64_INSTR_PER_CELL[args.arithmetic]
@@ -402,28 +655,33 @@ def main():
     e2e = {"value": cells * world * e2e_steps / e2e_t, "unit": UNIT, "h2d_bytes_per_step": 3 * cells * FT_B * world,
            "d2h_bytes_per_step": 4 * cells * FT_B * world, "steps": e2e_steps}
 
+    # ---- the rest of the contract's configurations, in the same process ----
+    targets = None
+    if not args.no_targets:
+        del model, host_np, host_out
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+        if world == 1:
+            targets = single_gpu_targets(oc, args, exact)
+        else:
+            targets = multi_gpu_targets(oc, D, world, rank, local_rank, exact)
+
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            rate, sps, cores = cpu_oracle_rate(args.ref_size, 10)
+            rs = args.ref_size or args.size
+            rate, sps, cores, done = cpu_oracle_rate(rs, 10, 1, budget_s=25.0)
             cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": CPU_SAMPLE.format(n=args.ref_size, k=10, c=cores, s=sps)}
+                   "sample": CPU_SAMPLE.format(n=rs, k=done, c=cores, s=sps)}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-                "data": "synthetic",
-                "config": {"workload": f"3D triply-periodic NonhydrostaticModel {N}^3 Float64 WENO5 RK3 FFTBasedPoissonSolver"
-                           + (f" per GPU (global {gsize[0]}x{gsize[1]}x{gsize[2]})" if world > 1 else ""),
-                           "arithmetic": ("exact: bit-identical to the reference's CPU arithmetic (no FMA contraction)" if exact else
-                                          "contracted: FMA contraction + regrouped WENO5 weights in the tendency sweep, "
-                                          "rel. L2 <= 1e-12 vs the oracle after 100 steps (tests/test_gpu_parity.py)"),
-                           "other_arithmetic": other,
-                           "l2_policy": "working set (>= 10 fields x %.0f MB) exceeds the 126 MB L2" % (cells * FT_B / 1e6),
-                           "parallelism": "single GPU" if world == 1 else
-                           (f"y-slabs over {world} GPUs: kernels store halo rows and FFT transpose blocks into the peers' "
-                            "buffers over NVLink (CUDA IPC), 5 one-element NCCL all-reduces per stage as barriers"
-                            if getattr(model, "p2p", False) else
-                            f"y-slabs over {world} GPUs: NCCL halo exchange + 2 all-to-all transposes per pressure solve")},
-                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+                "data": "synthetic", "config": workload_config(args, world), "other_arithmetic": other,
+                "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+                "max_abs_divergence": max_div}
+        if parity is not None:
+            line["parity"] = parity
+        if targets is not None:
+            line["targets"] = targets
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -104,6 +104,12 @@ int32_t nh_grid_destroy(nh_grid* grid);
 int32_t nh_grid_info(const nh_grid* grid, nh_grid_desc* out);          /* desc with the final halo; z_faces = NULL */
 /* Δzᵃᵃᶜ[k], Δzᵃᵃᶠ[k] for k = 1-Hz … Nz+Hz as doubles (src/Grids/grid_generation.jl:34-135); spacing[0] = Δx, [1] = Δy */
 int32_t nh_grid_spacings(const nh_grid* grid, double* dxdy, double* dzc, double* dzf, int64_t nz_entries);
+/* uniform_reconstruction_coefficients(FT, Val(bias), buffer) — src/Advection/reconstruction_coefficients.jl:138-140 — and the
+ * WENO sub-stencil coefficients / optimal weights (weno_interpolants.jl:77-93): the tables the kernels use, as generated on the
+ * host (exact rational -> FT, last = 1 - sum).  which: 0 symmetric (2*buffer values), 1 left, 2 right (2*buffer-1 values),
+ * 3 WENO sub-stencil r (buffer values), 4 WENO optimal weights C* (buffer values).  Values are returned as doubles (exact
+ * images of the FT numbers); *count = how many.  Host-only: needs no device. */
+int32_t nh_reconstruction_coefficients(int32_t float_type, int32_t which, int32_t buffer, int32_t r, double out[8], int32_t* count);
 
 /* ---- model ----------------------------------------------------------------------------------------------- */
 int32_t nh_model_create(nh_grid* grid, const nh_model_desc* desc, nh_model** out);
@@ -209,8 +215,18 @@ int32_t nh_dist_ipc_export(nh_model* model, unsigned char* blob, int64_t capacit
 int32_t nh_dist_ipc_import(nh_model* model, const unsigned char* all_blobs, int64_t nbytes);
 /* Stream-ordered barrier of the peer-to-peer group (replaces the MPI/NCCL synchronisation between the pieces of a stage,
  * cf. sync_device! + MPI.Waitall of halo_communication.jl:91-112): one small kernel publishes an epoch into every peer's flag
- * array over NVLink (release, system scope) and waits for all peers' epochs (acquire).  No reference counterpart. */
+ * array over NVLink (release, system scope) and waits for all peers' epochs (acquire).  No reference counterpart.
+ * The wait is on the GPU: a rank that waits longer than NHSTEP_BARRIER_TIMEOUT_S seconds (environment, default 600, 0 = for ever)
+ * for a peer traps its context, like a collective watchdog.  On a complete-path slab model (nh_dist_mode = 2) every call that
+ * fills halos (nh_set_field(INTERIOR) + nh_fill_halo_regions, nh_set_state_finalize, nh_time_step, nh_get_field(PARENT) …)
+ * issues such barriers and is therefore COLLECTIVE: every rank must make it, in the same order. */
 int32_t nh_dist_barrier(nh_model* model);
+/* transpose_z_to_y!(…) (direction 0) / transpose_y_to_z!(…) (direction 1) — src/DistributedComputations/distributed_transpose.jl:
+ * 25-191 — as pure data movement between the two spectral buffers of nh_dist_buffer over NVLink peer stores (peer-to-peer mode):
+ * block d of this rank's source buffer lands, bit for bit, in block `rank` of rank d's destination buffer.  The time step folds
+ * these copies into its FFT passes; callers bracket this entry with nh_dist_barrier.  A -> B -> A is the identity
+ * (test/test_distributed_transpose.jl:13-54). */
+int32_t nh_dist_transpose(nh_model* model, int32_t direction);
 
 /* ---- standalone solvers ---------------------------------------------------------------------------------- */
 /* FFTBasedPoissonSolver(grid) — src/Solvers/fft_based_poisson_solver.jl:52-74;

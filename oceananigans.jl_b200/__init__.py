@@ -105,6 +105,15 @@ class RectilinearGrid:
     def z_stretched(self):
         return self._zfaces is not None
 
+    def spacings(self):
+        """(Δx, Δy, Δzᵃᵃᶜ[1-Hz … Nz+Hz], Δzᵃᵃᶠ[1-Hz … Nz+Hz]) as the library holds them (xspacings / yspacings / zspacings,
+        src/Grids/nodes_and_spacings.jl); the z arrays start at index 1 - Hz."""
+        n = self.N[2] + 2 * self.H[2]
+        dxdy, dzc, dzf = (C.c_double * 2)(), (C.c_double * n)(), (C.c_double * n)()
+        check(lib().nh_grid_spacings(self._h, dxdy, dzc, dzf, n))
+        return (self.FT(dxdy[0]), self.FT(dxdy[1]), np.array(dzc, dtype=np.float64).astype(self.FT),
+                np.array(dzf, dtype=np.float64).astype(self.FT))
+
     def nodes(self, d, loc):
         """Interior node coordinates along dim d at 'c' or 'f' (src/Grids/grid_generation.jl:98-135, :34-95)."""
         FT, N = self.FT, self.N[d]
@@ -118,6 +127,16 @@ class RectilinearGrid:
         dl = (c2 - c1) / N
         start = c1 if loc == "f" else c1 + dl / 2
         return np.array([float(start + i * dl) for i in range(n)], dtype=np.float64).astype(FT)
+
+
+def reconstruction_coefficients(FT, bias, buffer, r=0):
+    """uniform_reconstruction_coefficients(FT, Val(bias), buffer) (bias = "symmetric" | "left" | "right"), the WENO sub-stencil
+    coefficients (bias = "weno", stencil r) or optimal weights (bias = "weno_optimal") as the kernels' tables hold them —
+    src/Advection/reconstruction_coefficients.jl:138-140, weno_interpolants.jl:77-93.  Host-only (no device needed)."""
+    which = {"symmetric": 0, "left": 1, "right": 2, "weno": 3, "weno_optimal": 4}[bias]
+    out, n = (C.c_double * 8)(), C.c_int32(0)
+    check(lib().nh_reconstruction_coefficients(_ft_code(FT), which, int(buffer), int(r), out, C.byref(n)))
+    return tuple(np.dtype(FT).type(out[q]) for q in range(n.value))
 
 
 # ---- advection schemes, physics ----------------------------------------------------------------------------

@@ -55,7 +55,7 @@ SYMBOLS = [
     "nh_dist_configure", "nh_dist_buffer", "nh_dist_halo", "nh_dist_tendency_substep", "nh_dist_poisson",
     "nh_dist_pressure_correct", "nh_dist_ipc_export", "nh_dist_ipc_import", "nh_model_set_boundary_condition",
     "nh_model_set_boundary_condition_array", "nh_dist_mode",
-    "nh_dist_barrier", "nh_tridiag_solve_static",
+    "nh_dist_barrier", "nh_dist_transpose", "nh_tridiag_solve_static", "nh_reconstruction_coefficients",
 ]
 BC_DEFAULT, BC_FLUX, BC_VALUE, BC_GRADIENT = range(4)
 DIST_SEND_LO, DIST_SEND_HI, DIST_RECV_LO, DIST_RECV_HI, DIST_SPECTRAL_A, DIST_SPECTRAL_B = range(6)
@@ -119,6 +119,7 @@ def lib():
             "nh_dist_ipc_export": [p, p, C.c_int64, C.POINTER(C.c_int64)],
             "nh_dist_ipc_import": [p, p, C.c_int64],
             "nh_dist_barrier": [p],
+            "nh_dist_transpose": [p, C.c_int32],
             "nh_poisson_create": [p, C.c_int32, C.POINTER(p)],
             "nh_poisson_destroy": [p],
             "nh_poisson_solve": [p, p, p, C.c_double, C.c_int32],
@@ -129,6 +130,7 @@ def lib():
                                   C.c_int32, C.POINTER(p)],
             "nh_tridiag_solve": [p, p, p],
             "nh_tridiag_destroy": [p],
+            "nh_reconstruction_coefficients": [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int32)],
             "nh_tridiag_solve_static": [C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.c_int32, p, p, C.c_int32, p, p, p, p],
             "nh_device_count": [C.POINTER(C.c_int32)],
         }

@@ -152,6 +152,28 @@ int32_t nh_grid_spacings(const nh_grid* grid, double* dxdy, double* dzc, double*
   NH_CATCH
 }
 
+int32_t nh_reconstruction_coefficients(int32_t float_type, int32_t which, int32_t buffer, int32_t r, double out[8], int32_t* count) {
+  NH_TRY
+  NH_REQUIRE(out && count, "null argument");
+  NH_REQUIRE(float_type == NH_F32 || float_type == NH_F64, "float_type must be NH_F32 or NH_F64");
+  auto fill = [&](auto tag) {
+    typedef decltype(tag) FT;
+    nhhost::Tables<FT> T;
+    nhhost::make_scheme_tables<FT>(T);
+    int n = 0;
+    const FT* src = nullptr;
+    if (which == 0) { NH_REQUIRE(buffer >= 1 && buffer <= 2, "symmetric tables exist for buffer 1, 2"); src = T.sym[buffer]; n = 2 * buffer; }
+    else if (which == 1 || which == 2) { NH_REQUIRE(buffer >= 1 && buffer <= 3, "upwind tables exist for buffer 1..3"); src = which == 1 ? T.upl[buffer] : T.upr[buffer]; n = 2 * buffer - 1; }
+    else if (which == 3) { NH_REQUIRE(buffer >= 2 && buffer <= 3 && r >= 0 && r < buffer, "WENO tables exist for buffer 2, 3 and 0 <= r < buffer"); src = T.wc[buffer][r]; n = buffer; }
+    else if (which == 4) { NH_REQUIRE(buffer >= 2 && buffer <= 3, "WENO tables exist for buffer 2, 3"); src = T.cstar[buffer]; n = buffer; }
+    else throw NhError("which must be 0..4");
+    for (int q = 0; q < n; ++q) out[q] = (double)src[q];
+    *count = n;
+  };
+  if (float_type == NH_F32) fill(float()); else fill(double());
+  NH_CATCH
+}
+
 int32_t nh_model_create(nh_grid* grid, const nh_model_desc* desc, nh_model** out) {
   NH_TRY
   NH_REQUIRE(grid && desc && out, "null argument");
@@ -195,6 +217,7 @@ int32_t nh_dist_poisson(nh_model* m, int32_t phase, double stage_dt) { MODEL_CAL
 int32_t nh_dist_pressure_correct(nh_model* m, double stage_dt) { MODEL_CALL(m, m->dist_pressure_correct(stage_dt)) }
 int32_t nh_dist_ipc_export(nh_model* m, unsigned char* blob, int64_t capacity, int64_t* nbytes) { MODEL_CALL(m, int64_t n = m->dist_ipc_export(blob, capacity); if (nbytes) *nbytes = n) }
 int32_t nh_dist_barrier(nh_model* m) { MODEL_CALL(m, m->dist_barrier()) }
+int32_t nh_dist_transpose(nh_model* m, int32_t direction) { MODEL_CALL(m, m->dist_transpose(direction)) }
 int32_t nh_dist_ipc_import(nh_model* m, const unsigned char* blobs, int64_t nbytes) { MODEL_CALL(m, NH_REQUIRE(blobs, "null argument"); m->dist_ipc_import(blobs, nbytes)) }
 int32_t nh_launch_count(const nh_model* m, int64_t* count) { NH_TRY NH_REQUIRE(m && count, "null argument"); *count = m->lc.n; NH_CATCH }
 

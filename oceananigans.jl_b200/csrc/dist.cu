@@ -20,6 +20,7 @@ void Model<FT>::dist_configure(int rank, int nranks, double y0, double y1, int N
   FT dy;
   dist.create(gh, rank, nranks, y0, y1, Ny, dy, generic);
   gh.g.dy = dy;                       // the global spacing, so every rank computes with the same metric bits
+  if (desc.has_closure == NH_CLOSURE_SMAGORINSKY || desc.has_closure == NH_CLOSURE_SMAGORINSKY_LILLY) build_filter_width();
   pfast.ok = false;                   // the single-GPU solve would wrap y locally
 }
 
@@ -194,7 +195,31 @@ void Model<FT>::dist_barrier() {
   PeerBarrierJob J;
   for (int r = 0; r < PF_MAXR; ++r) J.peer_flags[r] = dist.peer_flags[r];
   J.rank = dist.rank; J.R = dist.R; J.epoch = ++dist.epoch;
+  static const unsigned long long timeout_ns = [] {
+    const char* e = getenv("NHSTEP_BARRIER_TIMEOUT_S");
+    const double s = e ? atof(e) : 600.0;
+    return s > 0 ? (unsigned long long)(s * 1e9) : 0ull;
+  }();
+  J.timeout_ns = timeout_ns;
   peer_barrier_kernel<<<1, 32, 0, stream>>>(J);
+  lc.n++;
+  CUDA_CHECK(cudaGetLastError());
+}
+
+// transpose_z_to_y! (direction 0: block d of the z-local buffer A → block `rank` of rank d's y-local buffer B) and
+// transpose_y_to_z! (direction 1: block s of B → block `rank` of rank s's A) on their own, as peer stores over NVLink
+// (distributed_transpose.jl:25-191).  The step itself folds these copies into the FFT passes on either side; this entry is the
+// pure data movement, bit for bit, for callers and for the round-trip test of test_distributed_transpose.jl:13-54.
+template <typename FT>
+void Model<FT>::dist_transpose(int direction) {
+  NH_REQUIRE(dist.on && dist.p2p, "nh_dist_transpose needs the peer-to-peer mode (nh_dist_ipc_import)");
+  NH_REQUIRE(direction == 0 || direction == 1, "direction must be 0 (z-local -> y-local) or 1 (y-local -> z-local)");
+  ScatterJob<CT> Sj;
+  Sj.src = direction == 0 ? dist.A.p : dist.B.p;
+  Sj.chunk = (long long)dist.J.Cx * dist.J.Ny * dist.J.Nz;
+  Sj.R = dist.R; Sj.rank = dist.rank;
+  for (int d = 0; d < PF_MAXR; ++d) Sj.peer[d] = direction == 0 ? dist.peerB[d] : dist.peerA[d];
+  pd_scatter_kernel<CT><<<(unsigned)ceil_div(Sj.chunk * dist.R, 256), 256, 0, stream>>>(Sj);
   lc.n++;
   CUDA_CHECK(cudaGetLastError());
 }
@@ -208,6 +233,7 @@ void Model<FT>::dist_barrier() {
   template void Model<FT>::dist_pressure_correct(double);                                \
   template int64_t Model<FT>::dist_ipc_export(unsigned char*, int64_t);                  \
   template void Model<FT>::dist_ipc_import(const unsigned char*, int64_t);               \
-  template void Model<FT>::dist_barrier();
+  template void Model<FT>::dist_barrier();                                               \
+  template void Model<FT>::dist_transpose(int);
 NH_DIST_INSTANTIATE(float)
 NH_DIST_INSTANTIATE(double)

@@ -170,11 +170,14 @@ __global__ void __launch_bounds__(256) y_halo_pack_kernel(const __grid_constant_
 // Thread r < R publishes this rank's epoch into slot `rank` of rank r's flag array (release, system scope: every store of
 // the kernels that ran before this one on the stream — including their stores into peer memory — is ordered before it),
 // then waits until slot r of its own array has reached the epoch (acquire).  All ranks issue the same sequence of
-// barriers, so epochs only grow.  A wait that lasts longer than 20 s traps (a peer died) instead of hanging the GPU.
+// barriers, so epochs only grow.  A wait that lasts longer than `timeout_ns` traps (a peer died) instead of hanging the GPU:
+// 10 minutes by default, like a collective watchdog (ordinary host skew between ranks — output, a gather, a Python pause —
+// must not kill the context); NHSTEP_BARRIER_TIMEOUT_S overrides it, 0 waits for ever.
 struct PeerBarrierJob {
   unsigned int* peer_flags[PF_MAXR];     // flag arrays of all ranks (own array at index rank)
   int rank, R;
   unsigned int epoch;
+  unsigned long long timeout_ns;         // 0: no timeout
 };
 
 static __global__ void peer_barrier_kernel(const __grid_constant__ PeerBarrierJob J) {
@@ -192,7 +195,7 @@ static __global__ void peer_barrier_kernel(const __grid_constant__ PeerBarrierJo
     if ((int)(v - J.epoch) >= 0) break;
     unsigned long long t1;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-    if (t1 - t0 > 20000000000ull) __trap();
+    if (J.timeout_ns != 0ull && t1 - t0 > J.timeout_ns) __trap();
   }
   __threadfence_system();
 }

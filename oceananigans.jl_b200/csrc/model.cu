@@ -76,20 +76,12 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   } else if (d.has_closure >= NH_CLOSURE_SMAGORINSKY) {
     // build_diffusivity_fields (smagorinsky.jl:123-133); filter width Δᶠ = cbrt(Δx·Δy·Δz), correctly rounded on the host
     nue = alloc_field();
-    std::vector<FT> t(gh.g.N[2]);
-    for (int k = 1; k <= gh.g.N[2]; ++k) {
-      FT dz = gh.g.topo[2] == NH_FLAT ? FT(1) : gh.dzc_h[k + gh.g.zoff];
-      FT d3 = gh.g.dx * gh.g.dy * dz;
-      FT df = nhhost::cbrt_correctly_rounded<FT>(d3);
-      t[k - 1] = df * df;
-    }
-    df2.upload(t);
+    build_filter_width();
     for (int n = 0; n < ntr; ++n) NH_REQUIRE(d.smagorinsky_Pr[n] != 0, "Smagorinsky: Pr must be non-zero for every tracer");
   }
 
   solver.lc = &lc;
-  solver.stream = stream;
-  solver.create(gh, gh.z_stretched ? NH_SOLVER_FOURIER_TRIDIAGONAL : NH_SOLVER_FFT);
+  solver.stream = stream;               // the complete solver's N³ complex buffers are allocated on first use (ensure_solver)
   red.alloc(1024);
 
   rk_g1 = (FT)8 / (FT)15; rk_g2 = (FT)5 / (FT)12; rk_g3 = (FT)3 / (FT)4;
@@ -112,6 +104,27 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
     CUDA_CHECK(cudaFuncSetAttribute(tendency_fast_kernel<FT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TF_SMEM_ELEMS * sizeof(FT))));
   }
   update_state(0);
+}
+
+// Smagorinsky filter width Δᶠ² per level from the CURRENT metrics (dist_configure replaces Δy by the global spacing)
+template <typename FT>
+void Model<FT>::build_filter_width() {
+  std::vector<FT> t(gh.g.N[2]);
+  for (int k = 1; k <= gh.g.N[2]; ++k) {
+    FT dz = gh.g.topo[2] == NH_FLAT ? FT(1) : gh.dzc_h[k + gh.g.zoff];
+    FT d3 = gh.g.dx * gh.g.dy * dz;
+    FT df = nhhost::cbrt_correctly_rounded<FT>(d3);
+    t[k - 1] = df * df;
+  }
+  df2.upload(t);
+}
+
+// the complete (any topology, any size) Poisson solver: only models that the fused passes do not cover ever need it
+template <typename FT>
+void Model<FT>::ensure_solver() {
+  if (solver_ready) return;
+  solver.create(gh, gh.z_stretched ? NH_SOLVER_FOURIER_TRIDIAGONAL : NH_SOLVER_FFT);
+  solver_ready = true;
 }
 
 template <typename FT>
@@ -161,6 +174,7 @@ void Model<FT>::fast_pressure(double stage_dt) {
   periodic_halo_all_kernel<FT><<<hg, 128, 0, stream>>>(H);
   KLAUNCH(lc);
   dim3 blk(64, 4, 1);
+  ensure_solver();
   source_term_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(g, F[0], F[1], F[2], stage_dt, 0, solver.A.p);
   KLAUNCH(lc);
   CT* sol = solver.solve(0.0);
@@ -566,6 +580,7 @@ void Model<FT>::calculate_pressure_correction(double dt) {
     CUDA_CHECK(cudaGetLastError());
     return;
   }
+  ensure_solver();
   CT* rhs = solver.A.p;
   source_term_kernel<FT, CT><<<grid3(blk), blk, 0, stream>>>(gh.g, F[0], F[1], F[2], dt,
                                                             solver.kind == NH_SOLVER_FOURIER_TRIDIAGONAL ? 1 : 0, rhs);
@@ -594,6 +609,9 @@ void Model<FT>::time_step(double dt, int euler) {
   if (fast) {
     // same sequence as below with compute_tendencies! + the next substep fused and the halo fills folded into the
     // pressure-correction kernel; Gⁿ of the final state is refreshed lazily (ensure_tendencies).
+    // update_state! at iteration 0 (runge_kutta_3.jl:81, quasi_adams_bashforth_2.jl:80): a field set without the set!
+    // tail (Field.set → nh_set_field) has stale halos, and the fused sweep reads filled ones
+    if (clock.iteration == 0) update_state(0);
     if (desc.timestepper == NH_RK3) {
       double first = (double)rk_g1 * dt, second = (double)(FT)(rk_g2 + rk_z2) * dt, third = (double)(FT)(rk_g3 + rk_z3) * dt;
       double t_next = clock.time + dt;

@@ -307,6 +307,7 @@ struct nh_model {
   virtual int64_t dist_ipc_export(unsigned char* blob, int64_t capacity) = 0;
   virtual void dist_ipc_import(const unsigned char* blobs, int64_t nbytes) = 0;
   virtual void dist_barrier() = 0;
+  virtual void dist_transpose(int direction) = 0;
   // phase timing (nh_time_step_profiled): CUDA events on the model's stream between the phases of one step
   bool profiling = false;
   std::vector<std::pair<int, cudaEvent_t>> marks;
@@ -364,6 +365,9 @@ struct Model : nh_model {
   void fast_stage(int mode, FT dt, FT c1, FT c2, double stage_dt);
   void fast_pressure(double stage_dt);
   void ensure_tendencies();
+  void ensure_solver();
+  void build_filter_width();
+  bool solver_ready = false;
   void ensure_p_halo();
 
   Model(const nh_grid& grid, const nh_model_desc& d);
@@ -419,6 +423,7 @@ struct Model : nh_model {
   int64_t dist_ipc_export(unsigned char* blob, int64_t capacity) override;
   void dist_ipc_import(const unsigned char* blobs, int64_t nbytes) override;
   void dist_barrier() override;
+  void dist_transpose(int direction) override;
 };
 
 struct nh_poisson {

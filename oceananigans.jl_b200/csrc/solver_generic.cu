@@ -63,6 +63,8 @@ void PoissonGeneric<FT>::create(const GridHost<FT>& gh, int kind_) {
   if (kind == NH_SOLVER_FOURIER_TRIDIAGONAL)
     NH_REQUIRE(topo[2] == NH_BOUNDED, "`FourierTridiagonalPoissonSolver` can only be used when the stretched direction's topology is `Bounded`.");
   A.alloc(count());
+  // per device, so once per solver (the current device is the solver's)
+  CUDA_CHECK(cudaFuncSetAttribute(line_transform_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   int ndims = kind == NH_SOLVER_FFT ? 3 : 2;
   for (int e = 0; e < 3; ++e) {
     // h = L/N evaluated in FT like the reference's `L / N` (poisson_eigenvalues.jl:10)
@@ -116,11 +118,6 @@ void PoissonGeneric<FT>::transform(CT* a, int d, int mode) {
   NH_REQUIRE(per_line <= 200 * 1024, "line too long for the shared-memory transform");
   J.lpb = lpb;
   size_t smem = per_line * lpb;
-  static bool attr_set = false;
-  if (!attr_set) {
-    CUDA_CHECK(cudaFuncSetAttribute(line_transform_kernel<FT, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set = true;
-  }
   int blocks = (int)((J.nlines + lpb - 1) / lpb);
   if (N[d] == 1) {
     // dummy tables are never read for N == 1 except tw4[0] = 1 in the DCT modes

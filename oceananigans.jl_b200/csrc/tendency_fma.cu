@@ -17,11 +17,14 @@
 
 template <typename FT>
 void launch_fused_tendency_fma(const FastTendJob<FT>& J, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  // the attribute is per device: set once for each device a model of this process lives on
+  static bool attr_set[64] = {};
+  int dev = 0;
+  CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev >= 64 || !attr_set[dev]) {
     CUDA_CHECK(cudaFuncSetAttribute(tendency_fast_kernel<FT, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)(TF_SMEM_ELEMS * sizeof(FT))));
-    attr_set = true;
+    if (dev < 64) attr_set[dev] = true;
   }
   const GridDev<FT>& g = J.g;
   dim3 grd(ceil_div(g.N[0], TF_TX), ceil_div(g.N[1], TF_TY), ceil_div(g.N[2], TF_TZ));

@@ -392,56 +392,6 @@ __global__ void __launch_bounds__(128) tendency_generic_kernel(const __grid_cons
 #ifndef TG_MINBLOCKS
 #define TG_MINBLOCKS 1
 #endif
-#ifndef TG_FASTFLUX
-#define TG_FASTFLUX 0    // WENO5 full-order flux points read their stencil by pointer stepping (tiled_adv_flux); off until measured
-#endif
-
-// Advective face flux of the tiled kernel.  Where the scheme is WENO(order = 5) and the flux point is far enough from any wall
-// that topologically_conditional_interpolation keeps the full order (recon_level == 3 along the flux direction and along the
-// direction of the advecting-velocity interpolation), the stencil is read by stepping a pointer and the level / kind dispatch is
-// skipped; the arithmetic is that of momentum_flux / tracer_flux (symmetric_interp's four-point sum with the area folded in per
-// point, biased_interp's upwind selection, weno5_from_q), so the bits are the same.  Everything else takes the generic functions.
-template <typename FT, int a, int b>
-__device__ __forceinline__ FT tiled_adv_flux(const TendParams<FT>& P, const FT* c, int i, int j, int k) {
-  const GridDev<FT>& g = P.g;
-  constexpr int av = a == 3 ? 0 : a;
-  constexpr int sym_dim = a == 3 ? b : (av == b ? b : av);
-  constexpr int stag_c = (a != 3 && av == b) ? 1 : 0;
-  const SchemeDev s = P.adv[b];
-  const int idx_b = b == 0 ? i : (b == 1 ? j : k), idx_s = sym_dim == 0 ? i : (sym_dim == 1 ? j : k);
-  auto full_order = [&](int d, int idx) {
-    return g.topo[d] == NH_PERIODIC || (g.topo[d] == NH_BOUNDED && idx >= (stag_c ? 3 : 4) && idx <= g.N[d] - 2);
-  };
-  if (TG_FASTFLUX && s.kind == NH_ADV_WENO && s.B == 3 && full_order(b, idx_b) && (a == 3 || full_order(sym_dim, idx_s))) {
-    const long long n = g.idx(i, j, k);
-    const long long sb = b == 0 ? 1 : (b == 1 ? g.sy : g.sz);
-    if (a == 3) {
-      const FT A = area_at(g, b, b == 2 ? 0 : 1, k);
-      const FT ub = P.U[b][n];
-      const bool left = ub > FT(0);
-      // q_m at offset -3 + m (left-biased) or 2 - m (right-biased): start at the far upwind point and step towards downwind
-      const long long step = left ? sb : -sb;
-      const FT* q = c + n + (left ? -3 * sb : 2 * sb);
-      const FT q0 = q[0], q1 = q[step], q2 = q[2 * step], q3 = q[3 * step], q4 = q[4 * step];
-      return A * ub * weno5_from_q<FT>(P.tab, q0, q1, q2, q3, q4);
-    }
-    const long long ss = sym_dim == 0 ? 1 : (sym_dim == 1 ? g.sy : g.sz);
-    constexpr int zcb = b == 2 ? 0 : 1;
-    constexpr int kz = sym_dim == 2 ? 1 : 0;           // the four points differ in k only when the interpolation runs along z
-    const FT* ub = P.U[b] + n;
-    FT ut = P.tab.sym[2][3] * (area_at(g, b, zcb, k + kz * (-2 + stag_c)) * ub[(-2 + stag_c) * ss]);
-    ut = ut + P.tab.sym[2][2] * (area_at(g, b, zcb, k + kz * (-1 + stag_c)) * ub[(-1 + stag_c) * ss]);
-    ut = ut + P.tab.sym[2][1] * (area_at(g, b, zcb, k + kz * stag_c) * ub[stag_c * ss]);
-    ut = ut + P.tab.sym[2][0] * (area_at(g, b, zcb, k + kz * (1 + stag_c)) * ub[(1 + stag_c) * ss]);
-    const bool left = ut > FT(0);
-    const long long step = left ? sb : -sb;
-    const FT* q = P.U[av] + n + stag_c * sb + (left ? -3 * sb : 2 * sb);
-    const FT q0 = q[0], q1 = q[step], q2 = q[2 * step], q3 = q[3 * step], q4 = q[4 * step];
-    return ut * weno5_from_q<FT>(P.tab, q0, q1, q2, q3, q4);
-  }
-  if (a == 3) return tracer_flux<FT, b>(P, c, i, j, k);
-  return momentum_flux<FT, av, b>(P, i, j, k);
-}
 
 template <typename FT, int a>    // a = 0,1,2: velocity component; a = 3: tracer P.c[t]
 __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, FT* sm) {
@@ -474,11 +424,7 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
         if (fi > nx || fj >= ny || fk >= nz) continue;
         const int i = i0 + fi + ox, j = j0 + fj, k = k0 + fk;
         if (a == 0 && g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i < 1) continue;   // only the (skipped) periphery cell would read it
-        #if TG_FASTFLUX
-        if (pass == 0) Fx[fk][fj][fi] = tiled_adv_flux<FT, a, 0>(P, c, i, j, k);
-#else
         if (pass == 0) Fx[fk][fj][fi] = a == 3 ? tracer_flux<FT, 0>(P, c, i, j, k) : momentum_flux<FT, av, 0>(P, i, j, k);
-#endif
         else Fx[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 0>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 0>(P, i, j, k);
       }
     if (g.topo[1] != NH_FLAT)
@@ -487,11 +433,7 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
         if (fi >= nx || fj > ny || fk >= nz) continue;
         const int i = i0 + fi, j = j0 + fj + oy, k = k0 + fk;
         if (a == 1 && g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j < 1) continue;
-        #if TG_FASTFLUX
-        if (pass == 0) Fy[fk][fj][fi] = tiled_adv_flux<FT, a, 1>(P, c, i, j, k);
-#else
         if (pass == 0) Fy[fk][fj][fi] = a == 3 ? tracer_flux<FT, 1>(P, c, i, j, k) : momentum_flux<FT, av, 1>(P, i, j, k);
-#endif
         else Fy[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 1>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 1>(P, i, j, k);
       }
     if (g.topo[2] != NH_FLAT)
@@ -500,11 +442,7 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
         if (fi >= nx || fj >= ny || fk > nz) continue;
         const int i = i0 + fi, j = j0 + fj, k = k0 + fk + oz;
         if (a == 2 && g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k < 1) continue;
-        #if TG_FASTFLUX
-        if (pass == 0) Fz[fk][fj][fi] = tiled_adv_flux<FT, a, 2>(P, c, i, j, k);
-#else
         if (pass == 0) Fz[fk][fj][fi] = a == 3 ? tracer_flux<FT, 2>(P, c, i, j, k) : momentum_flux<FT, av, 2>(P, i, j, k);
-#endif
         else Fz[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 2>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 2>(P, i, j, k);
       }
     __syncthreads();

@@ -194,6 +194,19 @@ class DistributedNonhydrostaticModel:
             else:
                 check(lib().nh_dist_barrier(self._h))
 
+    def transpose(self, direction):
+        """transpose_z_to_y! (0) / transpose_y_to_z! (1) between the two spectral buffers (distributed_transpose.jl:25-191):
+        peer stores over NVLink bracketed by barriers in the peer-to-peer mode, one all-to-all otherwise."""
+        b = self._buf
+        if self.p2p:
+            self._barrier()
+            check(lib().nh_dist_transpose(self._h, int(direction)))
+            self._barrier()
+        elif direction == 0:
+            transpose_blocks(b[L.DIST_SPECTRAL_B], b[L.DIST_SPECTRAL_A], self.R, self.arch.group)
+        else:
+            transpose_blocks(b[L.DIST_SPECTRAL_A], b[L.DIST_SPECTRAL_B], self.R, self.arch.group)
+
     # -- pieces ---------------------------------------------------------------------------------------------------
     def exchange(self, mask, width):
         """fill_halo_regions! in y for the fields of ``mask``: pack → NCCL send/recv → unpack."""
@@ -236,6 +249,12 @@ class DistributedNonhydrostaticModel:
             return
         stages = 3 if self.model.timestepper_name in ("RungeKutta3", "RK3") else 1
         sdt = C.c_double()
+        if self.clock.iteration == 0:
+            # update_state! at iteration 0 (runge_kutta_3.jl:81): halos of fields that were set without the set! tail
+            check(lib().nh_fill_halo_regions(self._h, self._uvw, 1))
+            self.exchange(self._uvw, self.halo[1])
+            if self.p2p:
+                self._barrier()
         for _ in range(n_steps):
             for s in range(stages):
                 check(lib().nh_dist_tendency_substep(self._h, float(dt), s, int(euler), C.byref(sdt)))

@@ -209,10 +209,15 @@ def _upwind_inner(scheme, get, d, s0, R, left):
     return np.where(left, outs[0], outs[1])
 
 
+def weno_window_offsets(B):
+    """load_weno_stencil(buffer, dir) — weno_interpolants.jl:376-404: the 2B values ψ[i + c], c = -B … B-1."""
+    return range(-B, B)
+
+
 def _weno_inner(scheme, get, d, s0, R, left):
     """inner_biased_interpolate for WENO{B}: stencil selection, Z-WENO weights, reconstruction."""
     B, FT = scheme.B, scheme.FT
-    S = [get(*shift(R, d, c + s0)) for c in range(-B, B)]                  # S[0..2B-1] ↔ reference S[1..2B]
+    S = [get(*shift(R, d, c + s0)) for c in weno_window_offsets(B)]                  # S[0..2B-1] ↔ reference S[1..2B]
     # q[m], m = 0..2B-2: left bias takes S[1..2B-1], right bias takes S[2B..2] (reversed)
     q = [np.where(left, S[m], S[2 * B - 1 - m]) for m in range(2 * B - 1)]
     # ψ_r = (q[B-1-r], ..., q[2B-2-r])  (S₀ is the most upwind-centred stencil)

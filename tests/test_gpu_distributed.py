@@ -118,7 +118,7 @@ def _worker(rank, world, port, size, FT, timestepper, steps, dt, path, p2p):
 
 
 @pytest.mark.parametrize("p2p", [False, True], ids=["nccl", "p2p"])
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("FT,timestepper,size", [(np.float64, "RungeKutta3", (32, 64, 16)),
                                                  (np.float64, "QuasiAdamsBashforth2", (64, 32, 32)),
                                                  (np.float32, "RungeKutta3", (32, 64, 32))])
@@ -127,6 +127,7 @@ def test_multi_gpu_matches_single_gpu(world, FT, timestepper, size, p2p, tmp_pat
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     steps, dt = 10, 2e-3
+    size = (size[0], max(size[1], 8 * world), size[2])          # the fused sweep needs slabs of at least 2·H = 6 rows
     ref = _single_gpu(size, FT, timestepper, steps, dt)
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
@@ -250,7 +251,7 @@ def _generic_worker(rank, world, port, name, FT, timestepper, steps, dt, path):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("FT,timestepper", [(np.float64, "RungeKutta3"), (np.float32, "QuasiAdamsBashforth2")])
 @pytest.mark.parametrize("name", list(GENERIC))
 def test_multi_gpu_complete_path_slab_matches_single_gpu(name, FT, timestepper, world, tmp_path):
@@ -266,3 +267,66 @@ def test_multi_gpu_complete_path_slab_matches_single_gpu(name, FT, timestepper, 
     mp.spawn(_generic_worker, args=(world, port, name, FT, timestepper, steps, dt, path), nprocs=world, join=True)
     res = dict(np.load(path))
     _generic_check(res, ref, FT, name)
+
+
+# ---- bit-identical transpose round trip (test/test_distributed_transpose.jl:13-54) ---------------------------------------------
+def _transpose_round_trip(rank, world, size, p2p):
+    """Fill the z-local spectral buffer A with rank- and position-dependent values, transpose z → y → z through the library's
+    peer-store kernels (or the NCCL all-to-all), and require A back bit for bit; B in between must hold, for every source
+    rank s, block s = the block `rank` of rank s's A."""
+    import oceananigans_jl_b200 as oc
+    from oceananigans_jl_b200 import distributed as D
+    from oceananigans_jl_b200 import _lib as L
+    arch = D.Distributed(D.Partition(y=world))
+    m = D.DistributedNonhydrostaticModel(arch, np.float64, size=size, x=(0, 1), y=(0, 1), z=(0, 1), advection=oc.WENO(order=5),
+                                         device=rank, p2p=p2p)
+    A, B = m._buf[L.DIST_SPECTRAL_A], m._buf[L.DIST_SPECTRAL_B]
+    n = A.numel()
+    chunk = n // world
+    gen = torch.Generator(device="cpu").manual_seed(100 + rank)
+    a0 = torch.view_as_complex(torch.randn(n, 2, dtype=torch.float64, generator=gen)).to(A.device)
+    A.copy_(a0)
+    B.zero_()
+    torch.cuda.synchronize()
+    m.transpose(0)
+    torch.cuda.synchronize()
+    # what B must hold: block s = block `rank` of rank s's A (regenerated from rank s's seed)
+    for s_ in range(world):
+        gs = torch.Generator(device="cpu").manual_seed(100 + s_)
+        as_ = torch.view_as_complex(torch.randn(n, 2, dtype=torch.float64, generator=gs))
+        want = as_[rank * chunk:(rank + 1) * chunk].to(A.device)
+        assert torch.equal(B[s_ * chunk:(s_ + 1) * chunk], want), (rank, s_)
+    A.zero_()
+    torch.cuda.synchronize()
+    m.transpose(1)
+    torch.cuda.synchronize()
+    assert torch.equal(A, a0), "A -> B -> A must be the identity, bit for bit"
+    return True
+
+
+def _transpose_worker(rank, world, port, size, p2p):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        _transpose_round_trip(rank, world, size, p2p)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_transpose_round_trip_is_bit_identical_on_one_rank():
+    assert _transpose_round_trip(0, 1, (32, 32, 16), True)
+
+
+@pytest.mark.parametrize("p2p", [False, True], ids=["nccl", "p2p"])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_transpose_round_trip_is_bit_identical(world, p2p):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_transpose_worker, args=(world, port, (32, 16 * world, 16), p2p), nprocs=world, join=True)

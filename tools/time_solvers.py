@@ -1,6 +1,6 @@
 """Standalone Poisson solvers on device-resident data (BASELINE.json configs[2], configs[3]):
    python tools/time_solvers.py [reps]
-Prints ms per solve (CUDA events inside nh_poisson_time_solves) and the effective HBM rate for 12 words per cell."""
+Prints ms per solve (CUDA events inside nh_poisson_time_solves) and the HBM rate for the 10 words per cell of SURVEY.md §8d."""
 import ctypes as C
 import os
 import sys
@@ -43,7 +43,7 @@ def main():
         ms = timed(solver, shape, FT, reps)
         cells = shape[0] * shape[1] * shape[2]
         w = np.dtype(FT).itemsize
-        print(f"{name:70s} {ms:8.3f} ms/solve  {cells / ms / 1e6:8.2f} Gcell/s   12w-equivalent {12 * w * cells / ms / 1e9:7.2f} TB/s... "
+        print(f"{name:70s} {ms:8.3f} ms/solve  {cells / ms / 1e6:8.2f} Gcell/s   10w {10 * w * cells / ms / 1e9:7.2f} TB/s  "
               f"launches/solve {solver.launch_count() // (reps + 2 + 0)}")
         del solver
 
