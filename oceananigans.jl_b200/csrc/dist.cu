@@ -77,7 +77,7 @@ double Model<FT>::dist_tendency_substep(double dt, int stage, int euler) {
   J.g = gh.g; J.tab = tab; J.dt = (FT)dt; J.gamma = c1; J.zeta = c2; J.mode = mode;
   for (int a = 0; a < 3; ++a) { J.U[a] = F[a]; J.Unew[a] = F2[a]; J.Gn[a] = Gn[a]; J.Gm[a] = Gm[a]; }
   if (dist.p2p) J.v_prev = dist.prevF2[1];
-  launch_fused_tendency<FT>(J, stream, desc.exact_arithmetic != 0);
+  launch_fused_sweep(J);
   lc.n++;
   CUDA_CHECK(cudaGetLastError());
   for (int a = 0; a < 3; ++a) { std::swap(F[a], F2[a]); std::swap(dist.prevF[a], dist.prevF2[a]); std::swap(dist.nextF[a], dist.nextF2[a]); }

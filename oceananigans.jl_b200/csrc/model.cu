@@ -102,6 +102,16 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   if (fast) {
     for (int a = 0; a < 3; ++a) F2[a] = alloc_field();
     CUDA_CHECK(cudaFuncSetAttribute(tendency_fast_kernel<FT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TF_SMEM_ELEMS * sizeof(FT))));
+    CUDA_CHECK(cudaFuncSetAttribute(tendency_plane_kernel<FT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, TPSizes<FT>::total));
+    // contracted arithmetic: the plane-marching TMA sweep (0.94 vs 1.11 ms per launch at 256³); exact arithmetic: the tile sweep
+    // (its reconstruction with checked divisions needs the tile kernel's 32 warps per SM: 1.75 vs 1.82 ms).  Both produce the
+    // same bits in either mode; NHSTEP_TILE_SWEEP=1 / NHSTEP_PLANE_SWEEP=1 force one or the other (A/B, tests).
+    plane_sweep = desc.exact_arithmetic == 0;
+    if (getenv("NHSTEP_TILE_SWEEP")) plane_sweep = false;
+    if (getenv("NHSTEP_PLANE_SWEEP")) plane_sweep = true;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    plane_zseg = getenv("NHSTEP_PLANE_ZSEG") ? std::max(1, atoi(getenv("NHSTEP_PLANE_ZSEG"))) : tp_choose_zseg(gh.g.N[0], gh.g.N[1], gh.g.N[2], sms);
   }
   update_state(0);
 }
@@ -117,6 +127,26 @@ void Model<FT>::build_filter_width() {
     t[k - 1] = df * df;
   }
   df2.upload(t);
+}
+
+// The fused sweep of the fast path.  Tensor maps are cached per field pointer (u, v, w and their ping-pong twins).
+template <typename FT>
+void Model<FT>::launch_fused_sweep(const FastTendJob<FT>& J) {
+  const bool exact = desc.exact_arithmetic != 0;
+  if (!plane_sweep) { launch_fused_tendency<FT>(J, stream, exact); return; }
+  PlaneJob<FT> P;
+  P.J = J;
+  P.zseg = plane_zseg;
+  for (int a = 0; a < 3; ++a) {
+    auto it = tmaps.find((const void*)J.U[a]);
+    if (it == tmaps.end()) {
+      CUtensorMap m;
+      tp_encode_field_map<FT>(&m, J.U[a], J.g);
+      it = tmaps.emplace((const void*)J.U[a], m).first;
+    }
+    P.tm[a] = it->second;
+  }
+  launch_plane_tendency<FT>(P, stream, exact);
 }
 
 // the complete (any topology, any size) Poisson solver: only models that the fused passes do not cover ever need it
@@ -147,7 +177,7 @@ void Model<FT>::fast_stage(int mode, FT dt, FT c1, FT c2, double stage_dt) {
   FastTendJob<FT> J;
   J.g = gh.g; J.tab = tab; J.dt = dt; J.gamma = c1; J.zeta = c2; J.mode = mode;
   for (int a = 0; a < 3; ++a) { J.U[a] = F[a]; J.Unew[a] = F2[a]; J.Gn[a] = Gn[a]; J.Gm[a] = Gm[a]; }
-  launch_fused_tendency<FT>(J, stream, desc.exact_arithmetic != 0);
+  launch_fused_sweep(J);
   KLAUNCH(lc);
   mark(0);
   for (int a = 0; a < 3; ++a) std::swap(F[a], F2[a]);

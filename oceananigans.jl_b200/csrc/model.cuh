@@ -3,9 +3,11 @@
 #include "kernels_basic.cuh"
 #include "fft_generic.cuh"
 #include "tendency_fast.cuh"
+#include "tendency_plane.cuh"
 #include "poisson_fast.cuh"
 #include "grid_host.h"
 #include <memory>
+#include <map>
 #include <deque>
 #include <cstring>
 #include <cmath>
@@ -366,6 +368,11 @@ struct Model : nh_model {
   void fast_pressure(double stage_dt);
   void ensure_tendencies();
   void ensure_solver();
+  // fused tendency + substep sweep: plane-marching TMA kernel (tendency_plane.cuh) or the tile kernel (tendency_fast.cuh)
+  void launch_fused_sweep(const FastTendJob<FT>& J);
+  bool plane_sweep = true;
+  int plane_zseg = 32;
+  std::map<const void*, CUtensorMap> tmaps;
   void build_filter_width();
   bool solver_ready = false;
   void ensure_p_halo();

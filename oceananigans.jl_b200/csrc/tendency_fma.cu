@@ -14,6 +14,7 @@
 #endif
 #include "fft_generic.cuh"      // cx_of (two-element vector types)
 #include "tendency_fast.cuh"
+#include "tendency_plane.cuh"
 
 template <typename FT>
 void launch_fused_tendency_fma(const FastTendJob<FT>& J, cudaStream_t stream) {
@@ -33,3 +34,20 @@ void launch_fused_tendency_fma(const FastTendJob<FT>& J, cudaStream_t stream) {
 
 template void launch_fused_tendency_fma<float>(const FastTendJob<float>&, cudaStream_t);
 template void launch_fused_tendency_fma<double>(const FastTendJob<double>&, cudaStream_t);
+
+// the plane-marching TMA kernel (tendency_plane.cuh) in the contracted build
+template <typename FT>
+void launch_plane_tendency_fma(const PlaneJob<FT>& P, cudaStream_t stream) {
+  static bool attr_set[64] = {};
+  int dev = 0;
+  CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev >= 64 || !attr_set[dev]) {
+    CUDA_CHECK(cudaFuncSetAttribute(tendency_plane_kernel<FT, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TPSizes<FT>::total));
+    if (dev < 64) attr_set[dev] = true;
+  }
+  const GridDev<FT>& g = P.J.g;
+  dim3 grd(ceil_div(g.N[0], TP_TX), ceil_div(g.N[1], TP_TY), ceil_div(g.N[2], P.zseg));
+  tendency_plane_kernel<FT, 1><<<grd, TP_THREADS, TPSizes<FT>::total, stream>>>(P);
+}
+template void launch_plane_tendency_fma<float>(const PlaneJob<float>&, cudaStream_t);
+template void launch_plane_tendency_fma<double>(const PlaneJob<double>&, cudaStream_t);

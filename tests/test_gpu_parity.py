@@ -539,6 +539,31 @@ def test_fused_fast_path_is_bit_identical_to_complete_path(oc, FT, timestepper, 
         np.testing.assert_array_equal(a, b)
 
 
+@pytest.mark.parametrize("exact", [True, False], ids=["exact", "contracted"])
+@pytest.mark.parametrize("FT", [np.float64, np.float32])
+@pytest.mark.parametrize("timestepper", ["RungeKutta3", "QuasiAdamsBashforth2"])
+@pytest.mark.parametrize("size", [(40, 24, 16), (33, 13, 9), (64, 64, 40)])
+def test_plane_marching_tma_sweep_is_bit_identical_to_the_tile_sweep(oc, FT, timestepper, size, exact, monkeypatch):
+    """The two fused tendency + substep sweeps — the plane-marching kernel that stages u, v, w planes by TMA
+    (csrc/tendency_plane.cuh, the default in contracted arithmetic) and the tile kernel (csrc/tendency_fast.cuh, the default in
+    exact arithmetic) — evaluate the same flux functions once per face, so they must agree bit for bit in both arithmetic
+    modes, on partial tiles and partial z segments too."""
+    rng = np.random.default_rng(5)
+    ics = {n: rng.uniform(-1, 1, size).astype(FT) for n in "uvw"}
+    out = {}
+    for which, var in (("plane", "NHSTEP_PLANE_SWEEP"), ("tile", "NHSTEP_TILE_SWEEP")):
+        monkeypatch.setenv(var, "1")
+        g = oc.RectilinearGrid(FT, size=size, extent=(1, 1, 1), topology=(P, P, P))
+        m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), timestepper=timestepper, exact_arithmetic=exact)
+        monkeypatch.delenv(var)
+        oc.set_model(m, **ics)
+        oc.time_step(m, 1e-3, n_steps=3)
+        out[which] = [m.velocities[n].interior() for n in "uvw"] + [m.pressures.pNHS.interior()] + \
+                     [m.timestepper.Gn[n].interior() for n in "uvw"]
+    for a, b in zip(out["plane"], out["tile"]):
+        np.testing.assert_array_equal(a, b)
+
+
 @pytest.mark.parametrize("FT", [np.float64, np.float32])
 @pytest.mark.parametrize("cfg", [((37, 9, 11), (P, P, B), "stretched", ("WENO", 5),
                                   dict(buoyancy="seawater", tracers=("T", "S"), coriolis=1e-2, closure=("lilly", 0.16, 1.0, 1.0))),
