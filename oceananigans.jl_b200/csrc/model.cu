@@ -94,6 +94,12 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   fast = fast && gh.volume() < (1ll << 31);        // the fused kernel uses 32-bit element offsets
   if (getenv("NHSTEP_NO_FAST")) fast = false;
   tiled = getenv("NHSTEP_NO_TILED") == nullptr;
+  CUDA_CHECK(cudaFuncSetAttribute(tendency_tiled_kernel<FT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TG_SMEM_ELEMS * sizeof(FT))));
+  tiled_fast_ok = gh.volume() < (1ll << 31) && getenv("NHSTEP_NO_FAST_FLUX") == nullptr;
+  for (int e = 0; e < 3; ++e) {
+    const bool topo_ok = gh.g.topo[e] == NH_PERIODIC || (e == 2 && gh.g.topo[e] == NH_BOUNDED);
+    tiled_fast_ok = tiled_fast_ok && topo_ok && adv[e].kind == NH_ADV_WENO && adv[e].B == 3 && gh.g.H[e] >= 3 && gh.g.N[e] >= 2 * gh.g.H[e];
+  }
   if (!getenv("NHSTEP_NO_FAST_POISSON")) {
     // fused FFT / DCT / Thomas passes for (Periodic, Periodic, Periodic | Bounded) power-of-two grids, any model physics
     if (!gh.z_stretched && PoissonFast<FT>::supported(gh, true)) pfast.create(gh);
@@ -469,14 +475,17 @@ void Model<FT>::compute_tendencies() {
   // tiled kernel (each advective face flux once, staged in shared memory); NHSTEP_NO_TILED selects the per-cell kernel that
   // evaluates every face from both neighbours like the reference (bit-identical results, kept as the cross-check)
   dim3 blk(32, 4, 1);
-  for (int what = 0; what < nf; ++what) {
-    if (tiled) {
-      dim3 tb(TG_TX, TG_TY, 1), tg(ceil_div(gh.g.N[0], TG_TX), ceil_div(gh.g.N[1], TG_TY), ceil_div(gh.g.N[2], TG_TZ));
-      tendency_tiled_kernel<FT><<<tg, tb, 0, stream>>>(P, what);
-    } else {
-      tendency_generic_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, what);
-    }
+  if (tiled) {
+    // one launch for all prognostic fields; interior tiles of WENO5 models on (Periodic, Periodic, Periodic | Bounded) regular
+    // grids take the fast flux stage (tendency_generic.cuh)
+    dim3 tb(TG_TX, TG_TY, 1), tg(ceil_div(gh.g.N[0], TG_TX), ceil_div(gh.g.N[1], TG_TY), ceil_div(gh.g.N[2], TG_TZ));
+    tendency_tiled_kernel<FT><<<tg, tb, TG_SMEM_ELEMS * sizeof(FT), stream>>>(P, -1, tiled_fast_ok ? 1 : 0);
     KLAUNCH(lc);
+  } else {
+    for (int what = 0; what < nf; ++what) {
+      tendency_generic_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, what);
+      KLAUNCH(lc);
+    }
   }
   // compute_boundary_tendency_contributions! (compute_nonhydrostatic_tendencies.jl:202-207): x, then y, then z walls
   if (has_flux_bcs) {

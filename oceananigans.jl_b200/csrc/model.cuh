@@ -371,6 +371,7 @@ struct Model : nh_model {
   // fused tendency + substep sweep: plane-marching TMA kernel (tendency_plane.cuh) or the tile kernel (tendency_fast.cuh)
   void launch_fused_sweep(const FastTendJob<FT>& J);
   bool plane_sweep = true;
+  bool tiled_fast_ok = false;        // the tiled tendency kernel may use its fast flux stage on interior tiles
   int plane_zseg = 32;
   std::map<const void*, CUtensorMap> tmaps;
   void build_filter_width();

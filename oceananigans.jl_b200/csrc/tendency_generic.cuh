@@ -387,14 +387,173 @@ __global__ void __launch_bounds__(128) tendency_generic_kernel(const __grid_cons
 #define TG_TY 8          // 32×8×4 tile, 256 threads: 256³ (P,P,B) tendencies 3.50 → 3.24 ms per substep against 32×4×4 (32×4×8: 3.51)
 #endif
 #ifndef TG_TZ
-#define TG_TZ 4
+#define TG_TZ 8          // = TG_TY: every thread owns one line of faces in the y- and in the z-marching of the fast flux stage
 #endif
+#define TG_SMEM_ELEMS (TG_TZ * TG_TY * (TG_TX + 1) + TG_TZ * (TG_TY + 1) * TG_TX + (TG_TZ + 1) * TG_TY * TG_TX)
 #ifndef TG_MINBLOCKS
-#define TG_MINBLOCKS 1
+#define TG_MINBLOCKS 4      // 64 registers, four CTAs per SM: 256³ LES tendencies 6.15 → 4.76 ms per substep against 128 registers / two CTAs
 #endif
 
+// ---- fast flux stage of the tiled kernel ---------------------------------------------------------------------------------
+// Interior tiles of a WENO(order = 5) model on a grid that is Periodic and regular in x, y, with a regular or stretched z (Periodic,
+// or Bounded with the tile at least four cells away from either wall, where topologically_conditional_interpolation keeps the full order):
+// the advective face fluxes of the tile are evaluated from a six-point window — read by pointer stepping along x, carried in
+// registers along y and z (one new value per face) — with 32-bit offsets and no kind / level dispatch.  The arithmetic is that
+// of momentum_flux / tracer_flux above (symmetric_interp's four-point sum with the area folded in per point, biased_interp's
+// upwind selection, weno5_from_q), so the staged values are the same bits.
+// KIND 0: momentum flux across a direction other than the component's (advecting velocity interpolated along the component's
+// direction); 1: along the component's own direction (flux at Centres, advecting velocity from the window itself); 2: tracer.
+// A0 … A3: the face area at each of the four advecting-velocity points (they differ only when that interpolation runs along a
+// stretched z: Ax = Δy·Δzᶜ[k′]); KIND 1 and 2 use A0 alone.
+template <typename FT, int KIND>
+__device__ __forceinline__ FT tg_window_flux(const SchemeTables<FT>& T, FT S0, FT S1, FT S2, FT S3, FT S4, FT S5, FT v0, FT v1,
+                                             FT v2, FT v3, FT A0, FT A1, FT A2, FT A3) {
+  FT ut;
+  bool left;
+  if (KIND == 2) { ut = A0 * v0; left = v0 > FT(0); }
+  else {
+    const FT u0 = KIND == 1 ? S1 : v0, u1 = KIND == 1 ? S2 : v1, u2 = KIND == 1 ? S3 : v2, u3 = KIND == 1 ? S4 : v3;
+    ut = T.sym[2][3] * ((KIND == 1 ? A0 : A0) * u0);
+    ut = ut + T.sym[2][2] * ((KIND == 1 ? A0 : A1) * u1);
+    ut = ut + T.sym[2][1] * ((KIND == 1 ? A0 : A2) * u2);
+    ut = ut + T.sym[2][0] * ((KIND == 1 ? A0 : A3) * u3);
+    left = ut > FT(0);
+  }
+  const FT q0 = left ? S0 : S5, q1 = left ? S1 : S4, q2 = left ? S2 : S3, q3 = left ? S3 : S2, q4 = left ? S4 : S1;
+  return ut * weno5_from_q<FT>(T, q0, q1, q2, q3, q4);
+}
+
+// `count` consecutive fluxes along a direction with stride sb, the first at flux location n: window carried in registers.
+// pb: advecting velocity U_b, sa: stride of the component's direction (KIND 0)
+template <typename FT, int KIND>
+__device__ __forceinline__ void tg_march(const SchemeTables<FT>& T, const FT* __restrict__ fa, const FT* __restrict__ ub, int n,
+                                         int sb, int sa, FT A0, FT A1, FT A2, FT A3, int count, FT* out, int ostride) {
+  const FT* p = fa + (n + ((KIND == 1 ? 1 : 0) - 3) * sb);
+  FT S0 = p[0], S1 = p[sb], S2 = p[2 * sb], S3 = p[3 * sb], S4 = p[4 * sb];
+  p += 5 * sb;
+  const FT* pb = ub + (KIND == 0 ? n - 2 * sa : n);
+#pragma unroll 1
+  for (int c = 0; c < count; ++c) {
+    const FT S5 = *p;
+    FT v0 = FT(0), v1 = FT(0), v2 = FT(0), v3 = FT(0);
+    if (KIND == 0) { v0 = pb[0]; v1 = pb[sa]; v2 = pb[2 * sa]; v3 = pb[3 * sa]; }
+    if (KIND == 2) v0 = pb[0];
+    *out = tg_window_flux<FT, KIND>(T, S0, S1, S2, S3, S4, S5, v0, v1, v2, v3, A0, A1, A2, A3);
+    out += ostride; p += sb; pb += sb;
+    S0 = S1; S1 = S2; S2 = S3; S3 = S4; S4 = S5;
+  }
+}
+
+template <typename FT, int a>    // a = 0,1,2: velocity component; a = 3: tracer c
+__device__ __forceinline__ void tg_stage_fast(const TendParams<FT>& P, const FT* __restrict__ c, FT* Fx, FT* Fy, FT* Fz, int i0,
+                                              int j0, int k0, int nx, int ny, int nz, int tid) {
+  static_assert(TG_TX * TG_TY == TG_TX * TG_TZ, "one thread per line of faces in both marching directions");
+  const GridDev<FT>& g = P.g;
+  const int sy = (int)g.sy, sz = (int)g.sz;
+  const FT* __restrict__ fa = a == 3 ? c : P.U[a];
+  const int sa = a == 0 ? 1 : (a == 1 ? sy : sz);
+  const FT Az = g.dx * g.dy;
+  constexpr int NT = TG_TX * TG_TY;
+  // face areas Ax = Δy·Δzᶜ[k], Ay = Δx·Δzᶜ[k] of the advecting velocities u, v (they live at z-Centres); the x / y fluxes of w
+  // interpolate them along z, i.e. over the four levels k-2 … k+1
+  // x-direction: flux slot (li, lj, lk), li = 0 … TX
+  for (int t = tid; t < (TG_TX + 1) * TG_TY * TG_TZ; t += NT) {
+    const int li = t % (TG_TX + 1), r = t / (TG_TX + 1), lj = r % TG_TY, lk = r / TG_TY, k = k0 + min(lk, nz - 1);
+    const int n = g.idx32(i0 + min(li, nx) - (a == 0 ? 1 : 0), j0 + min(lj, ny - 1), k);
+    const FT* w = fa + n + (a == 0 ? -2 : -3);
+    const FT S0 = w[0], S1 = w[1], S2 = w[2], S3 = w[3], S4 = w[4], S5 = w[5];
+    const FT Ax = g.dy * g.Dzc(k);
+    FT f;
+    if (a == 0) f = tg_window_flux<FT, 1>(P.tab, S0, S1, S2, S3, S4, S5, FT(0), FT(0), FT(0), FT(0), Ax, Ax, Ax, Ax);
+    else if (a == 3) f = tg_window_flux<FT, 2>(P.tab, S0, S1, S2, S3, S4, S5, P.U[0][n], FT(0), FT(0), FT(0), Ax, Ax, Ax, Ax);
+    else {
+      const FT* q = P.U[0] + n - 2 * sa;
+      if (a == 2) f = tg_window_flux<FT, 0>(P.tab, S0, S1, S2, S3, S4, S5, q[0], q[sa], q[2 * sa], q[3 * sa], g.dy * g.Dzc(k - 2),
+                                            g.dy * g.Dzc(k - 1), Ax, g.dy * g.Dzc(k + 1));
+      else f = tg_window_flux<FT, 0>(P.tab, S0, S1, S2, S3, S4, S5, q[0], q[sa], q[2 * sa], q[3 * sa], Ax, Ax, Ax, Ax);
+    }
+    Fx[(lk * TG_TY + lj) * (TG_TX + 1) + li] = f;
+  }
+  // y- and z-direction: one thread per line of faces
+  const int li = tid & (TG_TX - 1), lo = tid / TG_TX, ci = i0 + min(li, nx - 1);
+  {
+    const int k = k0 + min(lo, nz - 1);
+    const int n0 = g.idx32(ci, j0, k);
+    const FT Ay = g.dx * g.Dzc(k);
+    FT* out = Fy + lo * (TG_TY + 1) * TG_TX + li;
+    if (a == 1) tg_march<FT, 1>(P.tab, fa, fa, n0 - sy, sy, sa, Ay, Ay, Ay, Ay, ny + 1, out, TG_TX);
+    else if (a == 3) tg_march<FT, 2>(P.tab, fa, P.U[1], n0, sy, sa, Ay, Ay, Ay, Ay, ny + 1, out, TG_TX);
+    else if (a == 2) tg_march<FT, 0>(P.tab, fa, P.U[1], n0, sy, sa, g.dx * g.Dzc(k - 2), g.dx * g.Dzc(k - 1), Ay, g.dx * g.Dzc(k + 1), ny + 1, out, TG_TX);
+    else tg_march<FT, 0>(P.tab, fa, P.U[1], n0, sy, sa, Ay, Ay, Ay, Ay, ny + 1, out, TG_TX);
+  }
+  {
+    const int n0 = g.idx32(ci, j0 + min(lo, ny - 1), k0);
+    FT* out = Fz + lo * TG_TX + li;
+    if (a == 2) tg_march<FT, 1>(P.tab, fa, fa, n0 - sz, sz, sa, Az, Az, Az, Az, nz + 1, out, TG_TY * TG_TX);
+    else if (a == 3) tg_march<FT, 2>(P.tab, fa, P.U[2], n0, sz, sa, Az, Az, Az, Az, nz + 1, out, TG_TY * TG_TX);
+    else tg_march<FT, 0>(P.tab, fa, P.U[2], n0, sz, sa, Az, Az, Az, Az, nz + 1, out, TG_TY * TG_TX);
+  }
+}
+
+// The same for the closure pass of a constant-coefficient ScalarDiffusivity (no eddy-viscosity field): viscous_Aflux /
+// diffusive_Aflux of every face of an interior tile with 32-bit offsets, the regular spacings as constants and the IEEE
+// divisions by Δx, Δy, Δz done with one refined reciprocal per spacing (recon.cuh: the same bits as `/`).
+template <typename FT>
+struct TgSpacing { FT d[3]; FT y[3]; bool ok[3]; };
+template <typename FT>
+__device__ __forceinline__ FT tg_div(FT a, const TgSpacing<FT>& S, int d) { return a / S.d[d]; }
+template <>
+__device__ __forceinline__ double tg_div<double>(double a, const TgSpacing<double>& S, int d) { return nh_div_checked(a, S.d[d], S.y[d], S.ok[d]); }
+
+template <typename FT, int a, int b>
+__device__ __forceinline__ FT tg_closure_flux(const TendParams<FT>& P, const FT* __restrict__ c, int t, const TgSpacing<FT>& S, int n,
+                                              const int (&st)[3], FT Ab) {
+  FT flux;
+  if (a == 3) {
+    if (b == 2 && P.vitd) flux = FT(0);
+    else flux = -P.kappa[t] * tg_div<FT>(c[n] - c[n - st[b]], S, b);
+  } else if (b == 2 && P.vitd) {
+    if (a == 2) flux = FT(0);
+    else flux = -(P.nu * tg_div<FT>(P.U[2][n] - P.U[2][n - st[a == 3 ? 0 : a]], S, a == 3 ? 0 : a));
+  } else if (a == b) {
+    flux = FT(-2) * (P.nu * tg_div<FT>(P.U[a == 3 ? 0 : a][n + st[b]] - P.U[a == 3 ? 0 : a][n], S, b));
+  } else {
+    constexpr int av = a == 3 ? 0 : a, lo = av < b ? av : b, hi = av < b ? b : av;
+    const FT d1 = tg_div<FT>(P.U[lo][n] - P.U[lo][n - st[hi]], S, hi), d2 = tg_div<FT>(P.U[hi][n] - P.U[hi][n - st[lo]], S, lo);
+    flux = FT(-2) * (P.nu * (FT(0.5) * (d1 + d2)));
+  }
+  return Ab * flux;
+}
+
+template <typename FT, int a>
+__device__ __forceinline__ void tg_stage_closure_fast(const TendParams<FT>& P, const FT* __restrict__ c, int t, FT* Fx, FT* Fy, FT* Fz,
+                                                      int i0, int j0, int k0, int nx, int ny, int nz, int tid) {
+  const GridDev<FT>& g = P.g;
+  const int st[3] = {1, (int)g.sy, (int)g.sz};
+  TgSpacing<FT> S;
+  S.d[0] = g.dx; S.d[1] = g.dy; S.d[2] = g.dz;
+  for (int e = 0; e < 3; ++e) { S.y[e] = nh_rcp_refined(S.d[e]); S.ok[e] = sizeof(FT) == 8 ? nh_den_ok((double)S.d[e]) : false; }
+  const FT Ax = g.dy * g.dz, Ay = g.dx * g.dz, Az = g.dx * g.dy;
+  constexpr int NT = TG_TX * TG_TY;
+  for (int s = tid; s < (TG_TX + 1) * TG_TY * TG_TZ; s += NT) {
+    const int li = s % (TG_TX + 1), r = s / (TG_TX + 1), lj = r % TG_TY, lk = r / TG_TY;
+    const int n = g.idx32(i0 + min(li, nx) - (a == 0 ? 1 : 0), j0 + min(lj, ny - 1), k0 + min(lk, nz - 1));
+    Fx[s] = tg_closure_flux<FT, a, 0>(P, c, t, S, n, st, Ax);
+  }
+  for (int s = tid; s < TG_TX * (TG_TY + 1) * TG_TZ; s += NT) {
+    const int li = s % TG_TX, r = s / TG_TX, lj = r % (TG_TY + 1), lk = r / (TG_TY + 1);
+    const int n = g.idx32(i0 + min(li, nx - 1), j0 + min(lj, ny) - (a == 1 ? 1 : 0), k0 + min(lk, nz - 1));
+    Fy[s] = tg_closure_flux<FT, a, 1>(P, c, t, S, n, st, Ay);
+  }
+  for (int s = tid; s < TG_TX * TG_TY * (TG_TZ + 1); s += NT) {
+    const int li = s % TG_TX, r = s / TG_TX, lj = r % TG_TY, lk = r / TG_TY;
+    const int n = g.idx32(i0 + min(li, nx - 1), j0 + min(lj, ny - 1), k0 + min(lk, nz) - (a == 2 ? 1 : 0));
+    Fz[s] = tg_closure_flux<FT, a, 2>(P, c, t, S, n, st, Az);
+  }
+}
+
 template <typename FT, int a>    // a = 0,1,2: velocity component; a = 3: tracer P.c[t]
-__device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, FT* sm) {
+__device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, FT* sm, bool fast) {
   const GridDev<FT>& g = P.g;
   typedef FT (*FxT)[TG_TY][TG_TX + 1];
   typedef FT (*FyT)[TG_TY + 1][TG_TX];
@@ -418,6 +577,11 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
   for (int pass = 0; pass < 2; ++pass) {
     if (pass == 1 && !P.has_closure) break;
     if (pass == 1) __syncthreads();            // everyone has read the advective fluxes
+    if (pass == 0 && fast) {
+      tg_stage_fast<FT, a>(P, c, &Fx[0][0][0], &Fy[0][0][0], &Fz[0][0][0], i0, j0, k0, nx, ny, nz, tid);
+    } else if (pass == 1 && fast && !P.nue && g.z_regular) {
+      tg_stage_closure_fast<FT, a>(P, c, t, &Fx[0][0][0], &Fy[0][0][0], &Fz[0][0][0], i0, j0, k0, nx, ny, nz, tid);
+    } else {
     if (g.topo[0] != NH_FLAT)
       for (int s = tid; s < (TG_TX + 1) * TG_TY * TG_TZ; s += NT) {
         const int fi = s % (TG_TX + 1), r = s / (TG_TX + 1), fj = r % TG_TY, fk = r / TG_TY;
@@ -445,6 +609,7 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
         if (pass == 0) Fz[fk][fj][fi] = a == 3 ? tracer_flux<FT, 2>(P, c, i, j, k) : momentum_flux<FT, av, 2>(P, i, j, k);
         else Fz[fk][fj][fi] = a == 3 ? diffusive_Aflux<FT, 2>(P, c, t, i, j, k) : viscous_Aflux<FT, av, 2>(P, i, j, k);
       }
+    }
     __syncthreads();
     if (mine) {
 #pragma unroll
@@ -477,16 +642,28 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
   }
 }
 
+// One launch for every prognostic field (what = -1: u, v, w, then the tracers, the tile's shared memory reused field after field)
+// or for one of them (what = 0, 1, 2 or 3 + tracer index).  fast_ok: the model qualifies for the fast flux stage (set by the
+// host: WENO5 in x, y, z; x, y Periodic; z Periodic or Bounded; regular spacing; parent volume below 2³¹ elements).
 template <typename FT>
 #if TG_MINBLOCKS > 1
 #define TG_BOUNDS __launch_bounds__(TG_TX * TG_TY, TG_MINBLOCKS)
 #else
 #define TG_BOUNDS __launch_bounds__(TG_TX * TG_TY)
 #endif
-__global__ void TG_BOUNDS tendency_tiled_kernel(const __grid_constant__ TendParams<FT> P, int what) {
-  __shared__ FT sm[TG_TZ * TG_TY * (TG_TX + 1) + TG_TZ * (TG_TY + 1) * TG_TX + (TG_TZ + 1) * TG_TY * TG_TX];
-  if (what == 0) tiled_tendency<FT, 0>(P, 0, sm);
-  else if (what == 1) tiled_tendency<FT, 1>(P, 0, sm);
-  else if (what == 2) tiled_tendency<FT, 2>(P, 0, sm);
-  else tiled_tendency<FT, 3>(P, what - 3, sm);
+__global__ void TG_BOUNDS tendency_tiled_kernel(const __grid_constant__ TendParams<FT> P, int what, int fast_ok) {
+  extern __shared__ __align__(16) unsigned char tg_smem[];
+  FT* sm = reinterpret_cast<FT*>(tg_smem);
+  const GridDev<FT>& g = P.g;
+  // full-order region of a Bounded z for every flux location the tile touches (faces and centres k0-1 … k0+TZ)
+  const int k0 = blockIdx.z * TG_TZ + 1, nz = min(TG_TZ, g.N[2] - k0 + 1);
+  const bool fast = fast_ok && (g.topo[2] == NH_PERIODIC || (k0 - 1 >= 4 && k0 + nz <= g.N[2] - 2));
+  const int first = what < 0 ? 0 : what, last = what < 0 ? 2 + P.ntr : what;
+  for (int f = first; f <= last; ++f) {
+    if (f == 0) tiled_tendency<FT, 0>(P, 0, sm, fast);
+    else if (f == 1) tiled_tendency<FT, 1>(P, 0, sm, fast);
+    else if (f == 2) tiled_tendency<FT, 2>(P, 0, sm, fast);
+    else tiled_tendency<FT, 3>(P, f - 3, sm, fast);
+    __syncthreads();
+  }
 }
