@@ -31,7 +31,7 @@ sys.path.insert(0, ROOT)
 METRIC = "cell-updates/s (NonhydrostaticModel WENO step)"
 UNIT = "cell-updates/s"
 # FP64-pipe instructions per cell of tendency_fast_kernel (ncu opcode mix, profiles/r1_tendency_sass_mix.md)
-FP64_INSTR_PER_CELL = {"exact": 1290.0, "contracted": 750.0}
+FP64_INSTR_PER_CELL = {"exact": 1290.0, "contracted": 690.0}
 
 
 def peaks():
@@ -345,47 +345,49 @@ def single_gpu_targets(oc, args, exact):
             torch.cuda.synchronize()
         return {"workload": "512^3 (P,P,P) Float64 WENO5 RK3 — the north_star target size", **res}
 
-    def model_les():
-        N = 256
-        g = oc.RectilinearGrid(np.float64, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=(oc.Periodic, oc.Periodic, oc.Bounded))
-        m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), buoyancy=oc.SeawaterBuoyancy(), tracers=("T", "S"),
-                                   coriolis=oc.FPlane(1e-4), closure=oc.ScalarDiffusivity(1e-4, 1e-4), exact_arithmetic=True)
-        ics = smooth_ics(N, 1234)
+    def timed_model(make, ics, dt, warm, n, words, cells, label):
+        """The same complete-path model in both arithmetic modes (exact: bit-identical to the reference's CPU arithmetic;
+        contracted: FMA contraction + quotient-free WENO5 weights on the interior tiles)."""
+        res = {"workload": label, "algorithmic_words_per_cell": words}
+        for name, ex in (("exact", True), ("contracted", False)):
+            m = make(ex)
+            oc.set_model(m, **ics)
+            oc.time_step(m, dt, n_steps=warm)
+            ms = event_time(lambda: oc.time_step(m, dt, n_steps=n), torch.cuda.synchronize) / n
+            gbs = words * FT_B * cells / (ms * 1e-3) / 1e9
+            res[name] = {"ms_per_step": ms, "value": cells / (ms * 1e-3), "unit": UNIT, "steps": n, "whole_step_frac": gbs / peak,
+                         "max_abs_divergence": m.max_abs_divergence()}
+            del m
+            torch.cuda.synchronize()
+        return res
+
+    def bounded_w(ics):
         ics["w"] = np.concatenate([ics["w"], ics["w"][:, :, :1]], axis=2)
         ics["w"][:, :, 0] = 0
         ics["w"][:, :, -1] = 0
+        return ics
+
+    def model_les():
+        N = 256
+        g = oc.RectilinearGrid(np.float64, size=(N, N, N), extent=(2 * np.pi,) * 3, topology=(oc.Periodic, oc.Periodic, oc.Bounded))
+        make = lambda ex: oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), buoyancy=oc.SeawaterBuoyancy(), tracers=("T", "S"),   # noqa: E731
+                                                 coriolis=oc.FPlane(1e-4), closure=oc.ScalarDiffusivity(1e-4, 1e-4), exact_arithmetic=ex)
+        ics = bounded_w(smooth_ics(N, 1234))
         z = (np.arange(N) + 0.5) / N
         ics["T"] = 20 + 0.01 * z[None, None, :] + 1e-3 * ics["u"]
         ics["S"] = np.full((N, N, N), 35.0)
-        oc.set_model(m, **ics)
-        dt = 0.2 * (2 * np.pi / N) / 2.0
-        oc.time_step(m, dt, n_steps=3)
-        n = 5
-        ms = event_time(lambda: oc.time_step(m, dt, n_steps=n), torch.cuda.synchronize) / n
-        words = 124                                                # SURVEY.md §8d for F = 5 prognostic fields + pHY′
-        gbs = words * FT_B * N ** 3 / (ms * 1e-3) / 1e9
-        return {"workload": "256^3 (P,P,B) Float64 WENO5 RK3, T + S, SeawaterBuoyancy, FPlane, ScalarDiffusivity (exact arithmetic)",
-                "ms_per_step": ms, "value": N ** 3 / (ms * 1e-3), "unit": UNIT, "steps": n, "algorithmic_words_per_cell": words,
-                "whole_step_frac": gbs / peak, "max_abs_divergence": m.max_abs_divergence()}
+        # SURVEY.md §8d for F = 5 prognostic fields + pHY′: 124 words per cell and step
+        return timed_model(make, ics, 0.2 * (2 * np.pi / N) / 2.0, 3, 5, 124, N ** 3,
+                           "256^3 (P,P,B) Float64 WENO5 RK3, T + S, SeawaterBuoyancy, FPlane, ScalarDiffusivity")
 
     def model_c3():
         Nx, Nz = 512, 256
         g = oc.RectilinearGrid(np.float64, size=(Nx, Nx, Nz), x=(0, 2 * np.pi), y=(0, 2 * np.pi), z=tanh_faces(Nz),
                                topology=(oc.Periodic, oc.Periodic, oc.Bounded))
-        m = oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), exact_arithmetic=True)
-        ics = smooth_ics(Nx, 1234, size=(Nx, Nx, Nz))
-        ics["w"] = np.concatenate([ics["w"], ics["w"][:, :, :1]], axis=2)
-        ics["w"][:, :, 0] = 0
-        ics["w"][:, :, -1] = 0
-        oc.set_model(m, **ics)
-        dt = 0.2 * (2 * np.pi / Nx) / 2.0
-        oc.time_step(m, dt, n_steps=2)
-        n = 3
-        ms = event_time(lambda: oc.time_step(m, dt, n_steps=n), torch.cuda.synchronize) / n
-        cells = Nx * Nx * Nz
-        gbs = STEP_WORDS * FT_B * cells / (ms * 1e-3) / 1e9
-        return {"workload": "configs[3]: 512x512x256 tanh-stretched Bounded z, WENO5 RK3, FourierTridiagonalPoissonSolver (exact arithmetic)",
-                "ms_per_step": ms, "value": cells / (ms * 1e-3), "unit": UNIT, "steps": n, "whole_step_frac": gbs / peak}
+        make = lambda ex: oc.NonhydrostaticModel(g, advection=oc.WENO(order=5), exact_arithmetic=ex)              # noqa: E731
+        ics = bounded_w(smooth_ics(Nx, 1234, size=(Nx, Nx, Nz)))
+        return timed_model(make, ics, 0.2 * (2 * np.pi / Nx) / 2.0, 2, 3, STEP_WORDS, Nx * Nx * Nz,
+                           "configs[3]: 512x512x256 tanh-stretched Bounded z, WENO5 RK3, FourierTridiagonalPoissonSolver")
 
     guarded("step_512", step_512)
     guarded("solver_c2_f64", lambda: solver_target(oc, np.float64, (512, 512, 512), (0, 1)))
@@ -581,7 +583,8 @@ def main():
     # pressure solve B = 3·12w, pressure correction C = 3·7w; the dominant kernel is launched 3x per step
     alg = {"tendencies_substep": (9 + 2 * 12) * FT_B * cells, "pressure_solve": 3 * 12 * FT_B * cells,
            "pressure_correct": 3 * 7 * FT_B * cells}
-    kernel_names = {"tendencies_substep": "tendency_fast_kernel (fused WENO5 tendencies + RK3 substep)",
+    kernel_names = {"tendencies_substep": ("tendency_fast_kernel (tile sweep: fused WENO5 tendencies + RK3 substep)" if exact else
+                                           "tendency_plane_kernel (TMA plane-marching sweep: fused WENO5 tendencies + RK3 substep)"),
                     "pressure_solve": "poisson (source term + transforms + spectral divide + real store)",
                     "pressure_correct": "pressure_correct_halo_kernel"}
     dom = max(alg, key=lambda k: phases[k])

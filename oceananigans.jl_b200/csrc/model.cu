@@ -479,7 +479,8 @@ void Model<FT>::compute_tendencies() {
     // one launch for all prognostic fields; interior tiles of WENO5 models on (Periodic, Periodic, Periodic | Bounded) regular
     // grids take the fast flux stage (tendency_generic.cuh)
     dim3 tb(TG_TX, TG_TY, 1), tg(ceil_div(gh.g.N[0], TG_TX), ceil_div(gh.g.N[1], TG_TY), ceil_div(gh.g.N[2], TG_TZ));
-    tendency_tiled_kernel<FT><<<tg, tb, TG_SMEM_ELEMS * sizeof(FT), stream>>>(P, -1, tiled_fast_ok ? 1 : 0);
+    if (desc.exact_arithmetic == 0 && tiled_fast_ok) launch_tiled_tendency_fma<FT>(P, tg, 1, stream);
+    else tendency_tiled_kernel<FT><<<tg, tb, TG_SMEM_ELEMS * sizeof(FT), stream>>>(P, -1, tiled_fast_ok ? 1 : 0);
     KLAUNCH(lc);
   } else {
     for (int what = 0; what < nf; ++what) {

@@ -15,6 +15,7 @@
 #include "fft_generic.cuh"      // cx_of (two-element vector types)
 #include "tendency_fast.cuh"
 #include "tendency_plane.cuh"
+#include "tendency_generic.cuh"
 
 template <typename FT>
 void launch_fused_tendency_fma(const FastTendJob<FT>& J, cudaStream_t stream) {
@@ -51,3 +52,19 @@ void launch_plane_tendency_fma(const PlaneJob<FT>& P, cudaStream_t stream) {
 }
 template void launch_plane_tendency_fma<float>(const PlaneJob<float>&, cudaStream_t);
 template void launch_plane_tendency_fma<double>(const PlaneJob<double>&, cudaStream_t);
+
+// the complete path's tiled tendency kernel (all fields, one launch) in the contracted build: the fast flux stage uses the
+// quotient-free WENO5 weights, everything else is the same source compiled with FMA contraction
+template <typename FT>
+void launch_tiled_tendency_fma(const TendParams<FT>& P, dim3 grid, int fast_ok, cudaStream_t stream) {
+  static bool attr_set[64] = {};
+  int dev = 0;
+  CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev >= 64 || !attr_set[dev]) {
+    CUDA_CHECK(cudaFuncSetAttribute(tendency_tiled_kernel<FT, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TG_SMEM_ELEMS * sizeof(FT))));
+    if (dev < 64) attr_set[dev] = true;
+  }
+  tendency_tiled_kernel<FT, 1><<<grid, dim3(TG_TX, TG_TY, 1), TG_SMEM_ELEMS * sizeof(FT), stream>>>(P, -1, fast_ok);
+}
+template void launch_tiled_tendency_fma<float>(const TendParams<float>&, dim3, int, cudaStream_t);
+template void launch_tiled_tendency_fma<double>(const TendParams<double>&, dim3, int, cudaStream_t);

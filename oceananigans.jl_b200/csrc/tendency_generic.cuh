@@ -405,7 +405,7 @@ __global__ void __launch_bounds__(128) tendency_generic_kernel(const __grid_cons
 // direction); 1: along the component's own direction (flux at Centres, advecting velocity from the window itself); 2: tracer.
 // A0 … A3: the face area at each of the four advecting-velocity points (they differ only when that interpolation runs along a
 // stretched z: Ax = Δy·Δzᶜ[k′]); KIND 1 and 2 use A0 alone.
-template <typename FT, int KIND>
+template <typename FT, int KIND, int VARIANT = 0>
 __device__ __forceinline__ FT tg_window_flux(const SchemeTables<FT>& T, FT S0, FT S1, FT S2, FT S3, FT S4, FT S5, FT v0, FT v1,
                                              FT v2, FT v3, FT A0, FT A1, FT A2, FT A3) {
   FT ut;
@@ -420,12 +420,13 @@ __device__ __forceinline__ FT tg_window_flux(const SchemeTables<FT>& T, FT S0, F
     left = ut > FT(0);
   }
   const FT q0 = left ? S0 : S5, q1 = left ? S1 : S4, q2 = left ? S2 : S3, q3 = left ? S3 : S2, q4 = left ? S4 : S1;
-  return ut * weno5_from_q<FT>(T, q0, q1, q2, q3, q4);
+  // VARIANT 1 (exact_arithmetic = 0; instantiated in tendency_fma.cu only): the regrouped, quotient-free weights of recon.cuh
+  return ut * (VARIANT == 0 ? weno5_from_q<FT>(T, q0, q1, q2, q3, q4) : weno5_contracted<FT>(T, q0, q1, q2, q3, q4));
 }
 
 // `count` consecutive fluxes along a direction with stride sb, the first at flux location n: window carried in registers.
 // pb: advecting velocity U_b, sa: stride of the component's direction (KIND 0)
-template <typename FT, int KIND>
+template <typename FT, int KIND, int VARIANT = 0>
 __device__ __forceinline__ void tg_march(const SchemeTables<FT>& T, const FT* __restrict__ fa, const FT* __restrict__ ub, int n,
                                          int sb, int sa, FT A0, FT A1, FT A2, FT A3, int count, FT* out, int ostride) {
   const FT* p = fa + (n + ((KIND == 1 ? 1 : 0) - 3) * sb);
@@ -438,13 +439,13 @@ __device__ __forceinline__ void tg_march(const SchemeTables<FT>& T, const FT* __
     FT v0 = FT(0), v1 = FT(0), v2 = FT(0), v3 = FT(0);
     if (KIND == 0) { v0 = pb[0]; v1 = pb[sa]; v2 = pb[2 * sa]; v3 = pb[3 * sa]; }
     if (KIND == 2) v0 = pb[0];
-    *out = tg_window_flux<FT, KIND>(T, S0, S1, S2, S3, S4, S5, v0, v1, v2, v3, A0, A1, A2, A3);
+    *out = tg_window_flux<FT, KIND, VARIANT>(T, S0, S1, S2, S3, S4, S5, v0, v1, v2, v3, A0, A1, A2, A3);
     out += ostride; p += sb; pb += sb;
     S0 = S1; S1 = S2; S2 = S3; S3 = S4; S4 = S5;
   }
 }
 
-template <typename FT, int a>    // a = 0,1,2: velocity component; a = 3: tracer c
+template <typename FT, int a, int VARIANT = 0>    // a = 0,1,2: velocity component; a = 3: tracer c
 __device__ __forceinline__ void tg_stage_fast(const TendParams<FT>& P, const FT* __restrict__ c, FT* Fx, FT* Fy, FT* Fz, int i0,
                                               int j0, int k0, int nx, int ny, int nz, int tid) {
   static_assert(TG_TX * TG_TY == TG_TX * TG_TZ, "one thread per line of faces in both marching directions");
@@ -464,13 +465,13 @@ __device__ __forceinline__ void tg_stage_fast(const TendParams<FT>& P, const FT*
     const FT S0 = w[0], S1 = w[1], S2 = w[2], S3 = w[3], S4 = w[4], S5 = w[5];
     const FT Ax = g.dy * g.Dzc(k);
     FT f;
-    if (a == 0) f = tg_window_flux<FT, 1>(P.tab, S0, S1, S2, S3, S4, S5, FT(0), FT(0), FT(0), FT(0), Ax, Ax, Ax, Ax);
-    else if (a == 3) f = tg_window_flux<FT, 2>(P.tab, S0, S1, S2, S3, S4, S5, P.U[0][n], FT(0), FT(0), FT(0), Ax, Ax, Ax, Ax);
+    if (a == 0) f = tg_window_flux<FT, 1, VARIANT>(P.tab, S0, S1, S2, S3, S4, S5, FT(0), FT(0), FT(0), FT(0), Ax, Ax, Ax, Ax);
+    else if (a == 3) f = tg_window_flux<FT, 2, VARIANT>(P.tab, S0, S1, S2, S3, S4, S5, P.U[0][n], FT(0), FT(0), FT(0), Ax, Ax, Ax, Ax);
     else {
       const FT* q = P.U[0] + n - 2 * sa;
-      if (a == 2) f = tg_window_flux<FT, 0>(P.tab, S0, S1, S2, S3, S4, S5, q[0], q[sa], q[2 * sa], q[3 * sa], g.dy * g.Dzc(k - 2),
+      if (a == 2) f = tg_window_flux<FT, 0, VARIANT>(P.tab, S0, S1, S2, S3, S4, S5, q[0], q[sa], q[2 * sa], q[3 * sa], g.dy * g.Dzc(k - 2),
                                             g.dy * g.Dzc(k - 1), Ax, g.dy * g.Dzc(k + 1));
-      else f = tg_window_flux<FT, 0>(P.tab, S0, S1, S2, S3, S4, S5, q[0], q[sa], q[2 * sa], q[3 * sa], Ax, Ax, Ax, Ax);
+      else f = tg_window_flux<FT, 0, VARIANT>(P.tab, S0, S1, S2, S3, S4, S5, q[0], q[sa], q[2 * sa], q[3 * sa], Ax, Ax, Ax, Ax);
     }
     Fx[(lk * TG_TY + lj) * (TG_TX + 1) + li] = f;
   }
@@ -481,17 +482,17 @@ __device__ __forceinline__ void tg_stage_fast(const TendParams<FT>& P, const FT*
     const int n0 = g.idx32(ci, j0, k);
     const FT Ay = g.dx * g.Dzc(k);
     FT* out = Fy + lo * (TG_TY + 1) * TG_TX + li;
-    if (a == 1) tg_march<FT, 1>(P.tab, fa, fa, n0 - sy, sy, sa, Ay, Ay, Ay, Ay, ny + 1, out, TG_TX);
-    else if (a == 3) tg_march<FT, 2>(P.tab, fa, P.U[1], n0, sy, sa, Ay, Ay, Ay, Ay, ny + 1, out, TG_TX);
-    else if (a == 2) tg_march<FT, 0>(P.tab, fa, P.U[1], n0, sy, sa, g.dx * g.Dzc(k - 2), g.dx * g.Dzc(k - 1), Ay, g.dx * g.Dzc(k + 1), ny + 1, out, TG_TX);
-    else tg_march<FT, 0>(P.tab, fa, P.U[1], n0, sy, sa, Ay, Ay, Ay, Ay, ny + 1, out, TG_TX);
+    if (a == 1) tg_march<FT, 1, VARIANT>(P.tab, fa, fa, n0 - sy, sy, sa, Ay, Ay, Ay, Ay, ny + 1, out, TG_TX);
+    else if (a == 3) tg_march<FT, 2, VARIANT>(P.tab, fa, P.U[1], n0, sy, sa, Ay, Ay, Ay, Ay, ny + 1, out, TG_TX);
+    else if (a == 2) tg_march<FT, 0, VARIANT>(P.tab, fa, P.U[1], n0, sy, sa, g.dx * g.Dzc(k - 2), g.dx * g.Dzc(k - 1), Ay, g.dx * g.Dzc(k + 1), ny + 1, out, TG_TX);
+    else tg_march<FT, 0, VARIANT>(P.tab, fa, P.U[1], n0, sy, sa, Ay, Ay, Ay, Ay, ny + 1, out, TG_TX);
   }
   {
     const int n0 = g.idx32(ci, j0 + min(lo, ny - 1), k0);
     FT* out = Fz + lo * TG_TX + li;
-    if (a == 2) tg_march<FT, 1>(P.tab, fa, fa, n0 - sz, sz, sa, Az, Az, Az, Az, nz + 1, out, TG_TY * TG_TX);
-    else if (a == 3) tg_march<FT, 2>(P.tab, fa, P.U[2], n0, sz, sa, Az, Az, Az, Az, nz + 1, out, TG_TY * TG_TX);
-    else tg_march<FT, 0>(P.tab, fa, P.U[2], n0, sz, sa, Az, Az, Az, Az, nz + 1, out, TG_TY * TG_TX);
+    if (a == 2) tg_march<FT, 1, VARIANT>(P.tab, fa, fa, n0 - sz, sz, sa, Az, Az, Az, Az, nz + 1, out, TG_TY * TG_TX);
+    else if (a == 3) tg_march<FT, 2, VARIANT>(P.tab, fa, P.U[2], n0, sz, sa, Az, Az, Az, Az, nz + 1, out, TG_TY * TG_TX);
+    else tg_march<FT, 0, VARIANT>(P.tab, fa, P.U[2], n0, sz, sa, Az, Az, Az, Az, nz + 1, out, TG_TY * TG_TX);
   }
 }
 
@@ -552,7 +553,7 @@ __device__ __forceinline__ void tg_stage_closure_fast(const TendParams<FT>& P, c
   }
 }
 
-template <typename FT, int a>    // a = 0,1,2: velocity component; a = 3: tracer P.c[t]
+template <typename FT, int a, int VARIANT = 0>    // a = 0,1,2: velocity component; a = 3: tracer P.c[t]
 __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, FT* sm, bool fast) {
   const GridDev<FT>& g = P.g;
   typedef FT (*FxT)[TG_TY][TG_TX + 1];
@@ -578,7 +579,7 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
     if (pass == 1 && !P.has_closure) break;
     if (pass == 1) __syncthreads();            // everyone has read the advective fluxes
     if (pass == 0 && fast) {
-      tg_stage_fast<FT, a>(P, c, &Fx[0][0][0], &Fy[0][0][0], &Fz[0][0][0], i0, j0, k0, nx, ny, nz, tid);
+      tg_stage_fast<FT, a, VARIANT>(P, c, &Fx[0][0][0], &Fy[0][0][0], &Fz[0][0][0], i0, j0, k0, nx, ny, nz, tid);
     } else if (pass == 1 && fast && !P.nue && g.z_regular) {
       tg_stage_closure_fast<FT, a>(P, c, t, &Fx[0][0][0], &Fy[0][0][0], &Fz[0][0][0], i0, j0, k0, nx, ny, nz, tid);
     } else {
@@ -645,7 +646,7 @@ __device__ __forceinline__ void tiled_tendency(const TendParams<FT>& P, int t, F
 // One launch for every prognostic field (what = -1: u, v, w, then the tracers, the tile's shared memory reused field after field)
 // or for one of them (what = 0, 1, 2 or 3 + tracer index).  fast_ok: the model qualifies for the fast flux stage (set by the
 // host: WENO5 in x, y, z; x, y Periodic; z Periodic or Bounded; regular spacing; parent volume below 2³¹ elements).
-template <typename FT>
+template <typename FT, int VARIANT = 0>
 #if TG_MINBLOCKS > 1
 #define TG_BOUNDS __launch_bounds__(TG_TX * TG_TY, TG_MINBLOCKS)
 #else
@@ -660,10 +661,13 @@ __global__ void TG_BOUNDS tendency_tiled_kernel(const __grid_constant__ TendPara
   const bool fast = fast_ok && (g.topo[2] == NH_PERIODIC || (k0 - 1 >= 4 && k0 + nz <= g.N[2] - 2));
   const int first = what < 0 ? 0 : what, last = what < 0 ? 2 + P.ntr : what;
   for (int f = first; f <= last; ++f) {
-    if (f == 0) tiled_tendency<FT, 0>(P, 0, sm, fast);
-    else if (f == 1) tiled_tendency<FT, 1>(P, 0, sm, fast);
-    else if (f == 2) tiled_tendency<FT, 2>(P, 0, sm, fast);
-    else tiled_tendency<FT, 3>(P, f - 3, sm, fast);
+    if (f == 0) tiled_tendency<FT, 0, VARIANT>(P, 0, sm, fast);
+    else if (f == 1) tiled_tendency<FT, 1, VARIANT>(P, 0, sm, fast);
+    else if (f == 2) tiled_tendency<FT, 2, VARIANT>(P, 0, sm, fast);
+    else tiled_tendency<FT, 3, VARIANT>(P, f - 3, sm, fast);
     __syncthreads();
   }
 }
+
+// the contracted build of the tiled kernel lives in tendency_fma.cu (compiled with FMA contraction)
+template <typename FT> void launch_tiled_tendency_fma(const TendParams<FT>& P, dim3 grid, int fast_ok, cudaStream_t stream);

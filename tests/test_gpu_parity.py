@@ -623,6 +623,20 @@ def test_contracted_arithmetic_100_steps_vs_oracle(oc, FT, tol, timestepper, siz
     assert m1.max_abs_divergence() < (1e-11 if FT == np.float64 else 5e-3)
 
 
+@pytest.mark.parametrize("FT,tol", [(np.float64, 1e-12), (np.float32, 1e-5)])
+def test_contracted_arithmetic_complete_path_100_steps_vs_oracle(oc, FT, tol):
+    """exact_arithmetic = 0 on the complete path (the tiled all-fields tendency kernel with the quotient-free WENO5 weights on
+    its interior tiles, compiled with FMA contraction): u, v, w, T, S, p after 100 steps of the full-physics (P,P,B) model stay
+    within the north_star tolerance of the oracle (10x the oracle's own 1-ulp sensitivity where that is larger)."""
+    kw = dict(extent=(1, 1, 1), buoyancy="seawater", tracers=("T", "S"), coriolis=1e-4, closure=(1e-3, 1e-3))
+    size = (32, 16, 32)                       # tiles k0 = 9, 17 are interior: the fast flux stage runs
+    m1, m2 = make_pair(oc, FT, size, (P, P, B), exact_arithmetic=False, **kw)
+    _, m3 = make_pair(oc, FT, size, (P, P, B), **kw)
+    ics = smooth_ics(m2, np.random.default_rng(1234), amp=0.5)
+    err, floor = _run_steps(oc, m1, m2, ics, 5e-3, 100, m3)
+    check_parity(err, tol, floor)
+
+
 def test_contracted_arithmetic_is_a_different_kernel_within_rounding(oc):
     """One tendency evaluation in both modes: not bit-identical (the contracted build really ran), equal to ~1e-13."""
     size = (40, 24, 16)
