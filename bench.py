@@ -30,8 +30,9 @@ sys.path.insert(0, ROOT)
 
 METRIC = "cell-updates/s (NonhydrostaticModel WENO step)"
 UNIT = "cell-updates/s"
-# FP64-pipe instructions per cell of tendency_fast_kernel (ncu opcode mix, profiles/r1_tendency_sass_mix.md)
-FP64_INSTR_PER_CELL = {"exact": 1290.0, "contracted": 690.0}
+# FP64-pipe instructions per cell of the fused sweep (ncu opcode mix, profiles/r2_tendency_sass_mix.md: DMUL + DFMA + DADD of
+# tendency_fast_kernel<double, 0> in exact and of tendency_plane_kernel<double, 1> in contracted arithmetic)
+FP64_INSTR_PER_CELL = {"exact": 1290.0, "contracted": 717.0}
 
 
 def peaks():
@@ -45,7 +46,7 @@ def peaks():
 def measured_traffic(phase, N):
     """DRAM bytes per launch of the phase's kernel(s) from the committed ncu capture, if it was taken at this size."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
             t = json.load(f)
         return t["dram_bytes_per_launch"][phase] if t["size"] == N else None
     except Exception:

@@ -200,6 +200,12 @@ int32_t nh_dist_buffer(nh_model* model, int32_t which, void** device_ptr, int64_
 int32_t nh_dist_halo(nh_model* model, uint32_t field_mask, int32_t width, int32_t unpack, int64_t* elements);
 /* stage 0…2 of RK3 (runge_kutta_3.jl:77-151) or 0 of AB2; compute_tendencies! fused with the substep; updates the clock */
 int32_t nh_dist_tendency_substep(nh_model* model, double dt, int32_t stage, int32_t euler, double* stage_dt);
+/* The same sweep in two launches, so that communication overlaps computation like the reference's interior / buffer split
+ * (src/Models/interleave_communication_and_computation.jl:9-67, NonhydrostaticModels/compute_nonhydrostatic_buffer_tendencies.jl:
+ * 10-83): part 1 = the tile rows whose stencils stay inside this slab's own rows — it needs no neighbour's halo row and is issued
+ * BEFORE the barrier that closes the previous stage's pressure correction; part 2 = the tile rows next to the two y faces,
+ * issued after that barrier; it also swaps the ping-pong buffers and advances the clock.  part 0 = nh_dist_tendency_substep. */
+int32_t nh_dist_tendency_substep_part(nh_model* model, double dt, int32_t stage, int32_t euler, int32_t part, double* stage_dt);
 /* phase 0: div(U*)/Δt → FFT x → FFT z into A;  1: FFT y, ÷(λx+λy+λz), IFFT y in B;  2: IFFT z, IFFT x from A → pNHS */
 int32_t nh_dist_poisson(nh_model* model, int32_t phase, double stage_dt);
 int32_t nh_dist_pressure_correct(nh_model* model, double stage_dt);

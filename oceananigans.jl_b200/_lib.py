@@ -52,7 +52,7 @@ SYMBOLS = [
     "nh_synchronize", "nh_field_device_ptr", "nh_model_set_stream", "nh_launch_count", "nh_poisson_create",
     "nh_poisson_destroy", "nh_poisson_solve", "nh_poisson_synchronize", "nh_poisson_launch_count",
     "nh_poisson_time_solves", "nh_tridiag_create", "nh_tridiag_solve", "nh_tridiag_destroy",
-    "nh_dist_configure", "nh_dist_buffer", "nh_dist_halo", "nh_dist_tendency_substep", "nh_dist_poisson",
+    "nh_dist_configure", "nh_dist_buffer", "nh_dist_halo", "nh_dist_tendency_substep", "nh_dist_tendency_substep_part", "nh_dist_poisson",
     "nh_dist_pressure_correct", "nh_dist_ipc_export", "nh_dist_ipc_import", "nh_model_set_boundary_condition",
     "nh_model_set_boundary_condition_array", "nh_dist_mode",
     "nh_dist_barrier", "nh_dist_transpose", "nh_tridiag_solve_static", "nh_reconstruction_coefficients",
@@ -114,6 +114,7 @@ def lib():
             "nh_dist_buffer": [p, C.c_int32, C.POINTER(p), C.POINTER(C.c_int64)],
             "nh_dist_halo": [p, C.c_uint32, C.c_int32, C.c_int32, C.POINTER(C.c_int64)],
             "nh_dist_tendency_substep": [p, C.c_double, C.c_int32, C.c_int32, C.POINTER(C.c_double)],
+            "nh_dist_tendency_substep_part": [p, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_double)],
             "nh_dist_poisson": [p, C.c_int32, C.c_double],
             "nh_dist_pressure_correct": [p, C.c_double],
             "nh_dist_ipc_export": [p, p, C.c_int64, C.POINTER(C.c_int64)],

@@ -212,6 +212,7 @@ int32_t nh_dist_mode(nh_model* m, int32_t* mode) { MODEL_CALL(m, *mode = m->dist
 int32_t nh_dist_configure(nh_model* m, int32_t rank, int32_t nranks, double y0, double y1, int32_t Ny) { MODEL_CALL(m, m->dist_configure(rank, nranks, y0, y1, Ny)) }
 int32_t nh_dist_buffer(nh_model* m, int32_t which, void** ptr, int64_t* bytes) { MODEL_CALL(m, NH_REQUIRE(ptr && bytes, "null argument"); m->dist_buffer(which, ptr, bytes)) }
 int32_t nh_dist_halo(nh_model* m, uint32_t mask, int32_t w, int32_t unpack, int64_t* elements) { MODEL_CALL(m, int64_t n = m->dist_halo(mask, w, unpack); if (elements) *elements = n) }
+int32_t nh_dist_tendency_substep_part(nh_model* m, double dt, int32_t stage, int32_t euler, int32_t part, double* stage_dt) { MODEL_CALL(m, double s = m->dist_tendency_substep(dt, stage, euler, part); if (stage_dt) *stage_dt = s) }
 int32_t nh_dist_tendency_substep(nh_model* m, double dt, int32_t stage, int32_t euler, double* stage_dt) { MODEL_CALL(m, double s = m->dist_tendency_substep(dt, stage, euler); if (stage_dt) *stage_dt = s) }
 int32_t nh_dist_poisson(nh_model* m, int32_t phase, double stage_dt) { MODEL_CALL(m, m->dist_poisson(phase, stage_dt)) }
 int32_t nh_dist_pressure_correct(nh_model* m, double stage_dt) { MODEL_CALL(m, m->dist_pressure_correct(stage_dt)) }

@@ -60,7 +60,8 @@ int64_t Model<FT>::dist_halo(uint32_t mask, int w, int unpack) {
 
 // Gⁿ = G(U) and U* = U + Δt(…) in one sweep (the velocities' halos must be current); returns the stage's Δt.
 template <typename FT>
-double Model<FT>::dist_tendency_substep(double dt, int stage, int euler) {
+double Model<FT>::dist_tendency_substep(double dt, int stage, int euler, int part) {
+  NH_REQUIRE(part >= 0 && part <= 2, "part must be 0 (whole sweep), 1 (interior tile rows) or 2 (boundary tile rows)");
   NH_REQUIRE(dist.on, "model is not configured for a distributed run");
   int mode; FT c1, c2; double stage_dt;
   if (desc.timestepper == NH_RK3) {
@@ -77,6 +78,21 @@ double Model<FT>::dist_tendency_substep(double dt, int stage, int euler) {
   J.g = gh.g; J.tab = tab; J.dt = (FT)dt; J.gamma = c1; J.zeta = c2; J.mode = mode;
   for (int a = 0; a < 3; ++a) { J.U[a] = F[a]; J.Unew[a] = F2[a]; J.Gn[a] = Gn[a]; J.Gm[a] = Gm[a]; }
   if (dist.p2p) J.v_prev = dist.prevF2[1];
+  // interior / boundary split: tile rows whose stencils (3 rows either side) stay inside this slab's own rows need no halo row
+  // of a neighbour and can run before the barrier that publishes those rows
+  const int TY = plane_sweep ? TP_TY : TF_TY, nty = ceil_div(gh.g.N[1], TY);
+  const int lo = 1, hi = (gh.g.N[1] - TY - 3) / TY;                 // interior = tile rows lo … hi (needs TY >= 3)
+  const bool has_interior = part != 0 && gh.g.N[1] >= 2 * TY + 3 && hi >= lo;
+  if (part == 1) {
+    if (has_interior) {
+      J.ty_split = 0; J.ty_gap = lo; J.ny_tiles = hi - lo + 1;
+      launch_fused_sweep(J);
+      lc.n++;
+      CUDA_CHECK(cudaGetLastError());
+    }
+    return stage_dt;                 // buffers, tendencies' roles and the clock change hands with part 2
+  }
+  if (part == 2 && has_interior) { J.ty_split = lo; J.ty_gap = hi + 1 - lo; J.ny_tiles = lo + (nty - 1 - hi); }
   launch_fused_sweep(J);
   lc.n++;
   CUDA_CHECK(cudaGetLastError());
@@ -228,7 +244,7 @@ void Model<FT>::dist_transpose(int direction) {
   template void Model<FT>::dist_configure(int, int, double, double, int);                \
   template void Model<FT>::dist_buffer(int, void**, int64_t*);                           \
   template int64_t Model<FT>::dist_halo(uint32_t, int, int);                             \
-  template double Model<FT>::dist_tendency_substep(double, int, int);                    \
+  template double Model<FT>::dist_tendency_substep(double, int, int, int);                    \
   template void Model<FT>::dist_poisson(int, double);                                    \
   template void Model<FT>::dist_pressure_correct(double);                                \
   template int64_t Model<FT>::dist_ipc_export(unsigned char*, int64_t);                  \

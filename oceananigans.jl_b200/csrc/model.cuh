@@ -303,7 +303,7 @@ struct nh_model {
   virtual void dist_configure(int rank, int nranks, double y0, double y1, int Ny) = 0;
   virtual void dist_buffer(int which, void** ptr, int64_t* bytes) = 0;
   virtual int64_t dist_halo(uint32_t mask, int w, int unpack) = 0;
-  virtual double dist_tendency_substep(double dt, int stage, int euler) = 0;
+  virtual double dist_tendency_substep(double dt, int stage, int euler, int part = 0) = 0;
   virtual void dist_poisson(int phase, double stage_dt) = 0;
   virtual void dist_pressure_correct(double stage_dt) = 0;
   virtual int64_t dist_ipc_export(unsigned char* blob, int64_t capacity) = 0;
@@ -425,7 +425,7 @@ struct Model : nh_model {
   void dist_configure(int rank, int nranks, double y0, double y1, int Ny) override;
   void dist_buffer(int which, void** ptr, int64_t* bytes) override;
   int64_t dist_halo(uint32_t mask, int w, int unpack) override;
-  double dist_tendency_substep(double dt, int stage, int euler) override;
+  double dist_tendency_substep(double dt, int stage, int euler, int part = 0) override;
   void dist_poisson(int phase, double stage_dt) override;
   void dist_pressure_correct(double stage_dt) override;
   int64_t dist_ipc_export(unsigned char* blob, int64_t capacity) override;

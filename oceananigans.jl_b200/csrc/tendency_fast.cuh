@@ -64,7 +64,14 @@ struct FastTendJob {
   // y-slab runs with peer-to-peer halos: row j = 1 of v* is also stored into row Ny+1 of the previous rank's v* (NVLink
   // peer pointer), which is all the divergence of that rank needs from here; nullptr otherwise
   FT* v_prev = nullptr;
+  // tile rows (in y) this launch covers: row t of the launch is tile row t for t < ty_split, t + ty_gap otherwise; ny_tiles = how
+  // many.  Whole grid: ty_split = ny_tiles, ty_gap = 0.  A y-slab run launches the interior tile rows (those whose stencils stay
+  // inside the slab's own rows) before the barrier that makes the neighbours' halo rows visible, and the rest after it
+  // (interior / boundary overlap, cf. src/Models/interleave_communication_and_computation.jl:9-67).
+  int ty_split = 1 << 30, ty_gap = 0, ny_tiles = 0;
 };
+template <typename FT>
+__device__ __forceinline__ int tf_tile_row(const FastTendJob<FT>& J) { return (int)blockIdx.y + ((int)blockIdx.y >= J.ty_split ? J.ty_gap : 0); }
 
 // face flux F_{b,a} at flux-location index n (linear), strides sa (dim a) and sb (dim b)
 template <typename FT, bool SAME, int VARIANT = 0>
@@ -234,7 +241,7 @@ __global__ void __launch_bounds__(TF_THREADS, TF_MINBLOCKS) tendency_fast_kernel
   FyT Fy = reinterpret_cast<FyT>(tf_smem + sizeof(FT) * TF_TZ * TF_TY * (TF_TX + 1));
   FzT Fz = reinterpret_cast<FzT>(tf_smem + sizeof(FT) * (TF_TZ * TF_TY * (TF_TX + 1) + TF_TZ * (TF_TY + 1) * TF_TX));
   const GridDev<FT>& g = J.g;
-  const int i0 = blockIdx.x * TF_TX + 1, j0 = blockIdx.y * TF_TY + 1, k0 = blockIdx.z * TF_TZ + 1;
+  const int i0 = blockIdx.x * TF_TX + 1, j0 = tf_tile_row(J) * TF_TY + 1, k0 = blockIdx.z * TF_TZ + 1;
   const int tid = threadIdx.x;
   const int st[3] = {1, (int)g.sy, (int)g.sz};   // 32-bit element offsets: the parent volume is < 2^31 elements
   const FT Ax = g.dy * g.dz, Ay = g.dx * g.dz, Az = g.dx * g.dy;
@@ -338,7 +345,7 @@ template <typename FT>
 inline void launch_fused_tendency(const FastTendJob<FT>& J, cudaStream_t stream, bool exact = true) {
   if (!exact) { launch_fused_tendency_fma<FT>(J, stream); return; }
   const GridDev<FT>& g = J.g;
-  dim3 grd(ceil_div(g.N[0], TF_TX), ceil_div(g.N[1], TF_TY), ceil_div(g.N[2], TF_TZ));
+  dim3 grd(ceil_div(g.N[0], TF_TX), J.ny_tiles > 0 ? J.ny_tiles : ceil_div(g.N[1], TF_TY), ceil_div(g.N[2], TF_TZ));
   tendency_fast_kernel<FT, 0><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
 }
 

@@ -29,7 +29,7 @@ void launch_fused_tendency_fma(const FastTendJob<FT>& J, cudaStream_t stream) {
     if (dev < 64) attr_set[dev] = true;
   }
   const GridDev<FT>& g = J.g;
-  dim3 grd(ceil_div(g.N[0], TF_TX), ceil_div(g.N[1], TF_TY), ceil_div(g.N[2], TF_TZ));
+  dim3 grd(ceil_div(g.N[0], TF_TX), J.ny_tiles > 0 ? J.ny_tiles : ceil_div(g.N[1], TF_TY), ceil_div(g.N[2], TF_TZ));
   tendency_fast_kernel<FT, 1><<<grd, TF_THREADS, TF_SMEM_ELEMS * sizeof(FT), stream>>>(J);
 }
 
@@ -47,7 +47,7 @@ void launch_plane_tendency_fma(const PlaneJob<FT>& P, cudaStream_t stream) {
     if (dev < 64) attr_set[dev] = true;
   }
   const GridDev<FT>& g = P.J.g;
-  dim3 grd(ceil_div(g.N[0], TP_TX), ceil_div(g.N[1], TP_TY), ceil_div(g.N[2], P.zseg));
+  dim3 grd(ceil_div(g.N[0], TP_TX), P.J.ny_tiles > 0 ? P.J.ny_tiles : ceil_div(g.N[1], TP_TY), ceil_div(g.N[2], P.zseg));
   tendency_plane_kernel<FT, 1><<<grd, TP_THREADS, TPSizes<FT>::total, stream>>>(P);
 }
 template void launch_plane_tendency_fma<float>(const PlaneJob<float>&, cudaStream_t);

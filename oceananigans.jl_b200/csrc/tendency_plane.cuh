@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(TP_THREADS, TP_MINBLOCKS) tendency_plane_kerne
   const unsigned bars = tp_smem_u32(base + Z::planes + Z::flux_bytes), fbars = bars + 8 * TP_STAGES;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const bool regular = warp < TP_TY;
-  const int i0 = blockIdx.x * TP_TX + 1, j0 = blockIdx.y * TP_TY + 1, k0 = blockIdx.z * P.zseg + 1;
+  const int i0 = blockIdx.x * TP_TX + 1, j0 = tf_tile_row(J) * TP_TY + 1, k0 = blockIdx.z * P.zseg + 1;
   const int nx = min(TP_TX, g.N[0] - i0 + 1), ny = min(TP_TY, g.N[1] - j0 + 1), nz = min(P.zseg, g.N[2] - k0 + 1);
   const int sz = (int)g.sz;
   const FT Ax = g.dy * g.dz, Ay = g.dx * g.dz, Az = g.dx * g.dy;
@@ -391,6 +391,6 @@ template <typename FT>
 inline void launch_plane_tendency(const PlaneJob<FT>& P, cudaStream_t stream, bool exact) {
   if (!exact) { launch_plane_tendency_fma<FT>(P, stream); return; }
   const GridDev<FT>& g = P.J.g;
-  dim3 grd(ceil_div(g.N[0], TP_TX), ceil_div(g.N[1], TP_TY), ceil_div(g.N[2], P.zseg));
+  dim3 grd(ceil_div(g.N[0], TP_TX), P.J.ny_tiles > 0 ? P.J.ny_tiles : ceil_div(g.N[1], TP_TY), ceil_div(g.N[2], P.zseg));
   tendency_plane_kernel<FT, 0><<<grd, TP_THREADS, TPSizes<FT>::total, stream>>>(P);
 }

@@ -217,8 +217,10 @@ class DistributedNonhydrostaticModel:
                          self.rank, self.R, self.arch.group)
         check(lib().nh_dist_halo(self._h, mask, width, 1, None))
 
-    def pressure_phase(self, stage_dt):
-        """calculate_pressure_correction! + pressure_correct_velocities! + fill_halo_regions!(velocities)."""
+    def pressure_phase(self, stage_dt, trailing_barrier=True):
+        """calculate_pressure_correction! + pressure_correct_velocities! + fill_halo_regions!(velocities).  In the peer-to-peer
+        mode ``trailing_barrier=False`` leaves the barrier that publishes the neighbours' halo rows to the caller (time_step puts
+        the interior part of the next tendency sweep in front of it)."""
         h, b = self._h, self._buf
         if self.p2p:
             # the kernels have already stored into the peers' buffers: only barriers remain
@@ -230,7 +232,8 @@ class DistributedNonhydrostaticModel:
             check(lib().nh_dist_poisson(h, 2, stage_dt))      # … also writes p[0] of the next rank
             self._barrier()
             check(lib().nh_dist_pressure_correct(h, stage_dt))   # … also writes the neighbours' u, v, w halo rows
-            self._barrier()
+            if trailing_barrier:
+                self._barrier()
             return
         self.exchange(1 << L.FIELD_V, 1)
         check(lib().nh_dist_poisson(h, 0, stage_dt))
@@ -255,6 +258,21 @@ class DistributedNonhydrostaticModel:
             self.exchange(self._uvw, self.halo[1])
             if self.p2p:
                 self._barrier()
+        if self.p2p and not os.environ.get("NHSTEP_NO_OVERLAP"):
+            # interior / boundary overlap (interleave_communication_and_computation.jl:9-67): the tile rows of the sweep that need
+            # no neighbour's halo row are issued BEFORE the barrier that closes the previous stage's pressure correction, so that
+            # barrier's wait (the skew between the ranks) is spent computing; the two boundary tile rows follow it
+            pending = False
+            for _ in range(n_steps):
+                for s in range(stages):
+                    check(lib().nh_dist_tendency_substep_part(self._h, float(dt), s, int(euler), 1, C.byref(sdt)))
+                    if pending:
+                        self._barrier()
+                    check(lib().nh_dist_tendency_substep_part(self._h, float(dt), s, int(euler), 2, C.byref(sdt)))
+                    self.pressure_phase(sdt.value, trailing_barrier=False)
+                    pending = True
+            self._barrier()              # the state is consistent on every rank when time_step returns
+            return
         for _ in range(n_steps):
             for s in range(stages):
                 check(lib().nh_dist_tendency_substep(self._h, float(dt), s, int(euler), C.byref(sdt)))
