@@ -478,10 +478,19 @@ def multi_gpu_targets(oc, D, world, rank, local_rank, exact):
         except Exception as e:
             out[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
 
-    guarded("weak_512_per_gpu", lambda: {"scaling": "weak", **timed_slab_run(
-        oc, D, world, rank, local_rank, (512 * fx, 512 * fy, 512), (2 * np.pi * fx, 2 * np.pi * fy), exact, 2, 5)})
+    # 512³ cells per GPU: the global grid grows in y, then x, then z, no direction beyond the 1024 points the transforms take
+    dims, left = [512, 512, 512], world
+    for e in (1, 0, 2):
+        while left > 1 and dims[e] < 1024:
+            dims[e] *= 2
+            left //= 2
     guarded("c4_1024_cubed", lambda: {"scaling": "strong", **timed_slab_run(
         oc, D, world, rank, local_rank, (1024, 1024, 1024), (2 * np.pi, 2 * np.pi), exact, 2, 3)})
+    if tuple(dims) == (1024, 1024, 1024):
+        out["weak_512_per_gpu"] = {"scaling": "weak", "same_run_as": "c4_1024_cubed", **{k: v for k, v in out["c4_1024_cubed"].items() if k != "scaling"}}
+    else:
+        guarded("weak_512_per_gpu", lambda: {"scaling": "weak", **timed_slab_run(
+            oc, D, world, rank, local_rank, tuple(dims), (2 * np.pi * dims[0] / 512, 2 * np.pi * dims[1] / 512), exact, 2, 5)})
     return out
 
 

@@ -93,7 +93,7 @@ double Model<FT>::dist_tendency_substep(double dt, int stage, int euler, int par
     return stage_dt;                 // buffers, tendencies' roles and the clock change hands with part 2
   }
   if (part == 2 && has_interior) { J.ty_split = lo; J.ty_gap = hi + 1 - lo; J.ny_tiles = lo + (nty - 1 - hi); }
-  launch_fused_sweep(J);
+  launch_fused_sweep(J, part == 2 && has_interior ? 8 : 0);      // two tile rows: 8-plane segments keep every SM busy
   lc.n++;
   CUDA_CHECK(cudaGetLastError());
   for (int a = 0; a < 3; ++a) { std::swap(F[a], F2[a]); std::swap(dist.prevF[a], dist.prevF2[a]); std::swap(dist.nextF[a], dist.nextF2[a]); }

@@ -137,12 +137,12 @@ void Model<FT>::build_filter_width() {
 
 // The fused sweep of the fast path.  Tensor maps are cached per field pointer (u, v, w and their ping-pong twins).
 template <typename FT>
-void Model<FT>::launch_fused_sweep(const FastTendJob<FT>& J) {
+void Model<FT>::launch_fused_sweep(const FastTendJob<FT>& J, int zseg) {
   const bool exact = desc.exact_arithmetic != 0;
   if (!plane_sweep) { launch_fused_tendency<FT>(J, stream, exact); return; }
   PlaneJob<FT> P;
   P.J = J;
-  P.zseg = plane_zseg;
+  P.zseg = zseg > 0 ? std::min(zseg, plane_zseg) : plane_zseg;
   for (int a = 0; a < 3; ++a) {
     auto it = tmaps.find((const void*)J.U[a]);
     if (it == tmaps.end()) {

@@ -369,7 +369,7 @@ struct Model : nh_model {
   void ensure_tendencies();
   void ensure_solver();
   // fused tendency + substep sweep: plane-marching TMA kernel (tendency_plane.cuh) or the tile kernel (tendency_fast.cuh)
-  void launch_fused_sweep(const FastTendJob<FT>& J);
+  void launch_fused_sweep(const FastTendJob<FT>& J, int zseg = 0);      // zseg > 0: shorter z segments (few tile rows: more CTAs)
   bool plane_sweep = true;
   bool tiled_fast_ok = false;        // the tiled tendency kernel may use its fast flux stage on interior tiles
   int plane_zseg = 32;

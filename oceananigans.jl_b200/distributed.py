@@ -258,7 +258,9 @@ class DistributedNonhydrostaticModel:
             self.exchange(self._uvw, self.halo[1])
             if self.p2p:
                 self._barrier()
-        if self.p2p and not os.environ.get("NHSTEP_NO_OVERLAP"):
+        if self.p2p and os.environ.get("NHSTEP_OVERLAP", "0") == "1":
+            # (off by default: measured 5.48 vs 5.31 ms per step at 2 GPUs, 256³ per GPU — the second launch of two tile rows
+            # costs more than the skew it hides; profiles/r2_scaling.md)
             # interior / boundary overlap (interleave_communication_and_computation.jl:9-67): the tile rows of the sweep that need
             # no neighbour's halo row are issued BEFORE the barrier that closes the previous stage's pressure correction, so that
             # barrier's wait (the skew between the ranks) is spent computing; the two boundary tile rows follow it

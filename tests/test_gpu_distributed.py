@@ -181,9 +181,15 @@ def _generic_ics(size, FT, bounded, names):
     return ics
 
 
-def _generic_single(name, FT, timestepper, steps, dt):
-    import oceananigans_jl_b200 as oc
+def _generic_size(name, world):
+    """The configuration's size with Ny raised so that every slab keeps at least 8 rows (a slab needs 2·H = 6)."""
     size, bounded, stretched = GENERIC[name]
+    return (size[0], max(size[1], 8 * world), size[2]), bounded, stretched
+
+
+def _generic_single(name, FT, timestepper, steps, dt, world=1):
+    import oceananigans_jl_b200 as oc
+    size, bounded, stretched = _generic_size(name, world)
     topo = (oc.Periodic, oc.Periodic, oc.Bounded if bounded else oc.Periodic)
     g = oc.RectilinearGrid(FT, size=size, x=(0, 1), y=(0, 2), z=_zfaces(size[2], stretched), halo=(3, 3, 3), topology=topo)
     kw = _generic_kwargs(oc, name, FT)
@@ -198,7 +204,7 @@ def _generic_single(name, FT, timestepper, steps, dt):
 def _generic_distributed(rank, world, name, FT, timestepper, steps, dt, out):
     import oceananigans_jl_b200 as oc
     from oceananigans_jl_b200 import distributed as D
-    size, bounded, stretched = GENERIC[name]
+    size, bounded, stretched = _generic_size(name, world)
     topo = (oc.Periodic, oc.Periodic, oc.Bounded if bounded else oc.Periodic)
     kw = _generic_kwargs(oc, name, FT)
     arch = D.Distributed(D.Partition(y=world))
@@ -259,7 +265,7 @@ def test_multi_gpu_complete_path_slab_matches_single_gpu(name, FT, timestepper, 
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     steps, dt = 10, 2e-3
-    ref = _generic_single(name, FT, timestepper, steps, dt)
+    ref = _generic_single(name, FT, timestepper, steps, dt, world)
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
