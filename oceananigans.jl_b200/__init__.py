@@ -168,8 +168,21 @@ class FluxFormAdvection:
         self.x, self.y, self.z = x, y, z
 
 
+OMEGA_EARTH = 7.292115e-5          # src/Coriolis/Coriolis.jl:19
+
+
 class FPlane:
-    def __init__(self, f):
+    """FPlane(f) or FPlane(rotation_rate=Ω_Earth, latitude=φ): f = 2·rotation_rate·sind(latitude) — src/Coriolis/f_plane.jl:25-40."""
+
+    def __init__(self, f=None, rotation_rate=OMEGA_EARTH, latitude=None):
+        if (f is None) == (latitude is None):
+            raise ValueError("Either both keywords rotation_rate and latitude must be specified, *or* only f must be specified.")
+        if f is None:
+            import math
+            # sind: exact at multiples of 30° like Julia's; elsewhere sin of the degree → radian conversion
+            lat = float(latitude)
+            s = {0.0: 0.0, 30.0: 0.5, 90.0: 1.0, -30.0: -0.5, -90.0: -1.0}.get(lat, math.sin(math.radians(lat)))
+            f = 2 * rotation_rate * s
         self.f = f
 
 

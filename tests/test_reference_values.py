@@ -197,3 +197,38 @@ def test_library_set_and_periodic_halo_fill_equal_the_reference_doctest(oc):
     assert np.array_equal(c.parent()[:, :, 1], before)       # parent index 1 = k = 1 with Hz = 1
     oc.fill_halo_regions(c)
     assert np.array_equal(c.parent()[:, :, 1], after)
+
+
+# ---- constants and constructor defaults the reference states ---------------------------------------------------------------
+def test_fplane_from_latitude_matches_the_reference_doctest():
+    import oceananigans_jl_b200 as oc
+    for mod in (o, oc):
+        for case in GOLD["coriolis"]["cases"]:
+            c = mod.FPlane(case["f"]) if "f" in case else mod.FPlane(rotation_rate=case["rotation_rate"], latitude=case["latitude"])
+            assert sig6(c.f) == float(case["printed"]), (mod.__name__, case)
+        with pytest.raises(ValueError):
+            mod.FPlane()
+        with pytest.raises(ValueError):
+            mod.FPlane(1e-4, latitude=45)
+
+
+def test_time_stepper_and_closure_defaults_match_the_reference_constructors():
+    from fractions import Fraction
+    from oracle.grid import round_fraction
+    K = GOLD["constants"]
+    g = o.RectilinearGrid(np.float64, size=(4, 4, 4), extent=(1, 1, 1))
+    m = o.NonhydrostaticModel(g)
+    for key, name in (("gamma1", "g1"), ("gamma2", "g2"), ("gamma3", "g3"), ("zeta2", "z2"), ("zeta3", "z3")):
+        for FT in (np.float64, np.float32):
+            want = round_fraction(Fraction(*K["rk3"][key]), FT)
+            if FT == np.float64:
+                assert m.rk3[name] == want, key
+    b = o.SeawaterBuoyancy()
+    assert (b.g, b.alpha, b.beta) == (float(K["g_Earth"]), float(K["thermal_expansion"]), float(K["haline_contraction"]))
+    import oceananigans_jl_b200 as oc
+    b1 = oc.SeawaterBuoyancy()
+    assert (b1.g, b1.alpha, b1.beta) == (b.g, b.alpha, b.beta)
+    c = oc.SmagorinskyLilly()
+    assert (c.C, c.Cb, c.Pr) == (float(K["smagorinsky_C"]), float(K["smagorinsky_Cb"]), float(K["smagorinsky_Pr"]))
+    assert o.WENO(np.float64, 5).eps == np.float64(np.float32(float(K["weno_epsilon_float32"])))
+    assert np.float64(oc.reconstruction_coefficients(np.float64, "weno_optimal", 3)[0]) == np.float64(0.3)

@@ -9,10 +9,10 @@ ARCH="-gencode arch=compute_100a,code=sm_100a"
 FLAGS="-O3 -std=c++17 $ARCH -lineinfo -Xcompiler -fPIC --expt-relaxed-constexpr -Xptxas -v"
 if [ "$2" = "exact" ]; then
   nvcc $FLAGS -fmad=false $1 -c model.cu -o build/model.o 2> build/model.ptxas.log
-  grep -A2 "tendency_fast_kernelIdLi0" build/model.ptxas.log | grep -E "registers|spill" | head -3
+  grep -A2 "tendency_fast_kernelIdLi0\|tendency_tiled_kernelIdLi0" build/model.ptxas.log | grep -E "registers|spill" | head -3
 else
   nvcc $FLAGS -fmad=true $1 -c tendency_fma.cu -o build/tendency_fma.o 2> build/tendency_fma.ptxas.log
-  grep -A2 "tendency_fast_kernelIdLi1" build/tendency_fma.ptxas.log | grep -E "registers|spill" | head -3
+  grep -A2 "tendency_plane_kernelIdLi1\|tendency_fast_kernelIdLi1" build/tendency_fma.ptxas.log | grep -E "registers|spill" | head -3
 fi
 nvcc $ARCH -shared -o ../libnhstep.so build/api.o build/model.o build/dist.o build/tendency_fma.o build/solver_generic.o \
-     build/grid_host.o -cudart static
+     build/no_alloc.o build/grid_host.o -cudart static
