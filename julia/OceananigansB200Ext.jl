@@ -224,4 +224,25 @@ end
 solve!(ϕ::Array, s::B200PoissonSolver, b::Array, m = 0) =
     check(ccall((:nh_poisson_solve, libnhstep), Int32, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}, Float64, Int32), s.handle, b, ϕ, m, 0))
 
+# Checkpoints written by oceananigans.jl_b200/checkpointer.py (classic HDF5 with the reference Checkpointer's addresses,
+# src/OutputWriters/checkpointer.jl:223-282): set!(model, filepath) for a Julia NonhydrostaticModel, read with HDF5.jl.
+# `data` datasets have the Julia size of parent(field); the clock is stored member by member.
+function set_from_b200_checkpoint!(model::NonhydrostaticModel, filepath::AbstractString; h5open)   # pass HDF5.h5open
+    h5open(filepath, "r") do file
+        g = file["NonhydrostaticModel"]
+        for (name, field) in pairs(Oceananigans.prognostic_fields(model))
+            haskey(g, string(name)) || (@warn "Field $name does not exist in checkpoint and could not be restored."; continue)
+            copyto!(parent(field), read(g["$name/data"]))
+            if haskey(g, "timestepper") && haskey(g["timestepper/Gⁿ"], string(name))
+                copyto!(parent(model.timestepper.Gⁿ[name]), read(g["timestepper/Gⁿ/$name/data"]))
+                copyto!(parent(model.timestepper.G⁻[name]), read(g["timestepper/G⁻/$name/data"]))
+            end
+        end
+        model.clock.iteration = read(g["clock/iteration"])
+        model.clock.time = read(g["clock/time"])
+        model.clock.last_Δt = read(g["clock/last_Δt"])
+    end
+    return nothing
+end
+
 end # module

@@ -114,6 +114,20 @@ class RectilinearGrid:
         return (self.FT(dxdy[0]), self.FT(dxdy[1]), np.array(dzc, dtype=np.float64).astype(self.FT),
                 np.array(dzf, dtype=np.float64).astype(self.FT))
 
+    def extents(self):
+        """(Lx, Ly, Lz) in the grid's float type: c₂ − c₁ of the FT-converted interval, 1 for a Flat direction."""
+        FT, out = self.FT, []
+        for d in range(3):
+            if self.topology[d] == Flat:
+                out.append(FT(1))
+            elif d == 2 and self._zfaces is not None:
+                F = self._zfaces.astype(FT)
+                out.append(FT(F[-1] - F[0]))
+            else:
+                c1, c2 = (Fraction(float(FT(v))) for v in self._specs[d])
+                out.append(FT(float(c2 - c1)))
+        return tuple(out)
+
     def nodes(self, d, loc):
         """Interior node coordinates along dim d at 'c' or 'f' (src/Grids/grid_generation.jl:98-135, :34-95)."""
         FT, N = self.FT, self.N[d]
@@ -248,3 +262,5 @@ from .model import (Field, NonhydrostaticModel, fill_halo_regions, update_state,
                     cache_previous_tendencies, time_step, time_step_profiled, set_model, FFTBasedPoissonSolver,
                     FourierTridiagonalPoissonSolver, BatchedTridiagonalSolver, BoundaryCondition,
                     FieldBoundaryConditions, ValueBoundaryCondition, GradientBoundaryCondition, FluxBoundaryCondition)
+from .checkpointer import (Checkpointer, write_output, checkpoint_path, latest_checkpoint, cleanup_checkpoints,  # noqa: E402,F401
+                           set_from_checkpoint, pickup)

@@ -1,0 +1,430 @@
+"""A small HDF5 reader and writer in numpy (no libhdf5 / h5py in this image): the subset the checkpoint files need.
+
+The reference writes checkpoints with JLD2.jl (src/OutputWriters/checkpointer.jl:177-201), whose files are HDF5 containers; the
+arrays in them (``<address>/<field>/data`` = ``Array(parent(field))``, output_writer_utils.jl:144-149) are plain contiguous
+datasets.  This module writes and reads the classic HDF5 layout every libhdf5 (HDF5.jl, h5py, h5dump) opens:
+
+* superblock version 0, 8-byte offsets and lengths;
+* groups as version-1 object headers with a symbol-table message → version-1 B-tree → symbol-table nodes → local heap;
+* datasets as version-1 object headers with dataspace (v1), datatype (v1: IEEE floats, integers, fixed-length strings),
+  fill-value (v2) and contiguous data-layout (v3) messages.
+
+The reader additionally follows object-header continuation blocks, compact layouts, version-2 dataspaces, attributes (v1) and a
+non-zero base address / user block, which is what the one libhdf5-written file in this image needs
+(scipy/io/matlab/tests/data/testhdf5_7.4_GLNX86.mat — tests/test_checkpointer.py parses it as the reader's pin).
+Version-2 object headers ("OHDR", what JLD2 itself writes) are NOT parsed: reading a Julia-written checkpoint is out of reach
+here and raises ``NotImplementedError`` naming the structure.
+
+Array order: a Julia / Fortran-ordered array of size (n1, n2, n3) is an HDF5 dataspace (n3, n2, n1) over the same bytes (JLD2 and
+HDF5.jl both reverse the dimensions); ``write`` and ``File.read`` apply that convention, so numpy arrays round-trip with their
+logical shape and Julia sees ``size(data) == (n1, n2, n3)``.
+"""
+import struct
+
+import numpy as np
+
+SIGNATURE = b"\x89HDF\r\n\x1a\n"
+UNDEF = 0xFFFFFFFFFFFFFFFF
+HEAP_FREE_NULL = 1                      # "end of free list" in a local heap (H5HL_FREE_NULL)
+LEAF_K, INTERNAL_K = 4, 16              # libhdf5 defaults: ≤ 2·4 symbols per node, ≤ 2·16 children per B-tree node
+SNOD_SIZE = 8 + 2 * LEAF_K * 40
+BTREE_SIZE = 24 + 2 * INTERNAL_K * 8 + (2 * INTERNAL_K + 1) * 8
+
+MSG_NIL, MSG_DATASPACE, MSG_DATATYPE, MSG_FILL, MSG_LAYOUT, MSG_ATTRIBUTE = 0x0, 0x1, 0x3, 0x5, 0x8, 0xC
+MSG_CONTINUATION, MSG_SYMBOL_TABLE = 0x10, 0x11
+
+
+def _pad8(n):
+    return (n + 7) & ~7
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# datatypes
+# ---------------------------------------------------------------------------------------------------------------------
+
+def _encode_datatype(dt):
+    """Datatype message (version 1) of a numpy dtype: IEEE float, two's-complement integer or fixed-length string."""
+    dt = np.dtype(dt)
+    if dt.kind == "f" and dt.itemsize in (4, 8):
+        size = dt.itemsize
+        exp_bits, man_bits, bias = ((8, 23, 127), (11, 52, 1023))[size == 8]
+        head = struct.pack("<BBBBI", 0x10 | 1, 0x20, size * 8 - 1, 0, size)          # little-endian, implied msb, sign bit
+        return head + struct.pack("<HHBBBBI", 0, size * 8, man_bits, exp_bits, 0, man_bits, bias)
+    if dt.kind in "iu" and dt.itemsize in (1, 2, 4, 8):
+        head = struct.pack("<BBBBI", 0x10 | 0, 0x08 if dt.kind == "i" else 0x00, 0, 0, dt.itemsize)
+        return head + struct.pack("<HH", 0, dt.itemsize * 8)
+    if dt.kind == "S":
+        return struct.pack("<BBBBI", 0x10 | 3, 0x10, 0, 0, max(dt.itemsize, 1))      # null-terminated, UTF-8
+    raise TypeError(f"hdf5.write: unsupported dtype {dt}")
+
+
+def _decode_datatype(b):
+    """(numpy dtype, bytes consumed) of a datatype message."""
+    cls, version = b[0] & 0x0F, b[0] >> 4
+    bits0, bits1 = b[1], b[2]
+    size = struct.unpack_from("<I", b, 4)[0]
+    order = ">" if bits0 & 1 else "<"
+    if version not in (1, 2, 3):
+        raise NotImplementedError(f"hdf5: datatype message version {version}")
+    if cls == 0:
+        return np.dtype(f"{order}{'i' if bits0 & 0x08 else 'u'}{size}"), 8 + 4
+    if cls == 1:
+        if size not in (4, 8):
+            raise NotImplementedError(f"hdf5: {size}-byte floating point")
+        return np.dtype(f"{order}f{size}"), 8 + 12
+    if cls == 3:
+        return np.dtype(f"S{size}"), 8
+    if cls == 7:                                                                         # object / region reference
+        return np.dtype(f"V{size}"), 8
+    raise NotImplementedError(f"hdf5: datatype class {cls}")
+
+
+def _encode_dataspace(shape):
+    """Dataspace message (version 1) for HDF5 dimensions ``shape`` (already in file order); () is a scalar."""
+    return struct.pack("<BBBBI", 1, len(shape), 0, 0, 0) + b"".join(struct.pack("<Q", n) for n in shape)
+
+
+def _decode_dataspace(b):
+    version, rank, flags = b[0], b[1], b[2]
+    if version == 1:
+        off = 8
+    elif version == 2:
+        off = 4
+        if b[3] == 2:                                                                    # H5S_NULL
+            return None
+    else:
+        raise NotImplementedError(f"hdf5: dataspace message version {version}")
+    return tuple(struct.unpack_from("<Q", b, off + 8 * i)[0] for i in range(rank))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# reader
+# ---------------------------------------------------------------------------------------------------------------------
+
+class Dataset:
+    def __init__(self, file, name, messages):
+        self.file, self.name, self._messages = file, name, messages
+        self.attrs = file._attributes(messages)
+
+    def read(self):
+        """The array in its Julia / Fortran shape (reversed HDF5 dimensions), a scalar for a scalar dataspace, str for strings."""
+        return self.file._read_dataset(self._messages, self.name)
+
+
+class Group:
+    def __init__(self, file, name, messages):
+        self.file, self.name, self._messages = file, name, messages
+        self.attrs = file._attributes(messages)
+        self._links = None
+
+    def _entries(self):
+        if self._links is None:
+            self._links = self.file._group_links(self._messages, self.name)
+        return self._links
+
+    def keys(self):
+        return list(self._entries())
+
+    def __contains__(self, key):
+        try:
+            self[key]
+            return True
+        except KeyError:
+            return False
+
+    def __getitem__(self, path):
+        node = self
+        for part in [p for p in path.split("/") if p]:
+            if not isinstance(node, Group):
+                raise KeyError(path)
+            links = node._entries()
+            if part not in links:
+                raise KeyError(f"{path}: no '{part}' in {node.name or '/'}")
+            node = node.file._object(links[part], (node.name + "/" + part))
+        return node
+
+    def read(self, path):
+        """file.read("a/b/data") → array / scalar / str."""
+        obj = self[path]
+        if not isinstance(obj, Dataset):
+            raise KeyError(f"{path} is a group")
+        return obj.read()
+
+    def tree(self):
+        """Nested dict of everything below this group (datasets read)."""
+        return {k: (v.tree() if isinstance(v, Group) else v.read()) for k, v in ((k, self[k]) for k in self.keys())}
+
+
+class File(Group):
+    """Read-only view of an HDF5 file: ``File(path)["NonhydrostaticModel/u/data"].read()``."""
+
+    def __init__(self, path):
+        with open(path, "rb") as fh:
+            self.buf = fh.read()
+        at = 0
+        while self.buf[at:at + 8] != SIGNATURE:                   # the superblock sits at 0, 512, 1024, … (user block before it)
+            at = 512 if at == 0 else at * 2
+            if at + 8 > len(self.buf):
+                raise ValueError(f"{path}: not an HDF5 file (no superblock signature)")
+        b = self.buf
+        version = b[at + 8]
+        if version not in (0, 1):
+            raise NotImplementedError(f"hdf5: superblock version {version} (JLD2 / libhdf5 ≥ 1.8 'latest' files) is not parsed; "
+                                      "this reader covers the classic version-0/1 layout")
+        if b[at + 13] != 8 or b[at + 14] != 8:
+            raise NotImplementedError("hdf5: only 8-byte offsets and lengths")
+        self.leaf_k, self.internal_k = struct.unpack_from("<HH", b, at + 16)
+        p = at + 24 + (4 if version == 1 else 0)                  # v1 adds indexed-storage K + reserved
+        self.base, _free, self.eof, _driver = struct.unpack_from("<QQQQ", b, p)
+        if self.base == 0 and at != 0:
+            self.base = 0                                          # addresses are absolute unless a base address is recorded
+        _name, header, _cache = struct.unpack_from("<QQI", b, p + 32)
+        Group.__init__(self, self, "", self._object_header(header))
+
+    # -- low level ---------------------------------------------------------------------------------------------------
+    def _abs(self, addr):
+        return self.base + addr
+
+    def _object_header(self, addr):
+        """Messages [(type, flags, bytes)] of the object header at ``addr``, continuation blocks followed."""
+        b, at = self.buf, self._abs(addr)
+        if b[at:at + 4] == b"OHDR":
+            raise NotImplementedError("hdf5: version-2 object header (OHDR) — files written by JLD2 or with libver='latest'")
+        version, _r, nmsg, _refs, size = struct.unpack_from("<BBHII", b, at)
+        if version != 1:
+            raise NotImplementedError(f"hdf5: object header version {version}")
+        blocks, messages = [(at + 16, size)], []
+        while blocks and len(messages) < nmsg:
+            p, n = blocks.pop(0)
+            end = p + n
+            while p + 8 <= end and len(messages) < nmsg:
+                mtype, msize, flags = struct.unpack_from("<HHB", b, p)
+                data = bytes(b[p + 8:p + 8 + msize])
+                p += 8 + msize
+                messages.append((mtype, flags, data))
+                if mtype == MSG_CONTINUATION:
+                    off, length = struct.unpack_from("<QQ", data, 0)
+                    blocks.append((self._abs(off), length))
+        return messages
+
+    def _object(self, addr, name):
+        messages = self._object_header(addr)
+        kinds = {m[0] for m in messages}
+        if MSG_SYMBOL_TABLE in kinds:
+            return Group(self, name, messages)
+        if MSG_LAYOUT in kinds:
+            return Dataset(self, name, messages)
+        raise NotImplementedError(f"hdf5: {name} is neither a symbol-table group nor a dataset (message types {sorted(kinds)})")
+
+    def _heap_name(self, heap_data, off):
+        end = self.buf.index(b"\x00", heap_data + off)
+        return self.buf[heap_data + off:end].decode("utf-8")
+
+    def _group_links(self, messages, name):
+        data = next(m[2] for m in messages if m[0] == MSG_SYMBOL_TABLE)
+        btree, heap = struct.unpack_from("<QQ", data, 0)
+        b, h = self.buf, self._abs(heap)
+        if b[h:h + 4] != b"HEAP":
+            raise ValueError(f"hdf5: {name or '/'}: bad local heap signature")
+        _size, _free, heap_data = struct.unpack_from("<QQQ", b, h + 8)
+        heap_data = self._abs(heap_data)
+        links = {}
+
+        def walk(addr):
+            t = self._abs(addr)
+            if b[t:t + 4] != b"TREE":
+                raise ValueError(f"hdf5: {name or '/'}: bad B-tree signature")
+            node_type, level, used = struct.unpack_from("<BBH", b, t + 4)
+            if node_type != 0:
+                raise ValueError("hdf5: group B-tree expected")
+            for i in range(used):
+                child = struct.unpack_from("<Q", b, t + 24 + 8 + 16 * i)[0]
+                if level > 0:
+                    walk(child)
+                    continue
+                s = self._abs(child)
+                if b[s:s + 4] != b"SNOD":
+                    raise ValueError(f"hdf5: {name or '/'}: bad symbol-table node signature")
+                count = struct.unpack_from("<H", b, s + 6)[0]
+                for e in range(count):
+                    name_off, header = struct.unpack_from("<QQ", b, s + 8 + 40 * e)
+                    links[self._heap_name(heap_data, name_off)] = header
+
+        walk(btree)
+        return links
+
+    def _attributes(self, messages):
+        out = {}
+        for mtype, _flags, d in messages:
+            if mtype != MSG_ATTRIBUTE:
+                continue
+            version = d[0]
+            if version != 1:
+                continue                                             # newer encodings: ignored, not needed by any reader here
+            nsize, tsize, ssize = struct.unpack_from("<HHH", d, 2)
+            p = 8
+            aname = d[p:p + nsize].split(b"\x00")[0].decode("utf-8")
+            p += _pad8(nsize)
+            dt, _ = _decode_datatype(d[p:p + tsize])
+            p += _pad8(tsize)
+            shape = _decode_dataspace(d[p:p + ssize])
+            p += _pad8(ssize)
+            out[aname] = self._to_value(d[p:], dt, shape)
+        return out
+
+    @staticmethod
+    def _to_value(raw, dt, shape):
+        if shape is None:
+            return None
+        count = int(np.prod(shape, dtype=np.int64)) if shape else 1
+        a = np.frombuffer(raw, dtype=dt, count=count)
+        if dt.kind == "S":
+            vals = [v.split(b"\x00")[0].decode("utf-8") for v in a]
+            return vals[0] if not shape else np.array(vals, dtype=object).reshape(shape[::-1], order="F")
+        if dt.kind == "V":
+            return a.copy()
+        a = a.astype(dt.newbyteorder("="))
+        return a[0] if not shape else np.asfortranarray(a.reshape(shape).transpose())
+
+    def _read_dataset(self, messages, name):
+        msg = {m[0]: m[2] for m in messages}
+        if MSG_DATASPACE not in msg or MSG_DATATYPE not in msg or MSG_LAYOUT not in msg:
+            raise ValueError(f"hdf5: {name}: dataset header lacks a dataspace, datatype or layout message")
+        shape = _decode_dataspace(msg[MSG_DATASPACE])
+        dt, _ = _decode_datatype(msg[MSG_DATATYPE])
+        lay = msg[MSG_LAYOUT]
+        count = (int(np.prod(shape, dtype=np.int64)) if shape else 1) if shape is not None else 0
+        nbytes = count * dt.itemsize
+        if lay[0] in (1, 2):                                          # libhdf5 < 1.6.3: rank + 1 dimensions, the last = element size
+            if lay[2] != 1:
+                raise NotImplementedError(f"hdf5: {name}: version-{lay[0]} layout of class {lay[2]}")
+            addr = struct.unpack_from("<Q", lay, 8)[0]
+            raw = bytes(nbytes) if addr == UNDEF else self.buf[self._abs(addr):self._abs(addr) + nbytes]
+        elif lay[0] != 3:
+            raise NotImplementedError(f"hdf5: {name}: data layout message version {lay[0]}")
+        elif lay[1] == 0:                                             # compact: the data sit in the message
+            size = struct.unpack_from("<H", lay, 2)[0]
+            raw = lay[4:4 + size]
+        elif lay[1] == 1:                                             # contiguous
+            addr, size = struct.unpack_from("<QQ", lay, 2)
+            if addr == UNDEF:
+                raw = bytes(nbytes)                                   # never written: fill value (zero)
+            else:
+                raw = self.buf[self._abs(addr):self._abs(addr) + size]
+        else:
+            raise NotImplementedError(f"hdf5: {name}: chunked layout")
+        if len(raw) < nbytes:
+            raise ValueError(f"hdf5: {name}: {len(raw)} bytes stored, {nbytes} expected")
+        return self._to_value(raw, dt, shape)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# writer
+# ---------------------------------------------------------------------------------------------------------------------
+
+class _Writer:
+    def __init__(self):
+        self.buf = bytearray(96)                                      # the superblock is patched in last
+
+    def alloc(self, nbytes):
+        at = _pad8(len(self.buf))
+        self.buf.extend(bytes(at - len(self.buf) + nbytes))
+        return at
+
+    def put(self, at, data):
+        self.buf[at:at + len(data)] = data
+
+    @staticmethod
+    def _message(mtype, data, flags=0):
+        data = data + bytes(_pad8(len(data)) - len(data))
+        return struct.pack("<HHB3x", mtype, len(data), flags) + data
+
+    def object_header(self, messages):
+        body = b"".join(messages)
+        at = self.alloc(16 + len(body))
+        self.put(at, struct.pack("<BBHII4x", 1, 0, len(messages), 1, len(body)) + body)
+        return at
+
+    def dataset(self, value):
+        if isinstance(value, str):
+            raw = value.encode("utf-8") + b"\x00"
+            dt, shape, raw = np.dtype(f"S{len(raw)}"), (), raw
+        else:
+            a = np.asarray(value)
+            if a.dtype == np.bool_:
+                a = a.astype(np.uint8)
+            if a.dtype.byteorder == ">":
+                a = a.astype(a.dtype.newbyteorder("<"))
+            dt, shape = a.dtype, a.shape[::-1]                        # Fortran order in memory ⇒ reversed HDF5 dimensions
+            raw = a.tobytes(order="F")
+        data_at = self.alloc(len(raw)) if raw else UNDEF
+        if raw:
+            self.put(data_at, raw)
+        return self.object_header([
+            self._message(MSG_DATASPACE, _encode_dataspace(shape)),
+            self._message(MSG_DATATYPE, _encode_datatype(dt), 1),
+            self._message(MSG_FILL, struct.pack("<BBBBI", 2, 2, 2, 1, 0), 1),           # late allocation, default fill value
+            self._message(MSG_LAYOUT, struct.pack("<BBQQ", 3, 1, data_at, len(raw)), 1),
+        ])
+
+    def group(self, members):
+        """Write the members, then this group's heap, symbol-table nodes, B-tree and header; → (header, btree, heap)."""
+        entries = []
+        for name in sorted(members, key=lambda s: s.encode("utf-8")):                  # symbol tables are sorted bytewise
+            if "/" in name or not name:
+                raise ValueError(f"hdf5.write: bad link name {name!r}")
+            v = members[name]
+            if isinstance(v, dict):
+                header, btree, heap = self.group(v)
+                entries.append((name, header, 1, btree, heap))
+            else:
+                entries.append((name, self.dataset(v), 0, 0, 0))
+        # local heap: "" at offset 0, the names, one free block to the end of the segment
+        seg, offsets = bytearray(8), []
+        for name, *_ in entries:
+            offsets.append(len(seg))
+            raw = name.encode("utf-8") + b"\x00"
+            seg.extend(raw + bytes(_pad8(len(raw)) - len(raw)))
+        free_at = len(seg)
+        seg_size = _pad8(max(free_at + 16, 88))
+        seg.extend(struct.pack("<QQ", HEAP_FREE_NULL, seg_size - free_at))
+        seg.extend(bytes(seg_size - len(seg)))
+        heap = self.alloc(32)
+        seg_at = self.alloc(seg_size)
+        self.put(seg_at, seg)
+        self.put(heap, b"HEAP" + struct.pack("<B3xQQQ", 0, seg_size, free_at, seg_at))
+        # symbol-table nodes of at most 2·LEAF_K entries
+        nodes = []
+        for lo in range(0, len(entries), 2 * LEAF_K):
+            chunk = list(zip(entries[lo:lo + 2 * LEAF_K], offsets[lo:lo + 2 * LEAF_K]))
+            at = self.alloc(SNOD_SIZE)
+            body = b"SNOD" + struct.pack("<BBH", 1, 0, len(chunk))
+            for (name, header, cache, bt, hp), off in chunk:
+                body += struct.pack("<QQI4xQQ", off, header, cache, bt, hp)
+            self.put(at, body)
+            nodes.append((at, chunk[-1][1]))
+        if len(nodes) > 2 * INTERNAL_K:
+            raise ValueError("hdf5.write: more than 256 links in one group")
+        btree = self.alloc(BTREE_SIZE)
+        body = b"TREE" + struct.pack("<BBHQQ", 0, 0, len(nodes), UNDEF, UNDEF) + struct.pack("<Q", 0)
+        for at, last_name in nodes:
+            body += struct.pack("<QQ", at, last_name)
+        self.put(btree, body)
+        header = self.object_header([self._message(MSG_SYMBOL_TABLE, struct.pack("<QQ", btree, heap), 1)])
+        return header, btree, heap
+
+
+def write(path, tree):
+    """Write the nested dict ``tree`` ({name: dict | array | number | str}) as an HDF5 file: dicts become groups, everything else
+    a contiguous dataset (arrays with reversed dimensions, see the module docstring)."""
+    w = _Writer()
+    header, btree, heap = w.group(tree)
+    eof = _pad8(len(w.buf))
+    w.buf.extend(bytes(eof - len(w.buf)))
+    sb = SIGNATURE + struct.pack("<BBBBBBBBHHI", 0, 0, 0, 0, 0, 8, 8, 0, LEAF_K, INTERNAL_K, 0)
+    sb += struct.pack("<QQQQ", 0, UNDEF, eof, UNDEF)
+    sb += struct.pack("<QQI4xQQ", 0, header, 1, btree, heap)
+    assert len(sb) == 96
+    w.put(0, sb)
+    with open(path, "wb") as fh:
+        fh.write(w.buf)

@@ -1,5 +1,6 @@
 """NonhydrostaticModel, fields, time stepping and solvers over the C ABI (host mirror; see package docstring)."""
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -27,6 +28,10 @@ class Field:
     @property
     def size(self):
         return self._size(L.INTERIOR)
+
+    @property
+    def parent_size(self):
+        return self._size(L.PARENT)
 
     def _get(self, region, out=None):
         shape = self._size(region)
@@ -239,6 +244,19 @@ class NonhydrostaticModel:
         check(lib().nh_clock_get(self._h, C.byref(c)))
         return c
 
+    def set_clock(self, **values):
+        """Overwrite members of the clock (time, iteration, stage, last_dt, last_stage_dt): what set!(model, filepath) does with
+        the checkpointed clock (checkpointer.jl:251-256)."""
+        c = self.clock
+        for k, v in values.items():
+            if k not in ("time", "iteration", "stage", "last_dt", "last_stage_dt"):
+                raise ValueError(f"the clock has no member {k}")
+            setattr(c, k, v)
+        check(lib().nh_clock_set(self._h, C.byref(c)))
+
+    def update_state(self, compute_tendencies=True):
+        check(lib().nh_update_state(self._h, int(compute_tendencies)))
+
     def launch_count(self):
         n = C.c_int64(0)
         check(lib().nh_launch_count(self._h, C.byref(n)))
@@ -310,7 +328,13 @@ def time_step_profiled(model, dt, euler=False):
 
 
 def set_model(model, enforce_incompressibility=True, **kwargs):
-    """set!(model; u=…, v=…, w=…, T=…, …, enforce_incompressibility=true)."""
+    """set!(model; u=…, v=…, w=…, T=…, …, enforce_incompressibility=true); set!(model, filepath) with a checkpoint file's path
+    in second place restores the checkpointed state (checkpointer.jl:223-260)."""
+    if isinstance(enforce_incompressibility, (str, os.PathLike)):
+        from .checkpointer import set_from_checkpoint
+        if kwargs:
+            raise ValueError("set!(model, filepath) takes no field values")
+        return set_from_checkpoint(model, enforce_incompressibility)
     names = ["u", "v", "w"] + list(model.tracer_names)
     for name, value in kwargs.items():
         if name not in names:
