@@ -58,3 +58,21 @@ def test_library_halo_regions_initialized_and_filled_like_the_reference(N, FT):
     assert np.all(data[~interior] == 0)
     oc.fill_halo_regions(c)
     assert _checks(c.parent(), N, (1, 1, 1))
+
+
+# ---- test_field.jl:262-292: parent sizes of the four field locations on the four topologies ------------------------------------
+
+_SIZES = {  # topology → +1 in which (location, direction)
+    (P, P, P): set(), (P, P, B): {("w", 2)}, (P, B, B): {("v", 1), ("w", 2)}, (B, B, B): {("u", 0), ("v", 1), ("w", 2)}}
+
+
+@pytest.mark.parametrize("FT", [np.float32, np.float64])
+@pytest.mark.parametrize("topo", list(_SIZES), ids=lambda t: "".join(x[0] for x in t))
+def test_oracle_field_initialization_sizes(topo, FT):
+    N, H = (4, 6, 8), (1, 1, 1)
+    g = o.RectilinearGrid(FT, size=N, extent=(2 * np.pi, 3 * np.pi, 5 * np.pi), halo=H, topology=topo)
+    locs = {"c": ("c", "c", "c"), "u": ("f", "c", "c"), "v": ("c", "f", "c"), "w": ("c", "c", "f")}
+    for name, loc in locs.items():
+        want = tuple(N[d] + 2 * H[d] + ((name, d) in _SIZES[topo]) for d in range(3))
+        f = Field(g, loc, name=name)
+        assert f.data.shape == want and f.data.dtype == FT, (name, f.data.shape, want)
