@@ -315,9 +315,9 @@ def test_constructor_checks_follow_the_reference(tmp_path):
         c = ck.Checkpointer(view, dir=str(tmp_path), properties=["grid", "particles", "clock"])
     assert "timestepper" in c.properties
     with pytest.raises(ValueError, match="not a model property"):
-        ck.Checkpointer(view, dir=str(tmp_path), properties=["grid", "particles", "clock", "nonsense"])
+        ck.Checkpointer(view, dir=str(tmp_path), properties=["grid", "particles", "clock", "timestepper", "nonsense"])
     with pytest.raises(ValueError, match="must be a string"):
-        ck.Checkpointer(view, dir=str(tmp_path), properties=["grid", "particles", "clock", 3])
+        ck.Checkpointer(view, dir=str(tmp_path), properties=["grid", "particles", "clock", "timestepper", 3])
     assert os.path.isdir(ck.Checkpointer(view, dir=str(tmp_path / "new" / "dir")).dir)   # mkpath(dir)
 
 
