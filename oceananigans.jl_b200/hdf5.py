@@ -299,7 +299,7 @@ class File(Group):
             if lay[2] != 1:
                 raise NotImplementedError(f"hdf5: {name}: version-{lay[0]} layout of class {lay[2]}")
             addr = struct.unpack_from("<Q", lay, 8)[0]
-            raw = bytes(nbytes) if addr == UNDEF else self.buf[self._abs(addr):self._abs(addr) + nbytes]
+            raw = bytes(nbytes) if addr == UNDEF else memoryview(self.buf)[self._abs(addr):self._abs(addr) + nbytes]
         elif lay[0] != 3:
             raise NotImplementedError(f"hdf5: {name}: data layout message version {lay[0]}")
         elif lay[1] == 0:                                             # compact: the data sit in the message
@@ -310,7 +310,7 @@ class File(Group):
             if addr == UNDEF:
                 raw = bytes(nbytes)                                   # never written: fill value (zero)
             else:
-                raw = self.buf[self._abs(addr):self._abs(addr) + size]
+                raw = memoryview(self.buf)[self._abs(addr):self._abs(addr) + size]
         else:
             raise NotImplementedError(f"hdf5: {name}: chunked layout")
         if len(raw) < nbytes:
@@ -357,9 +357,10 @@ class _Writer:
                 a = a.astype(a.dtype.newbyteorder("<"))
             dt, shape = a.dtype, a.shape[::-1]                        # Fortran order in memory ⇒ reversed HDF5 dimensions
             raw = a.tobytes(order="F")
-        data_at = self.alloc(len(raw)) if raw else UNDEF
+        data_at = UNDEF
         if raw:
-            self.put(data_at, raw)
+            data_at = self.alloc(0)
+            self.buf += raw                                           # appended directly: no zero-filled copy for large arrays
         return self.object_header([
             self._message(MSG_DATASPACE, _encode_dataspace(shape)),
             self._message(MSG_DATATYPE, _encode_datatype(dt), 1),
