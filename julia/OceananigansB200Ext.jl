@@ -238,9 +238,10 @@ function set_from_b200_checkpoint!(model::NonhydrostaticModel, filepath::Abstrac
                 copyto!(parent(model.timestepper.G⁻[name]), read(g["timestepper/G⁻/$name/data"]))
             end
         end
-        model.clock.iteration = read(g["clock/iteration"])
-        model.clock.time = read(g["clock/time"])
-        model.clock.last_Δt = read(g["clock/last_Δt"])
+        c = read(g["clock"])                                   # compound scalar → NamedTuple (time, last_Δt, last_stage_Δt, iteration, stage)
+        model.clock.iteration = c.iteration
+        model.clock.time = c.time
+        model.clock.last_Δt = c.last_Δt
     end
     return nothing
 end

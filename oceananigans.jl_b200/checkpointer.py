@@ -11,8 +11,8 @@ What the reference writes with JLD2 (``write_output!(c::Checkpointer, model)``, 
 
 Here the same addresses hold the same arrays (``data`` has the parent array's Julia size, see hdf5.py) next to ``location``;
 the two Julia structs are written property by property the way the reference's own ``saveproperty!`` writes structs that have to
-be readable outside Julia (output_writer_utils.jl:74-85): ``clock/time``, ``clock/iteration``, …, ``grid/Nx``, ``grid/Δxᶜᵃᵃ``,
-``grid/z/Δᵃᵃᶜ`` ….  The file is a classic HDF5 file (any libhdf5 opens it; ``julia/OceananigansB200Ext.jl`` reads it with
+be readable outside Julia (output_writer_utils.jl:74-85) — ``grid/Nx``, ``grid/Δxᶜᵃᵃ``, ``grid/z/Δᵃᵃᶜ`` … — except the clock, which
+is one compound scalar with the struct's members (``time``, ``last_Δt``, ``last_stage_Δt``, ``iteration``, ``stage``).  The file is a classic HDF5 file (any libhdf5 opens it; ``julia/OceananigansB200Ext.jl`` reads it with
 HDF5.jl into a Julia model), NOT a JLD2 file: JLD2's encoding of Julia structs cannot be produced, or a Julia-written file
 parsed, without Julia, and this image has neither Julia nor libhdf5.  File names follow the reference
 (``<prefix>_iteration<N>``) with the extension ``.h5``.
@@ -145,10 +145,14 @@ def grid_tree(model):
     return tree
 
 
+CLOCK_DTYPE = np.dtype([("time", "<f8"), ("last_Δt", "<f8"), ("last_stage_Δt", "<f8"), ("iteration", "<i8"), ("stage", "<i8")])
+
+
 def clock_tree(clock):
-    """Clock (clock.jl:16-22), property by property."""
-    return {"time": np.float64(clock.time), "last_Δt": np.float64(clock.last_dt), "last_stage_Δt": np.float64(clock.last_stage_dt),
-            "iteration": np.int64(clock.iteration), "stage": np.int64(clock.stage)}
+    """Clock (clock.jl:16-22) as ONE compound scalar with the struct's member names and order — the HDF5 form JLD2 gives a Julia
+    struct, so that `file["…/clock"].iteration` / `.time` / `.last_Δt` (checkpointer.jl:251-256) resolve on whatever a reader builds
+    from a compound (JLD2: a reconstructed struct, HDF5.jl: a NamedTuple, h5py: a structured scalar)."""
+    return np.array((clock.time, clock.last_dt, clock.last_stage_dt, clock.iteration, clock.stage), dtype=CLOCK_DTYPE)
 
 
 def state_tree(model, properties=None):
@@ -225,11 +229,10 @@ def set_from_checkpoint(model, filepath):
                 G.set_parent(_checked(T.read(f"G⁻/{fld.name}/data"), G, filepath))
             else:
                 warnings.warn(f"Tendencies for {fld.name} do not exist in checkpoint and could not be restored.")
-    c = A["clock"]
+    c = A.read("clock")
     now = model.clock
-    model.set_clock(time=float(c.read("time")), iteration=int(c.read("iteration")), last_dt=float(c.read("last_Δt")),
-                    stage=int(c.read("stage")) if "stage" in c else now.stage,
-                    last_stage_dt=float(c.read("last_stage_Δt")) if "last_stage_Δt" in c else now.last_stage_dt)
+    model.set_clock(time=float(c["time"]), iteration=int(c["iteration"]), last_dt=float(c["last_Δt"]),
+                    stage=int(c.get("stage", now.stage)), last_stage_dt=float(c.get("last_stage_Δt", now.last_stage_dt)))
 
 
 def _checked(data, field, filepath):

@@ -6,8 +6,8 @@ datasets.  This module writes and reads the classic HDF5 layout every libhdf5 (H
 
 * superblock version 0, 8-byte offsets and lengths;
 * groups as version-1 object headers with a symbol-table message → version-1 B-tree → symbol-table nodes → local heap;
-* datasets as version-1 object headers with dataspace (v1), datatype (v1: IEEE floats, integers, fixed-length strings),
-  fill-value (v2) and contiguous data-layout (v3) messages.
+* datasets as version-1 object headers with dataspace (v1), datatype (v1: IEEE floats, integers, fixed-length strings; v3:
+  compound scalars of those, the form JLD2 gives Julia structs), fill-value (v2) and contiguous data-layout (v3) messages.
 
 The reader additionally follows object-header continuation blocks, compact layouts, version-2 dataspaces, attributes (v1) and a
 non-zero base address / user block, which is what the one libhdf5-written file in this image needs
@@ -42,19 +42,29 @@ def _pad8(n):
 # datatypes
 # ---------------------------------------------------------------------------------------------------------------------
 
-def _encode_datatype(dt):
-    """Datatype message (version 1) of a numpy dtype: IEEE float, two's-complement integer or fixed-length string."""
+def _encode_datatype(dt, version=1):
+    """Datatype message of a numpy dtype: IEEE float, two's-complement integer, fixed-length string (version 1 at the top level,
+    the parent's version 3 inside a compound) or a compound of those."""
     dt = np.dtype(dt)
+    v = version << 4
     if dt.kind == "f" and dt.itemsize in (4, 8):
         size = dt.itemsize
         exp_bits, man_bits, bias = ((8, 23, 127), (11, 52, 1023))[size == 8]
-        head = struct.pack("<BBBBI", 0x10 | 1, 0x20, size * 8 - 1, 0, size)          # little-endian, implied msb, sign bit
+        head = struct.pack("<BBBBI", v | 1, 0x20, size * 8 - 1, 0, size)          # little-endian, implied msb, sign bit
         return head + struct.pack("<HHBBBBI", 0, size * 8, man_bits, exp_bits, 0, man_bits, bias)
     if dt.kind in "iu" and dt.itemsize in (1, 2, 4, 8):
-        head = struct.pack("<BBBBI", 0x10 | 0, 0x08 if dt.kind == "i" else 0x00, 0, 0, dt.itemsize)
+        head = struct.pack("<BBBBI", v | 0, 0x08 if dt.kind == "i" else 0x00, 0, 0, dt.itemsize)
         return head + struct.pack("<HH", 0, dt.itemsize * 8)
     if dt.kind == "S":
-        return struct.pack("<BBBBI", 0x10 | 3, 0x10, 0, 0, max(dt.itemsize, 1))      # null-terminated, UTF-8
+        return struct.pack("<BBBBI", v | 3, 0x10, 0, 0, max(dt.itemsize, 1))      # null-terminated, UTF-8
+    if dt.kind == "V" and dt.names:
+        # compound, version 3 (what JLD2 writes for Julia structs): names unpadded, byte offsets in the fewest bytes that hold the size
+        nbytes = max(1, (int(dt.itemsize).bit_length() + 7) // 8)
+        out = struct.pack("<BBBBI", 0x30 | 6, len(dt.names) & 0xFF, len(dt.names) >> 8, 0, dt.itemsize)
+        for name in dt.names:
+            member, offset = dt.fields[name][0], dt.fields[name][1]
+            out += name.encode("utf-8") + b"\x00" + int(offset).to_bytes(nbytes, "little") + _encode_datatype(member, 3)
+        return out
     raise TypeError(f"hdf5.write: unsupported dtype {dt}")
 
 
@@ -76,6 +86,24 @@ def _decode_datatype(b):
         return np.dtype(f"S{size}"), 8
     if cls == 7:                                                                         # object / region reference
         return np.dtype(f"V{size}"), 8
+    if cls == 6:
+        n, p = bits0 | (bits1 << 8), 8
+        nbytes = max(1, (int(size).bit_length() + 7) // 8)
+        names, formats, offsets = [], [], []
+        for _ in range(n):
+            end = b.index(b"\x00", p)
+            names.append(bytes(b[p:end]).decode("utf-8"))
+            p = end + 1 if version == 3 else p + _pad8(end + 1 - p)
+            if version == 3:
+                offsets.append(int.from_bytes(b[p:p + nbytes], "little"))
+                p += nbytes
+            else:
+                offsets.append(struct.unpack_from("<I", b, p)[0])
+                p += 4 + (28 if version == 1 else 0)                                     # v1: dimensionality, permutation, 4 sizes
+            member, used = _decode_datatype(b[p:])
+            formats.append(member)
+            p += used
+        return np.dtype({"names": names, "formats": formats, "offsets": offsets, "itemsize": size}), p
     raise NotImplementedError(f"hdf5: datatype class {cls}")
 
 
@@ -281,6 +309,9 @@ class File(Group):
         if dt.kind == "S":
             vals = [v.split(b"\x00")[0].decode("utf-8") for v in a]
             return vals[0] if not shape else np.array(vals, dtype=object).reshape(shape[::-1], order="F")
+        if dt.kind == "V" and dt.names:
+            rows = [{n: (v[n].item() if np.ndim(v[n]) == 0 else v[n]) for n in dt.names} for v in a]
+            return rows[0] if not shape else rows
         if dt.kind == "V":
             return a.copy()
         a = a.astype(dt.newbyteorder("="))
@@ -351,6 +382,8 @@ class _Writer:
             dt, shape, raw = np.dtype(f"S{len(raw)}"), (), raw
         else:
             a = np.asarray(value)
+            if a.dtype.names and a.shape != ():
+                raise TypeError("hdf5.write: compound values are written as scalars only")
             if a.dtype == np.bool_:
                 a = a.astype(np.uint8)
             if a.dtype.byteorder == ">":

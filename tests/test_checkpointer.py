@@ -122,6 +122,13 @@ def test_write_read_round_trip(tmp_path):
     assert h5._decode_dataspace(msgs[h5.MSG_DATASPACE]) == (3, 5, 7)
     with pytest.raises(TypeError):
         h5.write(tmp_path / "bad.h5", {"z": np.zeros(2, dtype=complex)})
+    # a compound scalar (the form a Julia struct takes in JLD2): members by name, UTF-8 names, mixed member types
+    dt = np.dtype([("time", "<f8"), ("last_Δt", "<f4"), ("iteration", "<i8"), ("stage", "<i2")])
+    h5.write(tmp_path / "c.h5", {"clock": np.array((0.3, 0.5, 2 ** 40, -3), dtype=dt)})
+    got = h5.File(tmp_path / "c.h5").read("clock")
+    assert got == {"time": 0.3, "last_Δt": 0.5, "iteration": 2 ** 40, "stage": -3}
+    decoded, used = h5._decode_datatype(h5._encode_datatype(dt))
+    assert decoded == dt and used == len(h5._encode_datatype(dt))
     with pytest.raises(ValueError):
         h5.File(__file__)
 
@@ -278,7 +285,7 @@ def test_checkpoint_file_has_the_reference_addresses(tmp_path):
             assert A.read(addr).shape == f_.data.shape == (22, 22, 22 + (name == "w")), addr
         assert np.array_equal(A.read(f"{name}/data"), f_.data)
     assert list(A.read("w/location")) == ["Center", "Center", "Face"]
-    assert A.read("clock/iteration") == 2 and A.read("clock/time") == 12.0 and A.read("clock/last_Δt") == 6.0
+    assert A.read("clock") == {"time": 12.0, "last_Δt": 6.0, "last_stage_Δt": 6.0, "iteration": 2, "stage": 1}
     G = A["grid"]
     assert [int(G.read(k)) for k in ("Nx", "Ny", "Nz", "Hx", "Hy", "Hz")] == [16, 16, 16, 3, 3, 3]
     assert G.read("Lz") == 100.0 and G.read("Δxᶜᵃᵃ") == 6.25 and G.read("z/Δᵃᵃᶜ") == 6.25

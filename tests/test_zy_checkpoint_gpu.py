@@ -92,7 +92,7 @@ def test_checkpoint_file_of_the_library_model_has_the_reference_addresses(tmp_pa
         for addr in (f"{f.name}/data", f"timestepper/Gⁿ/{f.name}/data", f"timestepper/G⁻/{f.name}/data"):
             assert A.read(addr).shape == (22, 22, 22 + (f.name == "w")), addr
         np.testing.assert_array_equal(A.read(f"{f.name}/data"), f.parent())
-    assert A.read("clock/iteration") == 2 and A.read("clock/time") == 12.0 and A.read("clock/last_Δt") == 6.0
+    assert A.read("clock") == {"time": 12.0, "last_Δt": 6.0, "last_stage_Δt": 6.0, "iteration": 2, "stage": 1}
     G = A["grid"]
     assert [int(G.read(k)) for k in ("Nx", "Ny", "Nz", "Hx", "Hy", "Hz")] == [16, 16, 16, 3, 3, 3]
     assert G.read("Lz") == 100.0 and G.read("Δxᶜᵃᵃ") == 6.25 and G.read("z/Δᵃᵃᶜ") == 6.25
