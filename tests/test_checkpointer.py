@@ -371,3 +371,72 @@ def test_the_gpu_pickup_check_itself_over_the_oracle(tmp_path):
     fake = types.SimpleNamespace(Checkpointer=ck.Checkpointer, pickup=ck.pickup, time_step=time_step,
                                  set_model=lambda v, path: ck.set_from_checkpoint(v, path))
     _check_pickup(fake, make, 6.0, tmp_path)
+
+
+# ---- the version-2 structures (JLD2's container): self-consistency only ---------------------------------------------------------
+
+def _v2_file(path, u, clock_dtype, clock):
+    """Assemble a file the way JLD2 lays one out — 512-byte text header, superblock 2 with base address 512, OHDR object headers with
+    link messages, an OCHK continuation chunk, a committed (shared) compound datatype, layout version 4 — from the HDF5 file-format
+    specification.  It is NOT a JLD2-written file: it only checks that the reader follows the specification the way this emitter
+    reads it; no checksum is computed (the reader ignores them)."""
+    buf = bytearray(b"HDF5-based Julia Data Format, version 0.1.1 (test stand-in)".ljust(512, b"\x00"))
+    base = 512
+
+    def alloc(data):
+        at = len(buf)
+        buf.extend(data)
+        return at - base                                               # addresses are relative to the base address
+
+    def msg(mtype, data, flags=0, order=None):
+        return struct.pack("<BHB", mtype, len(data), flags) + (struct.pack("<H", order) if order is not None else b"") + data
+
+    def ohdr(messages, flags=0, extra=b""):
+        body = b"".join(messages)
+        width = 1 << (flags & 3)
+        return alloc(b"OHDR" + bytes([2, flags]) + extra + len(body).to_bytes(width, "little") + body + b"\x00" * 4)
+
+    def link(name, addr, wide=False):
+        raw = name.encode("utf-8")
+        if wide:                                                       # link type + creation order + charset present, 2-byte length
+            return struct.pack("<BBBQBH", 1, 0x08 | 0x04 | 0x10 | 1, 0, 7, 1, len(raw)) + raw + struct.pack("<Q", addr)
+        return struct.pack("<BBB", 1, 0, len(raw)) + raw + struct.pack("<Q", addr)
+
+    superblock_at = alloc(bytes(48))
+    # dataset u/data: dataspace v2 (dimensions reversed), float datatype version 3, fill value v3, layout v4 contiguous
+    raw = u.tobytes(order="F")
+    data_at = alloc(raw)
+    float_t = bytes([0x30 | 1]) + h5._encode_datatype(u.dtype)[1:]
+    space = struct.pack("<BBBB", 2, u.ndim, 0, 1) + b"".join(struct.pack("<Q", n) for n in u.shape[::-1])
+    dset = ohdr([msg(0x1, space), msg(0x3, float_t, 1), msg(0x5, bytes([3, 0x09])), msg(0x8, struct.pack("<BBQQ", 4, 1, data_at, len(raw)))],
+                flags=0x20 | 1, extra=bytes(16))                       # times stored, 2-byte chunk size
+    ugroup = ohdr([msg(0x2, struct.pack("<BBQQ", 0, 0, h5.UNDEF, h5.UNDEF)), msg(0x6, link("data", dset))])
+    # clock: a scalar whose datatype message is shared — it points at a committed datatype object
+    committed = ohdr([msg(0x3, h5._encode_datatype(clock_dtype))])
+    shared = struct.pack("<BBQ", 3, 2, committed)
+    cdata = alloc(clock.tobytes())
+    cset = ohdr([msg(0x1, struct.pack("<BBBB", 2, 0, 0, 0)), msg(0x3, shared, 0x02), msg(0x8, struct.pack("<BBQQ", 3, 1, cdata, clock.nbytes))])
+    # the model group: creation order tracked (6-byte message headers), its second link in a continuation chunk
+    chunk = alloc(b"OCHK" + msg(0x6, link("clock", cset, wide=True), order=1) + b"\x00" * 4)
+    chunk_len = len(buf) - base - chunk
+    model = ohdr([msg(0x6, link("u", ugroup), order=0), msg(0x10, struct.pack("<QQ", chunk, chunk_len), order=2), msg(0x0, b"", order=3)],
+                 flags=0x04)
+    root = ohdr([msg(0x6, link("NonhydrostaticModel", model))])
+    sb = h5.SIGNATURE + struct.pack("<BBBBQQQQ", 2, 8, 8, 0, base, h5.UNDEF, len(buf) - base, root) + b"\x00" * 4
+    buf[base + superblock_at:base + superblock_at + len(sb)] = sb
+    with open(path, "wb") as fh:
+        fh.write(buf)
+
+
+def test_version_2_structures_are_parsed_as_the_specification_lays_them_out(tmp_path):
+    rng = np.random.default_rng(5)
+    u = np.asfortranarray(rng.random((6, 5, 4)))
+    clock = np.array((12.0, 6.0, 6.0, 2, 1), dtype=ck.CLOCK_DTYPE)
+    path = tmp_path / "checkpoint_iteration2.jld2"
+    _v2_file(path, u, ck.CLOCK_DTYPE, clock)
+    f = h5.File(path)
+    assert f.superblock_version == 2 and f.base == 512
+    assert f.keys() == ["NonhydrostaticModel"] and f["NonhydrostaticModel"].keys() == ["u", "clock"]
+    got = f.read("NonhydrostaticModel/u/data")
+    assert got.shape == (6, 5, 4) and np.array_equal(got, u)
+    assert f.read("NonhydrostaticModel/clock") == {"time": 12.0, "last_Δt": 6.0, "last_stage_Δt": 6.0, "iteration": 2, "stage": 1}
