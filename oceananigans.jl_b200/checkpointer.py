@@ -257,3 +257,32 @@ def pickup(model, which, checkpointer=None):
     set_from_checkpoint(model, path)
     model.update_state(compute_tendencies=True)
     return path
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# the layout of the reference's golden regression files
+# ---------------------------------------------------------------------------------------------------------------------
+
+def regression_tree(model):
+    """The older checkpoint layout the reference's downloaded regression files have (what get_fields_from_checkpoint reads,
+    test/test_nonhydrostatic_regression.jl:7-42): ``velocities/<u|v|w>/data``, ``tracers/<name>/data`` and
+    ``timestepper/Gⁿ|G⁻/<name>/data`` at the root of the file, parent arrays."""
+    fields = model.prognostic_fields()
+    return {"velocities": {f.name: {"data": f.parent()} for f in fields[:3]},
+            "tracers": {f.name: {"data": f.parent()} for f in fields[3:]},
+            "timestepper": {"Gⁿ": {f.name: {"data": model.timestepper.Gn[f.name].parent()} for f in fields},
+                            "G⁻": {f.name: {"data": model.timestepper.Gm[f.name].parent()} for f in fields}}}
+
+
+def get_fields_from_checkpoint(filename):
+    """get_fields_from_checkpoint (test/test_nonhydrostatic_regression.jl:7-42): (solution, Gⁿ, G⁻) dicts of parent arrays by field
+    name from a file in the regression layout — the reader a golden-file comparison starts from (the files themselves are remote
+    DataDeps, test/data_dependencies.jl:17-38, and JLD2-written: see hdf5.py on what of that container is verified)."""
+    f = hdf5.File(filename)
+    tracers = f["tracers"].keys() if "tracers" in f else []
+    names = ["u", "v", "w"] + list(tracers)
+    where = {n: ("velocities" if n in "uvw" else "tracers") for n in names}
+    solution = {n: f.read(f"{where[n]}/{n}/data") for n in names}
+    Gn = {n: f.read(f"timestepper/Gⁿ/{n}/data") for n in names}
+    Gm = {n: f.read(f"timestepper/G⁻/{n}/data") for n in names}
+    return solution, Gn, Gm

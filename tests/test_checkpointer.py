@@ -440,3 +440,18 @@ def test_version_2_structures_are_parsed_as_the_specification_lays_them_out(tmp_
     got = f.read("NonhydrostaticModel/u/data")
     assert got.shape == (6, 5, 4) and np.array_equal(got, u)
     assert f.read("NonhydrostaticModel/clock") == {"time": 12.0, "last_Δt": 6.0, "last_stage_Δt": 6.0, "iteration": 2, "stage": 1}
+
+
+def test_regression_file_layout_round_trip(tmp_path):
+    """The layout of the reference's golden regression files (test_nonhydrostatic_regression.jl:7-42) written from a model and read
+    back by get_fields_from_checkpoint."""
+    view = _ModelView(_thermal_bubble("QuasiAdamsBashforth2"))
+    _run(view, 6.0, 3)
+    path = tmp_path / "thermal_bubble_regression.h5"
+    h5.write(path, ck.regression_tree(view))
+    solution, Gn, Gm = ck.get_fields_from_checkpoint(path)
+    assert list(solution) == ["u", "v", "w", "S", "T"]                   # tracers in the file's (sorted) key order
+    for n, f in zip(view.m.prognostic_names(), view.m.prognostic_fields()):
+        assert np.array_equal(solution[n], f.data)
+        assert np.array_equal(Gn[n], view.m.Gn[n].data) and np.array_equal(Gm[n], view.m.Gm[n].data)
+    assert np.abs(Gm["T"]).max() > 0                                      # AB2 after three steps: G⁻ is populated
