@@ -27,7 +27,6 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
   ntr = d.n_tracers;
   NH_REQUIRE(ntr >= 0 && ntr <= NH_MAXTR, "too many tracers");
   nf = 3 + ntr;
-  int maxB = 1;
   for (int e = 0; e < 3; ++e) {
     int kind = d.advection_kind[e], order = d.advection_order[e], B = 1;
     if (kind == NH_ADV_CENTERED) { NH_REQUIRE(order == 2 || order == 4, "Centered order must be 2 or 4"); B = order / 2; }
@@ -39,11 +38,15 @@ Model<FT>::Model(const nh_grid& grid, const nh_model_desc& d) {
     } else NH_REQUIRE(kind == NH_ADV_NONE, "unknown advection kind");
     adapt_order(kind, B, grid.desc.N[e], grid.desc.topology[e]);
     adv[e].kind = kind; adv[e].B = B;
-    if (kind != NH_ADV_NONE && B > maxB) maxB = B;
   }
-  // inflate_grid_halo_size — nonhydrostatic_model.jl:243-257
+  // inflate_grid_halo_size — nonhydrostatic_model.jl:243-257 with inflate_halo_size (automatic_halo_sizing.jl:71-83): every direction
+  // is raised to what ITS (adapted) advection scheme needs — required_halo_size_x/y/z of the FluxFormAdvection — and to the 1 a
+  // closure and the pressure correction need; never to another direction's buffer
   int H[3];
-  for (int e = 0; e < 3; ++e) H[e] = grid.desc.topology[e] == NH_FLAT ? 0 : std::max(grid.desc.H[e], maxB);
+  for (int e = 0; e < 3; ++e) {
+    const int need = adv[e].kind != NH_ADV_NONE ? std::max(1, adv[e].B) : 1;
+    H[e] = grid.desc.topology[e] == NH_FLAT ? 0 : std::max(grid.desc.H[e], need);
+  }
   gh.build(grid.desc, grid.zfaces, H);
   gdesc = grid.desc; gdesc.z_faces = nullptr;
   for (int e = 0; e < 3; ++e) gdesc.H[e] = gh.g.H[e];

@@ -88,6 +88,11 @@ def transpose_blocks(dst, src, R, group=None):
     dist.all_to_all_single(dst, src, group=group)
 
 
+def _torch_device(index):
+    import torch
+    return torch.device("cuda", index)
+
+
 class _DeviceMemory:
     """A raw device allocation of the library, exposed to torch without a copy."""
 
@@ -134,7 +139,7 @@ class DistributedNonhydrostaticModel:
         self.model = NonhydrostaticModel(self.grid, advection=advection or WENO(FT, 5), timestepper=timestepper, **kw)
         self._h = self.model._h
         check(lib().nh_dist_configure(self._h, self.rank, self.R, y0, y1, Ny))
-        self.device = torch.device("cuda", device)
+        self.device = _torch_device(device)
         self.FT = np.dtype(FT)
         tdt = torch.float64 if self.FT == np.float64 else torch.float32
         cdt = torch.complex128 if self.FT == np.float64 else torch.complex64

@@ -129,13 +129,14 @@ class NonhydrostaticModel:
                 if req not in tracers:
                     raise ValueError(f"buoyancy requires tracer {req}")
         adv = adapt_advection_order(advection, grid)
-        # inflate_grid_halo_size: each non-Flat dim needs at least the scheme's buffer (and 1 for the closure)
+        # inflate_grid_halo_size (nonhydrostatic_model.jl:243-257, automatic_halo_sizing.jl:71-83): each non-Flat direction needs
+        # the buffer of ITS adapted scheme (required_halo_size_x/y/z of the FluxFormAdvection) and 1 for the closure
         need = []
         for d in range(3):
             if grid.topology[d] == Flat:
                 need.append(0)
                 continue
-            h = max([1] + [s.B for s in adv if s is not None])
+            h = max(1, adv[d].B if adv[d] is not None else 1)
             need.append(max(h, grid.H[d]))
         if tuple(need) != tuple(grid.H):
             grid = grid.with_halo(need)

@@ -47,12 +47,16 @@ def test_adjustment_of_advection_schemes_in_the_constructor():
     assert [s.B for s in adv] == [2, 2, 2]
 
 
-@pytest.mark.xfail(strict=True, reason="known deviation (DESIGN.md §8): the halo is inflated to the largest buffer over the three "
-                   "directions; the reference inflates per direction (automatic_halo_sizing.jl:71-83), which only differs when "
-                   "the adapted orders differ by direction — here (3, 2, 3) against the reference, and Hy = 3 > Ny = 2 is refused")
 def test_halo_is_inflated_per_direction_when_the_adapted_orders_differ():
+    """test_nonhydrostatic_models.jl:64-72 with inflate_halo_size (automatic_halo_sizing.jl:71-83): on the 4 × 2 × 4 grid WENO() needs
+    (3, 2, 3) — each direction its own adapted scheme's buffer — and Hy = 2 ≤ Ny = 2 keeps the Periodic y direction valid."""
     small = o.RectilinearGrid(np.float64, size=(4, 2, 4), extent=(1, 2, 3), halo=(1, 1, 1))
-    assert _halo(o.NonhydrostaticModel(small, advection=o.WENO(np.float64, 5))) == (3, 2, 3)
+    m = o.NonhydrostaticModel(small, advection=o.WENO(np.float64, 5))
+    assert _halo(m) == (3, 2, 3)
+    assert m.velocities[0].data.shape == (4 + 6, 2 + 4, 4 + 6)
+    o.time_step(m, 1e-3)
+    funny = o.RectilinearGrid(np.float64, size=(4, 2, 4), extent=(1, 2, 3), halo=(1, 2, 4), topology=(P, B, B))
+    assert _halo(o.NonhydrostaticModel(funny, advection=o.Centered(np.float64, 4))) == (2, 2, 4)
 
 
 def test_model_construction_with_single_tracer_and_nothing_tracer():
