@@ -115,9 +115,11 @@ struct cudaIpcMemHandle_t { char reserved[64]; };
 
 static inline const char* cudaGetErrorString(cudaError_t e) { return e == cudaSuccess ? "no error" : "emulated CUDA runtime error"; }
 static inline cudaError_t cudaGetLastError() { return cudaSuccess; }
-static inline cudaError_t cudaSetDevice(int) { return cudaSuccess; }
-static inline cudaError_t cudaGetDevice(int* d) { *d = 0; return cudaSuccess; }
-static inline cudaError_t cudaGetDeviceCount(int* n) { *n = 1; return cudaSuccess; }
+// sixteen "devices": a rank process of the multi-rank tests addresses the one with its rank's index
+inline int emu_current_device = 0;
+static inline cudaError_t cudaSetDevice(int d) { emu_current_device = d; return cudaSuccess; }
+static inline cudaError_t cudaGetDevice(int* d) { *d = emu_current_device; return cudaSuccess; }
+static inline cudaError_t cudaGetDeviceCount(int* n) { *n = 16; return cudaSuccess; }
 static inline cudaError_t cudaDeviceSynchronize() { return cudaSuccess; }
 static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 static inline cudaError_t cudaDeviceGetAttribute(int* v, int attr, int) { *v = attr == cudaDevAttrMultiProcessorCount ? 148 : 0; return cudaSuccess; }
@@ -135,10 +137,11 @@ static inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess
 static inline cudaError_t cudaEventDestroy(cudaEvent_t) { return cudaSuccess; }
 static inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0.0f; return cudaSuccess; }
 template <typename T> static inline cudaError_t cudaGetSymbolAddress(void** p, T& symbol) { *p = (void*)&symbol; return cudaSuccess; }
-// one process, one address space: an IPC handle is the pointer itself
-static inline cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t* h, void* p) { std::memset(h, 0, sizeof(*h)); std::memcpy(h, &p, sizeof(p)); return cudaSuccess; }
-static inline cudaError_t cudaIpcOpenMemHandle(void** p, cudaIpcMemHandle_t h, unsigned) { std::memcpy(p, &h, sizeof(*p)); return cudaSuccess; }
-static inline cudaError_t cudaIpcCloseMemHandle(void*) { return cudaSuccess; }
+// IPC handles: the pointer itself within one process; with NHSTEP_EMU_SHM=1 every allocation is a file under /dev/shm and the
+// handle names it, so that several rank processes open each other's buffers as they do over NVLink (emu_runtime.cpp)
+cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t* h, void* p);
+cudaError_t cudaIpcOpenMemHandle(void** p, cudaIpcMemHandle_t h, unsigned flags);
+cudaError_t cudaIpcCloseMemHandle(void* p);
 
 // ---- driver API pieces the TMA sweep names ---------------------------------------------------------------------------------
 typedef int CUresult;

@@ -5,7 +5,11 @@
 // barrier-free, and the remaining threads of that launch run as plain calls (no fiber switch).
 #include "emu_cuda.h"
 
+#include <fcntl.h>
 #include <sys/mman.h>
+#include <unistd.h>
+#include <map>
+#include <string>
 #include <unordered_map>
 #include <vector>
 
@@ -223,8 +227,67 @@ int guard_mode() {
 }
 }  // namespace
 
+// ---- NHSTEP_EMU_SHM=1: allocations other processes can open (the multi-rank tests: one process per rank, peer stores, flag barriers)
+namespace {
+struct Shared { std::string name; size_t bytes; };
+std::map<char*, Shared> shared_allocs;                 // own allocations by base address
+std::unordered_map<void*, size_t> opened_maps;         // peers' allocations mapped here
+bool shm_mode() { static const bool on = std::getenv("NHSTEP_EMU_SHM") != nullptr; return on; }
+void unlink_all() { for (auto& a : shared_allocs) unlink(a.second.name.c_str()); }
+}  // namespace
+
+cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t* h, void* p) {
+  std::memset(h, 0, sizeof(*h));
+  if (!shm_mode()) { std::memcpy(h, &p, sizeof(p)); return cudaSuccess; }
+  auto it = shared_allocs.upper_bound((char*)p);
+  if (it == shared_allocs.begin()) return cudaErrorInvalidValue;
+  --it;
+  const size_t off = (char*)p - it->first;
+  if (off >= it->second.bytes || it->second.name.size() > 47) return cudaErrorInvalidValue;
+  std::memcpy(h->reserved, it->second.name.c_str(), it->second.name.size());
+  std::memcpy(h->reserved + 48, &off, 8);
+  std::memcpy(h->reserved + 56, &it->second.bytes, 8);
+  return cudaSuccess;
+}
+cudaError_t cudaIpcOpenMemHandle(void** p, cudaIpcMemHandle_t h, unsigned) {
+  if (!shm_mode()) { std::memcpy(p, &h, sizeof(*p)); return cudaSuccess; }
+  size_t off, bytes;
+  std::memcpy(&off, h.reserved + 48, 8);
+  std::memcpy(&bytes, h.reserved + 56, 8);
+  h.reserved[47] = 0;
+  const int fd = open(h.reserved, O_RDWR);
+  if (fd < 0) return cudaErrorInvalidValue;
+  void* m = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+  close(fd);
+  if (m == MAP_FAILED) return cudaErrorInvalidValue;
+  opened_maps[(char*)m + off] = bytes;
+  *p = (char*)m + off;
+  return cudaSuccess;
+}
+cudaError_t cudaIpcCloseMemHandle(void* p) {
+  auto it = opened_maps.find(p);
+  if (it != opened_maps.end()) opened_maps.erase(it);      // the mapping itself is left to process exit (offset unknown here)
+  return cudaSuccess;
+}
+
 cudaError_t cudaMalloc(void** p, size_t bytes) {
   const size_t want = bytes ? bytes : 256;
+  if (shm_mode()) {
+    static int counter = 0;
+    static bool registered = false;
+    if (!registered) { std::atexit(unlink_all); registered = true; }
+    char name[64];
+    std::snprintf(name, sizeof name, "/dev/shm/nhstep_emu.%d.%d", (int)getpid(), counter++);
+    const int fd = open(name, O_RDWR | O_CREAT | O_EXCL, 0600);
+    if (fd < 0) return cudaErrorInvalidValue;
+    if (ftruncate(fd, (off_t)want) != 0) { close(fd); unlink(name); return cudaErrorInvalidValue; }
+    void* m = mmap(nullptr, want, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);      // fresh pages of the file read as zero
+    close(fd);
+    if (m == MAP_FAILED) { unlink(name); return cudaErrorInvalidValue; }
+    shared_allocs[(char*)m] = Shared{name, want};
+    *p = m;
+    return cudaSuccess;
+  }
   static const bool poison = std::getenv("NHSTEP_EMU_POISON") != nullptr;     // fresh device memory = NaN bit patterns instead of zeros
   if (guard_mode() == 0) {
     void* q = nullptr;
@@ -246,6 +309,13 @@ cudaError_t cudaMalloc(void** p, size_t bytes) {
 }
 cudaError_t cudaFree(void* p) {
   if (!p) return cudaSuccess;
+  auto sh = shared_allocs.find((char*)p);
+  if (sh != shared_allocs.end()) {
+    munmap(p, sh->second.bytes);
+    unlink(sh->second.name.c_str());
+    shared_allocs.erase(sh);
+    return cudaSuccess;
+  }
   auto it = guarded.find(p);
   if (it == guarded.end()) { std::free(p); return cudaSuccess; }
   munmap(it->second.map, it->second.map_bytes);

@@ -29,3 +29,20 @@ def test_gpu_tests_pass_against_the_kernels_compiled_for_the_host():
     tail = (r.stdout + r.stderr)[-3000:]
     assert r.returncode == 0, tail
     assert " passed" in r.stdout and "failed" not in r.stdout.splitlines()[-1], tail
+
+
+@pytest.mark.skipif(shutil.which("g++") is None, reason="needs g++ to compile the kernels for the host")
+def test_multi_rank_slab_tests_pass_against_the_kernels_compiled_for_the_host():
+    """Two and four rank PROCESSES on host cores (the deployment shape: one process per GPU): halo rows and FFT transpose blocks
+    stored into the peers' buffers (files under /dev/shm standing in for CUDA IPC over NVLink), the flag barrier between them."""
+    env = dict(os.environ, NHSTEP_EMU="1")
+    for k in ("NHSTEP_EMU_GUARD", "NHSTEP_EMU_ORDER", "NHSTEP_EMU_POISON", "NHSTEP_TILE_SWEEP", "NHSTEP_PLANE_SWEEP", "NHSTEP_OVERLAP"):
+        env.pop(k, None)
+    selection = ("test_multi_gpu_matches_single_gpu and float64-RungeKutta3-size0-2-p2p or "
+                 "test_transpose_round_trip_is_bit_identical and (2-p2p or 4-p2p or 2-nccl)")
+    cmd = [sys.executable, "-m", "pytest", "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider", "-k", selection,
+           "tests/test_gpu_distributed.py"]
+    r = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=1500)
+    tail = (r.stdout + r.stderr)[-3000:]
+    assert r.returncode == 0, tail
+    assert " passed" in r.stdout and "failed" not in r.stdout.splitlines()[-1], tail

@@ -18,6 +18,24 @@ sys.path.insert(0, ROOT)
 
 pytestmark = pytest.mark.gpu
 
+# tests/emu (NHSTEP_EMU=1, development aid): one process per rank on host cores, the peers' buffers as files under /dev/shm
+EMULATED = os.environ.get("NHSTEP_EMU") == "1"
+
+
+def _ranks_available():
+    return 8 if EMULATED else torch.cuda.device_count()
+
+
+def _init_rank(rank, world):
+    import torch.distributed as dist
+    if EMULATED:
+        os.environ["NHSTEP_EMU_SHM"] = "1"          # before the first allocation of this process
+        import conftest  # noqa: F401                 (switches this process to the host stand-in as it did for the parent)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        return
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+
 
 def _ics(size, FT, seed=3):
     rng = np.random.default_rng(seed)
@@ -106,8 +124,7 @@ def _worker(rank, world, port, size, FT, timestepper, steps, dt, path, p2p):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
-    torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    _init_rank(rank, world)
     try:
         out = {}
         _distributed(rank, world, size, FT, timestepper, steps, dt, out, p2p)
@@ -123,7 +140,7 @@ def _worker(rank, world, port, size, FT, timestepper, steps, dt, path, p2p):
                                                  (np.float64, "QuasiAdamsBashforth2", (64, 32, 32)),
                                                  (np.float32, "RungeKutta3", (32, 64, 32))])
 def test_multi_gpu_matches_single_gpu(world, FT, timestepper, size, p2p, tmp_path):
-    if torch.cuda.device_count() < world:
+    if _ranks_available() < world:
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     steps, dt = 10, 2e-3
@@ -246,8 +263,7 @@ def _generic_worker(rank, world, port, name, FT, timestepper, steps, dt, path):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
-    torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    _init_rank(rank, world)
     try:
         out = {}
         _generic_distributed(rank, world, name, FT, timestepper, steps, dt, out)
@@ -261,7 +277,7 @@ def _generic_worker(rank, world, port, name, FT, timestepper, steps, dt, path):
 @pytest.mark.parametrize("FT,timestepper", [(np.float64, "RungeKutta3"), (np.float32, "QuasiAdamsBashforth2")])
 @pytest.mark.parametrize("name", list(GENERIC))
 def test_multi_gpu_complete_path_slab_matches_single_gpu(name, FT, timestepper, world, tmp_path):
-    if torch.cuda.device_count() < world:
+    if _ranks_available() < world:
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     steps, dt = 10, 2e-3
@@ -314,8 +330,7 @@ def _transpose_worker(rank, world, port, size, p2p):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
-    torch.cuda.set_device(rank)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    _init_rank(rank, world)
     try:
         _transpose_round_trip(rank, world, size, p2p)
     finally:
@@ -329,7 +344,7 @@ def test_transpose_round_trip_is_bit_identical_on_one_rank():
 @pytest.mark.parametrize("p2p", [False, True], ids=["nccl", "p2p"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_transpose_round_trip_is_bit_identical(world, p2p):
-    if torch.cuda.device_count() < world:
+    if _ranks_available() < world:
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     with socket.socket() as s:
