@@ -284,6 +284,7 @@ cudaError_t cudaMalloc(void** p, size_t bytes) {
     void* m = mmap(nullptr, want, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);      // fresh pages of the file read as zero
     close(fd);
     if (m == MAP_FAILED) { unlink(name); return cudaErrorInvalidValue; }
+    if (std::getenv("NHSTEP_EMU_POISON")) std::memset(m, 0xFF, want);
     shared_allocs[(char*)m] = Shared{name, want};
     *p = m;
     return cudaSuccess;
