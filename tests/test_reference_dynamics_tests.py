@@ -148,3 +148,93 @@ def test_time_stepping_works_with_amd_without_buoyancy():
     m = o.NonhydrostaticModel(grid, closure=o.AnisotropicMinimumDissipation(), tracers=("T", "S"), buoyancy=None)
     o.time_step(m, 1.0)
     assert m.clock.iteration == 1 and _finite(m)
+
+
+# ---- the same tests against the library through the C ABI ---------------------------------------------------------------------
+
+def _lib_finite(m):
+    return all(np.all(np.isfinite(f.parent())) for f in m.prognostic_fields())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("which", ["y_periodic_regular", "y_flat_regular", "y_periodic_stretched", "y_flat_stretched"])
+def test_library_internal_wave_nonhydrostatic(which):
+    """test_dynamics.jl:673-684 on the CUDA library: the analytic inertia-gravity wave packet after 10 RK3 steps."""
+    import oceananigans_jl_b200 as oc
+    og = _internal_wave_grids()[which]
+    Nx = Nz = 128
+    Lx = Lz = 2 * np.pi
+    flat = og.topology[1] == F
+    z = (-Lz, 0) if og.regular_dim(2) else og.coords[2].F.r(1, Nz + 1).astype(np.float64)
+    kw = dict(topology=og.topology, size=(Nx, Nz) if flat else (Nx, 1, Nz), x=(0, Lx), z=z)
+    if not flat:
+        kw["y"] = (0, Lx)
+    grid = oc.RectilinearGrid(np.float64, **kw)
+    sol, _, dt = _internal_wave_solution(2 * np.pi)
+    m = oc.NonhydrostaticModel(grid, closure=oc.ScalarDiffusivity(nu=1e-9, kappa=1e-9), buoyancy=oc.BuoyancyTracer(), tracers=("b",),
+                               coriolis=oc.FPlane(f=0.2))
+    oc.set_model(m, **{n: (lambda x, y, z, n=n: sol[n](x, z, 0.0)) for n in "uvwb"})
+    oc.time_step(m, dt, n_steps=10)
+    t = m.clock.time
+    u = m.velocities.u
+    xs, zs = grid.nodes(0, "f")[:, None, None], grid.nodes(2, "c")[None, None, :]
+    ua = np.broadcast_to(sol["u"](xs, zs, t), u.size)
+    un = u.interior()
+    assert m.clock.iteration == 10
+    assert np.mean((un - ua) ** 2) / np.mean(ua ** 2) < 1e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 2])
+@pytest.mark.parametrize("topology", [(F, P, P), (P, F, P), (P, P, F), (F, F, B), (F, P, B), (P, F, B), (P, B, F), (F, B, B), (B, F, B),
+                                      (B, B, F)])
+def test_library_time_stepping_works_with_flat_dimensions(topology, n):
+    import oceananigans_jl_b200 as oc
+    size = tuple(n for t in topology if t != F)
+    grid = oc.RectilinearGrid(np.float64, size=size, extent=tuple(1 for _ in size), topology=topology)
+    m = oc.NonhydrostaticModel(grid)
+    oc.time_step(m, 1.0)
+    assert m.clock.iteration == 1 and _lib_finite(m)
+
+
+@pytest.mark.gpu
+def test_library_euler_time_stepping_doesnt_propagate_nans():
+    import oceananigans_jl_b200 as oc
+    grid = oc.RectilinearGrid(np.float64, size=(1, 1, 1), extent=(1, 2, 3))
+    m = oc.NonhydrostaticModel(grid, timestepper="QuasiAdamsBashforth2", buoyancy=oc.BuoyancyTracer(), tracers=("b",))
+    G = m.timestepper.Gm["u"]
+    G.set_parent(np.full(G.parent_size, np.nan))
+    oc.time_step(m, 1.0, euler=True)
+    assert not np.isnan(m.velocities.u.interior()).any()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,scheme", _ADVECTION, ids=[a[0] for a in _ADVECTION])
+def test_library_time_stepping_works_with_advection_scheme(name, scheme):
+    import oceananigans_jl_b200 as oc
+    lib_scheme = {"none": None, "Centered2": oc.Centered(np.float64, 2), "Centered4": oc.Centered(np.float64, 4),
+                  "UpwindBiased1": oc.UpwindBiased(np.float64, 1), "UpwindBiased3": oc.UpwindBiased(np.float64, 3),
+                  "UpwindBiased5": oc.UpwindBiased(np.float64, 5), "WENO3": oc.WENO(np.float64, 3), "WENO5": oc.WENO(np.float64, 5)}[name]
+    grid = oc.RectilinearGrid(np.float64, size=(3, 3, 3), extent=(1, 2, 3))
+    m = oc.NonhydrostaticModel(grid, advection=lib_scheme)
+    rng = np.random.default_rng(0)
+    oc.set_model(m, u=rng.standard_normal((3, 3, 3)), v=rng.standard_normal((3, 3, 3)))
+    oc.time_step(m, 1e-3)
+    assert m.clock.iteration == 1 and _lib_finite(m)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", [c[0] for c in _CLOSURES])
+@pytest.mark.parametrize("FT", [np.float32, np.float64])
+def test_library_time_stepping_works_with_closure(FT, name):
+    import oceananigans_jl_b200 as oc
+    closure = {"nothing": None, "ScalarDiffusivity": oc.ScalarDiffusivity(nu=1e-2, kappa=1e-2),
+               "ScalarDiffusivity-VITD": oc.ScalarDiffusivity(nu=1e-2, kappa=1e-2, vertically_implicit=True),
+               "SmagorinskyLilly": oc.SmagorinskyLilly(), "AnisotropicMinimumDissipation": oc.AnisotropicMinimumDissipation()}[name]
+    grid = oc.RectilinearGrid(FT, size=(3, 3, 3), extent=(1, 2, 3))
+    m = oc.NonhydrostaticModel(grid, closure=closure, tracers=("T", "S"), buoyancy=oc.SeawaterBuoyancy())
+    oc.time_step(m, 1.0)
+    assert m.clock.iteration == 1 and _lib_finite(m)
+    m = oc.NonhydrostaticModel(oc.RectilinearGrid(FT, size=(1, 1, 1), extent=(1, 2, 3)), coriolis=oc.FPlane(latitude=45))
+    oc.time_step(m, 1.0)
+    assert m.clock.iteration == 1 and _lib_finite(m)
