@@ -79,7 +79,8 @@ def rewrite_launches(text, name):
         rp = _matching(text, lp, "(", ")")
         args = text[lp + 1:rp - 1]
         shared = cfg[2] if len(cfg) > 2 else "0"
-        out += text[pos:k] + f"emu::launch(dim3({cfg[0]}), dim3({cfg[1]}), (size_t)({shared}), [&]() {{ {kernel}({args}); }})"
+        out += text[pos:k] + (f"emu::launch(dim3({cfg[0]}), dim3({cfg[1]}), (size_t)({shared}), [&]() {{ {kernel}({args}); }}, "
+                              f"(const void*)({kernel}), \"{kernel}\")")
         pos = rp
 
 

@@ -40,7 +40,9 @@ static inline int2 make_int2(int x, int y) { return int2{x, y}; }
 namespace emu {
 extern uint3 thread_idx, block_idx;
 extern dim3 block_dim, grid_dim;
-void launch(dim3 grid, dim3 block, size_t shared_bytes, const std::function<void()>& thread_body);
+void launch(dim3 grid, dim3 block, size_t shared_bytes, const std::function<void()>& thread_body, const void* kernel = nullptr,
+            const char* name = "");
+void set_max_dynamic_shared(const void* kernel, int bytes);
 void syncthreads();
 void syncwarp();
 unsigned char* dynamic_shared();
@@ -123,7 +125,10 @@ static inline cudaError_t cudaGetDeviceCount(int* n) { *n = 16; return cudaSucce
 static inline cudaError_t cudaDeviceSynchronize() { return cudaSuccess; }
 static inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 static inline cudaError_t cudaDeviceGetAttribute(int* v, int attr, int) { *v = attr == cudaDevAttrMultiProcessorCount ? 148 : 0; return cudaSuccess; }
-template <typename F> static inline cudaError_t cudaFuncSetAttribute(F, int, int) { return cudaSuccess; }
+template <typename F> static inline cudaError_t cudaFuncSetAttribute(F f, int attr, int value) {
+  if (attr == 8) emu::set_max_dynamic_shared((const void*)f, value);      // cudaFuncAttributeMaxDynamicSharedMemorySize
+  return value > 227 * 1024 ? 1 : 0;
+}
 cudaError_t cudaMalloc(void** p, size_t bytes);
 template <typename T> static inline cudaError_t cudaMalloc(T** p, size_t bytes) { return cudaMalloc((void**)p, bytes); }
 cudaError_t cudaFree(void* p);

@@ -179,8 +179,21 @@ void syncwarp() { yield_with(2); }
 unsigned char* dynamic_shared() { return dyn_shared.data(); }
 unsigned long long launches() { return n_launches; }
 
-void launch(dim3 grid, dim3 block, size_t shared_bytes, const std::function<void()>& thread_body) {
+static std::unordered_map<const void*, int> max_dynamic_shared;
+void set_max_dynamic_shared(const void* kernel, int bytes) { max_dynamic_shared[kernel] = bytes; }
+
+void launch(dim3 grid, dim3 block, size_t shared_bytes, const std::function<void()>& thread_body, const void* kernel, const char* name) {
   ++n_launches;
+  // the launch-configuration errors a GPU reports and a CPU would not: more than 48 KB of dynamic shared memory needs the opt-in
+  // of cudaFuncSetAttribute on THIS instantiation, and grid extents are limited
+  if (shared_bytes > 48 * 1024) {
+    auto it = max_dynamic_shared.find(kernel);
+    if (it == max_dynamic_shared.end() || (size_t)it->second < shared_bytes) {
+      std::fprintf(stderr, "emu: %s launched with %zu bytes of dynamic shared memory without a sufficient cudaFuncSetAttribute\n", name, shared_bytes);
+      std::abort();
+    }
+  }
+  if (grid.y > 65535 || grid.z > 65535) { std::fprintf(stderr, "emu: %s: grid.y / grid.z above 65535\n", name); std::abort(); }
   const unsigned nthreads = block.x * block.y * block.z;
   if (nthreads == 0 || nthreads > 1024) { std::fprintf(stderr, "emu: invalid block of %u threads\n", nthreads); std::abort(); }
   if ((unsigned long long)grid.x * grid.y * grid.z == 0) { std::fprintf(stderr, "emu: empty grid\n"); std::abort(); }
