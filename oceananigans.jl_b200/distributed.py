@@ -1,4 +1,5 @@
-"""Multi-GPU NonhydrostaticModel: one process per GPU, y-slab partition, NCCL over NVLink through ``torch.distributed``.
+"""Multi-GPU NonhydrostaticModel: one process per GPU, slab partition (y-slabs; x-slabs as their mirror image), NCCL over NVLink
+through ``torch.distributed``.
 
 Mirrors the reference's distributed architecture for the hot path:
   Distributed(GPU(); partition = Partition(1, R, 1))    src/DistributedComputations/distributed_architectures.jl:12-118,182-285
@@ -20,12 +21,56 @@ from ._lib import lib, check
 
 # ---- partition arithmetic (pure host logic) ------------------------------------------------------------------------
 class Partition:
-    """Partition(x=1, y=R, z=1): only y-slabs are supported on the B200 path (§8e)."""
+    """Partition(x=1, y=R, z=1) or Partition(x=R): slab decompositions (§8e).  The kernels partition in y; an x-slab run is the same
+    run on the mirror image of the problem (x ↔ y, u ↔ v, f → −f, west/east ↔ south/north), which the discretisation maps onto
+    itself — see DistributedNonhydrostaticModel.  Pencils (x and y together) and z partitions are not built."""
 
-    def __init__(self, x=1, y=1, z=1):
-        if x != 1 or z != 1:
-            raise NotImplementedError("the B200 path partitions in y only (slab decomposition)")
-        self.x, self.y, self.z = 1, int(y), 1
+    def __init__(self, x=None, y=None, z=1):
+        xi, yi = (1 if x is None else int(x)), (1 if y is None else int(y))
+        if z != 1:
+            raise NotImplementedError("the vertical direction is not partitioned (the reference's solvers do not either)")
+        if xi != 1 and yi != 1:
+            raise NotImplementedError("pencil (x × y) decompositions are not built: Partition(x=R) or Partition(y=R)")
+        self.x, self.y, self.z = xi, yi, 1
+        # Partition(R) / Partition(x=R) slabs along x (also with R = 1, which runs the mirrored code path on one rank); everything
+        # else — Partition(), Partition(y=R), Partition(1, R) — along y
+        self.direction = "x" if (x is not None and yi == 1 and (xi > 1 or y is None)) else "y"
+
+    @property
+    def ranks(self):
+        return self.x * self.y
+
+
+# ---- x-slabs as y-slabs of the mirrored problem ----------------------------------------------------------------------
+_SWAP_NAME = {"u": "v", "v": "u"}
+_SWAP_SIDE = {"west": "south", "east": "north", "south": "west", "north": "east", "bottom": "bottom", "top": "top"}
+
+
+def _swap3(t):
+    return None if t is None else (t[1], t[0], t[2])
+
+
+def _mirror_model_arguments(advection, kw):
+    """Model keyword arguments of the mirrored (x ↔ y) problem: per-direction advection schemes exchanged, the Coriolis
+    parameter negated (a reflection reverses the sense of rotation), boundary conditions moved to the mirrored field and wall."""
+    from . import FluxFormAdvection, FPlane
+    from .model import FieldBoundaryConditions
+    kw = dict(kw)
+    if isinstance(advection, FluxFormAdvection):
+        advection = FluxFormAdvection(x=advection.y, y=advection.x, z=advection.z)
+    if kw.get("coriolis") is not None:
+        kw["coriolis"] = FPlane(f=-kw["coriolis"].f)
+    if kw.get("boundary_conditions"):
+        out = {}
+        for name, fbcs in kw["boundary_conditions"].items():
+            sides = {}
+            for side, bc in fbcs.sides.items():
+                if np.ndim(bc.condition) != 0:
+                    raise NotImplementedError("array boundary conditions are not supported on an x-slab partition; use Partition(y=R)")
+                sides[_SWAP_SIDE[side]] = bc
+            out[_SWAP_NAME.get(name, name)] = FieldBoundaryConditions(**sides)
+        kw["boundary_conditions"] = out
+    return advection, kw
 
 
 def local_slab(Ny, R, rank):
@@ -111,8 +156,9 @@ class Distributed:
         else:
             self.rank, self.size = 0, 1
         self.partition = partition or Partition(y=self.size)
-        if self.partition.y != self.size:
-            raise ValueError(f"Partition(y={self.partition.y}) does not match the {self.size} ranks of the process group")
+        if self.partition.ranks != self.size:
+            raise ValueError(f"Partition(x={self.partition.x}, y={self.partition.y}) does not match the {self.size} ranks of the "
+                             "process group")
 
 
 class DistributedNonhydrostaticModel:
@@ -127,6 +173,11 @@ class DistributedNonhydrostaticModel:
         from . import RectilinearGrid, Periodic, WENO
         from .model import NonhydrostaticModel
         self.arch, self.rank, self.R = arch, arch.rank, arch.size
+        # Partition(x=R): the run is the y-slab run of the mirrored problem; set / gather / local_interior mirror the arrays back
+        self.mirrored = arch.partition.direction == "x"
+        if self.mirrored:
+            size, halo, topology, x, y = _swap3(size), _swap3(halo), _swap3(topology), y, x
+            advection, kw = _mirror_model_arguments(advection, kw)
         self.global_size = tuple(int(n) for n in size)
         Nx, Ny, Nz = self.global_size
         self.j0, self.NyL = local_slab(Ny, self.R, self.rank)
@@ -343,13 +394,16 @@ class DistributedNonhydrostaticModel:
     # -- state ----------------------------------------------------------------------------------------------------
     def set(self, enforce_incompressibility=True, **global_arrays):
         """set!(model; u=…, v=…, w=…) from GLOBAL (Nx, Ny, Nz) arrays; every rank keeps its own rows."""
+        if self.mirrored:
+            global_arrays = {_SWAP_NAME.get(n, n): np.asarray(a).transpose(1, 0, 2) for n, a in global_arrays.items()}
         rows = {}
         for name, a in global_arrays.items():
             a = np.asarray(a)
             if a.shape[:2] != self.global_size[:2]:
-                raise ValueError(f"{name} must have the global size {self.global_size}")
+                shown = (_SWAP_NAME.get(name, name), _swap3(self.global_size)) if self.mirrored else (name, self.global_size)
+                raise ValueError(f"{shown[0]} must have the global size {shown[1]}")
             rows[name] = a[:, self.j0:self.j0 + self.NyL, :]
-        self.set_local(enforce_incompressibility, **rows)
+        self._set_local_internal(enforce_incompressibility, **rows)
 
     def _field(self, name):
         for ns in (self.velocities, self.tracers, self.pressures):
@@ -358,7 +412,12 @@ class DistributedNonhydrostaticModel:
         raise KeyError(name)
 
     def set_local(self, enforce_incompressibility=True, **local_arrays):
-        """As ``set`` with this rank's own (Nx, Ny/R, Nz) rows."""
+        """As ``set`` with this rank's own (Nx, Ny/R, Nz) rows — (Nx/R, Ny, Nz) columns on an x-slab partition."""
+        if self.mirrored:
+            local_arrays = {_SWAP_NAME.get(n, n): np.asarray(a).transpose(1, 0, 2) for n, a in local_arrays.items()}
+        self._set_local_internal(enforce_incompressibility, **local_arrays)
+
+    def _set_local_internal(self, enforce_incompressibility=True, **local_arrays):
         if self.generic:
             # every rank sets the same fields in the same order (each set fills halos, i.e. meets the others at a barrier)
             from .model import set_model
@@ -372,19 +431,25 @@ class DistributedNonhydrostaticModel:
             self.pressure_phase(1.0)
 
     def local_interior(self, name):
+        """This rank's part of a field, in the user's orientation."""
+        if self.mirrored:
+            return self._field(_SWAP_NAME.get(name, name)).interior().transpose(1, 0, 2)
         return self._field(name).interior()
 
     def gather(self, name):
         """Global (Nx, Ny, Nz) array of a field on every rank (diagnostics / tests only)."""
         import torch
         import torch.distributed as dist
-        loc = np.ascontiguousarray(self.local_interior(name).transpose(1, 0, 2))       # rows first
+        internal = _SWAP_NAME.get(name, name) if self.mirrored else name
+        loc = np.ascontiguousarray(self._field(internal).interior().transpose(1, 0, 2))       # the partitioned direction first
         if self.R == 1:
-            return loc.transpose(1, 0, 2)
-        t = torch.from_numpy(loc).to(self.device)
-        out = [torch.empty_like(t) for _ in range(self.R)]
-        dist.all_gather(out, t, group=self.arch.group)
-        return torch.cat(out, dim=0).cpu().numpy().transpose(1, 0, 2)
+            glob = loc.transpose(1, 0, 2)
+        else:
+            t = torch.from_numpy(loc).to(self.device)
+            out = [torch.empty_like(t) for _ in range(self.R)]
+            dist.all_gather(out, t, group=self.arch.group)
+            glob = torch.cat(out, dim=0).cpu().numpy().transpose(1, 0, 2)
+        return glob.transpose(1, 0, 2) if self.mirrored else glob
 
     def max_abs_divergence(self):
         import torch

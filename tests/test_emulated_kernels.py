@@ -39,9 +39,11 @@ def test_multi_rank_slab_tests_pass_against_the_kernels_compiled_for_the_host():
     for k in ("NHSTEP_EMU_GUARD", "NHSTEP_EMU_ORDER", "NHSTEP_EMU_POISON", "NHSTEP_TILE_SWEEP", "NHSTEP_PLANE_SWEEP", "NHSTEP_OVERLAP"):
         env.pop(k, None)
     selection = ("test_multi_gpu_matches_single_gpu and float64-RungeKutta3-size0-2-p2p or "
-                 "test_transpose_round_trip_is_bit_identical and (2-p2p or 4-p2p or 2-nccl)")
+                 "test_transpose_round_trip_is_bit_identical and (2-p2p or 4-p2p or 2-nccl) or "
+                 "test_x_slabs_match_single_gpu and float64-RungeKutta3-2-p2p or "
+                 "test_complete_path_x_slabs_match_single_gpu and ppb-les-2")
     cmd = [sys.executable, "-m", "pytest", "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider", "-k", selection,
-           "tests/test_gpu_distributed.py"]
+           "tests/test_gpu_distributed.py", "tests/test_zx_slab_partition.py"]
     r = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=1500)
     tail = (r.stdout + r.stderr)[-3000:]
     assert r.returncode == 0, tail
