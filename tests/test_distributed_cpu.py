@@ -51,8 +51,13 @@ def test_partition_arithmetic():
         for R in (1, 2, 4, 8):
             Cx = D.spectral_block_width(Nx, R)
             assert Cx % 8 == 0 and Cx * R >= Nx // 2 + 1 and (Cx - 8) * R < Nx // 2 + 1 + 8 * R
+    # Partition(R) / Partition(x=R): x-slabs (run as the mirror image); Partition(y=R), Partition(1, R), Partition(): y-slabs
+    assert (D.Partition(2).direction, D.Partition(x=2).ranks, D.Partition(x=1).direction) == ("x", 2, "x")
+    assert (D.Partition(y=4).direction, D.Partition(1, 4).direction, D.Partition().direction, D.Partition(y=1).direction) == ("y",) * 4
     with pytest.raises(NotImplementedError):
-        D.Partition(x=2)
+        D.Partition(x=2, y=2)                      # pencils
+    with pytest.raises(NotImplementedError):
+        D.Partition(z=2)
 
 
 def test_blocked_layout_is_a_bijection():
