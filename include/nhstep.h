@@ -141,6 +141,18 @@ int32_t nh_model_set_boundary_condition(nh_model* model, int32_t field, int32_t 
 int32_t nh_model_set_boundary_condition_array(nh_model* model, int32_t field, int32_t dim, int32_t side, int32_t kind,
                                               const void* data, int64_t count, int32_t where);
 
+/* WENO(grid) — src/Advection/weno_reconstruction.jl:98-124 with compute_reconstruction_coefficients
+ * (reconstruction_coefficients.jl:237-324): on a grid stretched in z a WENO scheme built with the grid reconstructs with per-index
+ * sub-stencil coefficients (weno_interpolants.jl:124-127); smoothness indicators, optimal weights and the Centered / UpwindBiased
+ * schemes it hands down keep uniform coefficients, as in the reference.  `data` holds (Nz + 2) × (buffer + 1) × buffer values of the
+ * model's float type: entry [i][r + 1][t], i = 0 … Nz+1 the reconstruction index, r = −1 … buffer−1 the stencil, t the position in the
+ * stencil — `coeff_zᵃᵃᶠ[r + 2][i]` (location 0, Face targets) or `coeff_zᵃᵃᶜ[r + 2][i]` (location 1, Center targets), generated on the
+ * host (the reference computes them on the CPU too).  Call once per (buffer, location) the scheme uses: buffer 3 and its near-wall
+ * buffer scheme 2 for WENO(order = 5).  Without a call the uniform coefficients are used — `WENO()` without a grid.  The model must
+ * not be a fused triply periodic one (a stretched z never is). */
+int32_t nh_model_set_weno_z_coefficients(nh_model* model, int32_t buffer, int32_t location, const void* data, int64_t count,
+                                         int32_t where);
+
 /* fill_halo_regions!(fields…; fill_boundary_normal_velocities) — src/Fields/field_tuples.jl:56-119,
  * src/BoundaryConditions/fill_halo_regions.jl:50-82.  field_mask bit f = field id f (ids < 32). */
 int32_t nh_fill_halo_regions(nh_model* model, uint32_t field_mask, int32_t fill_boundary_normal_velocities);

@@ -171,10 +171,17 @@ def UpwindBiased(FT=None, order=3):
     return _Scheme(L.ADV_UPWIND, order)
 
 
-def WENO(FT=None, order=5):
+def WENO(FT=None, order=5, grid=None):
+    """WENO(FT; order, grid) — weno_reconstruction.jl:98-124.  With ``grid`` (``WENO(grid)`` in the reference) the scheme reconstructs
+    along the grid's stretched z with per-index coefficients (stretched_weno.py → nh_model_set_weno_z_coefficients); without it the
+    uniform coefficients are used in every direction, also on a stretched grid, as in the reference."""
+    if isinstance(FT, RectilinearGrid):                  # WENO(grid, …)
+        FT, grid = None, FT
     if order % 2 == 0:
         raise ValueError("WENO reconstruction scheme is defined only for odd orders")
-    return _Scheme(L.ADV_WENO, order)
+    s = _Scheme(L.ADV_WENO, order)
+    s.grid = grid
+    return s
 
 
 class FluxFormAdvection:

@@ -45,7 +45,7 @@ class Clock(C.Structure):
 # every symbol include/nhstep.h declares (tests check that the library exports all of them)
 SYMBOLS = [
     "nh_last_error", "nh_version", "nh_device_count", "nh_grid_create", "nh_grid_destroy", "nh_grid_info",
-    "nh_grid_spacings", "nh_model_create", "nh_model_destroy", "nh_model_grid_info", "nh_field_size", "nh_set_field",
+    "nh_grid_spacings", "nh_model_create", "nh_model_set_weno_z_coefficients", "nh_model_destroy", "nh_model_grid_info", "nh_field_size", "nh_set_field",
     "nh_get_field", "nh_set_state_finalize", "nh_fill_halo_regions", "nh_update_state", "nh_compute_tendencies",
     "nh_rk3_substep", "nh_ab2_step", "nh_cache_previous_tendencies", "nh_calculate_pressure_correction",
     "nh_pressure_correct_velocities", "nh_time_step", "nh_time_step_profiled", "nh_clock_get", "nh_clock_set", "nh_max_abs_divergence",
@@ -94,6 +94,7 @@ def lib():
             "nh_dist_mode": [p, C.POINTER(C.c_int32)],
             "nh_model_set_boundary_condition_array": [p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int64,
                                                       C.c_int32],
+            "nh_model_set_weno_z_coefficients": [p, C.c_int32, C.c_int32, C.c_void_p, C.c_int64, C.c_int32],
             "nh_update_state": [p, C.c_int32],
             "nh_compute_tendencies": [p],
             "nh_rk3_substep": [p, C.c_double, C.c_double, C.c_double, C.c_int32],

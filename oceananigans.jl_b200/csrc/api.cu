@@ -193,6 +193,7 @@ int32_t nh_set_state_finalize(nh_model* m, int32_t enforce) { MODEL_CALL(m, m->s
 int32_t nh_fill_halo_regions(nh_model* m, uint32_t mask, int32_t fill_normal) { MODEL_CALL(m, m->fill_halo_regions(mask, fill_normal)) }
 int32_t nh_model_set_boundary_condition(nh_model* m, int32_t field, int32_t dim, int32_t side, int32_t kind, double value) { MODEL_CALL(m, m->set_boundary_condition(field, dim, side, kind, value)) }
 int32_t nh_model_set_boundary_condition_array(nh_model* m, int32_t field, int32_t dim, int32_t side, int32_t kind, const void* data, int64_t count, int32_t where) { MODEL_CALL(m, m->set_boundary_condition_array(field, dim, side, kind, data, count, where)) }
+int32_t nh_model_set_weno_z_coefficients(nh_model* m, int32_t buffer, int32_t location, const void* data, int64_t count, int32_t where) { MODEL_CALL(m, m->set_weno_z_coefficients(buffer, location, data, count, where)) }
 int32_t nh_update_state(nh_model* m, int32_t compute) { MODEL_CALL(m, m->update_state(compute)) }
 int32_t nh_compute_tendencies(nh_model* m) { MODEL_CALL(m, m->compute_tendencies()) }
 int32_t nh_rk3_substep(nh_model* m, double dt, double gamma, double zeta, int32_t has_zeta) { MODEL_CALL(m, m->rk3_substep(dt, gamma, zeta, has_zeta)) }

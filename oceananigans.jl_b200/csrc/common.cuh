@@ -81,6 +81,9 @@ struct TendParams {
   const FT* nue;              // eddy viscosity νₑ at ccc (Smagorinsky closures); nullptr ⇒ the constants above
   const FT* kape[NH_MAXTR];   // eddy diffusivity field of each tracer at ccc: νₑ itself (Smagorinsky) or κₑ[n] (AMD)
   FT Pr[NH_MAXTR];            // κ on a face = ℑ(kape[n]) / Pr[n]  (Pr = 1 for AMD)
+  // WENO(grid) on a stretched z: per-index reconstruction coefficients wz[loc][B-2] (loc 0 = Face, 1 = Center target; B = 2, 3),
+  // each (Nz + 2) × (B + 1) × B values [i = 0 … Nz+1][r = −1 … B−1][t]; nullptr ⇒ the uniform coefficients of `tab`
+  const FT* wz[2][2];
 };
 
 struct FieldExtent { int n[3]; };   // interior size of a field (N, or N+1 on a Bounded Face dim)

@@ -337,6 +337,23 @@ void Model<FT>::set_boundary_condition_array(int field, int dim, int side, int k
   CUDA_CHECK(cudaStreamSynchronize(stream));
 }
 
+// WENO(grid) (weno_reconstruction.jl:98-124): the per-index reconstruction coefficients of the stretched z direction, generated on
+// the host as compute_reconstruction_coefficients does (include/nhstep.h: nh_model_set_weno_z_coefficients)
+template <typename FT>
+void Model<FT>::set_weno_z_coefficients(int buffer, int location, const void* data, long long count, int where) {
+  NH_REQUIRE(buffer == 2 || buffer == 3, "WENO(grid): buffer must be 2 (order 3) or 3 (order 5)");
+  NH_REQUIRE(location == 0 || location == 1, "WENO(grid): location must be 0 (Face targets) or 1 (Center targets)");
+  NH_REQUIRE(adv[2].kind == NH_ADV_WENO && adv[2].B >= buffer, "WENO(grid): the model's z advection is not a WENO scheme of that order");
+  NH_REQUIRE(data != nullptr && (where == NH_HOST || where == NH_DEVICE), "WENO(grid): bad data / where");
+  NH_REQUIRE(count == (long long)(gh.g.N[2] + 2) * (buffer + 1) * buffer, "WENO(grid): count must be (Nz + 2) × (buffer + 1) × buffer");
+  DevBuf<FT>& b = weno_z[location][buffer - 2];
+  b.alloc((size_t)count, false);
+  CUDA_CHECK(cudaMemcpyAsync(b.p, data, count * sizeof(FT), where == NH_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, stream));
+  CUDA_CHECK(cudaStreamSynchronize(stream));
+  weno_stretched = true;             // tendencies through the per-cell kernel instantiated with the tables (tendency_generic_kernel<FT, true>)
+  gn_stale = true;
+}
+
 // fill_halo_regions! — open fill, then the three directions sorted so that Periodic runs after the others
 // (fill_halo_regions.jl:50-67,121-123,159-196; field_tuples.jl:56-101)
 template <typename FT>
@@ -432,6 +449,7 @@ TendParams<FT> Model<FT>::tend_params() const {
   P.has_closure = desc.has_closure; P.nu = (FT)desc.nu;
   P.vitd = vitd ? 1 : 0;
   P.nue = nue;
+  for (int l = 0; l < 2; ++l) for (int q = 0; q < 2; ++q) P.wz[l][q] = weno_z[l][q].p;
   const bool amd = desc.has_closure == NH_CLOSURE_AMD;
   for (int t = 0; t < ntr; ++t) { P.Pr[t] = amd ? FT(1) : (FT)desc.smagorinsky_Pr[t]; P.kape[t] = amd ? kape[t] : nue; }
   return P;
@@ -478,7 +496,7 @@ void Model<FT>::compute_tendencies() {
   // tiled kernel (each advective face flux once, staged in shared memory); NHSTEP_NO_TILED selects the per-cell kernel that
   // evaluates every face from both neighbours like the reference (bit-identical results, kept as the cross-check)
   dim3 blk(32, 4, 1);
-  if (tiled) {
+  if (tiled && !weno_stretched) {
     // one launch for all prognostic fields; interior tiles of WENO5 models on (Periodic, Periodic, Periodic | Bounded) regular
     // grids take the fast flux stage (tendency_generic.cuh)
     dim3 tb(TG_TX, TG_TY, 1), tg(ceil_div(gh.g.N[0], TG_TX), ceil_div(gh.g.N[1], TG_TY), ceil_div(gh.g.N[2], TG_TZ));
@@ -487,7 +505,8 @@ void Model<FT>::compute_tendencies() {
     KLAUNCH(lc);
   } else {
     for (int what = 0; what < nf; ++what) {
-      tendency_generic_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, what);
+      if (weno_stretched) tendency_generic_kernel<FT, true><<<grid3(blk), blk, 0, stream>>>(P, what);      // WENO(grid)
+      else tendency_generic_kernel<FT><<<grid3(blk), blk, 0, stream>>>(P, what);
       KLAUNCH(lc);
     }
   }

@@ -286,6 +286,7 @@ struct nh_model {
   virtual void fill_halo_regions(uint32_t mask, int fill_normal) = 0;
   virtual void set_boundary_condition(int field, int dim, int side, int kind, double value) = 0;
   virtual void set_boundary_condition_array(int field, int dim, int side, int kind, const void* data, long long count, int where) = 0;
+  virtual void set_weno_z_coefficients(int buffer, int location, const void* data, long long count, int where) = 0;
   virtual int dist_mode() = 0;
   virtual void update_state(int compute_tendencies) = 0;
   virtual void compute_tendencies() = 0;
@@ -392,6 +393,9 @@ struct Model : nh_model {
   void fill_halo_regions(uint32_t mask, int fill_normal) override;
   void set_boundary_condition(int field, int dim, int side, int kind, double value) override;
   void set_boundary_condition_array(int field, int dim, int side, int kind, const void* data, long long count, int where) override;
+  void set_weno_z_coefficients(int buffer, int location, const void* data, long long count, int where) override;
+  DevBuf<FT> weno_z[2][2];   // WENO(grid) on a stretched z: [location Face / Center][buffer − 2] (TendParams::wz)
+  bool weno_stretched = false;
   int dist_mode() override { return !dist.on ? 0 : (dist.generic ? 2 : 1); }
   FT* halo_field_or_null(int id) {       // the field of a halo-fill mask bit, nullptr when the model has none
     if (id >= 0 && id < nf) return F[id];

@@ -44,7 +44,8 @@ struct AreaVelGet {
 };
 
 // advective_momentum_flux_{U_b}{u_a} at the flux location index (i,j,k)
-template <typename FT, int a, int b>
+// ZT: reconstruct along z with the stretched WENO tables of TendParams::wz (WENO(grid)); only the per-cell kernel instantiates it
+template <typename FT, int a, int b, bool ZT = false>
 __device__ __forceinline__ FT momentum_flux(const TendParams<FT>& P, int i, int j, int k) {
   const GridDev<FT>& g = P.g;
   SchemeDev s = P.adv[b];
@@ -55,7 +56,7 @@ __device__ __forceinline__ FT momentum_flux(const TendParams<FT>& P, int i, int 
   if (s.kind != NH_ADV_CENTERED) {
     AreaVelGet<FT, b> Aq{P.U[b], &g};
     FT ut = symmetric_interp<FT>(P.tab, s, g.topo[sym_dim], g.N[sym_dim], sym_dim, stag_c, i, j, k, Aq);
-    FT qR = biased_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, stag_c, ut > FT(0), i, j, k, ua);
+    FT qR = biased_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, stag_c, ut > FT(0), i, j, k, ua, (ZT && b == 2) ? P.wz[stag_c] : nullptr);
     return ut * qR;
   }
   constexpr int zc = (a != b && (a == 2 || b == 2)) ? 0 : 1;
@@ -65,23 +66,23 @@ __device__ __forceinline__ FT momentum_flux(const TendParams<FT>& P, int i, int 
          symmetric_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, stag_c, i, j, k, ua);
 }
 
-template <typename FT, int a, int b>
+template <typename FT, int a, int b, bool ZT = false>
 __device__ __forceinline__ FT momentum_flux_diff(const TendParams<FT>& P, int i, int j, int k) {
   if (P.g.topo[b] == NH_FLAT) return FT(0);
   constexpr int di = b == 0, dj = b == 1, dk = b == 2;
   if (a == b)  // target is a Face: F[i] - F[i-1]
-    return momentum_flux<FT, a, b>(P, i, j, k) - momentum_flux<FT, a, b>(P, i - di, j - dj, k - dk);
-  return momentum_flux<FT, a, b>(P, i + di, j + dj, k + dk) - momentum_flux<FT, a, b>(P, i, j, k);
+    return momentum_flux<FT, a, b, ZT>(P, i, j, k) - momentum_flux<FT, a, b, ZT>(P, i - di, j - dj, k - dk);
+  return momentum_flux<FT, a, b, ZT>(P, i + di, j + dj, k + dk) - momentum_flux<FT, a, b, ZT>(P, i, j, k);
 }
 
-template <typename FT, int a>
+template <typename FT, int a, bool ZT = false>
 __device__ __forceinline__ FT div_Uu(const TendParams<FT>& P, int i, int j, int k) {
-  FT total = momentum_flux_diff<FT, a, 0>(P, i, j, k) + momentum_flux_diff<FT, a, 1>(P, i, j, k);
-  total = total + momentum_flux_diff<FT, a, 2>(P, i, j, k);
+  FT total = momentum_flux_diff<FT, a, 0, ZT>(P, i, j, k) + momentum_flux_diff<FT, a, 1, ZT>(P, i, j, k);
+  total = total + momentum_flux_diff<FT, a, 2, ZT>(P, i, j, k);
   return FT(1) / volume_at(P.g, a == 2 ? 0 : 1, k) * total;
 }
 
-template <typename FT, int b>
+template <typename FT, int b, bool ZT = false>
 __device__ __forceinline__ FT tracer_flux(const TendParams<FT>& P, const FT* c, int i, int j, int k) {
   const GridDev<FT>& g = P.g;
   SchemeDev s = P.adv[b];
@@ -90,18 +91,18 @@ __device__ __forceinline__ FT tracer_flux(const TendParams<FT>& P, const FT* c, 
   FT ub = P.U[b][g.idx(i, j, k)];
   FieldGet<FT> cg{c, &g};
   if (s.kind != NH_ADV_CENTERED) {
-    FT cR = biased_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, 0, ub > FT(0), i, j, k, cg);
+    FT cR = biased_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, 0, ub > FT(0), i, j, k, cg, (ZT && b == 2) ? P.wz[0] : nullptr);
     return A * ub * cR;
   }
   return (A * ub) * symmetric_interp<FT>(P.tab, s, g.topo[b], g.N[b], b, 0, i, j, k, cg);
 }
 
-template <typename FT>
+template <typename FT, bool ZT = false>
 __device__ __forceinline__ FT div_Uc(const TendParams<FT>& P, const FT* c, int i, int j, int k) {
   const GridDev<FT>& g = P.g;
-  FT tx = g.topo[0] == NH_FLAT ? FT(0) : tracer_flux<FT, 0>(P, c, i + 1, j, k) - tracer_flux<FT, 0>(P, c, i, j, k);
-  FT ty = g.topo[1] == NH_FLAT ? FT(0) : tracer_flux<FT, 1>(P, c, i, j + 1, k) - tracer_flux<FT, 1>(P, c, i, j, k);
-  FT tz = g.topo[2] == NH_FLAT ? FT(0) : tracer_flux<FT, 2>(P, c, i, j, k + 1) - tracer_flux<FT, 2>(P, c, i, j, k);
+  FT tx = g.topo[0] == NH_FLAT ? FT(0) : tracer_flux<FT, 0, ZT>(P, c, i + 1, j, k) - tracer_flux<FT, 0, ZT>(P, c, i, j, k);
+  FT ty = g.topo[1] == NH_FLAT ? FT(0) : tracer_flux<FT, 1, ZT>(P, c, i, j + 1, k) - tracer_flux<FT, 1, ZT>(P, c, i, j, k);
+  FT tz = g.topo[2] == NH_FLAT ? FT(0) : tracer_flux<FT, 2, ZT>(P, c, i, j, k + 1) - tracer_flux<FT, 2, ZT>(P, c, i, j, k);
   FT total = tx + ty;
   total = total + tz;
   return FT(1) / volume_at(g, 1, k) * total;
@@ -356,7 +357,7 @@ __device__ __forceinline__ FT tracer_tendency(const TendParams<FT>& P, int n, in
 
 // One thread per cell of 1:Nx × 1:Ny × 1:Nz; Face fields skip index 1 in Bounded dims (exclude_periphery,
 // src/Utils/kernel_launching.jl:90-111; compute_nonhydrostatic_tendencies.jl:104-136).
-template <typename FT>
+template <typename FT, bool ZT = false>
 __global__ void __launch_bounds__(128) tendency_generic_kernel(const __grid_constant__ TendParams<FT> P, int what) {
   const GridDev<FT>& g = P.g;
   int i = blockIdx.x * blockDim.x + threadIdx.x + 1;
@@ -365,14 +366,14 @@ __global__ void __launch_bounds__(128) tendency_generic_kernel(const __grid_cons
   if (i > g.N[0] || j > g.N[1] || k > g.N[2]) return;
   long long n = g.idx(i, j, k);
   if (what == 0) {
-    if (!(g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i == 1)) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k, div_Uu<FT, 0>(P, i, j, k), P.has_closure ? div_viscous_flux<FT, 0>(P, i, j, k) : FT(0));
+    if (!(g.topo[0] == NH_BOUNDED && g.N[0] > 1 && i == 1)) P.GU[0][n] = velocity_tendency<FT, 0>(P, i, j, k, div_Uu<FT, 0, ZT>(P, i, j, k), P.has_closure ? div_viscous_flux<FT, 0>(P, i, j, k) : FT(0));
   } else if (what == 1) {
-    if (!(g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j == 1)) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k, div_Uu<FT, 1>(P, i, j, k), P.has_closure ? div_viscous_flux<FT, 1>(P, i, j, k) : FT(0));
+    if (!(g.topo[1] == NH_BOUNDED && g.N[1] > 1 && j == 1)) P.GU[1][n] = velocity_tendency<FT, 1>(P, i, j, k, div_Uu<FT, 1, ZT>(P, i, j, k), P.has_closure ? div_viscous_flux<FT, 1>(P, i, j, k) : FT(0));
   } else if (what == 2) {
-    if (!(g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k == 1)) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k, div_Uu<FT, 2>(P, i, j, k), P.has_closure ? div_viscous_flux<FT, 2>(P, i, j, k) : FT(0));
+    if (!(g.topo[2] == NH_BOUNDED && g.N[2] > 1 && k == 1)) P.GU[2][n] = velocity_tendency<FT, 2>(P, i, j, k, div_Uu<FT, 2, ZT>(P, i, j, k), P.has_closure ? div_viscous_flux<FT, 2>(P, i, j, k) : FT(0));
   } else {
     int t = what - 3;
-    P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k, div_Uc<FT>(P, P.c[t], i, j, k), P.has_closure ? div_diffusive_flux<FT>(P, P.c[t], t, i, j, k) : FT(0));
+    P.Gc[t][n] = tracer_tendency<FT>(P, t, i, j, k, div_Uc<FT, ZT>(P, P.c[t], i, j, k), P.has_closure ? div_diffusive_flux<FT>(P, P.c[t], t, i, j, k) : FT(0));
   }
 }
 

@@ -191,6 +191,18 @@ class NonhydrostaticModel:
         self.timestepper_name = timestepper
         self._h = C.c_void_p()
         check(lib().nh_model_create(grid._h, C.byref(d), C.byref(self._h)))
+        # WENO(grid): the stretched z coefficients of the scheme and of its near-wall buffer scheme, generated on the host
+        zs = per_dir[2]
+        if isinstance(zs, _Scheme) and zs.kind == L.ADV_WENO and getattr(zs, "grid", None) is not None and grid.z_stretched:
+            from .stretched_weno import weno_z_tables
+            if zs.grid is not grid and not (zs.grid.z_stretched and np.array_equal(zs.grid._zfaces, grid._zfaces)):
+                raise ValueError("WENO(grid): the scheme was built for another vertical coordinate than the model's grid")
+            top = min((zs.order + 1) // 2, grid.N[2])            # adapt_advection_order lowers the order on a short direction
+            for buffer in range(2, top + 1):
+                for location, a in weno_z_tables(grid._zfaces, grid.FT, buffer, grid.H[2]).items():
+                    a = np.ascontiguousarray(a)
+                    check(lib().nh_model_set_weno_z_coefficients(self._h, buffer, location, a.ctypes.data_as(C.c_void_p), a.size,
+                                                                 L.HOST))
         for name, fbcs in (boundary_conditions or {}).items():
             names_ = ["u", "v", "w"] + list(tracers)
             if name not in names_:

@@ -52,6 +52,53 @@ def stencil_coefficients(FT, r, order):
     return tuple(c) + (FT(FT(1) - s),)
 
 
+def stretched_stencil_coefficients(FT, i, r, coord, order):
+    """stencil_coefficients(FT, i, r, xr, xi; order) with xr = xi = ``coord`` (reconstruction_coefficients.jl:100-115,74-83), the form
+    create_reconstruction_coefficients (:316-324) calls for a stretched direction: numerators, denominators and spacings in FT
+    arithmetic (left folds, as Julia's sum / prod over a generator), the j-th coefficient accumulated exactly (BigFloat there),
+    rounded to FT, and the last coefficient = 1 − Σ of the others in FT."""
+    FT = np.dtype(FT).type
+    x = lambda idx: FT(coord[idx])
+    exact = [Fraction(0)] * order
+    for j in range(order):
+        for m in range(j + 1, order + 1):
+            numerator = None
+            for l in range(order + 1):
+                if l == m:
+                    continue
+                p = None
+                for q in range(order + 1):
+                    if q == m or q == l:
+                        continue
+                    term = FT(x(i) - x(i - (r - q + 1)))
+                    p = term if p is None else FT(p * term)
+                numerator = p if numerator is None else FT(numerator + p)
+            denominator = None
+            for l in range(order + 1):
+                if l == m:
+                    continue
+                term = FT(x(i - (r - m + 1)) - x(i - (r - l + 1)))
+                denominator = term if denominator is None else FT(denominator * term)
+            value = FT(FT(numerator / denominator) * FT(x(i - (r - j)) - x(i - (r - j + 1))))
+            exact[j] += Fraction(float(value))
+    c = [round_fraction(v, FT) for v in exact[:-1]]
+    total = c[0]
+    for v in c[1:]:
+        total = FT(total + v)
+    return tuple(c) + (FT(FT(1) - total),)
+
+
+def stretched_weno_tables(grid, FT, B, d=2):
+    """compute_reconstruction_coefficients(grid, FT, :WENO; order = B) for the stretched direction d (:251-272,306-314): for the Face
+    and the Center coordinate of the grid rebuilt with one more halo point, one table per stencil r = −1 … B−1, entries i = 0 … N+1.
+    → {"f" | "c": {r: [B-tuples for i = 0 … N+1]}}"""
+    H = tuple(max(h, B) + 1 if grid.topology[e] != Flat else 0 for e, h in enumerate(grid.H))
+    c = grid.with_halo(H).coords[d]
+    N = grid.N[d]
+    return {loc: {r: [stretched_stencil_coefficients(FT, i, r, coord, B) for i in range(N + 2)] for r in range(-1, B)}
+            for loc, coord in (("f", c.F), ("c", c.C))}
+
+
 class _Scheme:
     kind = None
 
@@ -105,26 +152,34 @@ _SMOOTH = {2: ((1, -2, 1), (1, -2, 1)),
            3: ((10, -31, 11, 25, -19, 4), (4, -13, 5, 13, -13, 4), (4, -19, 11, 25, -31, 10))}
 
 
-def WENO(FT=np.float64, order=5):
-    """WENO(FT; order): order < 3 returns UpwindBiased(order=1) (weno_reconstruction.jl:108-111)."""
+def WENO(FT=np.float64, order=5, grid=None):
+    """WENO(FT; order, grid): order < 3 returns UpwindBiased(order=1) (weno_reconstruction.jl:98-124).  With ``grid`` the scheme
+    carries per-index reconstruction coefficients for the grid's stretched direction (z on this path); the Centered and
+    UpwindBiased schemes it hands down keep uniform coefficients, as in the reference (centered_reconstruction.jl:47-58,
+    upwind_biased_reconstruction.jl:51-65)."""
+    if grid is not None:
+        FT = grid.FT
     if order % 2 == 0:
         raise ValueError("WENO reconstruction scheme is defined only for odd orders")
     if order < 3:
         return UpwindBiased(FT, 1)
-    return _WENO(FT, order)
+    return _WENO(FT, order, grid)
 
 
 class _WENO(_Scheme):
     kind = "WENO"
 
-    def __init__(self, FT, order):
+    def __init__(self, FT, order, grid=None):
         if order > 5:
             raise NotImplementedError("oracle restates WENO orders 3 and 5 only")
         self.FT = FT = np.dtype(FT).type
         self.order = order
         self.B = B = (order + 1) // 2
         self.advecting_velocity_scheme = Centered(FT, order - 1)
-        self.buffer_scheme = WENO(FT, order - 2)
+        self.buffer_scheme = WENO(FT, order - 2, grid)
+        self.grid = grid
+        # ztab[loc][r][i]: stretched coefficients of the z direction (None ⇒ uniform, reconstruction_coefficients.jl:276-283)
+        self.ztab = stretched_weno_tables(grid, FT, B) if (grid is not None and not grid.regular_dim(2)) else None
         self.coeff = tuple(stencil_coefficients(FT, r, B) for r in range(B))
         self.cstar = tuple(round_fraction(c, FT) for c in _CSTAR[B])
         self.smooth = tuple(tuple(FT(c) for c in row) for row in _SMOOTH[B])
@@ -242,9 +297,21 @@ def _weno_inner(scheme, get, d, s0, R, left):
     for a in alpha[1:]:
         asum = asum + a
     out = None
+    ztab = getattr(scheme, "ztab", None) if d == 2 else None
+    if ztab is not None:
+        # coeff_p for a stretched direction (weno_interpolants.jl:124-127): the table of stencil r at the target index for a left
+        # bias, the reversed table of stencil B − 2 − r for a right bias (ψ is stored in reversed order there)
+        tab = ztab["c" if s0 else "f"]
+        ks = range(R[2][0], R[2][1] + 1)
+        if ks[0] < 0 or ks[-1] > len(tab[0]) - 1:
+            raise IndexError("stretched WENO coefficients exist for indices 0 … N+1 only")
     for r in range(B):
         w = alpha[r] / asum
         c, p = scheme.coeff[r], psi[r]
+        if ztab is not None:
+            cl = [np.array([tab[r][k][t] for k in ks], dtype=FT).reshape(1, 1, -1) for t in range(B)]
+            cr = [np.array([tab[B - 2 - r][k][B - 1 - t] for k in ks], dtype=FT).reshape(1, 1, -1) for t in range(B)]
+            c = [np.where(left, cl[t], cr[t]) for t in range(B)]
         pr = c[0] * p[0]
         for t in range(1, B):
             pr = pr + c[t] * p[t]
@@ -303,5 +370,5 @@ def adapt_advection_order(advection, grid):
         elif isinstance(s, UpwindBiased):
             out.append(UpwindBiased(s.FT, 2 * N - 1))
         else:
-            out.append(WENO(s.FT, 2 * N - 1))
+            out.append(WENO(s.FT, 2 * N - 1, getattr(s, "grid", None)))
     return out
