@@ -15,7 +15,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SELECTION = ("tendencies_and_halos_bit_exact or substeps_and_normal or fused_fast_path_is_bit or "
-             "(plane_marching and size0 and RungeKutta3) or halo_regions or checkpointer")
+             "(plane_marching and size0 and RungeKutta3) or halo_regions or checkpointer or weno_grid_tendencies")
 
 
 @pytest.mark.skipif(shutil.which("g++") is None, reason="needs g++ to compile the kernels for the host")
@@ -24,7 +24,8 @@ def test_gpu_tests_pass_against_the_kernels_compiled_for_the_host():
     for k in ("NHSTEP_EMU_GUARD", "NHSTEP_EMU_ORDER", "NHSTEP_EMU_POISON", "NHSTEP_TILE_SWEEP", "NHSTEP_PLANE_SWEEP"):
         env.pop(k, None)
     cmd = [sys.executable, "-m", "pytest", "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider", "-k", SELECTION,
-           "tests/test_gpu_parity.py", "tests/test_reference_halo_tests.py", "tests/test_zy_checkpoint_gpu.py"]
+           "tests/test_gpu_parity.py", "tests/test_reference_halo_tests.py", "tests/test_zy_checkpoint_gpu.py",
+           "tests/test_reference_weno_grid.py"]
     r = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=1500)
     tail = (r.stdout + r.stderr)[-3000:]
     assert r.returncode == 0, tail
