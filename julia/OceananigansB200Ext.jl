@@ -156,11 +156,29 @@ function B200NonhydrostaticModel(arch::B200 = B200(); grid, advection = Centered
     h = Ref{Ptr{Cvoid}}()
     check(ccall((:nh_model_create, libnhstep), Int32, (Ptr{Cvoid}, Ref{NhModelDesc}, Ref{Ptr{Cvoid}}), gh, desc, h))
     m = B200Model(h[], gh, jm, names)
+    push_weno_z_coefficients!(h[], per_direction(jm.advection)[3], eltype(grid))
     finalizer(m) do x
         ccall((:nh_model_destroy, libnhstep), Int32, (Ptr{Cvoid},), x.handle)
         ccall((:nh_grid_destroy, libnhstep), Int32, (Ptr{Cvoid},), x.grid_handle)
     end
     return m
+end
+
+# WENO(grid) on a stretched z (weno_reconstruction.jl:98-124): the scheme's and its buffer scheme's per-index tables
+# coeff_zᵃᵃᶠ / coeff_zᵃᵃᶜ[r + 2][i], r = −1 … B−1, i = 0 … Nz+1 (reconstruction_coefficients.jl:306-324) → [t, r + 2, i + 1] arrays
+push_weno_z_coefficients!(handle, scheme, FT) = nothing
+function push_weno_z_coefficients!(handle, scheme::WENO{B}, FT) where B
+    for (location, tables) in enumerate((scheme.coeff_zᵃᵃᶠ, scheme.coeff_zᵃᵃᶜ))
+        tables === nothing && continue
+        n = length(parent(tables[1]))
+        a = Array{FT}(undef, B, B + 1, n)
+        for r in 1:B+1, i in 1:n, t in 1:B
+            a[t, r, i] = parent(tables[r])[i][t]
+        end
+        check(ccall((:nh_model_set_weno_z_coefficients, libnhstep), Int32, (Ptr{Cvoid}, Int32, Int32, Ptr{Cvoid}, Int64, Int32),
+                    handle, B, location - 1, a, length(a), 0))
+    end
+    push_weno_z_coefficients!(handle, scheme.buffer_scheme, FT)
 end
 
 field_id(m::B200Model, name::Symbol) =
