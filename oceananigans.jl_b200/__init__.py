@@ -159,13 +159,16 @@ class _Scheme:
         self.kind, self.order = kind, order
 
 
-def Centered(FT=None, order=2):
+def Centered(FT=None, order=2, grid=None):
+    """Centered(FT; grid, order): with or without ``grid`` the coefficients are the uniform ones, as in the reference
+    (centered_reconstruction.jl:47-58 keeps constant coefficients for stretched directions)."""
     if order % 2:
         raise ValueError("Centered reconstruction scheme is defined only for even orders")
     return _Scheme(L.ADV_CENTERED, order)
 
 
-def UpwindBiased(FT=None, order=3):
+def UpwindBiased(FT=None, order=3, grid=None):
+    """UpwindBiased(FT; grid, order): uniform coefficients with or without ``grid`` (upwind_biased_reconstruction.jl:51-65)."""
     if order % 2 == 0:
         raise ValueError("UpwindBiased reconstruction scheme is defined only for odd orders")
     return _Scheme(L.ADV_UPWIND, order)
