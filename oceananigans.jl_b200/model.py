@@ -195,6 +195,8 @@ class NonhydrostaticModel:
         zs = per_dir[2]
         if isinstance(zs, _Scheme) and zs.kind == L.ADV_WENO and getattr(zs, "grid", None) is not None and grid.z_stretched:
             from .stretched_weno import weno_z_tables
+            if grid.topology[2] != Bounded:
+                raise NotImplementedError("WENO(grid): the stretched z direction must be Bounded (as the Fourier-tridiagonal solve needs)")
             if zs.grid is not grid and not (zs.grid.z_stretched and np.array_equal(zs.grid._zfaces, grid._zfaces)):
                 raise ValueError("WENO(grid): the scheme was built for another vertical coordinate than the model's grid")
             top = min((zs.order + 1) // 2, grid.N[2])            # adapt_advection_order lowers the order on a short direction
