@@ -60,10 +60,21 @@ void yield_with(int state) {
 
 // NHSTEP_EMU_ORDER=reverse resumes the threads of a block (and walks the blocks of a grid) in the opposite order: a kernel whose
 // result depends on the order in which threads or blocks run between barriers — a race — then gives different bits.
+// NHSTEP_EMU_ORDER=random:<seed> reshuffles the order of the threads on every scheduler pass (a different interleaving around every
+// barrier and every mbarrier poll), with a fixed seed for reproducibility.
+unsigned long long rng_state = 0;
 int order_mode() {
   static int mode = -1;
-  if (mode < 0) { const char* o = std::getenv("NHSTEP_EMU_ORDER"); mode = (o && std::strcmp(o, "reverse") == 0) ? 1 : 0; }
+  if (mode < 0) {
+    const char* o = std::getenv("NHSTEP_EMU_ORDER");
+    mode = !o ? 0 : (std::strcmp(o, "reverse") == 0 ? 1 : (std::strncmp(o, "random:", 7) == 0 ? 2 : 0));
+    if (mode == 2) rng_state = std::strtoull(o + 7, nullptr, 10) * 2654435761ull + 88172645463325252ull;
+  }
   return mode;
+}
+unsigned next_random() {                                          // xorshift64
+  rng_state ^= rng_state << 13; rng_state ^= rng_state >> 7; rng_state ^= rng_state << 17;
+  return (unsigned)(rng_state >> 32);
 }
 
 void ensure_fibers(size_t n) {
@@ -91,11 +102,14 @@ void run_block_with_fibers(unsigned nthreads, int first) {
   }
   for (unsigned t = 0; t < (unsigned)first; ++t) fibers[t].state = 3;
   unsigned done = first;
-  const bool reversed = order_mode() == 1;
+  const bool reversed = order_mode() == 1, shuffled = order_mode() == 2;
+  std::vector<unsigned> perm(nthreads);
+  for (unsigned q = 0; q < nthreads; ++q) perm[q] = q;
   while (done < nthreads) {
     bool progressed = false;
+    if (shuffled) for (unsigned q = nthreads - 1; q > 0; --q) std::swap(perm[q], perm[next_random() % (q + 1)]);
     for (unsigned q = 0; q < nthreads; ++q) {
-      const unsigned t = reversed ? nthreads - 1 - q : q;
+      const unsigned t = shuffled ? perm[q] : (reversed ? nthreads - 1 - q : q);
       Fiber& f = fibers[t];
       if (f.state != 0) continue;
       current = (int)t;
