@@ -17,6 +17,11 @@ HDF5.jl into a Julia model), NOT a JLD2 file: JLD2's encoding of Julia structs c
 parsed, without Julia, and this image has neither Julia nor libhdf5.  File names follow the reference
 (``<prefix>_iteration<N>``) with the extension ``.h5``.
 
+Slab runs: every rank checkpoints its own local model (``Checkpointer(m.model, prefix=f"checkpoint_rank{m.rank}")``, the
+``_rank<r>`` naming of the reference's distributed output files, output_writer_utils.jl:220-226) — the parent arrays carry the
+neighbours' halo rows, so ``set_from_checkpoint(m.model, path)`` on every rank (without the update_state! of ``pickup``, which would
+refill the y halos locally) continues the run bit for bit (tests/test_zw_slab_checkpoint.py).
+
 Only host code lives here: the arrays travel through ``nh_get_field`` / ``nh_set_field`` (parent region) and the clock through
 ``nh_clock_get`` / ``nh_clock_set``.
 """
