@@ -165,6 +165,11 @@ class DistributedNonhydrostaticModel:
     """NonhydrostaticModel on a (Periodic, Periodic, Periodic) RectilinearGrid split into y-slabs over the ranks of ``arch``.
 
     ``size``, ``x``, ``y``, ``z`` describe the GLOBAL grid; each rank holds rows ``local_slab(Ny, R, rank)``.
+
+    With ``Partition(x=R)`` (``mirrored``) each rank holds columns ``local_slab(Nx, R, rank)`` instead: internally the model is the
+    y-slab model of the problem reflected in the plane x = y, and ``set`` / ``set_local`` / ``local_interior`` / ``gather`` translate
+    names (u ↔ v) and array axes, so that a caller only ever sees its own orientation.  ``self.model``, ``self.grid``,
+    ``self.velocities`` … are the INTERNAL (mirrored) objects.
     """
 
     def __init__(self, arch, FT=np.float64, size=None, x=None, y=None, z=None, halo=(3, 3, 3), advection=None,
