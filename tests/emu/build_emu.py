@@ -105,7 +105,7 @@ def rewrite_asm(text, name):
         elif "st.release.sys.global.u32" in body:
             new = f"*(volatile unsigned*)({ops[0]}) = ({ops[1]});"
         elif "ld.acquire.sys.global.u32" in body:
-            new = f"{ops[0]} = *(volatile unsigned*)({ops[1]});"
+            new = f"{ops[0]} = *(volatile unsigned*)({ops[1]}); emu_relax();"      # a polling load of the flag barrier
         elif "mbarrier.init" in body:
             new = f"emu::mbar_init({ops[0]}, {ops[1]});"
         elif "mbarrier.arrive.expect_tx" in body:
